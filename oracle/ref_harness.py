@@ -1,0 +1,67 @@
+"""TEST INFRASTRUCTURE ONLY — imports the *real* reference from /root/reference (read-only).
+
+This exists only in the build container: the GPU box has no /root/reference, so nothing in
+``-m gpu`` tests, ``smoke()`` or ``bench.py`` may call into this module.  It is used to
+(1) pin ``oracle/daft_oracle.py`` (our CPU restatement) against the live reference, and
+(2) generate the golden vectors under ``tests/golden/`` (``tests/golden/make_golden.py``).
+
+Accommodations (none modify the reference):
+  * ``librosa`` / ``matplotlib`` are not installed here and ``daft_exprt/model.py:11`` pulls them
+    in transitively → stub modules are injected into ``sys.modules`` before the import;
+  * ``HyperParams`` is not instantiated (MFA file asserts, ``hparams.py:218-229``) → a plain
+    namespace with the model-relevant fields is used instead.
+"""
+import os
+import sys
+import types
+
+REFERENCE_SRC = "/root/reference/src"
+
+
+def reference_available():
+    return os.path.isfile(os.path.join(REFERENCE_SRC, "daft_exprt", "model.py"))
+
+
+def _stub(name, **attrs):
+    if name in sys.modules:
+        return sys.modules[name]
+    m = types.ModuleType(name)
+    for k, v in attrs.items():
+        setattr(m, k, v)
+    sys.modules[name] = m
+    return m
+
+
+def import_reference_model():
+    """Return the reference's ``daft_exprt.model`` module."""
+    if not reference_available():
+        raise RuntimeError("reference not present (expected only in the build container)")
+    for name in ("librosa", "matplotlib", "soundfile"):
+        try:
+            __import__(name)
+        except Exception:
+            _stub(name, use=lambda *a, **k: None)
+    try:
+        import librosa.filters  # noqa: F401
+    except Exception:
+        lf = _stub("librosa.filters", mel=lambda *a, **k: None)
+        sys.modules["librosa"].filters = lf
+    try:
+        import matplotlib.pyplot  # noqa: F401
+    except Exception:
+        pp = _stub("matplotlib.pyplot")
+        sys.modules["matplotlib"].pyplot = pp
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import daft_exprt.model as ref_model
+    return ref_model
+
+
+def build_reference_model(hp, state_dict):
+    """Instantiate the reference ``DaftExprt`` on CPU (eval) and load ``state_dict`` strictly."""
+    import copy
+    ref_model = import_reference_model()
+    model = ref_model.DaftExprt(copy.deepcopy(hp))
+    model.load_state_dict(state_dict, strict=True)
+    model.eval()
+    return model

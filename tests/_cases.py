@@ -1,0 +1,57 @@
+"""Shared helpers: rebuild the golden cases' inputs from their seeds and load the frozen outputs."""
+import os
+import sys
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+from daft_exprt_b200.hparams import default_hparams      # noqa: E402
+from daft_exprt_b200.weights import make_state_dict       # noqa: E402
+from daft_exprt_b200 import synthetic                     # noqa: E402
+
+sys.path.insert(0, GOLDEN_DIR)
+import make_golden as MG                                  # noqa: E402
+
+_SD = {}
+
+
+def hparams():
+    return default_hparams()
+
+
+def state_dict(seed=MG.WEIGHT_SEED):
+    if seed not in _SD:
+        _SD[seed] = make_state_dict(default_hparams(), seed)
+    return _SD[seed]
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    return {k: z[k] for k in z.files}
+
+
+def forward_case(name):
+    hp = default_hparams()
+    batch = synthetic.forward_batch(hp, **MG.FORWARD_CASES[name])
+    g = load_golden(name)
+    assert str(g["inputs_digest"]) == MG.inputs_digest(batch), "synthetic generator drifted"
+    assert str(g["weights_digest"]) == MG.weights_digest(state_dict()), "weight generator drifted"
+    return hp, batch, g
+
+
+def inference_case(name):
+    hp = default_hparams()
+    kw = dict(MG.INFERENCE_CASES[name])
+    inputs, prosody, ext_emb, acc_emb = synthetic.inference_batch(hp, **kw)
+    g = load_golden(name)
+    dig = MG.inputs_digest(list(inputs) + [prosody[k] for k in sorted(prosody)] + [ext_emb, acc_emb])
+    assert str(g["inputs_digest"]) == dig, "synthetic generator drifted"
+    return hp, kw["pitch_transform"], inputs, prosody, ext_emb, acc_emb, g
+
+
+def t(a):
+    return torch.from_numpy(np.asarray(a))

@@ -1,0 +1,53 @@
+"""Model-relevant hyper-parameters of the reference, as a plain namespace.
+
+The reference's ``HyperParams`` class (``src/daft_exprt/hparams.py:19-161``) cannot be
+constructed unaided (it asserts MFA files exist, ``hparams.py:218-229``) and never defines
+``lambda_reversal`` although ``model.py:51`` reads it.  The hot path only reads the fields
+below (SURVEY.md §5 "config"), so a namespace with the same attribute names is the whole
+contract.  Values: ``hparams.py:41-46,72,106-127``.
+"""
+from types import SimpleNamespace
+import copy
+
+
+def default_hparams(**overrides):
+    hp = SimpleNamespace(
+        n_mel_channels=80,
+        n_symbols=76,
+        n_speakers=2,
+        lambda_reversal=1.0,
+        post_mult_weight=1e-3,
+        sampling_rate=22050,
+        filter_length=1024,
+        hop_length=256,
+        centered=False,
+        external_emb_dim=192,
+        stats={
+            "spk 0": {"pitch": {"mean": 5.0, "std": 0.25}, "energy": {"mean": 0.0, "std": 1.0}},
+            "spk 1": {"pitch": {"mean": 5.3, "std": 0.30}, "energy": {"mean": 0.1, "std": 1.1}},
+        },
+        phoneme_encoder={
+            "nb_blocks": 4, "hidden_embed_dim": 128, "attn_nb_heads": 2, "attn_dropout": 0.1,
+            "conv_kernel": 3, "conv_channels": 1024, "conv_dropout": 0.1,
+        },
+        gaussian_upsampling_module={"conv_kernel": 3},
+        frame_decoder={
+            "nb_blocks": 4, "attn_nb_heads": 2, "attn_dropout": 0.1,
+            "conv_kernel": 3, "conv_channels": 1024, "conv_dropout": 0.1,
+        },
+    )
+    for k, v in overrides.items():
+        setattr(hp, k, v)
+    return hp
+
+
+def clone_hparams(hp):
+    """Deep copy (the reference's FrameDecoder mutates ``hparams.frame_decoder`` at init,
+    ``model.py:534``; callers that build two models from one namespace want a copy)."""
+    return copy.deepcopy(hp)
+
+
+def accent_encoder_params(hp):
+    """``AccentEncoder`` / ``StyleAdapter`` fall back to the phoneme-encoder sub-dict when
+    ``hparams.accent_encoder`` is missing (``model.py:627-631,727-730``)."""
+    return getattr(hp, "accent_encoder", None) or hp.phoneme_encoder

@@ -1,0 +1,81 @@
+"""Seeded synthetic batches in the reference's tensor contract.
+
+``forward_batch`` builds the 12-tuple ``DaftExprt.forward`` takes (reference ``model.py:893-896``):
+rows sorted by symbol count descending and right-zero-padded, exactly as the reference's collate
+does (``data_loader.py:217-263``), with ``sum(durations_int[b]) == output_lengths[b]``
+(``data_loader.py:165-168``).  ``inference_batch`` builds the 6-tuple + external dicts of
+``DaftExprt.inference`` (``model.py:1035``, ``generate.py:273-279``).  All CPU tensors.
+"""
+import torch
+
+
+def _lengths(gen, batch, lmin, lmax):
+    if lmin == lmax:
+        lens = torch.full((batch,), lmin, dtype=torch.long)
+    else:
+        lens = torch.randint(lmin, lmax + 1, (batch,), generator=gen, dtype=torch.long)
+    return torch.sort(lens, descending=True)[0]
+
+
+def forward_batch(hp, batch, lmin, lmax, seed, dmin=1, dmax=9, const_dur=None):
+    """12-tuple for ``forward``.  cfg1: batch=1,lmin=lmax=60,const_dur=5,seed=0.
+    cfg2: batch=64,lmin=20,lmax=150,seed=42.  cfg4: lmin=lmax=400,const_dur=5,seed=9."""
+    g = torch.Generator().manual_seed(int(seed))
+    in_len = _lengths(g, batch, lmin, lmax)
+    L = int(in_len.max())
+    valid = torch.arange(L).unsqueeze(0) < in_len.unsqueeze(1)
+    symbols = torch.randint(1, hp.n_symbols, (batch, L), generator=g, dtype=torch.long) * valid
+    if const_dur is not None:
+        dint = torch.full((batch, L), int(const_dur), dtype=torch.long) * valid
+    else:
+        dint = torch.randint(dmin, dmax + 1, (batch, L), generator=g, dtype=torch.long) * valid
+    dfloat = dint.float() * (hp.hop_length / hp.sampling_rate)
+    s_energy = torch.randn(batch, L, generator=g) * valid
+    s_pitch = torch.randn(batch, L, generator=g) * valid
+    out_len = dint.sum(dim=1)
+    T = int(out_len.max())
+    fvalid = torch.arange(T).unsqueeze(0) < out_len.unsqueeze(1)
+    f_energy = torch.randn(batch, T, generator=g).abs() * fvalid
+    f_pitch = torch.randn(batch, T, generator=g).abs() * fvalid
+    mel = torch.randn(batch, hp.n_mel_channels, T, generator=g) * fvalid.unsqueeze(1)
+    spk_ids = torch.randint(0, hp.n_speakers, (batch,), generator=g, dtype=torch.long)
+    spk_embs = torch.randn(batch, getattr(hp, "external_emb_dim", 192), generator=g)
+    return (symbols, dfloat, dint, s_energy, s_pitch, in_len, f_energy, f_pitch, mel, out_len,
+            spk_ids, spk_embs)
+
+
+def inference_batch(hp, batch, lmin, lmax, seed, pitch_transform="add"):
+    """(inputs6, external_prosody, external_embeddings, external_accent_emb) for ``inference``.
+    Durations are 1..9 hops (+ jitter) per valid symbol so every symbol gets ≥ 1 frame."""
+    g = torch.Generator().manual_seed(int(seed))
+    in_len = _lengths(g, batch, lmin, lmax)
+    L = int(in_len.max())
+    valid = torch.arange(L).unsqueeze(0) < in_len.unsqueeze(1)
+    symbols = torch.randint(1, hp.n_symbols, (batch, L), generator=g, dtype=torch.long) * valid
+    hops = torch.randint(1, 10, (batch, L), generator=g).float() + torch.rand(batch, L, generator=g) * 0.5
+    dur = hops * (hp.hop_length / hp.sampling_rate) * valid
+    energy = torch.randn(batch, L, generator=g) * valid
+    pitch = torch.randn(batch, L, generator=g) * valid
+    dur_f = torch.ones(batch, L)
+    en_f = torch.ones(batch, L)
+    pi_f = torch.zeros(batch, L) if pitch_transform == "add" else torch.ones(batch, L)
+    spk_ids = torch.randint(0, hp.n_speakers, (batch,), generator=g, dtype=torch.long)
+    ext_emb = torch.randn(batch, getattr(hp, "external_emb_dim", 192), generator=g)
+    acc_emb = torch.randn(batch, hp.phoneme_encoder["hidden_embed_dim"], generator=g)
+    inputs = (symbols, dur_f, en_f, pi_f, in_len, spk_ids)
+    prosody = {"duration_preds": dur, "durations_int": torch.zeros(batch, L, dtype=torch.long),
+               "energy_preds": energy, "pitch_preds": pitch}
+    return inputs, prosody, ext_emb, acc_emb
+
+
+CONFIGS = {
+    # name: kwargs of forward_batch
+    "cfg1": dict(batch=1, lmin=60, lmax=60, seed=0, const_dur=5),
+    "cfg2": dict(batch=64, lmin=20, lmax=150, seed=42),
+    "cfg4_b1": dict(batch=1, lmin=400, lmax=400, seed=9, const_dur=5),
+    "cfg4_b8": dict(batch=8, lmin=400, lmax=400, seed=9, const_dur=5),
+}
+
+
+def config_batch(hp, name):
+    return forward_batch(hp, **CONFIGS[name])
