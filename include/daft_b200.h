@@ -1,0 +1,174 @@
+/*
+ * daft_b200.h — C ABI of libdaft_b200.so: Daft-Exprt's batched synthesis forward pass on B200 (sm_100a).
+ *
+ * The reference (claussss/ubisoft-laforge-daft-exprt) has no FFI/plugin interface: its boundary is the
+ * Python class daft_exprt.model.DaftExprt (src/daft_exprt/model.py:833-1114).  This header is the
+ * boundary a binding for that class calls into; the Python mirror of the class lives in
+ * ubisoft-laforge-daft-exprt_b200/model.py and INTEGRATION.md shows the ctypes stub a maintainer of the
+ * reference would add.  Every entry point cites the reference code it replaces.
+ *
+ * Conventions
+ *   - plain C: device pointers, ints, a cudaStream_t passed as void*; no torch types, no C++ exceptions.
+ *   - every function returns 0 on success, non-zero on error; dx_last_error_string() explains.
+ *   - no allocation inside: callers pass outputs and scratch.
+ *   - all pointers are DEVICE pointers unless the name ends in _host.
+ *   - "rows": activations live in a packed row stream (see DESIGN.md "data layout"): utterance b owns rows
+ *     row_start[b] .. row_start[b]+len[b]+DX_GAP-1; the last DX_GAP rows of each utterance are gap rows.
+ *
+ * Two arithmetic modes (BASELINE.json north_star): DX_MODE_F32 = fp32 SIMT kernels (parity gate: mel max-abs
+ * <= 1e-3 vs the reference CPU forward) and DX_MODE_BF16 = bf16 operands on tcgen05 tensor cores with fp32
+ * accumulation, LayerNorm, softmax and Gaussian weights (parity gate: relative L1 <= 2e-2).
+ */
+#ifndef DAFT_B200_H
+#define DAFT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DX_GAP 3            /* gap rows after every utterance in the packed row stream (H1 ghost rows) */
+#define DX_HALO 8           /* zero rows in front of every bf16 channel-interleaved buffer (conv tap -1)  */
+#define DX_TAIL 136         /* zero rows behind the row range (tile overruns of the last utterance)           */
+#define DX_D 128            /* hidden_embed_dim  (hparams.py:108)                                         */
+#define DX_HEADS 2          /* attn_nb_heads     (hparams.py:109)                                         */
+#define DX_DH 64            /* head dim                                                                   */
+#define DX_C 1024           /* conv_channels     (hparams.py:112)                                         */
+#define DX_TAPS 3           /* conv_kernel       (hparams.py:111)                                         */
+#define DX_MEL_PAD 96       /* mel channels padded to a multiple of the K stage (bf16 tensor-core path)      */
+#define DX_MEL 80           /* n_mel_channels    (hparams.py:44)                                          */
+#define DX_SPK 192          /* ECAPA embedding size (model.py:855)                                        */
+#define DX_MODE_F32 0
+#define DX_MODE_BF16 1
+
+/* ---- library ------------------------------------------------------------------------------------------- */
+int         dx_version(void);
+const char* dx_last_error_string(void);
+/* number of kernels launched by this library since load (bench.py's "gpu_launches") */
+int64_t     dx_launch_count(void);
+/* bring-up switches (all 0 in production).  key 0: swap LBO/SBO in the UMMA shared-memory descriptors. */
+int         dx_set_debug(int key, int value);
+
+/* ---- row stream (replaces get_mask_from_lengths, model.py:14-24, and the padded layouts) --------------- */
+/* lengths: int64[B].  n_max: width of the caller's padded tensor.  Writes row_start int32[B+1] (row_start[B] =
+ * total rows), row_b int32[row_cap], row_p int32[row_cap] (utterance / position of every row; -1 / 0 beyond
+ * the total).  row_cap must be >= dx_row_cap(B, n_max). */
+int64_t dx_row_cap(int B, int n_max);
+int dx_build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int32_t* row_b,
+                  int32_t* row_p, int64_t row_cap, void* stream);
+
+/* ---- weights -------------------------------------------------------------------------------------------- */
+/* One FFT block (model.py:238-259).  fp32 tensors are in GEMM layout (prepared once by the host mirror):
+ *   w_qkv  [128][384]  = in_proj_weight^T           b_qkv [384]
+ *   w_out  [128][128]  = out_proj.weight^T          b_out [128]
+ *   w_c1   [3][128][1024] = convs.0.conv.weight permuted (tap, cin, cout)     b_c1 [1024]
+ *   w_c2   [3][1024][128] = convs.2.conv.weight permuted                      b_c2 [128]
+ * bf16 tensors (tensor-core mode) are in the tile-packed layout dx_pack_weight_bf16 produces. */
+typedef struct {
+    const float *w_qkv, *b_qkv, *w_out, *b_out, *ln1_g, *ln1_b;
+    const float *w_c1, *b_c1, *w_c2, *b_c2, *ln2_g, *ln2_b;
+    const void  *w_qkv_bf, *w_out_bf, *w_c1_bf, *w_c2_bf;
+} DxBlockWeights;
+
+typedef struct {
+    /* accent encoder (model.py:614-716) */
+    const float *ae_energy_w, *ae_energy_b, *ae_pitch_w, *ae_pitch_b;     /* [128][3], [128] */
+    const float *ae_c0_w, *ae_c0_b, *ae_ln0_g, *ae_ln0_b;                 /* [3][80][1024]   */
+    const float *ae_c1_w, *ae_c1_b, *ae_ln1_g, *ae_ln1_b;                 /* [3][1024][1024] */
+    const float *ae_c2_w, *ae_c2_b, *ae_ln2_g, *ae_ln2_b;                 /* [3][1024][128]  */
+    const void  *ae_c0_w_bf, *ae_c1_w_bf, *ae_c2_w_bf;
+    DxBlockWeights ae_blocks[4];
+    /* speaker projection + classifier + style adapter (model.py:719-830, 855-856) */
+    const float *spk_w, *spk_b;                                           /* [128][192] (torch layout) */
+    const float *cls_w1, *cls_b1, *cls_w2, *cls_b2, *cls_w3, *cls_b3;     /* torch layouts */
+    const float *film_g_w, *film_g_b, *film_b_w, *film_b_b;               /* [1024][128], [1024] */
+    const float *post_mult;                                               /* [2][8] or NULL (== 1.0) */
+    /* phoneme encoder (model.py:567-610) */
+    const float *symbols_embedding;                                       /* [n_symbols][128] */
+    DxBlockWeights pe_blocks[4];
+    /* gaussian upsampling (model.py:385-510) */
+    const float *gu_dur_w, *gu_dur_b, *gu_energy_w, *gu_energy_b, *gu_pitch_w, *gu_pitch_b;  /* [128][3],[128] */
+    const float *gu_range_w, *gu_range_b;                                 /* [128], [1] */
+    /* frame decoder (model.py:513-564) */
+    DxBlockWeights fd_blocks[4];
+    const float *mel_w, *mel_b;                                           /* [128][80] = projection^T, [80] */
+    const void  *mel_w_bf;
+    /* shared */
+    const float *pos_table;                                               /* [5000][128], model.py:126-130 */
+    int32_t n_symbols, n_speakers, pos_rows, pad_;
+} DxModelWeights;
+
+/* Pack an fp32 GEMM-layout weight [taps][K][N] into the bf16 tile layout the tensor-core kernels stream with
+ * one bulk copy per stage:  [n_tile][k_stage][tap][ks/8][nt][8]  (N zero-padded to a multiple of nt). */
+int64_t dx_packed_weight_elems(int taps, int K, int N, int nt, int ks);
+int dx_pack_weight_bf16(const float* w, int taps, int K, int N, int nt, int ks, void* out, void* stream);
+
+/* ---- whole passes (replace DaftExprt.forward model.py:889-948 / .inference model.py:1026-1114) ---------- */
+typedef struct {
+    int32_t B, L_max, T_max, mode;
+    /* inputs, reference layouts (model.py:893-896) */
+    const int64_t *symbols;            /* (B, L_max) */
+    const float   *durations_float;    /* (B, L_max) seconds */
+    const int64_t *durations_int;      /* (B, L_max) frames  */
+    const float   *symbols_energy, *symbols_pitch;   /* (B, L_max) */
+    const int64_t *input_lengths;      /* (B,) */
+    const float   *frames_energy, *frames_pitch;     /* (B, T_max) or NULL when accent_emb_in is given */
+    const float   *mel_specs;          /* (B, 80, T_max) or NULL */
+    const int64_t *output_lengths;     /* (B,)  forward: given; inference: NULL → computed = max(sum dur,1) */
+    const float   *spk_embs;           /* (B, 192) raw ECAPA, or NULL when spk_emb_in is given */
+    const float   *accent_emb_in;      /* (B, 128) external accent embedding or NULL (run the accent encoder) */
+    const float   *spk_emb_in;         /* (B, 128) external projected speaker embedding or NULL */
+    /* outputs */
+    float   *accent_emb;               /* (B, 128)      */
+    float   *speaker_preds;            /* (B, n_speakers) or NULL */
+    float   *film;                     /* (B, 8, 256): blocks 0-3 phoneme encoder, 4-7 frame decoder */
+    float   *enc_out;                  /* (B, L_max, 128) phoneme-encoder output or NULL (debug/tests) */
+    float   *mel_out;                  /* (B, 80, T_max) */
+    float   *weights_out;              /* (B, L_max, T_max) alignments */
+    int64_t *output_lengths_out;       /* (B,) */
+    /* scratch: dx_forward_workspace_bytes(B, L_max, T_max, mode) bytes, 256-byte aligned */
+    void    *workspace;
+    int64_t  workspace_bytes;
+} DxForwardArgs;
+
+int64_t dx_forward_workspace_bytes(int B, int L_max, int T_max, int mode);
+int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream);
+
+/* ---- single stages (unit-test surface; same kernels dx_forward launches) -------------------------------- */
+/* AccentEncoder.forward, model.py:679-716 */
+int dx_accent_encoder(const DxModelWeights* w, int mode, int B, int T_max, const float* frames_energy,
+                      const float* frames_pitch, const float* mel_specs, const int64_t* output_lengths,
+                      float* accent_emb, void* workspace, int64_t workspace_bytes, void* stream);
+/* speaker projection + classifier + StyleAdapter.forward, model.py:904-920, 764-806, 829-830 */
+int dx_style(const DxModelWeights* w, int B, const float* spk_embs, const float* spk_emb_in,
+             const float* accent_emb, float* film, float* speaker_preds, void* stream);
+/* integer side of the length regulator, model.py:485-497, 1096-1100 (bit-exact contract, int64) */
+int dx_length_regulator_integers(const int64_t* durations_int, const int64_t* input_lengths, int B, int L_max,
+                                 int T_max, int64_t* cumsum, int64_t* two_mu, int64_t* output_lengths,
+                                 int64_t* frame2symbol, void* stream);
+/* get_int_durations + duration_to_integer, model.py:950-973, extract_features.py:69-125.  One thread per
+ * utterance, IEEE double arithmetic in the reference's order.  duration (B,L) fp32 is thresholded in place.
+ * status int32[B]: 0 ok, 1 = reference would raise (count mismatch / empty pop). */
+int dx_int_durations(float* duration, int B, int L_max, int sampling_rate, int filter_length, int hop_length,
+                     int centered, int64_t* durations_int, int32_t* status, void* stream);
+/* pitch_shift / pitch_multiply + the zero-duration masking, model.py:1077-1087, 975-1024 (in place) */
+int dx_prosody_transform(float* energy, float* pitch, const float* energy_factors, const float* pitch_factors,
+                         const int64_t* durations_int, const float* pitch_mean, const float* pitch_std,
+                         int B, int L_max, int transform /*0=add,1=multiply*/, void* stream);
+
+/* ---- tensor-core self tests (GPU unit tests of the tcgen05 building blocks) ----------------------------- */
+/* out[M][N] fp32 = sum_taps A[row+tap-(taps/2)] * W[tap]  with A bf16 channel-interleaved, W packed bf16. */
+int dx_tc_gemm_test(const void* a_il, int64_t a_rows_phys, int M, int K, int N, int taps, const void* w_packed,
+                    int nt, int ks, float* out, void* stream);
+
+/* Masked multi-head self-attention alone (MultiHeadAttention.forward's nn.MultiheadAttention call, model.py:182-186).
+ * mode F32: qkv fp32 [row_cap][384] → out fp32 [row_cap][128].  mode BF16: qkv bf16 channel-interleaved
+ * [48][rows_phys][8] → out [16][rows_phys][8].  rowmap_scratch: int32[(B + 1) + 2 * row_cap]. */
+int dx_test_attention(int mode, const void* qkv, void* out, int64_t rows_phys, const int64_t* lengths, int B, int n_max,
+                      int32_t* rowmap_scratch, int64_t row_cap, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAFT_B200_H */

@@ -1,0 +1,116 @@
+"""ctypes binding of libdaft_b200.so (include/daft_b200.h).  Plain pointers and sizes only.
+
+The product has NO CPU fallback: if the shared library is missing or a call fails, this raises.
+"""
+import ctypes as C
+import os
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libdaft_b200.so")
+
+MODE_F32, MODE_BF16 = 0, 1
+GAP, HALO, TAIL = 3, 8, 136
+D, HEADS, DH, CCH, TAPS, MEL, MEL_PAD, SPK = 128, 2, 64, 1024, 3, 80, 96, 192
+
+_p = C.c_void_p
+
+
+class DxBlockWeights(C.Structure):
+    _fields_ = [(n, _p) for n in (
+        "w_qkv", "b_qkv", "w_out", "b_out", "ln1_g", "ln1_b",
+        "w_c1", "b_c1", "w_c2", "b_c2", "ln2_g", "ln2_b",
+        "w_qkv_bf", "w_out_bf", "w_c1_bf", "w_c2_bf")]
+
+
+class DxModelWeights(C.Structure):
+    _fields_ = (
+        [(n, _p) for n in ("ae_energy_w", "ae_energy_b", "ae_pitch_w", "ae_pitch_b",
+                           "ae_c0_w", "ae_c0_b", "ae_ln0_g", "ae_ln0_b",
+                           "ae_c1_w", "ae_c1_b", "ae_ln1_g", "ae_ln1_b",
+                           "ae_c2_w", "ae_c2_b", "ae_ln2_g", "ae_ln2_b",
+                           "ae_c0_w_bf", "ae_c1_w_bf", "ae_c2_w_bf")]
+        + [("ae_blocks", DxBlockWeights * 4)]
+        + [(n, _p) for n in ("spk_w", "spk_b", "cls_w1", "cls_b1", "cls_w2", "cls_b2", "cls_w3", "cls_b3",
+                             "film_g_w", "film_g_b", "film_b_w", "film_b_b", "post_mult",
+                             "symbols_embedding")]
+        + [("pe_blocks", DxBlockWeights * 4)]
+        + [(n, _p) for n in ("gu_dur_w", "gu_dur_b", "gu_energy_w", "gu_energy_b", "gu_pitch_w", "gu_pitch_b",
+                             "gu_range_w", "gu_range_b")]
+        + [("fd_blocks", DxBlockWeights * 4)]
+        + [(n, _p) for n in ("mel_w", "mel_b", "mel_w_bf", "pos_table")]
+        + [("n_symbols", C.c_int32), ("n_speakers", C.c_int32), ("pos_rows", C.c_int32), ("pad_", C.c_int32)]
+    )
+
+
+class DxForwardArgs(C.Structure):
+    _fields_ = (
+        [("B", C.c_int32), ("L_max", C.c_int32), ("T_max", C.c_int32), ("mode", C.c_int32)]
+        + [(n, _p) for n in ("symbols", "durations_float", "durations_int", "symbols_energy", "symbols_pitch",
+                             "input_lengths", "frames_energy", "frames_pitch", "mel_specs", "output_lengths",
+                             "spk_embs", "accent_emb_in", "spk_emb_in",
+                             "accent_emb", "speaker_preds", "film", "enc_out", "mel_out", "weights_out",
+                             "output_lengths_out", "workspace")]
+        + [("workspace_bytes", C.c_int64)]
+    )
+
+
+# name -> (restype, argtypes); must list every function include/daft_b200.h declares
+SIGNATURES = {
+    "dx_version": (C.c_int, []),
+    "dx_last_error_string": (C.c_char_p, []),
+    "dx_launch_count": (C.c_int64, []),
+    "dx_set_debug": (C.c_int, [C.c_int, C.c_int]),
+    "dx_row_cap": (C.c_int64, [C.c_int, C.c_int]),
+    "dx_build_rows": (C.c_int, [_p, C.c_int, C.c_int, _p, _p, _p, C.c_int64, _p]),
+    "dx_packed_weight_elems": (C.c_int64, [C.c_int] * 5),
+    "dx_pack_weight_bf16": (C.c_int, [_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p]),
+    "dx_forward_workspace_bytes": (C.c_int64, [C.c_int] * 4),
+    "dx_forward": (C.c_int, [C.POINTER(DxModelWeights), C.POINTER(DxForwardArgs), _p]),
+    "dx_accent_encoder": (C.c_int, [C.POINTER(DxModelWeights), C.c_int, C.c_int, C.c_int, _p, _p, _p, _p, _p, _p,
+                                    C.c_int64, _p]),
+    "dx_style": (C.c_int, [C.POINTER(DxModelWeights), C.c_int, _p, _p, _p, _p, _p, _p]),
+    "dx_length_regulator_integers": (C.c_int, [_p, _p, C.c_int, C.c_int, C.c_int, _p, _p, _p, _p, _p]),
+    "dx_int_durations": (C.c_int, [_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p, _p]),
+    "dx_prosody_transform": (C.c_int, [_p, _p, _p, _p, _p, _p, _p, C.c_int, C.c_int, C.c_int, _p]),
+    "dx_tc_gemm_test": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p, C.c_int, C.c_int, _p, _p]),
+    "dx_test_attention": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p, C.c_int64, _p]),
+}
+
+_LIB = None
+
+
+class DxError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libdaft_b200.so (built by build.py / __graft_entry__.build()).  Raises if it is missing."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.isfile(LIB_PATH):
+        raise DxError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                      f"(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)     # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = lib
+    return lib
+
+
+def check(status, what=""):
+    if status != 0:
+        msg = load().dx_last_error_string()
+        raise DxError(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def ptr(t):
+    """Device/host pointer of a tensor (None → NULL)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,259 @@
+// Masked multi-head self-attention on tcgen05 (bf16 operands, fp32 scores/softmax/accumulation).
+//
+// Reference: nn.MultiheadAttention slow path as called from MultiHeadAttention.forward (model.py:182-186):
+//   S_h = (Q_h · d^-0.5) K_h^T, -inf at padded keys, softmax over keys, O_h = A_h V_h.  The head-averaged
+//   weights torch also returns are discarded by FFTBlock (model.py:255) and never materialised here.
+//
+// One CTA = (utterance, head, 128-query tile).  K/V are streamed in 128-key tiles (2-stage ring, bulk copies).
+//   S  = Q K^T      : tcgen05.mma, A = Q [128 x 64] K-major, B = K tile [128 keys x 64] K-major → TMEM cols 0..127
+//   P  = softmax    : 4 warps, thread ↔ query row, online max/sum in fp32, P written to smem as the bf16 K-major
+//                     A operand of the next MMA
+//   PV = P V        : tcgen05.mma, B = V tile [64 dh x 128 keys] MN-major (the channel-interleaved global layout
+//                     IS that canonical layout) → TMEM cols 128..191 (fresh accumulator per tile)
+//   O  += corr * .. : the softmax threads keep O (64 fp32) in registers and fold each PV tile in with the
+//                     online-softmax correction, so no TMEM read-modify-write is needed.
+// All operand tiles use the no-swizzle canonical layouts, which are exactly what the channel-interleaved global
+// layout [chunk][row][8] gives per chunk, so every operand arrives by plain 2 KB bulk copies.
+#include "dx_common.cuh"
+#include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
+
+namespace dx {
+
+constexpr int ATC_BQ = 128, ATC_BK = 128;
+constexpr int ATC_THREADS = 192;
+constexpr uint32_t ATC_TILE_BYTES = 8 * 128 * 16;      // one 128-row x 64-channel bf16 tile = 16 KB
+constexpr uint32_t ATC_P_BYTES = 16 * 128 * 16;        // P: 128 rows x 128 keys bf16 = 32 KB
+constexpr uint32_t ATC_TMEM_COLS = 256;
+
+struct AtcParams {
+    const __nv_bfloat16* qkv;   // [48][rows_phys][8]
+    __nv_bfloat16* out;         // [16][rows_phys][8]
+    int64_t rows_phys;
+    Rows R;
+    uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
+};
+
+__global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcParams p) {
+    extern __shared__ __align__(1024) uint8_t at_smem[];
+    const int b = blockIdx.z, h = blockIdx.y;
+    const int len = (int)min((long long)p.R.len[b], (long long)p.R.n_max);
+    const int q0 = blockIdx.x * ATC_BQ;
+    if (q0 >= len) return;
+    const int64_t rs = p.R.row_start[b];
+    const int n_kv = (len + ATC_BK - 1) / ATC_BK;
+
+    uint8_t* sQ = at_smem;
+    uint8_t* sKV = sQ + ATC_TILE_BYTES;                 // 2 stages x (K | V)
+    uint8_t* sP = sKV + 4 * ATC_TILE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + ATC_P_BYTES);
+    uint64_t* q_full = bars;            // 1
+    uint64_t* kv_full = bars + 1;       // 2
+    uint64_t* kv_empty = bars + 3;      // 2
+    uint64_t* s_full = bars + 5;
+    uint64_t* p_full = bars + 6;
+    uint64_t* o_full = bars + 7;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        ptx::mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+        ptx::mbar_init(s_full, 1);
+        ptx::mbar_init(p_full, 4);
+        ptx::mbar_init(o_full, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<ATC_TMEM_COLS>(tmem_ptr);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t tm_s = tmem_base, tm_o = tmem_base + 128;
+
+    if (warp == 0) {
+        if (ptx::elect_one()) {
+            // Q tile
+            ptx::mbar_expect_tx(q_full, ATC_TILE_BYTES);
+            for (int c = 0; c < 8; ++c) {
+                const __nv_bfloat16* src = p.qkv + ((int64_t)(h * 8 + c) * p.rows_phys + DX_HALO + rs + q0) * 8;
+                ptx::bulk_g2s(sQ + c * 2048, src, 2048, q_full);
+            }
+            for (int j = 0; j < n_kv; ++j) {
+                const int st = j & 1;
+                const uint32_t ph = (j >> 1) & 1;
+                ptx::mbar_wait(&kv_empty[st], ph ^ 1);
+                uint8_t* sk = sKV + (size_t)st * 2 * ATC_TILE_BYTES;
+                uint8_t* sv = sk + ATC_TILE_BYTES;
+                ptx::mbar_expect_tx(&kv_full[st], 2 * ATC_TILE_BYTES);
+                const int64_t krow = DX_HALO + rs + (int64_t)j * ATC_BK;
+                for (int c = 0; c < 8; ++c) {
+                    ptx::bulk_g2s(sk + c * 2048, p.qkv + ((int64_t)(16 + h * 8 + c) * p.rows_phys + krow) * 8, 2048, &kv_full[st]);
+                    ptx::bulk_g2s(sv + c * 2048, p.qkv + ((int64_t)(32 + h * 8 + c) * p.rows_phys + krow) * 8, 2048, &kv_full[st]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // MMA issuer.  idesc_s: M=128, N=128, A/B K-major.  idesc_o: M=128, N=64, B MN-major (bit 16).
+        constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, 128);
+        constexpr uint32_t idesc_o = ptx::make_idesc_bf16(128, 64) | (1u << 16);
+        ptx::mbar_wait(q_full, 0);
+        const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
+        for (int j = 0; j < n_kv; ++j) {
+            const int st = j & 1;
+            const uint32_t ph = (j >> 1) & 1;
+            ptx::mbar_wait(&kv_full[st], ph);
+            ptx::tc_fence_after();
+            const uint32_t aK = ptx::smem_u32(sKV + (size_t)st * 2 * ATC_TILE_BYTES);
+            const uint32_t aV = aK + ATC_TILE_BYTES;
+            if (ptx::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {   // dh = 64 = 4 x 16
+                    const uint64_t da = ptx::make_desc(aQ + kk * 2 * 2048, 2048, 128);
+                    const uint64_t db = ptx::make_desc(aK + kk * 2 * 2048, 2048, 128);
+                    ptx::mma_bf16(tm_s, da, db, idesc_s, kk != 0);
+                }
+                ptx::mma_commit(s_full);
+            }
+            __syncwarp();
+            ptx::mbar_wait(p_full, j & 1);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {   // 128 keys = 8 x 16
+                    const uint64_t da = ptx::make_desc(aP + kk * 2 * 2048, 2048, 128);
+                    const uint64_t db = ptx::make_desc(aV + kk * 256, p.v_lbo, p.v_sbo);
+                    ptx::mma_bf16(tm_o, da, db, idesc_o, kk != 0);
+                }
+                ptx::mma_commit(o_full);
+                ptx::mma_commit(&kv_empty[st]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // softmax + output: thread ↔ query row
+        const int lane_grp = warp & 3;
+        const int row = lane_grp * 32 + lane;
+        const uint32_t t_s = tm_s + ((uint32_t)(lane_grp * 32) << 16);
+        const uint32_t t_o = tm_o + ((uint32_t)(lane_grp * 32) << 16);
+        const float sl2 = 0.125f * 1.4426950408889634f;   // d^-0.5 * log2(e)
+        float o[64];
+#pragma unroll
+        for (int i = 0; i < 64; ++i) o[i] = 0.f;
+        float m = -INFINITY, l = 0.f;
+        for (int j = 0; j < n_kv; ++j) {
+            const int k0 = j * ATC_BK;
+            ptx::mbar_wait(s_full, j & 1);
+            ptx::tc_fence_after();
+            // pass A: row max over valid keys
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int q = 0; q < 4; ++q) {
+                float v[32];
+                ptx::tmem_ld32(t_s + q * 32, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e)
+                    if (k0 + q * 32 + e < len) mx = fmaxf(mx, v[e]);
+            }
+            const float m_new = fmaxf(m, mx * sl2);
+            const float corr = exp2f(m - m_new);
+            float ps = 0.f;
+            // pass B: probabilities → bf16 P tile in smem (K-major, chunk = 8 keys)
+#pragma unroll 1
+            for (int q = 0; q < 4; ++q) {
+                float v[32];
+                ptx::tmem_ld32(t_s + q * 32, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                    for (int e = 0; e < 8; e += 2) {
+                        const int kidx = k0 + q * 32 + c * 8 + e;
+                        float p0 = (kidx < len) ? exp2f(v[c * 8 + e] * sl2 - m_new) : 0.f;
+                        float p1 = (kidx + 1 < len) ? exp2f(v[c * 8 + e + 1] * sl2 - m_new) : 0.f;
+                        ps += p0 + p1;
+                        o2[e / 2] = __floats2bfloat162_rn(p0, p1);
+                    }
+                    *reinterpret_cast<uint4*>(sP + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                }
+            }
+            l = l * corr + ps;
+            m = m_new;
+            // make the generic-proxy smem writes visible to the tensor core (async proxy), then signal
+            ptx::fence_proxy_async();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(p_full);
+            // fold PV_j into the register accumulator
+            ptx::mbar_wait(o_full, j & 1);
+            ptx::tc_fence_after();
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                float v[32];
+                ptx::tmem_ld32(t_o + q * 32, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) o[q * 32 + e] = fmaf(o[q * 32 + e], corr, v[e]);
+            }
+            ptx::tc_fence_before();
+        }
+        if (q0 + row < len) {
+            const float inv = 1.f / l;
+            const int64_t r = rs + q0 + row;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(o[c * 8 + 2 * e] * inv, o[c * 8 + 2 * e + 1] * inv);
+                *reinterpret_cast<uint4*>(p.out + ((int64_t)(h * 8 + c) * p.rows_phys + DX_HALO + r) * 8) =
+                    *reinterpret_cast<const uint4*>(o2);
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<ATC_TMEM_COLS>(tmem_base);
+    }
+}
+
+// zero `n_rows` rows starting at the stream's total (tiles of the last utterance read a little past the end of
+// the stream; those rows must hold finite values because 0 * NaN would poison the P·V product)
+__global__ void zero_tail_rows_kernel(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, Rows R, int n_rows) {
+    const int64_t total = R.row_start[R.B];
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)nchunks * n_rows) return;
+    const int c = (int)(i / n_rows);
+    const int64_t row = DX_HALO + total + (i % n_rows);
+    if (row >= rows_phys) return;
+    *reinterpret_cast<uint4*>(buf + ((int64_t)c * rows_phys + row) * 8) = make_uint4(0u, 0u, 0u, 0u);
+}
+
+int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Rows& R, int n_rows, cudaStream_t s) {
+    const int64_t n = (int64_t)nchunks * n_rows;
+    zero_tail_rows_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(buf, nchunks, rows_phys, R, n_rows);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s) {
+    const size_t smem = ATC_TILE_BYTES * 5 + ATC_P_BYTES + 8 * sizeof(uint64_t) + 16;
+    static bool configured = false;
+    if (!configured) {
+        DX_CHECK_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    AtcParams p;
+    p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R;
+    p.v_lbo = 128; p.v_sbo = 2048;
+    if (debug_knob(1)) { p.v_lbo = 2048; p.v_sbo = 128; }
+    dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
+    attention_tc_kernel<<<grid, ATC_THREADS, smem, s>>>(p);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace dx
