@@ -1,0 +1,203 @@
+"""GPU parity tests proper: the CUDA path (through the reference-shaped Python mirror → C ABI) against
+(1) the golden vectors frozen from the live reference and (2) the oracle port on the same seeded inputs.
+
+Gates (BASELINE.json north_star): integer length-regulator quantities bit-exact; fp32 mode mel max-abs <= 1e-3;
+bf16 mode relative L1 <= 2e-2 (over valid frames; padded frames must be exactly 0)."""
+import pytest
+import torch
+
+import _cases as C
+from daft_exprt_b200.model import DaftExprt
+from oracle import daft_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+FP32_MAX_ABS = 1e-3
+BF16_REL_L1 = 2e-2
+
+
+@pytest.fixture(scope="module")
+def models():
+    hp = C.hparams()
+    out = {}
+    for mode in ("fp32", "bf16"):
+        m = DaftExprt(hp, mode=mode).cuda()
+        m.load_state_dict(C.state_dict())
+        out[mode] = m
+    return out
+
+
+def _valid_mask(lengths, width):
+    return torch.arange(width).unsqueeze(0) < lengths.unsqueeze(1)
+
+
+def _check_mel(mel, ref_mel, out_len, mode):
+    mel = mel.float().cpu()
+    valid = _valid_mask(out_len.cpu(), mel.shape[2]).unsqueeze(1).expand_as(mel)
+    assert torch.all(mel[~valid] == 0), "padded frames must be exactly zero (FrameDecoder mask, model.py:562)"
+    diff = (mel - ref_mel).abs()
+    if mode == "fp32":
+        assert diff[valid].max().item() <= FP32_MAX_ABS, f"fp32 mel max-abs {diff[valid].max().item():.3e}"
+    else:
+        rel = (diff[valid].sum() / ref_mel[valid].abs().sum()).item()
+        assert rel <= BF16_REL_L1, f"bf16 mel rel-L1 {rel:.3e}"
+
+
+def _check_weights(w, ref_w, in_len, out_len, mode):
+    w = w.cpu()
+    B, L, T = ref_w.shape
+    lv = _valid_mask(in_len.cpu(), L).unsqueeze(2)
+    tv = _valid_mask(out_len.cpu(), T).unsqueeze(1)
+    valid = (lv & tv).expand_as(ref_w)
+    tol = 1e-4 if mode == "fp32" else 5e-2
+    assert (w - ref_w)[valid].abs().max().item() <= tol
+    # padded symbols carry exactly zero weight (model.py:503)
+    assert torch.all(w[(~lv).expand_as(w)] == 0)
+    # columns of valid frames sum to 1
+    colsum = (w * lv).sum(dim=1)
+    assert (colsum - 1)[tv.squeeze(1)].abs().max().item() <= 1e-4
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", sorted(C.MG.FORWARD_CASES))
+def test_forward_vs_golden(models, mode, name):
+    hp, batch, g = C.forward_case(name)
+    m = models[mode]
+    dev = tuple(t.cuda() for t in batch)
+    spk, film, enc, dec, w = m(dev)
+    torch.cuda.synchronize()
+    assert torch.equal(dec[1].cpu(), C.t(g["output_lengths"]))
+    _check_mel(dec[0], C.t(g["mel"]), batch[9], mode)
+    _check_weights(w, C.t(g["weights"]), batch[5], batch[9], mode)
+    tol = 1e-3 if mode == "fp32" else 6e-2
+    assert (film[3].cpu() - C.t(g["film_dec"])).abs().max().item() <= tol
+    assert (spk.cpu() - C.t(g["speaker_preds"])).abs().max().item() <= tol
+    # the tuple carries the caller's own tensors through, like the reference (model.py:943-946)
+    assert enc[0] is dev[1] and enc[3] is dev[5] and dec[1] is dev[9]
+    acc = m.accent_encoder(dev[6], dev[7], dev[8], dev[9]).cpu()
+    assert (acc - C.t(g["accent_emb"])).abs().max().item() <= (1e-4 if mode == "fp32" else 3e-2)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", sorted(C.MG.INFERENCE_CASES))
+def test_inference_vs_golden(models, mode, name):
+    hp, pt, inputs, prosody, ext_emb, acc_emb, g = C.inference_case(name)
+    m = models[mode]
+    dev_in = tuple(t.cuda() for t in inputs)
+    dev_pros = {k: v.clone().cuda() for k, v in prosody.items()}
+    enc, dec, w = m.inference(dev_in, pt, hp, dev_pros, ext_emb.cuda(), acc_emb.cuda())
+    torch.cuda.synchronize()
+    # integer contract: bit-exact in both modes
+    assert torch.equal(enc[1].cpu(), C.t(g["durations_int"]))
+    assert torch.equal(dec[1].cpu(), C.t(g["output_lengths"]))
+    assert torch.equal(enc[0].cpu(), C.t(g["duration_preds"]))
+    assert (enc[2].cpu() - C.t(g["energy_preds"])).abs().max().item() <= 1e-6
+    assert (enc[3].cpu() - C.t(g["pitch_preds"])).abs().max().item() <= 2e-5
+    # H8: the reference mutates the caller's pitch tensor
+    assert torch.equal(dev_pros["pitch_preds"], enc[3])
+    _check_mel(dec[0], C.t(g["mel"]), C.t(g["output_lengths"]), mode)
+    _check_weights(w, C.t(g["weights"]), inputs[4], C.t(g["output_lengths"]), mode)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("kw", [
+    dict(batch=1, lmin=1, lmax=1, seed=31, const_dur=1),            # single symbol, single frame
+    dict(batch=2, lmin=2, lmax=3, seed=32),                         # tiny ragged
+    dict(batch=7, lmin=5, lmax=61, seed=33),                        # ragged, crosses 128-row tiles
+    dict(batch=3, lmin=40, lmax=40, seed=34, const_dur=4),          # no padding at all (true zero pad at the end)
+    dict(batch=16, lmin=20, lmax=90, seed=35),                      # several tiles per utterance
+])
+def test_forward_vs_oracle(models, mode, kw):
+    hp = C.hparams()
+    batch = C.synthetic.forward_batch(hp, **kw)
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))
+    m = models[mode]
+    out = m(tuple(t.cuda() for t in batch), _want_enc_out=True)
+    torch.cuda.synchronize()
+    _check_mel(out[3][0], ref[3][0], batch[9], mode)
+    _check_weights(out[4], ref[4], batch[5], batch[9], mode)
+    sd = C.state_dict()
+    accent = O.accent_encoder(sd, hp, batch[6], batch[7], batch[8], batch[9])
+    film = O.style_adapter(sd, hp, accent + O.speaker_projection(sd, batch[11]))
+    enc_ref = O.phoneme_encoder(sd, hp, batch[0], film["phoneme_encoder"], batch[5])
+    enc = m._last_debug["enc_out"].cpu()
+    tol = 1e-3 if mode == "fp32" else 0.15
+    assert (enc - enc_ref).abs().max().item() <= tol
+
+
+def test_forward_external_embeddings_and_errors(models):
+    hp = C.hparams()
+    m = models["fp32"]
+    batch = C.synthetic.forward_batch(hp, batch=3, lmin=6, lmax=14, seed=41)
+    g = torch.Generator().manual_seed(1)
+    acc = torch.randn(3, 128, generator=g)
+    spk = torch.randn(3, 128, generator=g)
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch), external_accent_emb=acc, external_spk_emb=spk)
+    out = m(tuple(t.cuda() for t in batch), external_accent_emb=acc.cuda(), external_spk_emb=spk.cuda())
+    _check_mel(out[3][0], ref[3][0], batch[9], "fp32")
+    assert (out[0].cpu() - ref[0]).abs().max().item() <= 1e-4
+    with pytest.raises(ValueError):
+        m(tuple(t.cuda() for t in batch)[:11])
+    no_spk = tuple(t.cuda() for t in batch[:11]) + (None,)
+    with pytest.raises(ValueError):
+        m(no_spk)
+    inputs, prosody, ee, ae = C.synthetic.inference_batch(hp, 2, 5, 6, 1)
+    dev_in = tuple(t.cuda() for t in inputs)
+    pros = {k: v.cuda() for k, v in prosody.items()}
+    with pytest.raises(ValueError):
+        m.inference(dev_in, "add", hp, pros, None, ae.cuda())
+    with pytest.raises(ValueError):
+        m.inference(dev_in, "add", hp, pros, ee.cuda(), None)
+    with pytest.raises(ValueError):
+        m.inference(dev_in, "add", hp, None, ee.cuda(), ae.cuda())
+    with pytest.raises(NotImplementedError):
+        m.inference(dev_in, "bogus", hp, pros, ee.cuda(), ae.cuda())
+
+
+def test_batch_composition_matters_like_the_reference(models):
+    """H1: an utterance's result depends on whether it is padded in its batch.  Solo vs padded-batch results differ
+    in the reference; ours must reproduce each, not an idealised padding-neutral result."""
+    hp = C.hparams()
+    m = models["fp32"]
+    batch = C.synthetic.forward_batch(hp, batch=2, lmin=10, lmax=20, seed=52)
+    if int(batch[5][0]) == int(batch[5][1]):
+        pytest.skip("lengths equal")
+    ref_b = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))[3][0]
+    # second (shorter) utterance alone, cropped to its own length
+    l1, t1 = int(batch[5][1]), int(batch[9][1])
+    solo = tuple([batch[0][1:2, :l1], batch[1][1:2, :l1], batch[2][1:2, :l1], batch[3][1:2, :l1], batch[4][1:2, :l1],
+                  batch[5][1:2], batch[6][1:2, :t1], batch[7][1:2, :t1], batch[8][1:2, :, :t1], batch[9][1:2],
+                  batch[10][1:2], batch[11][1:2]])
+    ref_s = O.forward(C.state_dict(), hp, tuple(t.clone() for t in solo))[3][0]
+    out_b = m(tuple(t.cuda() for t in batch))[3][0].cpu()
+    out_s = m(tuple(t.contiguous().cuda() for t in solo))[3][0].cpu()
+    assert (ref_b[1, :, :t1] - ref_s[0]).abs().max() > 1e-3          # the reference itself differs
+    assert (out_b[1, :, :t1] - ref_b[1, :, :t1]).abs().max() <= FP32_MAX_ABS
+    assert (out_s[0] - ref_s[0]).abs().max() <= FP32_MAX_ABS
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_cfg2_full_size_properties(models, mode):
+    """BASELINE cfg2 (B=64, L in 20..150): size-independent properties + parity against the oracle."""
+    hp = C.hparams()
+    batch = C.synthetic.config_batch(hp, "cfg2")
+    m = models[mode]
+    out = m(tuple(t.cuda() for t in batch))
+    torch.cuda.synchronize()
+    mel, w = out[3][0].cpu(), out[4].cpu()
+    assert torch.isfinite(mel).all() and torch.isfinite(w).all()
+    out_len, in_len = batch[9], batch[5]
+    valid = _valid_mask(out_len, mel.shape[2]).unsqueeze(1).expand_as(mel)
+    assert torch.all(mel[~valid] == 0)
+    lv = _valid_mask(in_len, w.shape[1]).unsqueeze(2)
+    tv = _valid_mask(out_len, w.shape[2])
+    assert ((w * lv).sum(dim=1) - 1)[tv].abs().max() <= 1e-4
+    # idempotence: same inputs, same result (no stale-workspace dependence)
+    out2 = m(tuple(t.cuda() for t in batch))
+    if mode == "fp32":
+        assert torch.equal(out2[3][0].cpu(), mel)
+    else:   # the pre-net row statistics are accumulated with atomics: last-bit differences allowed
+        assert (out2[3][0].cpu() - mel).abs().max() <= 5e-2
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))
+    _check_mel(out[3][0], ref[3][0], out_len, mode)
+    _check_weights(out[4], ref[4], in_len, out_len, mode)

@@ -96,6 +96,10 @@ def load():
         fn = getattr(lib, name)     # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
+    # bring-up switches, e.g. DX_DEBUG="0=1,1=1" (all 0 in production)
+    for kv in filter(None, os.environ.get("DX_DEBUG", "").split(",")):
+        k, v = kv.split("=")
+        lib.dx_set_debug(int(k), int(v))
     _LIB = lib
     return lib
 
