@@ -1,0 +1,357 @@
+"""bench.py — mel frames/s of the batched synthesis forward pass (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Our arm: one process per GPU, every rank runs DaftExprt.forward (the reference's full teacher-forced pass:
+accent/prosody encoder, style adapter, phoneme encoder, length regulator, frame decoder) on its own cfg2-shaped
+batch (B=64, 20-150 symbols, 1-9 frames per symbol) — utterances shard across GPUs with no
+collective ("weak" scaling).  Prints ONE JSON line (rank 0).
+
+  value     valid mel frames/s, inputs resident in HBM, CUDA events per step, L2 flushed between steps
+  e2e       same metric through the public API with HOST (pinned) buffers: H2D of the 12 inputs + forward +
+            D2H of mel and output_lengths inside the timed region
+  roofline  tensor-bound: algorithmic FLOPs of the tcgen05 GEMM family / its summed launch durations (events
+            recorded around every launch by the library's profiler in a separate, untimed pass)
+  cpu_baseline  the oracle port (oracle/daft_oracle.py) timed on this box's host cores on a bounded sample
+
+--impl reference: the reference's CPU path for the same config = the oracle port (the reference itself is Python
+and lives only in the build container; the port is bit-identical to it there, tests/test_oracle_vs_reference.py).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "mel frames/sec, batched synthesis fwd"
+UNIT = "frames/s"
+WORKLOAD = "cfg2: DaftExprt.forward, B=64 per GPU, 20-150 symbols/utt, 1-9 frames/symbol, padding masks"
+
+
+# ------------------------------------------------------------------------------------------------------------
+# closed-form algorithmic FLOPs: valid tokens only, 2 FLOPs per MAC
+# ------------------------------------------------------------------------------------------------------------
+D, CC, KT, M, E = 128, 1024, 3, 80, 192
+
+
+def blk_flops(n):
+    return 8 * n * D * D + 4 * n * n * D + 4 * n * KT * D * CC
+
+
+def gemm_flops_forward(L, T):
+    """FLOPs of the dense contractions the tcgen05 GEMM kernel executes (attention excluded)."""
+    blk = lambda n: 8 * n * D * D + 4 * n * KT * D * CC     # noqa: E731
+    prenet = 2 * T * KT * (M * CC + CC * CC + CC * D)
+    return prenet + 4 * blk(T) + 4 * blk(L) + 4 * blk(T) + 2 * T * D * M
+
+
+def forward_flops(L, T):
+    acc = 2 * T * KT * (M * CC + CC * CC + CC * D) + 4 * T * KT * D + 4 * blk_flops(T)
+    enc = 4 * blk_flops(L)
+    dec = 4 * blk_flops(T) + 2 * T * D * M
+    ups = 2 * L * T * D + 6 * L * KT * D + 2 * L * D
+    sty = 2 * E * D + 4 * D * 8 * D
+    return acc + enc + dec + ups + sty
+
+
+def batch_flops(batch, fn):
+    return float(sum(fn(int(l), int(t)) for l, t in zip(batch[5].tolist(), batch[9].tolist())))
+
+
+# ------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        # keep the samples taken under load (upper half of the observed clocks)
+        sm_sorted = sorted(sm)
+        load = sm_sorted[len(sm_sorted) // 2:] if sm_sorted else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+def reference_arm(args):
+    """--impl reference: the oracle port (the reference's algorithm, fp32, eval, no_grad) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from daft_exprt_b200.hparams import default_hparams
+    from daft_exprt_b200.weights import make_state_dict
+    from daft_exprt_b200 import synthetic
+    from oracle import daft_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    hp = default_hparams()
+    sd = make_state_dict(hp, 1234)
+    full = synthetic.config_batch(hp, "cfg2")
+    sample = tuple(t[::4].contiguous() for t in full)          # 16 of the 64 utterances, same length mix
+    # crop the padding to the sample's own maxima, as the reference's collate would (data_loader.py:219,246)
+    L, T = int(sample[5].max()), int(sample[9].max())
+    sample = (sample[0][:, :L], sample[1][:, :L], sample[2][:, :L], sample[3][:, :L], sample[4][:, :L], sample[5],
+              sample[6][:, :T], sample[7][:, :T], sample[8][:, :, :T], sample[9], sample[10], sample[11])
+    sample = tuple(t.contiguous() for t in sample)
+    frames = int(sample[9].sum())
+    for _ in range(max(1, args.warmup)):
+        O.forward(sd, hp, sample)
+    times = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        O.forward(sd, hp, sample)
+        times.append(time.perf_counter() - t0)
+    ms = 1000 * sum(times) / len(times)
+    value = frames / (ms / 1000)
+    cores = torch.get_num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "every 4th utterance of the cfg2 batch (16 of 64)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"16 of the 64 cfg2 utterances per step ({frames} valid frames), {args.steps} steps"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+def parse_profile(text):
+    out = {}
+    for ln in text.strip().splitlines():
+        tag, n, ms = ln.split()
+        out[tag] = (int(n), float(ms))
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    args.warmup = max(args.warmup, 3)
+
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    from daft_exprt_b200.hparams import default_hparams
+    from daft_exprt_b200.weights import make_state_dict
+    from daft_exprt_b200 import synthetic, _lib
+    from daft_exprt_b200.model import DaftExprt
+    import __graft_entry__ as entry
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank == 0:
+        entry.build()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+    lib = _lib.load()
+    dev = torch.device("cuda", local_rank)
+
+    hp = default_hparams()
+    sd = make_state_dict(hp, 1234)
+    model = DaftExprt(hp, mode=args.mode).to(dev)
+    model.load_state_dict(sd)
+    # every rank gets its own cfg2-shaped shard of the utterance stream (cfg3: bulk generation, no collective)
+    kw = dict(synthetic.CONFIGS["cfg2"])
+    kw["seed"] = kw["seed"] + 1000 * rank
+    host_batch = tuple(t.pin_memory() for t in synthetic.forward_batch(hp, **kw))
+    dev_batch = tuple(t.to(dev) for t in host_batch)
+    frames = int(host_batch[9].sum())
+    B, L_max, T_max = host_batch[0].shape[0], host_batch[0].shape[1], host_batch[8].shape[2]
+    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in ev:
+            flush.zero_()                     # L2 flush between timed iterations (outside the event pair)
+            a.record()
+            fn()
+            b.record()
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) for a, b in ev]
+
+    def step_resident():
+        return model(dev_batch)
+
+    host_mel = torch.empty(B, 80, T_max).pin_memory()
+    host_len = torch.empty(B, dtype=torch.long).pin_memory()
+
+    def step_e2e():
+        d = tuple(t.to(dev, non_blocking=True) for t in host_batch)
+        out = model(d)
+        host_mel.copy_(out[3][0], non_blocking=True)
+        host_len.copy_(out[3][1], non_blocking=True)
+        return out
+
+    for _ in range(args.warmup):
+        step_resident()
+        step_e2e()
+    sync_all()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    l0 = lib.dx_launch_count()
+    t_res = timed(step_resident, args.steps)
+    launches = (lib.dx_launch_count() - l0) // args.steps
+    sync_all()
+    t_e2e = timed(step_e2e, args.steps)
+    sync_all()
+    clk = clocks.stop()
+
+    ms_res, ms_e2e = sum(t_res) / len(t_res), sum(t_e2e) / len(t_e2e)
+    tt = torch.tensor([ms_res, ms_e2e, float(frames)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tt.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_res, ms_e2e, total_frames = float(mx[0]), float(mx[1]), float(sm[2])
+    else:
+        total_frames = float(frames)
+
+    # ---- per-kernel timing pass (untimed for the headline): events around every launch of the main families
+    prof = {}
+    roofline = None
+    if rank == 0:
+        lib.dx_profile_enable(1)
+        nprof = 5
+        for _ in range(nprof):
+            flush.zero_()
+            step_resident()
+        buf = ctypes.create_string_buffer(1 << 16)
+        _lib.check(lib.dx_profile_report(buf, len(buf)), "dx_profile_report")
+        lib.dx_profile_enable(0)
+        prof = {k: (n // nprof, ms / nprof) for k, (n, ms) in parse_profile(buf.value.decode()).items()}
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "fallback 1.4 PFLOP/s sustained"
+        gemm_tags = [k for k in prof if k.startswith("tc_")] if args.mode == "bf16" else [k for k in prof if k == "gemm_f32"]
+        gemm_ms = sum(prof[k][1] for k in gemm_tags)
+        gflop = batch_flops(host_batch, gemm_flops_forward)
+        if gemm_ms > 0:
+            ach = gflop / (gemm_ms * 1e-3) / 1e12
+            roofline = {"bound": "tensor", "kernel": "tc_gemm_kernel (all tcgen05 conv/linear GEMM launches of one step)"
+                        if args.mode == "bf16" else "gemm_f32_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+                        "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                        "algorithmic_flops_per_step": gflop, "kernel_ms_per_step": gemm_ms,
+                        "launches_per_step": sum(prof[k][0] for k in gemm_tags)}
+
+    # ---- p50 single-utterance latency (cfg1 shape, inference(), host sync per call)
+    lat_p50 = None
+    if rank == 0:
+        inp, pros, ee, ae = synthetic.inference_batch(hp, 1, 60, 60, 0)
+        d_in = tuple(t.to(dev) for t in inp)
+        ee_d, ae_d = ee.to(dev), ae.to(dev)
+        lats = []
+        for i in range(60):
+            d_pros = {k: v.to(dev) for k, v in pros.items()}
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            o = model.inference(d_in, "add", hp, d_pros, ee_d, ae_d)
+            o[1][0].cpu()
+            if i >= 10:
+                lats.append(1000 * (time.perf_counter() - t0))
+        lat_p50 = statistics.median(lats)
+
+    # ---- CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import daft_oracle as O
+        torch.set_num_threads(os.cpu_count() or 1)
+        cpu_batch = tuple(t.clone() for t in host_batch)
+        O.forward(sd, hp, cpu_batch)                       # warm-up
+        t0 = time.perf_counter()
+        reps = 2
+        for _ in range(reps):
+            O.forward(sd, hp, cpu_batch)
+        dt = (time.perf_counter() - t0) / reps
+        cpu = {"value": frames / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"the full cfg2 batch (64 utterances, {frames} valid frames), {reps} timed calls after 1 warm-up, {dt:.2f} s/call"}
+
+    if rank == 0:
+        in_bytes = sum(t.numel() * t.element_size() for t in host_batch)
+        out_bytes = host_mel.numel() * 4 + host_len.numel() * 8
+        line = {
+            "metric": METRIC, "value": total_frames / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.mode, "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "L_max": L_max, "T_max": T_max,
+                       "valid_frames_per_gpu_step": frames, "l2": "flushed between timed iterations (512 MiB memset)",
+                       "weights": "random-init, seed 1234"},
+            "e2e": {"value": total_frames / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes},
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "latency_ms_p50_single_utterance_inference": lat_p50,
+            "kernels_ms_per_step": {k: round(v[1], 4) for k, v in sorted(prof.items())},
+            "whole_model_tflops": batch_flops(host_batch, forward_flops) * world / (ms_res * 1e-3) / 1e12,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -47,8 +47,15 @@ int         dx_version(void);
 const char* dx_last_error_string(void);
 /* number of kernels launched by this library since load (bench.py's "gpu_launches") */
 int64_t     dx_launch_count(void);
-/* bring-up switches (all 0 in production).  key 0: swap LBO/SBO in the UMMA shared-memory descriptors. */
+/* bring-up switches (all 0 in production).  key 0: swap LBO/SBO in the UMMA shared-memory descriptors;
+ * key 1: same for the MN-major V operand of attention; key 2: synchronise after every launch (fault location). */
 int         dx_set_debug(int key, int value);
+
+/* Per-launch timing for bench.py's roofline: while enabled, the library records a CUDA event pair around every
+ * launch of its main kernel families on the launching stream.  dx_profile_report synchronises the device and
+ * writes one line per tag: "<tag> <launches> <total_ms>\n" (NUL-terminated), then clears the records. */
+int dx_profile_enable(int on);
+int dx_profile_report(char* buf, int64_t buf_bytes);
 
 /* ---- row stream (replaces get_mask_from_lengths, model.py:14-24, and the padded layouts) --------------- */
 /* lengths: int64[B].  n_max: width of the caller's padded tensor.  Writes row_start int32[B+1] (row_start[B] =

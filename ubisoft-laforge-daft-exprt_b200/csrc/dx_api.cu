@@ -4,6 +4,9 @@
 #include <stdarg.h>
 #include <string.h>
 #include <atomic>
+#include <map>
+#include <string>
+#include <vector>
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_plan.cuh"
@@ -23,6 +26,27 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static int g_knobs[16] = {0};
 int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
 
+// ---- launch profiler ----------------------------------------------------------------------------------------
+static bool g_prof_on = false;
+struct ProfRec { const char* tag; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof;
+static size_t g_prof_used = 0;
+
+ProfScope::ProfScope(const char* tag, cudaStream_t stream) : s(stream), slot(-1) {
+    if (!g_prof_on) return;
+    if (g_prof_used == g_prof.size()) {
+        ProfRec r{tag, nullptr, nullptr};
+        if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+        g_prof.push_back(r);
+    }
+    slot = (int)g_prof_used++;
+    g_prof[slot].tag = tag;
+    cudaEventRecord(g_prof[slot].a, s);
+}
+ProfScope::~ProfScope() {
+    if (slot >= 0) cudaEventRecord(g_prof[slot].b, s);
+}
+
 int64_t row_cap(int B, int n_max) { return round_up((int64_t)B * (n_max + DX_GAP), 256); }
 
 }  // namespace dx
@@ -37,6 +61,35 @@ int64_t dx_launch_count(void) { return g_launches.load(); }
 int dx_set_debug(int key, int value) {
     if (key < 0 || key >= 16) return 2;
     g_knobs[key] = value;
+    return 0;
+}
+
+int dx_profile_enable(int on) {
+    g_prof_on = on != 0;
+    g_prof_used = 0;
+    return 0;
+}
+
+int dx_profile_report(char* buf, int64_t cap) {
+    DX_REQUIRE(buf != nullptr && cap > 0, "dx_profile_report: buffer required");
+    DX_CHECK_CUDA(cudaDeviceSynchronize());
+    std::map<std::string, std::pair<int, double>> acc;
+    for (size_t i = 0; i < g_prof_used; ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_prof[i].a, g_prof[i].b) != cudaSuccess) continue;
+        auto& e = acc[g_prof[i].tag];
+        e.first += 1;
+        e.second += ms;
+    }
+    g_prof_used = 0;
+    std::string out;
+    char line[160];
+    for (auto& kv : acc) {
+        snprintf(line, sizeof(line), "%s %d %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += line;
+    }
+    DX_REQUIRE((int64_t)out.size() + 1 <= cap, "dx_profile_report: buffer of %lld bytes too small", (long long)cap);
+    memcpy(buf, out.c_str(), out.size() + 1);
     return 0;
 }
 

@@ -251,6 +251,7 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
     p.v_lbo = 128; p.v_sbo = 2048;
     if (debug_knob(1)) { p.v_lbo = 2048; p.v_sbo = 128; }
     dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
+    ProfScope prof("attn_tc", s);
     attention_tc_kernel<<<grid, ATC_THREADS, smem, s>>>(p);
     DX_CHECK_LAUNCH();
     return 0;

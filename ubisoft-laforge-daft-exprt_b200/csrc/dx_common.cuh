@@ -13,6 +13,14 @@ void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int debug_knob(int key);   // dx_set_debug(key, value): bring-up switches, all 0 in production
 
+// Optional per-launch timing (dx_profile_enable): events recorded around a launch on its stream, keyed by a tag.
+struct ProfScope {
+    cudaStream_t s;
+    int slot;
+    ProfScope(const char* tag, cudaStream_t stream);
+    ~ProfScope();
+};
+
 #define DX_CHECK_CUDA(expr)                                                                   \
     do {                                                                                      \
         cudaError_t _e = (expr);                                                              \
@@ -26,6 +34,7 @@ int debug_knob(int key);   // dx_set_debug(key, value): bring-up switches, all 0
     do {                                                                                      \
         dx::count_launch();                                                                   \
         cudaError_t _e = cudaGetLastError();                                                  \
+        if (_e == cudaSuccess && dx::debug_knob(2)) _e = cudaDeviceSynchronize();             \
         if (_e != cudaSuccess) {                                                              \
             dx::set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
             return 1;                                                                         \

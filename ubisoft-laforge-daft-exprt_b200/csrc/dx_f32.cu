@@ -121,6 +121,7 @@ int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, in
              const Rows& R, int live_ext, float* out, cudaStream_t s) {
     DX_REQUIRE(K % GF_BK == 0 && N % 4 == 0, "gemm_f32: K=%d must be a multiple of 16 and N=%d of 4", K, N);
     dim3 grid((unsigned)(R.cap / GF_BM), (unsigned)((N + GF_BN - 1) / GF_BN));
+    ProfScope prof("gemm_f32", s);
     gemm_f32_kernel<<<grid, 256, 0, s>>>(A, K, W, bias, N, taps, relu ? 1 : 0, R, live_ext, out);
     DX_CHECK_LAUNCH();
     return 0;
@@ -193,6 +194,7 @@ __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __
 int ln_rows_f32(const float* in, const float* res, const float* g, const float* b, int C, const float* film,
                 int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s) {
     int grid = (int)((R.cap + 7) / 8);
+    ProfScope prof("ln_rows_f32", s);
     if (C == 128)
         ln_rows_f32_kernel<128><<<grid, 256, 0, s>>>(in, res, g, b, film, film_stride, R, live_ext, out);
     else if (C == 1024)
@@ -336,6 +338,7 @@ int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s) {
         configured = true;
     }
     dim3 grid((unsigned)((R.n_max + AT_Q - 1) / AT_Q), DX_HEADS, (unsigned)R.B);
+    ProfScope prof("attn_f32", s);
     attention_f32_kernel<<<grid, 256, AT_SMEM, s>>>(qkv, R, out);
     DX_CHECK_LAUNCH();
     return 0;

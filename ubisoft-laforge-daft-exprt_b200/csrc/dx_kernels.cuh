@@ -80,6 +80,7 @@ struct TcGemmArgs {
     int film_stride;
     // optional per-row statistics for a following LayerNorm over N > 128 (pre-net): sum / sum of squares
     float* row_stats;           // [rows][2] or null (accumulated with atomics)
+    const char* tag;            // profiler tag (dx_profile_report)
 };
 int tc_gemm(const TcGemmArgs& g, const Rows& R, cudaStream_t s);
 int tc_gemm_plain(const TcGemmArgs& g, int64_t M, cudaStream_t s);   // no row map: rows [0, M) all live

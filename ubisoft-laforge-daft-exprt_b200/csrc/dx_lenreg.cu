@@ -179,10 +179,11 @@ lenreg_frames_kernel(const float* __restrict__ xs, Rows RL, Rows RT, const float
                      int64_t rows_phys_t) {
     extern __shared__ __align__(16) float lr_smem[];
     const int L = RL.n_max, T = RT.n_max;
-    float* s_mu = lr_smem;            // [L]
-    float* s_sg = s_mu + L;           // [L]
-    float* s_lsg = s_sg + L;          // [L]
-    float* s_part = s_lsg + L;        // [8][32]
+    const int Lp = (L + 3) & ~3;      // keep the float4-read tile below 16-byte aligned
+    float* s_mu = lr_smem;            // [Lp]
+    float* s_sg = s_mu + Lp;          // [Lp]
+    float* s_lsg = s_sg + Lp;         // [Lp]
+    float* s_part = s_lsg + Lp;       // [8][32]
     float* s_den = s_part + 8 * LR_FT;  // [32]
     float* s_w = s_den + LR_FT;       // [32 l][32 t]
     int* s_any = reinterpret_cast<int*>(s_w + 32 * LR_FT);  // [32]
@@ -268,7 +269,7 @@ int lenreg_frames(const float* xs, const Rows& RL, const Rows& RT, const float* 
                   const float* pos, float* weights, float* xo_f32, __nv_bfloat16* xo_bf, int64_t rows_phys_t,
                   cudaStream_t s) {
     const int L = RL.n_max;
-    const size_t smem = (size_t)(3 * L + 8 * LR_FT + LR_FT + 32 * LR_FT) * sizeof(float) + 32 * sizeof(int);
+    const size_t smem = (size_t)(3 * ((L + 3) & ~3) + 8 * LR_FT + LR_FT + 32 * LR_FT) * sizeof(float) + 32 * sizeof(int);
     DX_REQUIRE(smem <= 200 * 1024, "lenreg_frames: L_max=%d too large", L);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
@@ -277,6 +278,7 @@ int lenreg_frames(const float* xs, const Rows& RL, const Rows& RT, const float* 
         configured = smem;
     }
     dim3 grid((unsigned)((RT.n_max + DX_GAP + LR_FT - 1) / LR_FT), (unsigned)RT.B);
+    ProfScope prof("lenreg_frames", s);
     if (xo_bf)
         lenreg_frames_kernel<true><<<grid, 256, smem, s>>>(xs, RL, RT, mu, sigma, pos, weights, nullptr, xo_bf, rows_phys_t);
     else

@@ -106,25 +106,25 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
     DX_REQUIRE(bw.w_qkv_bf && bw.w_out_bf && bw.w_c1_bf && bw.w_c2_bf, "bf16 mode: packed weights missing (model not prepared for DX_MODE_BF16)");
     {   // QKV projection
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, 3 * DX_D, 1, bw.w_qkv_bf, 128, 64, bw.b_qkv, 0, TC_EPI_BF16, -1);
-        g.out_bf = p.qkvb;
+        g.out_bf = p.qkvb; g.tag = "tc_qkv";
         DX_TRY(tc_gemm(g, R, s));
     }
     DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
     {   // out-proj + residual + LN + mask
         TcGemmArgs g = tc_args(p.ob, rp, DX_D, DX_D, 1, bw.w_out_bf, 128, 64, bw.b_out, 0, TC_EPI_LN, 0);
-        g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b;
+        g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b; g.tag = "tc_outproj_ln";
         DX_TRY(tc_gemm(g, R, s));
     }
     {   // conv1 + ReLU (hidden live one row past the utterance: H1)
         TcGemmArgs g = tc_args(p.yb, rp, DX_D, DX_C, DX_TAPS, bw.w_c1_bf, 256, 32, bw.b_c1, 1, TC_EPI_BF16, 1);
-        g.out_bf = p.h1b;
+        g.out_bf = p.h1b; g.tag = "tc_ffn_conv1";
         DX_TRY(tc_gemm(g, R, s));
     }
     {   // conv2 + residual + LN + FiLM + mask
         TcGemmArgs g = tc_args(p.h1b, rp, DX_C, DX_D, DX_TAPS, bw.w_c2_bf, 128, 64, bw.b_c2, 0, TC_EPI_LN, 0);
         g.out_bf = p.xb; g.res = p.yb; g.ln_g = bw.ln2_g; g.ln_b = bw.ln2_b;
         g.film = film ? film + film_block * 256 : nullptr;
-        g.film_stride = 8 * 256;
+        g.film_stride = 8 * 256; g.tag = "tc_ffn_conv2_ln";
         DX_TRY(tc_gemm(g, R, s));
     }
     return 0;
@@ -166,20 +166,20 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         DX_CHECK_CUDA(cudaMemsetAsync(p.row_stats, 0, p.cap * 2 * sizeof(float), s));
         {
             TcGemmArgs g = tc_args(p.melb, rp, DX_MEL_PAD, DX_C, DX_TAPS, w.ae_c0_w_bf, 256, 32, w.ae_c0_b, 1, TC_EPI_BF16, 2);
-            g.out_bf = p.h1b; g.row_stats = p.row_stats;
+            g.out_bf = p.h1b; g.row_stats = p.row_stats; g.tag = "tc_prenet0";
             DX_TRY(tc_gemm(g, RT, s));
         }
         DX_TRY(ln_apply_bf16(p.h1b, rp, DX_C, p.row_stats, w.ae_ln0_g, w.ae_ln0_b, RT, 2, s));
         DX_CHECK_CUDA(cudaMemsetAsync(p.row_stats, 0, p.cap * 2 * sizeof(float), s));
         {
             TcGemmArgs g = tc_args(p.h1b, rp, DX_C, DX_C, DX_TAPS, w.ae_c1_w_bf, 256, 32, w.ae_c1_b, 1, TC_EPI_BF16, 1);
-            g.out_bf = p.h2b; g.row_stats = p.row_stats;
+            g.out_bf = p.h2b; g.row_stats = p.row_stats; g.tag = "tc_prenet1";
             DX_TRY(tc_gemm(g, RT, s));
         }
         DX_TRY(ln_apply_bf16(p.h2b, rp, DX_C, p.row_stats, w.ae_ln1_g, w.ae_ln1_b, RT, 1, s));
         {
             TcGemmArgs g = tc_args(p.h2b, rp, DX_C, DX_D, DX_TAPS, w.ae_c2_w_bf, 128, 64, w.ae_c2_b, 1, TC_EPI_LN, 0);
-            g.out_bf = p.ob; g.ln_g = w.ae_ln2_g; g.ln_b = w.ae_ln2_b;
+            g.out_bf = p.ob; g.ln_g = w.ae_ln2_g; g.ln_b = w.ae_ln2_b; g.tag = "tc_prenet2_ln";
             DX_TRY(tc_gemm(g, RT, s));
         }
         DX_TRY(accent_input(nullptr, p.ob, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
@@ -247,7 +247,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     if (bf) {
         DX_REQUIRE(w.mel_w_bf, "bf16 mode: packed mel projection missing");
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, DX_MEL, 1, w.mel_w_bf, 128, 64, w.mel_b, 0, TC_EPI_F32, -1);
-        g.out_f32 = p.melo;
+        g.out_f32 = p.melo; g.tag = "tc_melproj";
         DX_TRY(tc_gemm(g, RT, s));
     } else {
         DX_TRY(gemm_f32(p.x, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));

@@ -392,6 +392,7 @@ __global__ void ln_apply_bf16_kernel(__nv_bfloat16* __restrict__ x, int64_t rows
 int ln_apply_bf16(__nv_bfloat16* x, int64_t rows_phys, int C, const float* stats, const float* g, const float* b,
                   const Rows& R, int live_ext, cudaStream_t s) {
     dim3 grid((unsigned)((R.cap + 255) / 256), (unsigned)(C / 8));
+    ProfScope prof("ln_apply_bf16", s);
     ln_apply_bf16_kernel<<<grid, 256, 0, s>>>(x, rows_phys, C, stats, g, b, R, live_ext);
     DX_CHECK_LAUNCH();
     return 0;

@@ -292,6 +292,7 @@ static int tc_launch(const TcParams& p, size_t smem, int grid, cudaStream_t s) {
         DX_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<NT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
+    ProfScope prof(p.g.tag ? p.g.tag : "tc_gemm", s);
     tc_gemm_kernel<NT, EPI><<<grid, TC_THREADS, smem, s>>>(p);
     DX_CHECK_LAUNCH();
     return 0;
