@@ -263,32 +263,55 @@ int accent_input(const float* z2_f32, const __nv_bfloat16* z2_bf, const float* e
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// masked_mean: accent[b] = sum_{p < len} x[b, p] / len   (model.py:714).  One CTA per utterance, 128 threads
-// (one per channel), rows streamed with 4 independent accumulators per thread.
+// masked_mean: accent[b] = sum_{p < len} x[b, p] / len   (model.py:714).  Grid (B, 16): one CTA per utterance and
+// 8-channel chunk; 256 threads stride over the rows (16-byte / 32-byte coalesced loads), block reduction.
 // ---------------------------------------------------------------------------------------------------------
 template <bool BF16>
-__global__ void masked_mean_kernel(const float* __restrict__ x_f32, const __nv_bfloat16* __restrict__ x_bf,
-                                   int64_t rows_phys, Rows R, float* __restrict__ out) {
-    const int b = blockIdx.x;
-    const int c = threadIdx.x;  // 0..127
+__global__ void __launch_bounds__(256)
+masked_mean_kernel(const float* __restrict__ x_f32, const __nv_bfloat16* __restrict__ x_bf,
+                   int64_t rows_phys, Rows R, float* __restrict__ out) {
+    __shared__ float s_part[8][8];
+    const int b = blockIdx.x, c = blockIdx.y;   // chunk of 8 channels
     const int len = (int)min((long long)R.len[b], (long long)R.n_max);
     const int64_t rs = R.row_start[b];
-    float acc = 0.f;
-    if (!BF16) {
-        for (int p = 0; p < len; ++p) acc += x_f32[(rs + p) * DX_D + c];
-    } else {
-        const __nv_bfloat16* base = x_bf + ((int64_t)(c >> 3) * rows_phys + DX_HALO + rs) * 8 + (c & 7);
-        for (int p = 0; p < len; ++p) acc += __bfloat162float(base[(int64_t)p * 8]);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int p = threadIdx.x; p < len; p += 256) {
+        if (!BF16) {
+            const float4* src = reinterpret_cast<const float4*>(x_f32 + (rs + p) * DX_D + c * 8);
+            const float4 a = src[0], d = src[1];
+            acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
+            acc[4] += d.x; acc[5] += d.y; acc[6] += d.z; acc[7] += d.w;
+        } else {
+            const uint4 pk = *reinterpret_cast<const uint4*>(x_bf + ((int64_t)c * rows_phys + DX_HALO + rs + p) * 8);
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                acc[2 * e] += __low2float(h2[e]);
+                acc[2 * e + 1] += __high2float(h2[e]);
+            }
+        }
     }
-    out[b * DX_D + c] = acc / (float)R.len[b];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = warp_sum(acc[e]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0)
+        for (int e = 0; e < 8; ++e) s_part[warp][e] = acc[e];
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        float t = 0.f;
+#pragma unroll
+        for (int wv = 0; wv < 8; ++wv) t += s_part[wv][threadIdx.x];
+        out[b * DX_D + c * 8 + threadIdx.x] = t / (float)R.len[b];
+    }
 }
 
 int masked_mean(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys, const Rows& R, float* out,
                 cudaStream_t s) {
+    ProfScope prof("masked_mean", s);
     if (x_bf)
-        masked_mean_kernel<true><<<R.B, DX_D, 0, s>>>(nullptr, x_bf, rows_phys, R, out);
+        masked_mean_kernel<true><<<dim3(R.B, 16), 256, 0, s>>>(nullptr, x_bf, rows_phys, R, out);
     else
-        masked_mean_kernel<false><<<R.B, DX_D, 0, s>>>(x_f32, nullptr, 0, R, out);
+        masked_mean_kernel<false><<<dim3(R.B, 16), 256, 0, s>>>(x_f32, nullptr, 0, R, out);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -15,6 +15,8 @@ __device__ __forceinline__ float dot_row_128(const float* __restrict__ wrow, con
 
 // Reference: model.py:904-905 (F.normalize p=2 eps 1e-12 + spk_projection), :919 (accent + spk),
 // StyleAdapter.forward :764-806, SpeakerClassifier.forward :829-830 (GRL is the identity in forward).
+// Grid (B, 9): blockIdx.y = 0..7 → FiLM block (128 gammas + 128 betas), 8 → speaker classifier.  Every CTA
+// recomputes the 128-wide conditioning vector (24 K MACs) rather than synchronising across CTAs.
 __global__ void __launch_bounds__(256)
 style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_emb_in,
              const float* __restrict__ accent, DxModelWeights w, float* __restrict__ film,
@@ -25,9 +27,28 @@ style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_e
     __shared__ __align__(16) float s_h[DX_D];
     __shared__ __align__(16) float s_h2[DX_D];
     __shared__ float s_red[8];
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x, job = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     if (tid < DX_D) s_a[tid] = accent[b * DX_D + tid];
+    if (job == 8) {
+        if (speaker_preds == nullptr) return;
+        __syncthreads();
+        for (int n = warp; n < DX_D; n += 8) {
+            float v = dot_row_128(w.cls_w1 + n * DX_D, s_a, lane);
+            if (lane == 0) s_h[n] = fmaxf(v + w.cls_b1[n], 0.f);
+        }
+        __syncthreads();
+        for (int n = warp; n < DX_D; n += 8) {
+            float v = dot_row_128(w.cls_w2 + n * DX_D, s_h, lane);
+            if (lane == 0) s_h2[n] = fmaxf(v + w.cls_b2[n], 0.f);
+        }
+        __syncthreads();
+        for (int n = warp; n < w.n_speakers; n += 8) {
+            float v = dot_row_128(w.cls_w3 + n * DX_D, s_h2, lane);
+            if (lane == 0) speaker_preds[b * w.n_speakers + n] = v + w.cls_b3[n];
+        }
+        return;
+    }
     if (spk_emb_in != nullptr) {
         if (tid < DX_D) s_c[tid] = spk_emb_in[b * DX_D + tid];
         __syncthreads();
@@ -42,11 +63,12 @@ style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_e
         const float nrm = fmaxf(sqrtf(tot), 1e-12f);
         if (tid < DX_SPK) s_e[tid] = v / nrm;
         __syncthreads();
-        // spk projection: 128 outputs, warp per output, 192-long rows
+        // spk projection: 128 outputs, warp per output, 192-long rows (6 coalesced loads per lane)
         for (int n = warp; n < DX_D; n += 8) {
             const float* wr = w.spk_w + n * DX_SPK;
             float acc = 0.f;
-            for (int k = lane; k < DX_SPK; k += 32) acc += wr[k] * s_e[k];
+#pragma unroll
+            for (int k = 0; k < DX_SPK / 32; ++k) acc += wr[lane + 32 * k] * s_e[lane + 32 * k];
             acc = warp_sum(acc);
             if (lane == 0) s_c[n] = acc + w.spk_b[n];
         }
@@ -54,42 +76,40 @@ style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_e
     }
     if (tid < DX_D) s_c[tid] = s_a[tid] + s_c[tid];
     __syncthreads();
-    // FiLM: gammas / betas, 1024 outputs each; global block index k = n / 128
-    for (int n = warp; n < 8 * DX_D; n += 8) {
-        float g = dot_row_128(w.film_g_w + n * DX_D, s_c, lane);
-        float q = dot_row_128(w.film_b_w + n * DX_D, s_c, lane);
-        if (lane == 0) {
-            const int blk = n >> 7, i = n & 127;
-            g += w.film_g_b[n];
-            q += w.film_b_b[n];
-            const float pg = w.post_mult ? w.post_mult[blk] : 1.f;
-            const float pb = w.post_mult ? w.post_mult[8 + blk] : 1.f;
-            film[((int64_t)b * 8 + blk) * 256 + i] = pg * g + 1.f;
-            film[((int64_t)b * 8 + blk) * 256 + 128 + i] = pb * q;
+    // FiLM block `job`: outputs n = 128*job + i.  Each warp owns 16 outputs, 4 at a time for load-level parallelism.
+    const float pg = w.post_mult ? w.post_mult[job] : 1.f;
+    const float pb = w.post_mult ? w.post_mult[8 + job] : 1.f;
+    const float4 x = reinterpret_cast<const float4*>(s_c)[lane];
+    for (int i0 = warp * 16; i0 < warp * 16 + 16; i0 += 4) {
+        float g[4], q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int n = job * DX_D + i0 + u;
+            const float4 wg = reinterpret_cast<const float4*>(w.film_g_w + (int64_t)n * DX_D)[lane];
+            const float4 wb = reinterpret_cast<const float4*>(w.film_b_w + (int64_t)n * DX_D)[lane];
+            g[u] = (wg.x * x.x + wg.y * x.y) + (wg.z * x.z + wg.w * x.w);
+            q[u] = (wb.x * x.x + wb.y * x.y) + (wb.z * x.z + wb.w * x.w);
         }
-    }
-    if (speaker_preds == nullptr) return;
-    // classifier on the accent embedding
-    for (int n = warp; n < DX_D; n += 8) {
-        float v = dot_row_128(w.cls_w1 + n * DX_D, s_a, lane);
-        if (lane == 0) s_h[n] = fmaxf(v + w.cls_b1[n], 0.f);
-    }
-    __syncthreads();
-    for (int n = warp; n < DX_D; n += 8) {
-        float v = dot_row_128(w.cls_w2 + n * DX_D, s_h, lane);
-        if (lane == 0) s_h2[n] = fmaxf(v + w.cls_b2[n], 0.f);
-    }
-    __syncthreads();
-    for (int n = warp; n < w.n_speakers; n += 8) {
-        float v = dot_row_128(w.cls_w3 + n * DX_D, s_h2, lane);
-        if (lane == 0) speaker_preds[b * w.n_speakers + n] = v + w.cls_b3[n];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            g[u] = warp_sum(g[u]);
+            q[u] = warp_sum(q[u]);
+        }
+        if (lane < 4) {
+            const int i = i0 + lane, n = job * DX_D + i;
+            const float gv = (lane == 0 ? g[0] : lane == 1 ? g[1] : lane == 2 ? g[2] : g[3]) + w.film_g_b[n];
+            const float qv = (lane == 0 ? q[0] : lane == 1 ? q[1] : lane == 2 ? q[2] : q[3]) + w.film_b_b[n];
+            film[((int64_t)b * 8 + job) * 256 + i] = pg * gv + 1.f;
+            film[((int64_t)b * 8 + job) * 256 + 128 + i] = pb * qv;
+        }
     }
 }
 
 int style(const DxModelWeights* w, int B, const float* spk_embs, const float* spk_emb_in, const float* accent,
           float* film, float* speaker_preds, cudaStream_t s) {
     DX_REQUIRE(spk_embs != nullptr || spk_emb_in != nullptr, "style: speaker embeddings required");
-    style_kernel<<<B, 256, 0, s>>>(spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
+    ProfScope prof("style", s);
+    style_kernel<<<dim3(B, 9), 256, 0, s>>>(spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -27,6 +27,8 @@ namespace dx {
 constexpr int TC_BM = 128;          // rows per tile (UMMA M)
 constexpr int TC_RA = 136;          // staged A rows per chunk (130 used; stride kept 128-B aligned)
 constexpr int TC_THREADS = 192;
+constexpr int TC_MAX_N = 1024;      // widest output (conv_channels)
+constexpr size_t TC_PAR_BYTES = (TC_MAX_N + 256) * sizeof(float);
 
 struct TcParams {
     TcGemmArgs g;
@@ -36,6 +38,7 @@ struct TcParams {
     int nstages;
     uint32_t a_stage_bytes, w_stage_bytes;
     uint32_t a_lbo, a_sbo, b_lbo, b_sbo;   // descriptor strides (host-computed; debug knob can swap them)
+    uint32_t par_off;                      // byte offset of the staged epilogue parameters in dynamic smem
 };
 
 __device__ __forceinline__ int64_t tc_total_rows(const TcParams& p) {
@@ -53,8 +56,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
     uint64_t* tfull_bar = empty_bar + p.nstages;   // [2]
     uint64_t* tempty_bar = tfull_bar + 2;          // [2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    // epilogue parameters staged once per CTA (scalar global loads per element made the epilogue the bottleneck):
+    // bias zero-padded to n_tiles * NT (<= TC_MAX_N) floats, then LayerNorm gamma / beta (128 each)
+    float* s_bias = reinterpret_cast<float*>(tc_smem + p.par_off);
+    float* s_lng = s_bias + TC_MAX_N;
+    float* s_lnb = s_lng + 128;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < TC_MAX_N; i += TC_THREADS) s_bias[i] = (p.g.bias != nullptr && i < p.g.N) ? p.g.bias[i] : 0.f;
+    if (EPI == TC_EPI_LN && threadIdx.x < 128) {
+        s_lng[threadIdx.x] = p.g.ln_g[threadIdx.x];
+        s_lnb[threadIdx.x] = p.g.ln_b[threadIdx.x];
+    }
     const int64_t total = tc_total_rows(p);
     const int m_tiles = (int)((total + TC_BM - 1) / TC_BM);
     const int64_t n_items = (int64_t)m_tiles * p.n_tiles;
@@ -170,8 +183,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
                     float sum = 0.f;
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
-                        float4 b0 = reinterpret_cast<const float4*>(p.g.bias)[c * 2];
-                        float4 b1 = reinterpret_cast<const float4*>(p.g.bias)[c * 2 + 1];
+                        float4 b0 = reinterpret_cast<const float4*>(s_bias)[c * 2];
+                        float4 b1 = reinterpret_cast<const float4*>(s_bias)[c * 2 + 1];
                         const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
                         float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
                         if (p.g.res != nullptr && live) {
@@ -204,15 +217,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
 #pragma unroll
                     for (int c = 0; c < 16; ++c) {
                         __align__(16) __nv_bfloat162 o2[4];
+                        const float4 g0 = reinterpret_cast<const float4*>(s_lng)[c * 2], g1 = reinterpret_cast<const float4*>(s_lng)[c * 2 + 1];
+                        const float4 e0 = reinterpret_cast<const float4*>(s_lnb)[c * 2], e1 = reinterpret_cast<const float4*>(s_lnb)[c * 2 + 1];
+                        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                        const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                        float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        if (fp) {
+                            const float4 a0 = reinterpret_cast<const float4*>(fp)[c * 2], a1 = reinterpret_cast<const float4*>(fp)[c * 2 + 1];
+                            const float4 c0 = reinterpret_cast<const float4*>(fp + 128)[c * 2], c1 = reinterpret_cast<const float4*>(fp + 128)[c * 2 + 1];
+                            fg[0] = a0.x; fg[1] = a0.y; fg[2] = a0.z; fg[3] = a0.w; fg[4] = a1.x; fg[5] = a1.y; fg[6] = a1.z; fg[7] = a1.w;
+                            fb[0] = c0.x; fb[1] = c0.y; fb[2] = c0.z; fb[3] = c0.w; fb[4] = c1.x; fb[5] = c1.y; fb[6] = c1.z; fb[7] = c1.w;
+                        }
 #pragma unroll
                         for (int e = 0; e < 8; e += 2) {
                             const int i = c * 8 + e;
-                            float y0 = (v[i] - mean) * rstd * p.g.ln_g[i] + p.g.ln_b[i];
-                            float y1 = (v[i + 1] - mean) * rstd * p.g.ln_g[i + 1] + p.g.ln_b[i + 1];
-                            if (fp) {
-                                y0 = fp[i] * y0 + fp[128 + i];
-                                y1 = fp[i + 1] * y1 + fp[128 + i + 1];
-                            }
+                            float y0 = (v[i] - mean) * rstd * gg[e] + ee[e];
+                            float y1 = (v[i + 1] - mean) * rstd * gg[e + 1] + ee[e + 1];
+                            y0 = fg[e] * y0 + fb[e];
+                            y1 = fg[e + 1] * y1 + fb[e + 1];
                             if (!live) { y0 = 0.f; y1 = 0.f; }
                             o2[e / 2] = __floats2bfloat162_rn(y0, y1);
                         }
@@ -231,8 +253,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
                     if (nb < p.g.N && r < total) {
 #pragma unroll
                         for (int e = 0; e < 32; ++e) {
-                            float t = v[e];
-                            if (p.g.bias != nullptr && nb + e < p.g.N) t += p.g.bias[nb + e];
+                            float t = v[e] + s_bias[nb + e];
                             if (p.g.relu) t = fmaxf(t, 0.f);
                             if (!live) t = 0.f;
                             v[e] = t;
@@ -328,12 +349,15 @@ static int tc_gemm_impl(const TcGemmArgs& g, const Rows* R, int64_t M, cudaStrea
         t = p.b_lbo; p.b_lbo = p.b_sbo; p.b_sbo = t;
     }
     const size_t stage = (size_t)p.a_stage_bytes + p.w_stage_bytes;
+    DX_REQUIRE(p.n_tiles * g.nt <= TC_MAX_N, "tc_gemm: N=%d wider than %d", g.N, TC_MAX_N);
+    DX_REQUIRE(g.epilogue != TC_EPI_LN || (g.bias && g.ln_g && g.ln_b), "tc_gemm: LN epilogue needs bias, gamma, beta");
     const size_t budget = 220 * 1024;
     int nst = (int)(budget / stage);
     if (nst > 6) nst = 6;
     DX_REQUIRE(nst >= 2, "tc_gemm: stage of %zu bytes does not allow 2 stages (taps=%d ks=%d nt=%d)", stage, g.taps, g.ks, g.nt);
     p.nstages = nst;
-    const size_t smem = (size_t)nst * stage + (2 * nst + 4) * sizeof(uint64_t) + 16;
+    p.par_off = (uint32_t)round_up((int64_t)((size_t)nst * stage + (2 * nst + 4) * sizeof(uint64_t) + 16), 16);
+    const size_t smem = p.par_off + TC_PAR_BYTES;
     const int64_t max_rows = R ? R->cap : M;
     int64_t items = ((max_rows + TC_BM - 1) / TC_BM) * p.n_tiles;
     int grid = (int)(items < g_num_sms ? items : g_num_sms);
