@@ -30,7 +30,7 @@ extern "C" {
 
 #define DX_GAP 3            /* gap rows after every utterance in the packed row stream (H1 ghost rows) */
 #define DX_HALO 8           /* zero rows in front of every bf16 channel-interleaved buffer (conv tap -1)  */
-#define DX_TAIL 136         /* zero rows behind the row range (tile overruns of the last utterance)           */
+#define DX_TAIL 264         /* zero rows behind the row range (tile overruns of the last utterance)           */
 #define DX_D 128            /* hidden_embed_dim  (hparams.py:108)                                         */
 #define DX_HEADS 2          /* attn_nb_heads     (hparams.py:109)                                         */
 #define DX_DH 64            /* head dim                                                                   */
@@ -48,7 +48,8 @@ const char* dx_last_error_string(void);
 /* number of kernels launched by this library since load (bench.py's "gpu_launches") */
 int64_t     dx_launch_count(void);
 /* bring-up switches (all 0 in production).  key 0: swap LBO/SBO in the UMMA shared-memory descriptors;
- * key 1: same for the MN-major V operand of attention; key 2: synchronise after every launch (fault location). */
+ * key 1: same for the MN-major V operand of attention; key 2: synchronise after every launch (fault location);
+ * key 3: run the FFN as two GEMM launches instead of the fused kernel (A/B testing). */
 int         dx_set_debug(int key, int value);
 
 /* Per-launch timing for bench.py's roofline: while enabled, the library records a CUDA event pair around every
@@ -76,6 +77,8 @@ typedef struct {
     const float *w_qkv, *b_qkv, *w_out, *b_out, *ln1_g, *ln1_b;
     const float *w_c1, *b_c1, *w_c2, *b_c2, *ln2_g, *ln2_b;
     const void  *w_qkv_bf, *w_out_bf, *w_c1_bf, *w_c2_bf;
+    /* fused FFN kernel: conv1 packed with (nt 64, ks 128), conv2 packed with (nt 128, ks 64) */
+    const void  *w_ffn1_bf, *w_ffn2_bf;
 } DxBlockWeights;
 
 typedef struct {

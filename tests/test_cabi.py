@@ -42,9 +42,9 @@ def test_host_only_queries():
 def test_struct_sizes_match_header():
     # 16 pointers per block; the model struct is pointers + 3 block arrays + 4 int32
     import ctypes
-    assert ctypes.sizeof(_lib.DxBlockWeights) == 16 * 8
+    assert ctypes.sizeof(_lib.DxBlockWeights) == 18 * 8
     n_ptr = 19 + 14 + 8 + 4
-    assert ctypes.sizeof(_lib.DxModelWeights) == n_ptr * 8 + 3 * 4 * 16 * 8 + 16
+    assert ctypes.sizeof(_lib.DxModelWeights) == n_ptr * 8 + 3 * 4 * 18 * 8 + 16
     assert ctypes.sizeof(_lib.DxForwardArgs) == 16 + 21 * 8 + 8
 
 

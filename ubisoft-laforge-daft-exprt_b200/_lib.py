@@ -9,7 +9,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG_DIR, "libdaft_b200.so")
 
 MODE_F32, MODE_BF16 = 0, 1
-GAP, HALO, TAIL = 3, 8, 136
+GAP, HALO, TAIL = 3, 8, 264
 D, HEADS, DH, CCH, TAPS, MEL, MEL_PAD, SPK = 128, 2, 64, 1024, 3, 80, 96, 192
 
 _p = C.c_void_p
@@ -19,7 +19,7 @@ class DxBlockWeights(C.Structure):
     _fields_ = [(n, _p) for n in (
         "w_qkv", "b_qkv", "w_out", "b_out", "ln1_g", "ln1_b",
         "w_c1", "b_c1", "w_c2", "b_c2", "ln2_g", "ln2_b",
-        "w_qkv_bf", "w_out_bf", "w_c1_bf", "w_c2_bf")]
+        "w_qkv_bf", "w_out_bf", "w_c1_bf", "w_c2_bf", "w_ffn1_bf", "w_ffn2_bf")]
 
 
 class DxModelWeights(C.Structure):

@@ -1,0 +1,367 @@
+// Fused position-wise conv feed-forward for sm_100a (tcgen05 + TMEM + bulk-copy pipeline):
+//
+//   y = mask( FiLM( LN( conv1d_{C→D,k3}( ReLU( conv1d_{D→C,k3}(x) + b1 ) ) + b2 + x ) ) )
+//
+// = PositionWiseConvFF.forward (model.py:220-235) + the FFTBlock pad mask (model.py:258), evaluated on the packed row
+// stream with the reference's "live padding" semantics (H1): the hidden activation of the first row after an
+// utterance is live, everything beyond is true zero padding.  The 1024-wide hidden activation never leaves the SM.
+//
+// One CTA = 252 output rows = two "halves" of 128 hidden rows (126 outputs each, 1 halo row per side).
+//   X   [16 chunk][256 row][8]  bf16  rows R0-2 .. R0+253, loaded once per tile by 16 bulk copies; also the residual
+//   for hidden chunk c (64 channels, 16 chunks):
+//     G1  D1[h] (128x64 fp32, TMEM) = sum_tap X_h[. + tap] · W1[c][tap]         8 MMAs (128x64x16) per tap and half
+//     E1  Hs[h][c&1] = bf16(live ? ReLU(D1[h] + b1) : 0)                        4 epilogue warps, thread ↔ row
+//     G2  D2[h] (128x128 fp32, TMEM) += sum_tap Hs[h][. + tap] · W2[tap][c]     4 MMAs (128x128x16) per tap and half
+//   E2  out = mask(FiLM(LN(D2[h] + b2 + X_res)))                                 thread ↔ row, LN in registers
+// Issue order G1(c), G2(c-1): E1(c) runs under G2(c-1), so the tensor pipe only waits for an epilogue at start-up.
+// Every 16 KB weight stage (W1[c][tap] or W2[tap][c]) is used by both halves: 512 rows... 256 rows of MMA per fetch.
+// Conv taps are +16 B shifts of the no-swizzle K-major descriptors (see dx_tc_gemm.cu).
+#include "dx_common.cuh"
+#include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
+
+namespace dx {
+
+constexpr int FF_THREADS = 192;
+constexpr int FF_OUT = 126;                 // outputs per half
+constexpr int FF_TILE = 2 * FF_OUT;         // outputs per CTA tile
+constexpr int FF_NCH = 16;                  // hidden chunks of 64 channels
+constexpr int FF_WSTAGES = 5;
+constexpr uint32_t FF_X_BYTES = 16 * 256 * 16;          // 65536
+constexpr uint32_t FF_HS_ROWS = 136;
+constexpr uint32_t FF_HS_BYTES = 8 * FF_HS_ROWS * 16;   // 17408 per (half, buffer)
+constexpr uint32_t FF_W_BYTES = 16384;
+constexpr uint32_t FF_OFF_HS = FF_X_BYTES;
+constexpr uint32_t FF_OFF_W = FF_OFF_HS + 4 * FF_HS_BYTES;
+constexpr uint32_t FF_OFF_PAR = FF_OFF_W + FF_WSTAGES * FF_W_BYTES;
+constexpr uint32_t FF_PAR_FLOATS = 1024 + 128 + 128 + 128;          // b1, b2, gamma, beta
+constexpr uint32_t FF_OFF_BAR = FF_OFF_PAR + FF_PAR_FLOATS * 4;
+constexpr uint32_t FF_NBARS = 2 * FF_WSTAGES + 10;
+constexpr uint32_t FF_SMEM = FF_OFF_BAR + FF_NBARS * 8 + 16;
+
+struct FfnParams {
+    const __nv_bfloat16* x;     // [16][rows_phys][8] block input (also the residual)
+    __nv_bfloat16* out;         // [16][rows_phys][8]
+    int64_t rows_phys;
+    const __nv_bfloat16 *w1, *w2;   // packed: W1 (taps 3, K 128, N 1024, nt 64, ks 128), W2 (taps 3, K 1024, N 128, nt 128, ks 64)
+    const float *b1, *b2, *ln_g, *ln_b;
+    const float* film;          // pre-offset to the block, or null
+    int film_stride;
+    Rows R;
+};
+
+__global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
+    extern __shared__ __align__(1024) uint8_t ff_smem[];
+    uint8_t* sX = ff_smem;
+    uint8_t* sHs = ff_smem + FF_OFF_HS;         // [half][buf]
+    uint8_t* sW = ff_smem + FF_OFF_W;
+    float* s_b1 = reinterpret_cast<float*>(ff_smem + FF_OFF_PAR);
+    float* s_b2 = s_b1 + 1024;
+    float* s_g = s_b2 + 128;
+    float* s_be = s_g + 128;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ff_smem + FF_OFF_BAR);
+    uint64_t* w_full = bars;                       // [S]
+    uint64_t* w_empty = bars + FF_WSTAGES;         // [S]
+    uint64_t* x_full = bars + 2 * FF_WSTAGES;
+    uint64_t* x_empty = x_full + 1;
+    uint64_t* d1_full = x_full + 2;
+    uint64_t* d1_empty = x_full + 3;
+    uint64_t* hs_full = x_full + 4;                // [2]
+    uint64_t* hs_empty = x_full + 6;               // [2]
+    uint64_t* d2_full = x_full + 8;
+    uint64_t* d2_empty = x_full + 9;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + FF_NBARS);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t total = p.R.row_start[p.R.B];
+    const int n_tiles = (int)((total + FF_TILE - 1) / FF_TILE);
+
+    for (int i = threadIdx.x; i < 1024; i += FF_THREADS) s_b1[i] = p.b1[i];
+    if (threadIdx.x < 128) {
+        s_b2[threadIdx.x] = p.b2[threadIdx.x];
+        s_g[threadIdx.x] = p.ln_g[threadIdx.x];
+        s_be[threadIdx.x] = p.ln_b[threadIdx.x];
+    }
+    // rows 128..135 of the Hs buffers are read (taps of the two discarded output rows) but never written: zero once
+    for (int i = threadIdx.x; i < 4 * 8 * 8; i += FF_THREADS) {
+        const int hb = i >> 6, kc = (i >> 3) & 7, rr = 128 + (i & 7);
+        *reinterpret_cast<uint4*>(sHs + hb * FF_HS_BYTES + kc * FF_HS_ROWS * 16 + rr * 16) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < FF_WSTAGES; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
+        ptx::mbar_init(x_full, 1);
+        ptx::mbar_init(x_empty, 4);
+        ptx::mbar_init(d1_full, 1);
+        ptx::mbar_init(d1_empty, 4);
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&hs_full[i], 4); ptx::mbar_init(&hs_empty[i], 1); }
+        ptx::mbar_init(d2_full, 1);
+        ptx::mbar_init(d2_empty, 4);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_ptr);
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    // TMEM columns: D1[h] at 64h (64 cols each), D2[h] at 128 + 128h
+    const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 128;
+
+    if (warp == 0) {
+        // ===================== producer: X tile + weight stages =====================
+        if (ptx::elect_one()) {
+            uint32_t wit = 0, tile_it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+                const int64_t R0 = (int64_t)tile * FF_TILE;
+                ptx::mbar_wait(x_empty, (tile_it & 1) ^ 1);
+                ptx::mbar_expect_tx(x_full, FF_X_BYTES);
+                for (int kc = 0; kc < 16; ++kc)
+                    ptx::bulk_g2s(sX + kc * 4096, p.x + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, 4096, x_full);
+                // weight order must match the MMA issue order: W1(c) then W2(c-1)
+                for (int c = 0; c <= FF_NCH; ++c) {
+                    for (int which = 0; which < 2; ++which) {
+                        const int cc = which == 0 ? c : c - 1;
+                        if (cc < 0 || cc >= FF_NCH) continue;
+                        const __nv_bfloat16* base = which == 0 ? p.w1 : p.w2;
+                        for (int tap = 0; tap < 3; ++tap, ++wit) {
+                            const int s = wit % FF_WSTAGES;
+                            ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
+                            ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
+                            ptx::bulk_g2s(sW + s * FF_W_BYTES, reinterpret_cast<const uint8_t*>(base) + (size_t)(cc * 3 + tap) * FF_W_BYTES,
+                                          FF_W_BYTES, &w_full[s]);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc1 = ptx::make_idesc_bf16(128, 64);
+        constexpr uint32_t idesc2 = ptx::make_idesc_bf16(128, 128);
+        const uint32_t aX = ptx::smem_u32(sX), aHs = ptx::smem_u32(sHs), aW = ptx::smem_u32(sW);
+        uint32_t wit = 0, tile_it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+            ptx::mbar_wait(x_full, tile_it & 1);
+            ptx::mbar_wait(d2_empty, (tile_it & 1) ^ 1);
+            ptx::tc_fence_after();
+            for (int c = 0; c <= FF_NCH; ++c) {
+                if (c < FF_NCH) {
+                    // ---- G1(c): D1[h] = X_h (*) W1[c]
+                    const uint32_t n = tile_it * FF_NCH + c;
+                    ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
+                    ptx::tc_fence_after();
+                    for (int tap = 0; tap < 3; ++tap, ++wit) {
+                        const int s = wit % FF_WSTAGES;
+                        ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
+                        ptx::tc_fence_after();
+                        if (ptx::elect_one()) {
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                                for (int kk = 0; kk < 8; ++kk) {
+                                    const uint64_t da = ptx::make_desc(aX + kk * 2 * 4096 + (FF_OUT * h + tap) * 16, 4096, 128);
+                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 1024, 1024, 128);
+                                    ptx::mma_bf16(tm_d1 + 64 * h, da, db, idesc1, (tap | kk) != 0);
+                                }
+                            }
+                            ptx::mma_commit(&w_empty[s]);
+                            if (tap == 2) ptx::mma_commit(d1_full);
+                        }
+                        __syncwarp();
+                    }
+                }
+                if (c >= 1) {
+                    // ---- G2(c-1): D2[h] += Hs[h] (*) W2[c-1]
+                    const int cc = c - 1, buf = cc & 1;
+                    const uint32_t k = tile_it * (FF_NCH / 2) + (cc >> 1);
+                    ptx::mbar_wait(&hs_full[buf], k & 1);
+                    ptx::tc_fence_after();
+                    for (int tap = 0; tap < 3; ++tap, ++wit) {
+                        const int s = wit % FF_WSTAGES;
+                        ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
+                        ptx::tc_fence_after();
+                        if (ptx::elect_one()) {
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                                for (int kk = 0; kk < 4; ++kk) {
+                                    const uint64_t da = ptx::make_desc(aHs + (h * 2 + buf) * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16,
+                                                                       FF_HS_ROWS * 16, 128);
+                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
+                                    ptx::mma_bf16(tm_d2 + 128 * h, da, db, idesc2, (cc | tap | kk) != 0);
+                                }
+                            }
+                            ptx::mma_commit(&w_empty[s]);
+                            if (tap == 2) {
+                                ptx::mma_commit(&hs_empty[buf]);
+                                if (cc == FF_NCH - 1) ptx::mma_commit(d2_full);
+                            }
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps 2..5: thread ↔ row of each half =====================
+        const int lane_grp = warp & 3;
+        const int j = lane_grp * 32 + lane;                         // row inside a half
+        const uint32_t lane_off = (uint32_t)(lane_grp * 32) << 16;
+        uint32_t tile_it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+            const int64_t R0 = (int64_t)tile * FF_TILE;
+            bool hid_live[2], out_live[2], out_write[2];
+            int b_idx[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int64_t sh = R0 + FF_OUT * h - 1 + j;         // stream row of hidden row j
+                hid_live[h] = sh >= 0 && sh < total && row_live(p.R, sh, 1);
+                const int64_t so = R0 + FF_OUT * h + j;             // stream row of output row j
+                out_write[h] = j < FF_OUT && so < total;
+                out_live[h] = out_write[h] && row_live(p.R, so, 0);
+                b_idx[h] = out_write[h] ? max(p.R.row_b[so], 0) : 0;
+            }
+            ptx::mbar_wait(x_full, tile_it & 1);                     // residual rows are read from sX in E2
+            for (int c = 0; c < FF_NCH; ++c) {
+                const int buf = c & 1;
+                const uint32_t n = tile_it * FF_NCH + c;
+                const uint32_t k = tile_it * (FF_NCH / 2) + (c >> 1);
+                ptx::mbar_wait(&hs_empty[buf], (k & 1) ^ 1);         // G2(c-2) has finished reading this buffer
+                ptx::mbar_wait(d1_full, n & 1);
+                ptx::tc_fence_after();
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[64];
+                    ptx::tmem_ld32(tm_d1 + lane_off + 64 * h, v);
+                    ptx::tmem_ld32(tm_d1 + lane_off + 64 * h + 32, v + 32);
+                    ptx::tmem_ld_wait();
+                    uint8_t* dst = sHs + (h * 2 + buf) * FF_HS_BYTES + j * 16;
+#pragma unroll
+                    for (int kc = 0; kc < 8; ++kc) {
+                        const float4 ba = reinterpret_cast<const float4*>(s_b1 + c * 64)[kc * 2];
+                        const float4 bb = reinterpret_cast<const float4*>(s_b1 + c * 64)[kc * 2 + 1];
+                        const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+                        __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                        for (int e = 0; e < 8; e += 2) {
+                            float t0 = fmaxf(v[kc * 8 + e] + bz[e], 0.f);
+                            float t1 = fmaxf(v[kc * 8 + e + 1] + bz[e + 1], 0.f);
+                            if (!hid_live[h]) { t0 = 0.f; t1 = 0.f; }
+                            o2[e / 2] = __floats2bfloat162_rn(t0, t1);
+                        }
+                        *reinterpret_cast<uint4*>(dst + kc * FF_HS_ROWS * 16) = *reinterpret_cast<const uint4*>(o2);
+                    }
+                }
+                ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::mbar_arrive(d1_empty);
+                    ptx::mbar_arrive(&hs_full[buf]);
+                }
+            }
+            // ---- E2: LN epilogue of both halves
+            ptx::mbar_wait(d2_full, tile_it & 1);
+            ptx::tc_fence_after();
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                float v[128];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) ptx::tmem_ld32(tm_d2 + lane_off + 128 * h + q * 32, v + q * 32);
+                ptx::tmem_ld_wait();
+                if (!out_write[h]) continue;
+                const int64_t so = R0 + FF_OUT * h + j;
+                const uint8_t* xres = sX + (FF_OUT * h + j + 2) * 16;
+                float sum = 0.f;
+#pragma unroll
+                for (int kc = 0; kc < 16; ++kc) {
+                    const float4 ba = reinterpret_cast<const float4*>(s_b2)[kc * 2], bb = reinterpret_cast<const float4*>(s_b2)[kc * 2 + 1];
+                    const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+                    const uint4 pk = *reinterpret_cast<const uint4*>(xres + kc * 4096);
+                    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float t0 = v[kc * 8 + 2 * e] + bz[2 * e] + __low2float(h2[e]);
+                        const float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1] + __high2float(h2[e]);
+                        v[kc * 8 + 2 * e] = t0;
+                        v[kc * 8 + 2 * e + 1] = t1;
+                        sum += t0 + t1;
+                    }
+                }
+                const float mean = sum * (1.f / 128.f);
+                float sq = 0.f;
+#pragma unroll
+                for (int i = 0; i < 128; ++i) {
+                    const float d = v[i] - mean;
+                    sq = fmaf(d, d, sq);
+                }
+                const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
+                const float* fp = p.film ? p.film + (int64_t)b_idx[h] * p.film_stride : nullptr;
+#pragma unroll
+                for (int kc = 0; kc < 16; ++kc) {
+                    const float4 g0 = reinterpret_cast<const float4*>(s_g)[kc * 2], g1 = reinterpret_cast<const float4*>(s_g)[kc * 2 + 1];
+                    const float4 e0 = reinterpret_cast<const float4*>(s_be)[kc * 2], e1 = reinterpret_cast<const float4*>(s_be)[kc * 2 + 1];
+                    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                    const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                    float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    if (fp) {
+                        const float4 a0 = reinterpret_cast<const float4*>(fp)[kc * 2], a1 = reinterpret_cast<const float4*>(fp)[kc * 2 + 1];
+                        const float4 c0 = reinterpret_cast<const float4*>(fp + 128)[kc * 2], c1 = reinterpret_cast<const float4*>(fp + 128)[kc * 2 + 1];
+                        fg[0] = a0.x; fg[1] = a0.y; fg[2] = a0.z; fg[3] = a0.w; fg[4] = a1.x; fg[5] = a1.y; fg[6] = a1.z; fg[7] = a1.w;
+                        fb[0] = c0.x; fb[1] = c0.y; fb[2] = c0.z; fb[3] = c0.w; fb[4] = c1.x; fb[5] = c1.y; fb[6] = c1.z; fb[7] = c1.w;
+                    }
+                    __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                    for (int e = 0; e < 8; e += 2) {
+                        float y0 = fg[e] * ((v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e]) + fb[e];
+                        float y1 = fg[e + 1] * ((v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1]) + fb[e + 1];
+                        if (!out_live[h]) { y0 = 0.f; y1 = 0.f; }
+                        o2[e / 2] = __floats2bfloat162_rn(y0, y1);
+                    }
+                    *reinterpret_cast<uint4*>(p.out + ((int64_t)kc * p.rows_phys + DX_HALO + so) * 8) = *reinterpret_cast<const uint4*>(o2);
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                ptx::mbar_arrive(d2_empty);
+                ptx::mbar_arrive(x_empty);
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<512>(tmem_base);
+    }
+}
+
+int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
+             int film_stride, const Rows& R, cudaStream_t s) {
+    DX_REQUIRE(bw.w_ffn1_bf && bw.w_ffn2_bf, "ffn_bf16: fused-FFN packed weights missing");
+    DX_REQUIRE(x != out, "ffn_bf16: in-place operation is not supported (rows of neighbouring tiles are read as halos)");
+    static int num_sms = 0;
+    static bool configured = false;
+    if (!configured) {
+        int dev = 0;
+        DX_CHECK_CUDA(cudaGetDevice(&dev));
+        DX_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+        DX_CHECK_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FF_SMEM));
+        configured = true;
+    }
+    FfnParams p;
+    p.x = x; p.out = out; p.rows_phys = rows_phys;
+    p.w1 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn1_bf);
+    p.w2 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn2_bf);
+    p.b1 = bw.b_c1; p.b2 = bw.b_c2; p.ln_g = bw.ln2_g; p.ln_b = bw.ln2_b;
+    p.film = film; p.film_stride = film_stride; p.R = R;
+    int64_t tiles = (R.cap + FF_TILE - 1) / FF_TILE;
+    int grid = (int)(tiles < num_sms ? tiles : num_sms);
+    ProfScope prof("tc_ffn_fused", s);
+    ffn_tc_kernel<<<grid, FF_THREADS, FF_SMEM, s>>>(p);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace dx

@@ -30,6 +30,10 @@ int ln_apply_bf16(__nv_bfloat16* x, int64_t rows_phys, int C, const float* stats
 int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Rows& R, int n_rows, cudaStream_t s);
 int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s);
 
+// dx_ffn_tc.cu: fused conv1 + ReLU + conv2 + residual + LN + FiLM + mask
+int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
+             int film_stride, const Rows& R, cudaStream_t s);
+
 // dx_style.cu
 int style(const DxModelWeights* w, int B, const float* spk_embs, const float* spk_emb_in, const float* accent,
           float* film, float* speaker_preds, cudaStream_t s);

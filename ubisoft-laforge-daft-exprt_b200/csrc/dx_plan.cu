@@ -115,6 +115,8 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
         g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b; g.tag = "tc_outproj_ln";
         DX_TRY(tc_gemm(g, R, s));
     }
+    if (!debug_knob(3))
+        return ffn_bf16(p.yb, p.xb, rp, bw, film ? film + film_block * 256 : nullptr, 8 * 256, R, s);
     {   // conv1 + ReLU (hidden live one row past the utterance: H1)
         TcGemmArgs g = tc_args(p.yb, rp, DX_D, DX_C, DX_TAPS, bw.w_c1_bf, 256, 32, bw.b_c1, 1, TC_EPI_BF16, 1);
         g.out_bf = p.h1b; g.tag = "tc_ffn_conv1";
