@@ -52,6 +52,10 @@ int64_t     dx_launch_count(void);
  * key 3: run the FFN as two GEMM launches instead of the fused kernel (A/B testing). */
 int         dx_set_debug(int key, int value);
 
+/* Bring-up: while a device buffer (>= 2 KB) is set, the fused FFN kernel writes a clock64 timeline of its CTA 0
+ * into it (tools/ffn_trace.py decodes it).  NULL switches it off (the default). */
+int         dx_set_trace_buffer(void* device_ptr, int64_t bytes);
+
 /* Per-launch timing for bench.py's roofline: while enabled, the library records a CUDA event pair around every
  * launch of its main kernel families on the launching stream.  dx_profile_report synchronises the device and
  * writes one line per tag: "<tag> <launches> <total_ms>\n" (NUL-terminated), then clears the records. */

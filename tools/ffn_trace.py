@@ -1,0 +1,39 @@
+"""Timeline of CTA 0 of the fused FFN kernel (clock64 deltas), via dx_set_trace_buffer.
+
+    python tools/ffn_trace.py            # prints cycles relative to kernel start, per hidden chunk
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+from daft_exprt_b200.hparams import default_hparams  # noqa: E402
+from daft_exprt_b200.weights import make_state_dict  # noqa: E402
+from daft_exprt_b200 import synthetic, _lib  # noqa: E402
+from daft_exprt_b200.model import DaftExprt  # noqa: E402
+
+hp = default_hparams()
+model = DaftExprt(hp, mode="bf16").cuda()
+model.load_state_dict(make_state_dict(hp, 1234))
+batch = tuple(t.cuda() for t in synthetic.config_batch(hp, "cfg2"))
+for _ in range(3):
+    model(batch)
+torch.cuda.synchronize()
+lib = _lib.load()
+buf = torch.zeros(256, dtype=torch.long, device="cuda")
+lib.dx_set_trace_buffer(buf.data_ptr(), buf.numel() * 8)
+model(batch)          # every FFN launch overwrites the trace: the last one (decoder block 3, frame stream) remains
+torch.cuda.synchronize()
+lib.dx_set_trace_buffer(None, 0)
+t = buf.cpu().tolist()
+t0 = t[0]
+print(f"X landed        {t[1] - t0:8d}")
+names = ["d1_empty", "G1_issued", "hs_full", "G2_issued", "w_full0", "-", "hs_empty", "d1_full", "tmem_ld", "Hs_done"]
+print("chunk " + " ".join(f"{n:>9s}" for n in names))
+for c in range(16):
+    row = [t[8 + 12 * c + i] for i in range(10)]
+    print(f"{c:5d} " + " ".join(f"{(v - t0) if v else 0:9d}" for v in row))
+print(f"E2 start        {t[2] - t0:8d}")
+print(f"E2 done         {t[3] - t0:8d}")

@@ -60,6 +60,7 @@ SIGNATURES = {
     "dx_last_error_string": (C.c_char_p, []),
     "dx_launch_count": (C.c_int64, []),
     "dx_set_debug": (C.c_int, [C.c_int, C.c_int]),
+    "dx_set_trace_buffer": (C.c_int, [_p, C.c_int64]),
     "dx_profile_enable": (C.c_int, [C.c_int]),
     "dx_profile_report": (C.c_int, [C.c_char_p, C.c_int64]),
     "dx_row_cap": (C.c_int64, [C.c_int, C.c_int]),

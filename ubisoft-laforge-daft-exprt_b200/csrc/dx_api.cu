@@ -25,6 +25,9 @@ void set_error(const char* fmt, ...) {
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static int g_knobs[16] = {0};
 int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
+static void* g_trace = nullptr;
+static size_t g_trace_bytes = 0;
+void* trace_buffer(size_t min_bytes) { return (g_trace != nullptr && g_trace_bytes >= min_bytes) ? g_trace : nullptr; }
 
 // ---- launch profiler ----------------------------------------------------------------------------------------
 static bool g_prof_on = false;
@@ -61,6 +64,12 @@ int64_t dx_launch_count(void) { return g_launches.load(); }
 int dx_set_debug(int key, int value) {
     if (key < 0 || key >= 16) return 2;
     g_knobs[key] = value;
+    return 0;
+}
+
+int dx_set_trace_buffer(void* device_ptr, int64_t bytes) {
+    g_trace = device_ptr;
+    g_trace_bytes = device_ptr ? (size_t)bytes : 0;
     return 0;
 }
 

@@ -11,6 +11,7 @@ namespace dx {
 // ---- error handling: no exceptions cross the C ABI -------------------------------------------------------
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+void* trace_buffer(size_t min_bytes);   // dx_set_trace_buffer: device scratch for kernel timelines, or null
 int debug_knob(int key);   // dx_set_debug(key, value): bring-up switches, all 0 in production
 
 // Optional per-launch timing (dx_profile_enable): events recorded around a launch on its stream, keyed by a tag.

@@ -48,7 +48,14 @@ struct FfnParams {
     const float* film;          // pre-offset to the block, or null
     int film_stride;
     Rows R;
+    long long* trace;           // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer) or null
 };
+
+// timeline slots (CTA 0 only): [0] kernel start, [1] X landed, then per chunk c (base 8 + 12 c):
+//   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full ok, +3 G2 issued, +4 first w_full wait of G1 done
+//   epilog  +6 hs_empty ok, +7 d1_full ok, +8 TMEM loaded (half 1), +9 Hs stored + fenced
+// [2] d2_full ok (E2 start), [3] E2 done
+#define FF_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
     extern __shared__ __align__(1024) uint8_t ff_smem[];
@@ -73,6 +80,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + FF_NBARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2)) ? p.trace : nullptr;
+    if (warp == 1) FF_TRACE(0);
     const int64_t total = p.R.row_start[p.R.B];
     const int n_tiles = (int)((total + FF_TILE - 1) / FF_TILE);
 
@@ -142,6 +151,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         uint32_t wit = 0, tile_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
             ptx::mbar_wait(x_full, tile_it & 1);
+            if (tile_it == 0) FF_TRACE(1);
             ptx::mbar_wait(d2_empty, (tile_it & 1) ^ 1);
             ptx::tc_fence_after();
             for (int c = 0; c <= FF_NCH; ++c) {
@@ -150,10 +160,12 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                     const uint32_t n = tile_it * FF_NCH + c;
                     ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
                     ptx::tc_fence_after();
+                    if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
                     for (int tap = 0; tap < 3; ++tap, ++wit) {
                         const int s = wit % FF_WSTAGES;
                         ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
                         ptx::tc_fence_after();
+                        if (tile_it == 0 && tap == 0) FF_TRACE(8 + 12 * c + 4);
                         if (ptx::elect_one()) {
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
@@ -169,6 +181,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         }
                         __syncwarp();
                     }
+                    if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
                 }
                 if (c >= 1) {
                     // ---- G2(c-1): D2[h] += Hs[h] (*) W2[c-1]
@@ -176,6 +189,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                     const uint32_t k = tile_it * (FF_NCH / 2) + (cc >> 1);
                     ptx::mbar_wait(&hs_full[buf], k & 1);
                     ptx::tc_fence_after();
+                    if (tile_it == 0) FF_TRACE(8 + 12 * cc + 2);
                     for (int tap = 0; tap < 3; ++tap, ++wit) {
                         const int s = wit % FF_WSTAGES;
                         ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
@@ -199,6 +213,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         }
                         __syncwarp();
                     }
+                    if (tile_it == 0) FF_TRACE(8 + 12 * cc + 3);
                 }
             }
         }
@@ -227,14 +242,17 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 const uint32_t n = tile_it * FF_NCH + c;
                 const uint32_t k = tile_it * (FF_NCH / 2) + (c >> 1);
                 ptx::mbar_wait(&hs_empty[buf], (k & 1) ^ 1);         // G2(c-2) has finished reading this buffer
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 6);
                 ptx::mbar_wait(d1_full, n & 1);
                 ptx::tc_fence_after();
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     float v[64];
                     ptx::tmem_ld32(tm_d1 + lane_off + 64 * h, v);
                     ptx::tmem_ld32(tm_d1 + lane_off + 64 * h + 32, v + 32);
                     ptx::tmem_ld_wait();
+                    if (tile_it == 0 && h == 1) FF_TRACE(8 + 12 * c + 8);
                     uint8_t* dst = sHs + (h * 2 + buf) * FF_HS_BYTES + j * 16;
 #pragma unroll
                     for (int kc = 0; kc < 8; ++kc) {
@@ -255,6 +273,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
                 ptx::tc_fence_before();
                 __syncwarp();
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 9);
                 if (lane == 0) {
                     ptx::mbar_arrive(d1_empty);
                     ptx::mbar_arrive(&hs_full[buf]);
@@ -263,6 +282,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             // ---- E2: LN epilogue of both halves
             ptx::mbar_wait(d2_full, tile_it & 1);
             ptx::tc_fence_after();
+            if (tile_it == 0) FF_TRACE(2);
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
                 float v[128];
@@ -323,6 +343,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             }
             ptx::tc_fence_before();
             __syncwarp();
+            if (tile_it == 0) FF_TRACE(3);
             if (lane == 0) {
                 ptx::mbar_arrive(d2_empty);
                 ptx::mbar_arrive(x_empty);
@@ -356,6 +377,7 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
     p.w2 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn2_bf);
     p.b1 = bw.b_c1; p.b2 = bw.b_c2; p.ln_g = bw.ln2_g; p.ln_b = bw.ln2_b;
     p.film = film; p.film_stride = film_stride; p.R = R;
+    p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
     int64_t tiles = (R.cap + FF_TILE - 1) / FF_TILE;
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
     ProfScope prof("tc_ffn_fused", s);

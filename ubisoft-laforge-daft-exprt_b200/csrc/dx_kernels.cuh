@@ -56,6 +56,7 @@ int int_durations(float* duration, int B, int L, int sr, int flt, int hop, int c
                   int32_t* status, cudaStream_t s);
 
 // dx_tc_gemm.cu (tcgen05 tensor-core path)
+constexpr int TC_STAT_TILES = 4;   // N = 1024 as four 256-wide tiles (accent pre-net)
 enum TcEpilogue : int {
     TC_EPI_F32 = 0,        // out fp32 [rows][N] = acc (+bias)                        (tests, mel projection)
     TC_EPI_BF16 = 1,       // out bf16 interleaved = act(acc + bias), liveness-masked (QKV, conv1 hidden, pre-net)
@@ -83,7 +84,7 @@ struct TcGemmArgs {
     const float* film;          // (B, 8, 256) pre-offset to the block, or null
     int film_stride;
     // optional per-row statistics for a following LayerNorm over N > 128 (pre-net): sum / sum of squares
-    float* row_stats;           // [rows][2] or null (accumulated with atomics)
+    float* row_stats;           // [rows][TC_STAT_TILES][2] or null: per-N-tile partial sums (deterministic, no atomics)
     const char* tag;            // profiler tag (dx_profile_report)
 };
 int tc_gemm(const TcGemmArgs& g, const Rows& R, cudaStream_t s);

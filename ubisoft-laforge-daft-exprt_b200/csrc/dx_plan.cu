@@ -54,7 +54,7 @@ int plan_layout(Plan* p, int B, int L_max, int T_max, int mode, void* workspace,
         p->melp = c.take<float>(p->cap_t * DX_MEL);
     } else {
         const int64_t rp = p->rows_phys;
-        p->row_stats = c.take<float>(p->cap * 2);
+        p->row_stats = c.take<float>(p->cap * TC_STAT_TILES * 2);
         p->xb = c.take<__nv_bfloat16>(rp * DX_D);
         p->yb = c.take<__nv_bfloat16>(rp * DX_D);
         p->ob = c.take<__nv_bfloat16>(rp * DX_D);
@@ -165,14 +165,12 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         const int64_t rp = p.rows_phys;
         DX_REQUIRE(w.ae_c0_w_bf && w.ae_c1_w_bf && w.ae_c2_w_bf, "bf16 mode: packed pre-net weights missing");
         DX_TRY(pack_mel(mel_specs, RT, nullptr, p.melb, rp, s));
-        DX_CHECK_CUDA(cudaMemsetAsync(p.row_stats, 0, p.cap * 2 * sizeof(float), s));
         {
             TcGemmArgs g = tc_args(p.melb, rp, DX_MEL_PAD, DX_C, DX_TAPS, w.ae_c0_w_bf, 256, 32, w.ae_c0_b, 1, TC_EPI_BF16, 2);
             g.out_bf = p.h1b; g.row_stats = p.row_stats; g.tag = "tc_prenet0";
             DX_TRY(tc_gemm(g, RT, s));
         }
         DX_TRY(ln_apply_bf16(p.h1b, rp, DX_C, p.row_stats, w.ae_ln0_g, w.ae_ln0_b, RT, 2, s));
-        DX_CHECK_CUDA(cudaMemsetAsync(p.row_stats, 0, p.cap * 2 * sizeof(float), s));
         {
             TcGemmArgs g = tc_args(p.h1b, rp, DX_C, DX_C, DX_TAPS, w.ae_c1_w_bf, 256, 32, w.ae_c1_b, 1, TC_EPI_BF16, 1);
             g.out_bf = p.h2b; g.row_stats = p.row_stats; g.tag = "tc_prenet1";

@@ -18,7 +18,7 @@ struct Plan {
     // small per-utterance buffers
     float *accent, *sigma, *mu;
     int64_t* out_len;
-    float* row_stats;                   // [cap][2]
+    float* row_stats;                   // [cap][TC_STAT_TILES][2]
     // fp32 mode activations (row-major [cap][C])
     float *x, *y, *o, *tmp, *qkv, *h1, *h2, *melp;
     // length regulator

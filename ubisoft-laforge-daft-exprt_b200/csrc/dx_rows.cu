@@ -393,8 +393,10 @@ __global__ void ln_apply_bf16_kernel(__nv_bfloat16* __restrict__ x, int64_t rows
         *reinterpret_cast<uint4*>(ptr) = make_uint4(0u, 0u, 0u, 0u);
         return;
     }
-    const float mean = stats[r * 2] / (float)C;
-    float var = stats[r * 2 + 1] / (float)C - mean * mean;
+    const float4 s01 = reinterpret_cast<const float4*>(stats + r * (TC_STAT_TILES * 2))[0];
+    const float4 s23 = reinterpret_cast<const float4*>(stats + r * (TC_STAT_TILES * 2))[1];
+    const float mean = (((s01.x + s01.z) + s23.x) + s23.z) / (float)C;      // fixed summation order
+    float var = (((s01.y + s01.w) + s23.y) + s23.w) / (float)C - mean * mean;
     var = fmaxf(var, 0.f);
     const float rstd = rsqrtf(var + 1e-5f);
     uint4 pk = *reinterpret_cast<const uint4*>(ptr);

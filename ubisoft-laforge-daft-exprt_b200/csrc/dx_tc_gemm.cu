@@ -282,10 +282,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
                         }
                     }
                 }
-                if (p.g.row_stats != nullptr && live) {
-                    atomicAdd(p.g.row_stats + r * 2, ssum);
-                    atomicAdd(p.g.row_stats + r * 2 + 1, ssq);
-                }
+                // per-(row, N tile) partial sums, written without atomics: the consumer adds the tiles in a fixed
+                // order, so the LayerNorm statistics (and everything downstream) are run-to-run deterministic
+                if (p.g.row_stats != nullptr && r < total)
+                    *reinterpret_cast<float2*>(p.g.row_stats + (r * TC_STAT_TILES + n_tile) * 2) = make_float2(ssum, ssq);
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&tempty_bar[acc]);
@@ -351,6 +351,7 @@ static int tc_gemm_impl(const TcGemmArgs& g, const Rows* R, int64_t M, cudaStrea
     const size_t stage = (size_t)p.a_stage_bytes + p.w_stage_bytes;
     DX_REQUIRE(p.n_tiles * g.nt <= TC_MAX_N, "tc_gemm: N=%d wider than %d", g.N, TC_MAX_N);
     DX_REQUIRE(g.epilogue != TC_EPI_LN || (g.bias && g.ln_g && g.ln_b), "tc_gemm: LN epilogue needs bias, gamma, beta");
+    DX_REQUIRE(g.row_stats == nullptr || p.n_tiles == TC_STAT_TILES, "tc_gemm: row_stats needs exactly %d N tiles (got %d)", TC_STAT_TILES, p.n_tiles);
     const size_t budget = 220 * 1024;
     int nst = (int)(budget / stage);
     if (nst > 6) nst = 6;
