@@ -81,7 +81,7 @@ typedef struct {
     const float *w_qkv, *b_qkv, *w_out, *b_out, *ln1_g, *ln1_b;
     const float *w_c1, *b_c1, *w_c2, *b_c2, *ln2_g, *ln2_b;
     const void  *w_qkv_bf, *w_out_bf, *w_c1_bf, *w_c2_bf;
-    /* fused FFN kernel: conv1 packed with (nt 64, ks 128), conv2 packed with (nt 128, ks 64) */
+    /* fused FFN kernel: conv1 packed with (nt 128, ks 64), conv2 packed with (nt 128, ks 64) */
     const void  *w_ffn1_bf, *w_ffn2_bf;
 } DxBlockWeights;
 

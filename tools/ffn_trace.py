@@ -30,10 +30,21 @@ lib.dx_set_trace_buffer(None, 0)
 t = buf.cpu().tolist()
 t0 = t[0]
 print(f"X landed        {t[1] - t0:8d}")
-names = ["d1_empty", "G1_issued", "hs_full", "G2_issued", "w_full0", "-", "hs_empty", "d1_full", "tmem_ld", "Hs_done"]
+names = ["d1_empty", "G1_issued", "hs_full0", "G2_issued", "w_full0", "-", "d1_full", "tmem_ld1", "hs_empty1", "Hs_done1"]
 print("chunk " + " ".join(f"{n:>9s}" for n in names))
-for c in range(16):
+for c in range(8):
     row = [t[8 + 12 * c + i] for i in range(10)]
     print(f"{c:5d} " + " ".join(f"{(v - t0) if v else 0:9d}" for v in row))
 print(f"E2 start        {t[2] - t0:8d}")
 print(f"E2 done         {t[3] - t0:8d}")
+
+print("attention CTA (0,0,0) of the last launch (decoder block 3, longest utterance, head 0, q tile 0)")
+a0 = t[128]
+print(f"Q landed {t[129] - a0}   end {t[130] - a0}")
+an = ["kv_full", "S_issued", "p_full", "PV_issued", "s_full", "passA", "P_stored", "o_full", "folded"]
+print(" step " + " ".join(f"{n:>9s}" for n in an))
+for j in range(8):
+    row = [t[132 + 10 * j + i] for i in range(9)]
+    if not any(row):
+        break
+    print(f"{j:5d} " + " ".join(f"{(v - a0) if v else 0:9d}" for v in row))

@@ -1,8 +1,9 @@
-// tcgen05.mma issue-rate microbenchmark for sm_100a: cycles per MMA for the operand sources / layouts / CTA-group
+// tcgen05.mma throughput microbenchmark for sm_100a: cycles per MMA for the operand sources / layouts / CTA-group
 // modes the GEMM kernels can choose between.  Operand data is whatever is in shared memory (timing only).
+// The issuing code mirrors the production kernels: warp 1, elect_one, fully unrolled groups of 16 MMAs whose
+// descriptors are compile-time offsets from a uniform base (so ptxas emits straight UTCHMMA sequences).
 //
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/mma_bench tools/mma_bench.cu
-//   tools/mma_bench            # prints one line per variant: cycles/MMA, and the fraction of the 8192 MAC/clk/SM peak
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -13,7 +14,7 @@ using namespace dx;
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s -> %s\n", #x, cudaGetErrorString(e)); exit(1); } } while (0)
 
-enum { A_SMEM_NOSW = 0, A_SMEM_SW128 = 1, A_TMEM = 2 };
+enum { A_NOSW = 0, A_SW128 = 1, A_TMEM = 2 };
 
 __device__ __forceinline__ uint64_t desc_sw128(uint32_t addr) {
     uint64_t d = 0;
@@ -24,7 +25,6 @@ __device__ __forceinline__ uint64_t desc_sw128(uint32_t addr) {
     d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
     return d;
 }
-
 __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, bool acc) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -54,8 +54,8 @@ __device__ __forceinline__ uint32_t cluster_rank() {
 }
 
 // CG = 1: one CTA, M = 128.   CG = 2: CTA pair, M = 256 (128 rows per CTA), B split N/2 per CTA.
-template <int CG>
-__global__ void __launch_bounds__(128, 1) mma_bench_kernel(int N, int nmma, int a_mode, int b_sw, long long* out) {
+template <int CG, int N, int AMODE, int BSW>
+__global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long long* out) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar;
     __shared__ uint32_t tmem_ptr;
@@ -79,34 +79,44 @@ __global__ void __launch_bounds__(128, 1) mma_bench_kernel(int N, int nmma, int 
     ptx::tc_fence_after();
     const uint32_t tmem_base = tmem_ptr;
     const uint32_t sbase = ptx::smem_u32(smem);
-    // smem plan: A region 8 x 4 KB (16 KB used as one SW128 tile of 128 rows x 64 K), B region after 64 KB
-    const uint32_t sA = sbase, sB = sbase + 65536;
-    const int nb = CG == 2 ? N / 2 : N;        // B rows held by this CTA
-    if (threadIdx.x == 0 && rank == 0) {
-        const uint32_t idesc = ptx::make_idesc_bf16(CG == 2 ? 256 : 128, N);
-        long long t0 = clock64();
-        for (int i = 0; i < nmma; ++i) {
-            const int k = i & 3;               // 4 K-steps of 16 inside a 64-wide K slab, then the next "stage"
-            const int st = (i >> 2) & 3;       // 4 stages of 16 KB (A) / up to 32 KB (B)
-            uint64_t da, db;
-            if (a_mode == A_SMEM_SW128) da = desc_sw128(sA + st * 16384 + k * 32);
-            else da = ptx::make_desc(sA + st * 16384 + k * 2 * 2048, 2048, 128);
-            if (b_sw) db = desc_sw128(sB + st * 32768 + k * 32);
-            else db = ptx::make_desc(sB + st * 32768 + k * 2 * nb * 16, nb * 16, 128);
-            const uint32_t acc_stride = N <= 128 ? 128u : (a_mode == A_TMEM ? 0u : 256u);
-            const uint32_t d = tmem_base + (uint32_t)((i >> 4) & 1) * acc_stride;
-            if (CG == 2) mma_ss2(d, da, db, idesc, (i & 15) != 0);
-            else if (a_mode == A_TMEM) mma_ts(d, tmem_base + 384 + k * 8, db, idesc, (i & 15) != 0);
-            else ptx::mma_bf16(d, da, db, idesc, (i & 15) != 0);
+    const uint32_t sA = sbase, sB = sbase + 65536;     // A: 4 stages x 16 KB, B: 4 stages x 32 KB
+    constexpr int NB = CG == 2 ? N / 2 : N;            // B rows held by this CTA
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(CG == 2 ? 256 : 128, N);
+    constexpr uint32_t acc_stride = N <= 128 ? 128u : (AMODE == A_TMEM ? 0u : 256u);
+    if (warp == 1 && rank == 0) {
+        long long t0 = 0, t1 = 0, t2 = 0;
+        t0 = clock64();
+        for (int g = 0; g < ngroups; ++g) {
+            const uint32_t d = tmem_base + (uint32_t)(g & 1) * acc_stride;
+            if (ptx::elect_one()) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int k = i & 3, st = i >> 2;
+                    uint64_t da, db;
+                    if (AMODE == A_SW128) da = desc_sw128(sA + st * 16384 + k * 32);
+                    else da = ptx::make_desc(sA + st * 16384 + k * 2 * 2048, 2048, 128);
+                    if (BSW) db = desc_sw128(sB + st * 32768 + k * 32);
+                    else db = ptx::make_desc(sB + st * 32768 + k * 2 * NB * 16, NB * 16, 128);
+                    if (CG == 2) mma_ss2(d, da, db, idesc, i != 0);
+                    else if (AMODE == A_TMEM) mma_ts(d, tmem_base + 384 + k * 8, db, idesc, i != 0);
+                    else ptx::mma_bf16(d, da, db, idesc, i != 0);
+                }
+            }
+            __syncwarp();
         }
-        if (CG == 2) commit2(&bar);
-        else ptx::mma_commit(&bar);
-        long long t1 = clock64();
+        if (ptx::elect_one()) {
+            if (CG == 2) commit2(&bar);
+            else ptx::mma_commit(&bar);
+        }
+        __syncwarp();
+        t1 = clock64();
         ptx::mbar_wait(&bar, 0);
-        long long t2 = clock64();
-        out[blockIdx.x * 2] = t2 - t0;
-        out[blockIdx.x * 2 + 1] = t1 - t0;
-    } else if (CG == 2 && threadIdx.x == 0) {
+        t2 = clock64();
+        if ((threadIdx.x & 31) == 0) {
+            out[blockIdx.x * 2] = t2 - t0;
+            out[blockIdx.x * 2 + 1] = t1 - t0;
+        }
+    } else if (CG == 2 && warp == 1) {
         ptx::mbar_wait(&bar, 0);
     }
     ptx::tc_fence_before();
@@ -119,15 +129,16 @@ __global__ void __launch_bounds__(128, 1) mma_bench_kernel(int N, int nmma, int 
     }
 }
 
-template <int CG>
-static void run(const char* name, int N, int a_mode, int b_sw, int grid) {
-    const int nmma = 4096;
+template <int CG, int N, int AMODE, int BSW>
+static void run(const char* name, int grid) {
+    const int ngroups = 256, nmma = ngroups * 16;
     if (grid < CG) grid = CG;
     long long* d_out;
     CK(cudaMalloc(&d_out, grid * 2 * sizeof(long long)));
     CK(cudaMemset(d_out, 0, grid * 2 * sizeof(long long)));
     const size_t smem = 200 * 1024;
-    CK(cudaFuncSetAttribute(mma_bench_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kern = mma_bench_kernel<CG, N, AMODE, BSW>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     for (int rep = 0; rep < 2; ++rep) {
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(grid);
@@ -140,7 +151,7 @@ static void run(const char* name, int N, int a_mode, int b_sw, int grid) {
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        CK(cudaLaunchKernelEx(&cfg, mma_bench_kernel<CG>, N, nmma, a_mode, b_sw, d_out));
+        CK(cudaLaunchKernelEx(&cfg, kern, ngroups, d_out));
         CK(cudaDeviceSynchronize());
     }
     std::vector<long long> h(grid * 2);
@@ -151,25 +162,27 @@ static void run(const char* name, int N, int a_mode, int b_sw, int grid) {
     tot /= n; iss /= n;
     const double cyc = tot / nmma;
     const double macs = (double)(CG == 2 ? 256 : 128) * N * 16 / cyc / CG;    // MAC / clk / SM (peak 4096)
-    printf("%-44s N=%3d grid=%3d  %7.1f cyc/MMA (issue %6.1f)  %6.0f MAC/clk/SM = %5.1f%% of 4096\n", name, N, grid, cyc, iss / nmma,
-           macs, 100.0 * macs / 4096.0);
+    printf("%-46s N=%3d grid=%3d  %7.1f cyc/MMA (issue %6.1f)  %6.0f MAC/clk/SM = %5.1f%% of 4096\n", name, N, grid, cyc,
+           iss / nmma, macs, 100.0 * macs / 4096.0);
     fflush(stdout);
     CK(cudaFree(d_out));
 }
 
+template <int N>
+static void run_n(int grid) {
+    run<1, N, A_NOSW, 0>("cg1 SS  A no-swizzle  B no-swizzle", grid);
+    run<1, N, A_SW128, 1>("cg1 SS  A SW128       B SW128", grid);
+    run<1, N, A_TMEM, 0>("cg1 TS  A TMEM        B no-swizzle", grid);
+    run<1, N, A_TMEM, 1>("cg1 TS  A TMEM        B SW128", grid);
+    run<2, N, A_NOSW, 0>("cg2 SS  A no-swizzle  B no-swizzle (M=256)", grid);
+    run<2, N, A_SW128, 1>("cg2 SS  A SW128       B SW128      (M=256)", grid);
+}
+
 int main() {
-    for (int grid : {1, 148}) {
-        for (int N : {64, 128, 256}) {
-            run<1>("cg1 SS  A no-swizzle  B no-swizzle", N, A_SMEM_NOSW, 0, grid);
-            run<1>("cg1 SS  A SW128       B SW128", N, A_SMEM_SW128, 1, grid);
-            run<1>("cg1 SS  A no-swizzle  B SW128", N, A_SMEM_NOSW, 1, grid);
-            run<1>("cg1 TS  A TMEM        B no-swizzle", N, A_TMEM, 0, grid);
-            run<1>("cg1 TS  A TMEM        B SW128", N, A_TMEM, 1, grid);
-        }
-        for (int N : {64, 128, 256}) {
-            run<2>("cg2 SS  A no-swizzle  B no-swizzle (M=256)", N, A_SMEM_NOSW, 0, grid);
-            run<2>("cg2 SS  A SW128       B SW128      (M=256)", N, A_SMEM_SW128, 1, grid);
-        }
+    for (int grid : {2, 148}) {
+        run_n<64>(grid);
+        run_n<128>(grid);
+        run_n<256>(grid);
     }
     return 0;
 }

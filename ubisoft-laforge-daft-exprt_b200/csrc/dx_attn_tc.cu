@@ -32,7 +32,11 @@ struct AtcParams {
     int64_t rows_phys;
     Rows R;
     uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
+    long long* trace;           // bring-up: clock64 timeline of CTA (0,0,0) (dx_set_trace_buffer) or null
 };
+// timeline slots: [128] kernel start, [129] Q landed, [130] end; per KV step j (base 132 + 10 j):
+//   issuer +0 kv_full ok, +1 S issued, +2 p_full ok, +3 PV issued;  softmax +4 s_full ok, +5 pass A done, +6 P stored, +7 o_full ok, +8 folded
+#define AT_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcParams p) {
     extern __shared__ __align__(1024) uint8_t at_smem[];
@@ -56,6 +60,9 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp == 1 || warp == 2))
+                        ? p.trace : nullptr;
+    if (warp == 1) AT_TRACE(128);
     if (threadIdx.x == 0) {
         ptx::mbar_init(q_full, 1);
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
@@ -98,12 +105,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, 128);
         constexpr uint32_t idesc_o = ptx::make_idesc_bf16(128, 64) | (1u << 16);
         ptx::mbar_wait(q_full, 0);
+        AT_TRACE(129);
         const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
         for (int j = 0; j < n_kv; ++j) {
             const int st = j & 1;
             const uint32_t ph = (j >> 1) & 1;
             ptx::mbar_wait(&kv_full[st], ph);
             ptx::tc_fence_after();
+            if (j < 8) AT_TRACE(132 + 10 * j + 0);
             const uint32_t aK = ptx::smem_u32(sKV + (size_t)st * 2 * ATC_TILE_BYTES);
             const uint32_t aV = aK + ATC_TILE_BYTES;
             if (ptx::elect_one()) {
@@ -116,8 +125,10 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                 ptx::mma_commit(s_full);
             }
             __syncwarp();
+            if (j < 8) AT_TRACE(132 + 10 * j + 1);
             ptx::mbar_wait(p_full, j & 1);
             ptx::tc_fence_after();
+            if (j < 8) AT_TRACE(132 + 10 * j + 2);
             if (ptx::elect_one()) {
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {   // 128 keys = 8 x 16
@@ -129,6 +140,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                 ptx::mma_commit(&kv_empty[st]);
             }
             __syncwarp();
+            if (j < 8) AT_TRACE(132 + 10 * j + 3);
         }
     } else {
         // softmax + output: thread ↔ query row
@@ -145,40 +157,65 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
             const int k0 = j * ATC_BK;
             ptx::mbar_wait(s_full, j & 1);
             ptx::tc_fence_after();
-            // pass A: row max over valid keys
+            if (j < 8) AT_TRACE(132 + 10 * j + 4);
+            // pass A: row max over valid keys (TMEM loads double-buffered: chunk q+1 is in flight while q is reduced)
+            const int nvalid = len - k0;                       // keys of this tile that exist (>= 1)
+            const bool full = nvalid >= ATC_BK;
             float mx = -INFINITY;
-#pragma unroll 1
-            for (int q = 0; q < 4; ++q) {
-                float v[32];
-                ptx::tmem_ld32(t_s + q * 32, v);
-                ptx::tmem_ld_wait();
+            {
+                float va[32], vb[32];
+                ptx::tmem_ld32(t_s, va);
 #pragma unroll
-                for (int e = 0; e < 32; ++e)
-                    if (k0 + q * 32 + e < len) mx = fmaxf(mx, v[e]);
-            }
-            const float m_new = fmaxf(m, mx * sl2);
-            const float corr = exp2f(m - m_new);
-            float ps = 0.f;
-            // pass B: probabilities → bf16 P tile in smem (K-major, chunk = 8 keys)
-#pragma unroll 1
-            for (int q = 0; q < 4; ++q) {
-                float v[32];
-                ptx::tmem_ld32(t_s + q * 32, v);
-                ptx::tmem_ld_wait();
+                for (int q = 0; q < 4; ++q) {
+                    float* cur = (q & 1) ? vb : va;
+                    float* nxt = (q & 1) ? va : vb;
+                    ptx::tmem_ld_wait_dep(cur);
+                    if (q < 3) ptx::tmem_ld32(t_s + (q + 1) * 32, nxt);
+                    float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+                    if (full) {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    __align__(16) __nv_bfloat162 o2[4];
+                        for (int e = 0; e < 32; e += 4) {
+                            m0 = fmaxf(m0, cur[e]); m1 = fmaxf(m1, cur[e + 1]); m2 = fmaxf(m2, cur[e + 2]); m3 = fmaxf(m3, cur[e + 3]);
+                        }
+                    } else {
 #pragma unroll
-                    for (int e = 0; e < 8; e += 2) {
-                        const int kidx = k0 + q * 32 + c * 8 + e;
-                        float p0 = (kidx < len) ? exp2f(v[c * 8 + e] * sl2 - m_new) : 0.f;
-                        float p1 = (kidx + 1 < len) ? exp2f(v[c * 8 + e + 1] * sl2 - m_new) : 0.f;
-                        ps += p0 + p1;
-                        o2[e / 2] = __floats2bfloat162_rn(p0, p1);
+                        for (int e = 0; e < 32; ++e)
+                            if (q * 32 + e < nvalid) m0 = fmaxf(m0, cur[e]);
                     }
-                    *reinterpret_cast<uint4*>(sP + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                    mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
                 }
             }
+            if (j < 8) AT_TRACE(132 + 10 * j + 5);
+            const float m_new = fmaxf(m, mx * sl2);
+            const float corr = ptx::ex2_approx(m - m_new);     // m = -inf on the first tile → 0
+            float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
+            // pass B: probabilities → bf16 P tile in smem (K-major, chunk = 8 keys)
+            {
+                float va[32], vb[32];
+                ptx::tmem_ld32(t_s, va);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float* cur = (q & 1) ? vb : va;
+                    float* nxt = (q & 1) ? va : vb;
+                    ptx::tmem_ld_wait_dep(cur);
+                    if (q < 3) ptx::tmem_ld32(t_s + (q + 1) * 32, nxt);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        __align__(16) __nv_bfloat162 o2[4];
+                        float pe[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            pe[e] = ptx::ex2_approx(fmaf(cur[c * 8 + e], sl2, -m_new));
+                            if (!full && q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
+                        }
+                        ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
+                        *reinterpret_cast<uint4*>(sP + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                    }
+                }
+            }
+            const float ps = (ps0 + ps1) + (ps2 + ps3);
             l = l * corr + ps;
             m = m_new;
             // make the generic-proxy smem writes visible to the tensor core (async proxy), then signal
@@ -186,9 +223,11 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(p_full);
+            if (j < 8) AT_TRACE(132 + 10 * j + 6);
             // fold PV_j into the register accumulator
             ptx::mbar_wait(o_full, j & 1);
             ptx::tc_fence_after();
+            if (j < 8) AT_TRACE(132 + 10 * j + 7);
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 float v[32];
@@ -198,6 +237,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                 for (int e = 0; e < 32; ++e) o[q * 32 + e] = fmaf(o[q * 32 + e], corr, v[e]);
             }
             ptx::tc_fence_before();
+            if (j < 8) AT_TRACE(132 + 10 * j + 8);
         }
         if (q0 + row < len) {
             const float inv = 1.f / l;
@@ -212,6 +252,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
             }
         }
     }
+    if (warp == 2) AT_TRACE(130);
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -248,6 +289,7 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
     }
     AtcParams p;
     p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R;
+    p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
     p.v_lbo = 128; p.v_sbo = 2048;
     if (debug_knob(1)) { p.v_lbo = 2048; p.v_sbo = 128; }
     dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);

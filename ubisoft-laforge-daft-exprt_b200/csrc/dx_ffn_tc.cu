@@ -8,28 +8,34 @@
 //
 // One CTA = 252 output rows = two "halves" of 128 hidden rows (126 outputs each, 1 halo row per side).
 //   X   [16 chunk][256 row][8]  bf16  rows R0-2 .. R0+253, loaded once per tile by 16 bulk copies; also the residual
-//   for hidden chunk c (64 channels, 16 chunks):
-//     G1  D1[h] (128x64 fp32, TMEM) = sum_tap X_h[. + tap] · W1[c][tap]         8 MMAs (128x64x16) per tap and half
-//     E1  Hs[h][c&1] = bf16(live ? ReLU(D1[h] + b1) : 0)                        4 epilogue warps, thread ↔ row
-//     G2  D2[h] (128x128 fp32, TMEM) += sum_tap Hs[h][. + tap] · W2[tap][c]     4 MMAs (128x128x16) per tap and half
+//   for hidden chunk c (128 channels, 8 chunks):
+//     G1  D1[h] (128x128 fp32, TMEM) = sum_tap X_h[. + tap] · W1[c][tap]        24 MMAs (128x128x16) per half
+//     E1  Hs[h][sub] = bf16(live ? ReLU(D1[h][:, 64 sub ..] + b1) : 0)          sub = 0,1; thread ↔ row
+//     G2  D2[h] (128x128 fp32, TMEM) += sum_tap Hs[h][sub][. + tap] · W2[tap][c, sub]   12 MMAs per half and sub
 //   E2  out = mask(FiLM(LN(D2[h] + b2 + X_res)))                                 thread ↔ row, LN in registers
-// Issue order G1(c), G2(c-1): E1(c) runs under G2(c-1), so the tensor pipe only waits for an epilogue at start-up.
-// Every 16 KB weight stage (W1[c][tap] or W2[tap][c]) is used by both halves: 512 rows... 256 rows of MMA per fetch.
+// Issue order G1(c), G2(c-1, 0), G2(c-1, 1): E1(c) runs under G2(c-1).
+//
+// Why these shapes (profiles/r01b_mma_bench.txt, r01b_ffn_trace_before.txt): a 128xNx16 SS MMA reads (128+N)*32 B
+// of shared memory in N/2 cycles, so N = 64 needs 192 B/clk against the SM's 128 B/clk; the first version of this
+// kernel (64-wide hidden chunks) was shared-memory-bandwidth bound at 49 % of the tensor peak, exactly the byte
+// count / 128.  N = 128 halves G1's operand traffic.  Every 16 KB weight stage is used by both halves.
 // Conv taps are +16 B shifts of the no-swizzle K-major descriptors (see dx_tc_gemm.cu).
+// Warps: 0 = bulk-copy producer, 1 = TMEM owner + MMA issuer, 2-5 = epilogue of half 0, 6-9 = epilogue of half 1
+// (warp w may only touch TMEM lanes 32 (w % 4) .. +31).
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
 
 namespace dx {
 
-constexpr int FF_THREADS = 192;
+constexpr int FF_THREADS = 320;
 constexpr int FF_OUT = 126;                 // outputs per half
 constexpr int FF_TILE = 2 * FF_OUT;         // outputs per CTA tile
-constexpr int FF_NCH = 16;                  // hidden chunks of 64 channels
+constexpr int FF_NCH = 8;                   // hidden chunks of 128 channels
 constexpr int FF_WSTAGES = 5;
 constexpr uint32_t FF_X_BYTES = 16 * 256 * 16;          // 65536
 constexpr uint32_t FF_HS_ROWS = 136;
-constexpr uint32_t FF_HS_BYTES = 8 * FF_HS_ROWS * 16;   // 17408 per (half, buffer)
+constexpr uint32_t FF_HS_BYTES = 8 * FF_HS_ROWS * 16;   // 17408 per (half, sub)
 constexpr uint32_t FF_W_BYTES = 16384;
 constexpr uint32_t FF_OFF_HS = FF_X_BYTES;
 constexpr uint32_t FF_OFF_W = FF_OFF_HS + 4 * FF_HS_BYTES;
@@ -43,7 +49,7 @@ struct FfnParams {
     const __nv_bfloat16* x;     // [16][rows_phys][8] block input (also the residual)
     __nv_bfloat16* out;         // [16][rows_phys][8]
     int64_t rows_phys;
-    const __nv_bfloat16 *w1, *w2;   // packed: W1 (taps 3, K 128, N 1024, nt 64, ks 128), W2 (taps 3, K 1024, N 128, nt 128, ks 64)
+    const __nv_bfloat16 *w1, *w2;   // packed: W1 (taps 3, K 128, N 1024, nt 128, ks 64), W2 (taps 3, K 1024, N 128, nt 128, ks 64)
     const float *b1, *b2, *ln_g, *ln_b;
     const float* film;          // pre-offset to the block, or null
     int film_stride;
@@ -52,15 +58,15 @@ struct FfnParams {
 };
 
 // timeline slots (CTA 0 only): [0] kernel start, [1] X landed, then per chunk c (base 8 + 12 c):
-//   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full ok, +3 G2 issued, +4 first w_full wait of G1 done
-//   epilog  +6 hs_empty ok, +7 d1_full ok, +8 TMEM loaded (half 1), +9 Hs stored + fenced
+//   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full[0] ok, +3 G2 issued (both subs), +4 first w_full wait of G1 done
+//   epilog  +6 d1_full ok, +7 TMEM loaded (sub 1), +8 hs_empty[1] ok, +9 Hs stored + fenced (sub 1)
 // [2] d2_full ok (E2 start), [3] E2 done
 #define FF_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
     extern __shared__ __align__(1024) uint8_t ff_smem[];
     uint8_t* sX = ff_smem;
-    uint8_t* sHs = ff_smem + FF_OFF_HS;         // [half][buf]
+    uint8_t* sHs = ff_smem + FF_OFF_HS;         // [half][sub]
     uint8_t* sW = ff_smem + FF_OFF_W;
     float* s_b1 = reinterpret_cast<float*>(ff_smem + FF_OFF_PAR);
     float* s_b2 = s_b1 + 1024;
@@ -73,7 +79,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     uint64_t* x_empty = x_full + 1;
     uint64_t* d1_full = x_full + 2;
     uint64_t* d1_empty = x_full + 3;
-    uint64_t* hs_full = x_full + 4;                // [2]
+    uint64_t* hs_full = x_full + 4;                // [2] per sub
     uint64_t* hs_empty = x_full + 6;               // [2]
     uint64_t* d2_full = x_full + 8;
     uint64_t* d2_empty = x_full + 9;
@@ -83,7 +89,13 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2)) ? p.trace : nullptr;
     if (warp == 1) FF_TRACE(0);
     const int64_t total = p.R.row_start[p.R.B];
-    const int n_tiles = (int)((total + FF_TILE - 1) / FF_TILE);
+    // Short streams (symbol side): when the 252-row tiles would leave more than half of the CTAs idle, every CTA
+    // takes ONE half (126 outputs) instead, which halves the kernel's critical path.  Decided on the device: the
+    // valid row count is only known there.
+    const int halves = ((total + FF_TILE - 1) / FF_TILE) * 2 <= (int64_t)gridDim.x ? 1 : 2;
+    const int tile_rows = FF_OUT * halves;
+    const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
+    const uint32_t x_chunk_bytes = halves == 2 ? 4096u : 2176u;      // 256 / 136 rows of one 8-channel chunk
 
     for (int i = threadIdx.x; i < 1024; i += FF_THREADS) s_b1[i] = p.b1[i];
     if (threadIdx.x < 128) {
@@ -99,12 +111,12 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     if (threadIdx.x == 0) {
         for (int i = 0; i < FF_WSTAGES; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
         ptx::mbar_init(x_full, 1);
-        ptx::mbar_init(x_empty, 4);
+        ptx::mbar_init(x_empty, 4 * halves);
         ptx::mbar_init(d1_full, 1);
-        ptx::mbar_init(d1_empty, 4);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&hs_full[i], 4); ptx::mbar_init(&hs_empty[i], 1); }
+        ptx::mbar_init(d1_empty, 4 * halves);
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&hs_full[i], 4 * halves); ptx::mbar_init(&hs_empty[i], 1); }
         ptx::mbar_init(d2_full, 1);
-        ptx::mbar_init(d2_empty, 4);
+        ptx::mbar_init(d2_empty, 4 * halves);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<512>(tmem_ptr);
@@ -113,31 +125,30 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    // TMEM columns: D1[h] at 64h (64 cols each), D2[h] at 128 + 128h
-    const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 128;
+    // TMEM columns: D1[h] at 128 h, D2[h] at 256 + 128 h
+    const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 256;
 
     if (warp == 0) {
         // ===================== producer: X tile + weight stages =====================
         if (ptx::elect_one()) {
             uint32_t wit = 0, tile_it = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
-                const int64_t R0 = (int64_t)tile * FF_TILE;
+                const int64_t R0 = (int64_t)tile * tile_rows;
                 ptx::mbar_wait(x_empty, (tile_it & 1) ^ 1);
-                ptx::mbar_expect_tx(x_full, FF_X_BYTES);
+                ptx::mbar_expect_tx(x_full, 16 * x_chunk_bytes);
                 for (int kc = 0; kc < 16; ++kc)
-                    ptx::bulk_g2s(sX + kc * 4096, p.x + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, 4096, x_full);
-                // weight order must match the MMA issue order: W1(c) then W2(c-1)
+                    ptx::bulk_g2s(sX + kc * 4096, p.x + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, x_chunk_bytes, x_full);
+                // weight order must match the MMA issue order: W1(c) [2 K halves x 3 taps], then W2(c-1) [2 subs x 3 taps]
                 for (int c = 0; c <= FF_NCH; ++c) {
                     for (int which = 0; which < 2; ++which) {
                         const int cc = which == 0 ? c : c - 1;
                         if (cc < 0 || cc >= FF_NCH) continue;
-                        const __nv_bfloat16* base = which == 0 ? p.w1 : p.w2;
-                        for (int tap = 0; tap < 3; ++tap, ++wit) {
+                        const uint8_t* base = reinterpret_cast<const uint8_t*>(which == 0 ? p.w1 : p.w2) + (size_t)cc * 6 * FF_W_BYTES;
+                        for (int st = 0; st < 6; ++st, ++wit) {
                             const int s = wit % FF_WSTAGES;
                             ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
                             ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
-                            ptx::bulk_g2s(sW + s * FF_W_BYTES, reinterpret_cast<const uint8_t*>(base) + (size_t)(cc * 3 + tap) * FF_W_BYTES,
-                                          FF_W_BYTES, &w_full[s]);
+                            ptx::bulk_g2s(sW + s * FF_W_BYTES, base + (size_t)st * FF_W_BYTES, FF_W_BYTES, &w_full[s]);
                         }
                     }
                 }
@@ -145,8 +156,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc1 = ptx::make_idesc_bf16(128, 64);
-        constexpr uint32_t idesc2 = ptx::make_idesc_bf16(128, 128);
+        constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
         const uint32_t aX = ptx::smem_u32(sX), aHs = ptx::smem_u32(sHs), aW = ptx::smem_u32(sW);
         uint32_t wit = 0, tile_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
@@ -156,59 +166,65 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             ptx::tc_fence_after();
             for (int c = 0; c <= FF_NCH; ++c) {
                 if (c < FF_NCH) {
-                    // ---- G1(c): D1[h] = X_h (*) W1[c]
+                    // ---- G1(c): D1[h] = X_h (*) W1[c]   (stage = (K half, tap): 64 input channels x 128 hidden)
                     const uint32_t n = tile_it * FF_NCH + c;
                     ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
                     ptx::tc_fence_after();
                     if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
-                    for (int tap = 0; tap < 3; ++tap, ++wit) {
+                    for (int st = 0; st < 6; ++st, ++wit) {
+                        const int kh = st / 3, tap = st % 3;
                         const int s = wit % FF_WSTAGES;
                         ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
                         ptx::tc_fence_after();
-                        if (tile_it == 0 && tap == 0) FF_TRACE(8 + 12 * c + 4);
+                        if (tile_it == 0 && st == 0) FF_TRACE(8 + 12 * c + 4);
                         if (ptx::elect_one()) {
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
+                                if (h >= halves) break;
 #pragma unroll
-                                for (int kk = 0; kk < 8; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aX + kk * 2 * 4096 + (FF_OUT * h + tap) * 16, 4096, 128);
-                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 1024, 1024, 128);
-                                    ptx::mma_bf16(tm_d1 + 64 * h, da, db, idesc1, (tap | kk) != 0);
+                                for (int kk = 0; kk < 4; ++kk) {
+                                    const uint64_t da = ptx::make_desc(aX + (kh * 8 + kk * 2) * 4096 + (FF_OUT * h + tap) * 16, 4096, 128);
+                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
+                                    ptx::mma_bf16(tm_d1 + 128 * h, da, db, idesc, (st | kk) != 0);
                                 }
                             }
                             ptx::mma_commit(&w_empty[s]);
-                            if (tap == 2) ptx::mma_commit(d1_full);
+                            if (st == 5) ptx::mma_commit(d1_full);
                         }
                         __syncwarp();
                     }
                     if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
                 }
                 if (c >= 1) {
-                    // ---- G2(c-1): D2[h] += Hs[h] (*) W2[c-1]
-                    const int cc = c - 1, buf = cc & 1;
-                    const uint32_t k = tile_it * (FF_NCH / 2) + (cc >> 1);
-                    ptx::mbar_wait(&hs_full[buf], k & 1);
-                    ptx::tc_fence_after();
-                    if (tile_it == 0) FF_TRACE(8 + 12 * cc + 2);
-                    for (int tap = 0; tap < 3; ++tap, ++wit) {
+                    // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
+                    const int cc = c - 1;
+                    const uint32_t k = tile_it * FF_NCH + cc;
+                    for (int st = 0; st < 6; ++st, ++wit) {
+                        const int sub = st / 3, tap = st % 3;
+                        if (tap == 0) {
+                            ptx::mbar_wait(&hs_full[sub], k & 1);
+                            ptx::tc_fence_after();
+                            if (tile_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
+                        }
                         const int s = wit % FF_WSTAGES;
                         ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
                         ptx::tc_fence_after();
                         if (ptx::elect_one()) {
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
+                                if (h >= halves) break;
 #pragma unroll
                                 for (int kk = 0; kk < 4; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aHs + (h * 2 + buf) * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16,
+                                    const uint64_t da = ptx::make_desc(aHs + (h * 2 + sub) * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16,
                                                                        FF_HS_ROWS * 16, 128);
                                     const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
-                                    ptx::mma_bf16(tm_d2 + 128 * h, da, db, idesc2, (cc | tap | kk) != 0);
+                                    ptx::mma_bf16(tm_d2 + 128 * h, da, db, idesc, (cc | st | kk) != 0);
                                 }
                             }
                             ptx::mma_commit(&w_empty[s]);
                             if (tap == 2) {
-                                ptx::mma_commit(&hs_empty[buf]);
-                                if (cc == FF_NCH - 1) ptx::mma_commit(d2_full);
+                                ptx::mma_commit(&hs_empty[sub]);
+                                if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
                             }
                         }
                         __syncwarp();
@@ -217,128 +233,125 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 }
             }
         }
-    } else {
-        // ===================== epilogue warps 2..5: thread ↔ row of each half =====================
+    } else if (((warp - 2) >> 2) < halves) {
+        // ===================== epilogue: warps 2-5 own half 0, warps 6-9 own half 1; thread ↔ row =====================
+        const int h = (warp - 2) >> 2;
         const int lane_grp = warp & 3;
-        const int j = lane_grp * 32 + lane;                         // row inside a half
+        const int j = lane_grp * 32 + lane;                         // row inside the half
         const uint32_t lane_off = (uint32_t)(lane_grp * 32) << 16;
         uint32_t tile_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
-            const int64_t R0 = (int64_t)tile * FF_TILE;
-            bool hid_live[2], out_live[2], out_write[2];
-            int b_idx[2];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int64_t sh = R0 + FF_OUT * h - 1 + j;         // stream row of hidden row j
-                hid_live[h] = sh >= 0 && sh < total && row_live(p.R, sh, 1);
-                const int64_t so = R0 + FF_OUT * h + j;             // stream row of output row j
-                out_write[h] = j < FF_OUT && so < total;
-                out_live[h] = out_write[h] && row_live(p.R, so, 0);
-                b_idx[h] = out_write[h] ? max(p.R.row_b[so], 0) : 0;
-            }
+            const int64_t R0 = (int64_t)tile * tile_rows;
+            const int64_t sh = R0 + FF_OUT * h - 1 + j;             // stream row of hidden row j
+            const bool hid_live = sh >= 0 && sh < total && row_live(p.R, sh, 1);
+            const int64_t so = R0 + FF_OUT * h + j;                 // stream row of output row j
+            const bool out_write = j < FF_OUT && so < total;
+            const bool out_live = out_write && row_live(p.R, so, 0);
+            const int b_idx = out_write ? max(p.R.row_b[so], 0) : 0;
             ptx::mbar_wait(x_full, tile_it & 1);                     // residual rows are read from sX in E2
             for (int c = 0; c < FF_NCH; ++c) {
-                const int buf = c & 1;
                 const uint32_t n = tile_it * FF_NCH + c;
-                const uint32_t k = tile_it * (FF_NCH / 2) + (c >> 1);
-                ptx::mbar_wait(&hs_empty[buf], (k & 1) ^ 1);         // G2(c-2) has finished reading this buffer
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 6);
                 ptx::mbar_wait(d1_full, n & 1);
                 ptx::tc_fence_after();
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 6);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
+                for (int sub = 0; sub < 2; ++sub) {
                     float v[64];
-                    ptx::tmem_ld32(tm_d1 + lane_off + 64 * h, v);
-                    ptx::tmem_ld32(tm_d1 + lane_off + 64 * h + 32, v + 32);
+                    ptx::tmem_ld32(tm_d1 + lane_off + 128 * h + 64 * sub, v);
+                    ptx::tmem_ld32(tm_d1 + lane_off + 128 * h + 64 * sub + 32, v + 32);
                     ptx::tmem_ld_wait();
-                    if (tile_it == 0 && h == 1) FF_TRACE(8 + 12 * c + 8);
-                    uint8_t* dst = sHs + (h * 2 + buf) * FF_HS_BYTES + j * 16;
+                    if (sub == 1) {
+                        // D1 is in registers: G1(c+1) may overwrite it
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(d1_empty);
+                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
+                    }
+                    ptx::mbar_wait(&hs_empty[sub], (n & 1) ^ 1);     // G2(c-1, sub) has finished reading this buffer
+                    if (tile_it == 0 && sub == 1) FF_TRACE(8 + 12 * c + 8);
+                    uint8_t* dst = sHs + (h * 2 + sub) * FF_HS_BYTES + j * 16;
+                    const float* bias = s_b1 + c * 128 + sub * 64;
 #pragma unroll
                     for (int kc = 0; kc < 8; ++kc) {
-                        const float4 ba = reinterpret_cast<const float4*>(s_b1 + c * 64)[kc * 2];
-                        const float4 bb = reinterpret_cast<const float4*>(s_b1 + c * 64)[kc * 2 + 1];
+                        const float4 ba = reinterpret_cast<const float4*>(bias)[kc * 2];
+                        const float4 bb = reinterpret_cast<const float4*>(bias)[kc * 2 + 1];
                         const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
                         __align__(16) __nv_bfloat162 o2[4];
 #pragma unroll
                         for (int e = 0; e < 8; e += 2) {
                             float t0 = fmaxf(v[kc * 8 + e] + bz[e], 0.f);
                             float t1 = fmaxf(v[kc * 8 + e + 1] + bz[e + 1], 0.f);
-                            if (!hid_live[h]) { t0 = 0.f; t1 = 0.f; }
+                            if (!hid_live) { t0 = 0.f; t1 = 0.f; }
                             o2[e / 2] = __floats2bfloat162_rn(t0, t1);
                         }
                         *reinterpret_cast<uint4*>(dst + kc * FF_HS_ROWS * 16) = *reinterpret_cast<const uint4*>(o2);
                     }
-                }
-                ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 9);
-                if (lane == 0) {
-                    ptx::mbar_arrive(d1_empty);
-                    ptx::mbar_arrive(&hs_full[buf]);
+                    ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(&hs_full[sub]);
+                    if (tile_it == 0 && sub == 1) FF_TRACE(8 + 12 * c + 9);
                 }
             }
-            // ---- E2: LN epilogue of both halves
+            // ---- E2: LN epilogue of this half
             ptx::mbar_wait(d2_full, tile_it & 1);
             ptx::tc_fence_after();
             if (tile_it == 0) FF_TRACE(2);
-#pragma unroll 1
-            for (int h = 0; h < 2; ++h) {
+            {
                 float v[128];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) ptx::tmem_ld32(tm_d2 + lane_off + 128 * h + q * 32, v + q * 32);
                 ptx::tmem_ld_wait();
-                if (!out_write[h]) continue;
-                const int64_t so = R0 + FF_OUT * h + j;
-                const uint8_t* xres = sX + (FF_OUT * h + j + 2) * 16;
-                float sum = 0.f;
+                if (out_write) {
+                    const uint8_t* xres = sX + (FF_OUT * h + j + 2) * 16;
+                    float sum = 0.f;
 #pragma unroll
-                for (int kc = 0; kc < 16; ++kc) {
-                    const float4 ba = reinterpret_cast<const float4*>(s_b2)[kc * 2], bb = reinterpret_cast<const float4*>(s_b2)[kc * 2 + 1];
-                    const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-                    const uint4 pk = *reinterpret_cast<const uint4*>(xres + kc * 4096);
-                    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+                    for (int kc = 0; kc < 16; ++kc) {
+                        const float4 ba = reinterpret_cast<const float4*>(s_b2)[kc * 2], bb = reinterpret_cast<const float4*>(s_b2)[kc * 2 + 1];
+                        const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+                        const uint4 pk = *reinterpret_cast<const uint4*>(xres + kc * 4096);
+                        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float t0 = v[kc * 8 + 2 * e] + bz[2 * e] + __low2float(h2[e]);
-                        const float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1] + __high2float(h2[e]);
-                        v[kc * 8 + 2 * e] = t0;
-                        v[kc * 8 + 2 * e + 1] = t1;
-                        sum += t0 + t1;
+                        for (int e = 0; e < 4; ++e) {
+                            const float t0 = v[kc * 8 + 2 * e] + bz[2 * e] + __low2float(h2[e]);
+                            const float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1] + __high2float(h2[e]);
+                            v[kc * 8 + 2 * e] = t0;
+                            v[kc * 8 + 2 * e + 1] = t1;
+                            sum += t0 + t1;
+                        }
                     }
-                }
-                const float mean = sum * (1.f / 128.f);
-                float sq = 0.f;
+                    const float mean = sum * (1.f / 128.f);
+                    float sq = 0.f;
 #pragma unroll
-                for (int i = 0; i < 128; ++i) {
-                    const float d = v[i] - mean;
-                    sq = fmaf(d, d, sq);
-                }
-                const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
-                const float* fp = p.film ? p.film + (int64_t)b_idx[h] * p.film_stride : nullptr;
-#pragma unroll
-                for (int kc = 0; kc < 16; ++kc) {
-                    const float4 g0 = reinterpret_cast<const float4*>(s_g)[kc * 2], g1 = reinterpret_cast<const float4*>(s_g)[kc * 2 + 1];
-                    const float4 e0 = reinterpret_cast<const float4*>(s_be)[kc * 2], e1 = reinterpret_cast<const float4*>(s_be)[kc * 2 + 1];
-                    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                    const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
-                    float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                    if (fp) {
-                        const float4 a0 = reinterpret_cast<const float4*>(fp)[kc * 2], a1 = reinterpret_cast<const float4*>(fp)[kc * 2 + 1];
-                        const float4 c0 = reinterpret_cast<const float4*>(fp + 128)[kc * 2], c1 = reinterpret_cast<const float4*>(fp + 128)[kc * 2 + 1];
-                        fg[0] = a0.x; fg[1] = a0.y; fg[2] = a0.z; fg[3] = a0.w; fg[4] = a1.x; fg[5] = a1.y; fg[6] = a1.z; fg[7] = a1.w;
-                        fb[0] = c0.x; fb[1] = c0.y; fb[2] = c0.z; fb[3] = c0.w; fb[4] = c1.x; fb[5] = c1.y; fb[6] = c1.z; fb[7] = c1.w;
+                    for (int i = 0; i < 128; ++i) {
+                        const float d = v[i] - mean;
+                        sq = fmaf(d, d, sq);
                     }
-                    __align__(16) __nv_bfloat162 o2[4];
+                    const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
+                    const float* fp = p.film ? p.film + (int64_t)b_idx * p.film_stride : nullptr;
 #pragma unroll
-                    for (int e = 0; e < 8; e += 2) {
-                        float y0 = fg[e] * ((v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e]) + fb[e];
-                        float y1 = fg[e + 1] * ((v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1]) + fb[e + 1];
-                        if (!out_live[h]) { y0 = 0.f; y1 = 0.f; }
-                        o2[e / 2] = __floats2bfloat162_rn(y0, y1);
+                    for (int kc = 0; kc < 16; ++kc) {
+                        const float4 g0 = reinterpret_cast<const float4*>(s_g)[kc * 2], g1 = reinterpret_cast<const float4*>(s_g)[kc * 2 + 1];
+                        const float4 e0 = reinterpret_cast<const float4*>(s_be)[kc * 2], e1 = reinterpret_cast<const float4*>(s_be)[kc * 2 + 1];
+                        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                        const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                        float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        if (fp) {
+                            const float4 a0 = reinterpret_cast<const float4*>(fp)[kc * 2], a1 = reinterpret_cast<const float4*>(fp)[kc * 2 + 1];
+                            const float4 c0 = reinterpret_cast<const float4*>(fp + 128)[kc * 2], c1 = reinterpret_cast<const float4*>(fp + 128)[kc * 2 + 1];
+                            fg[0] = a0.x; fg[1] = a0.y; fg[2] = a0.z; fg[3] = a0.w; fg[4] = a1.x; fg[5] = a1.y; fg[6] = a1.z; fg[7] = a1.w;
+                            fb[0] = c0.x; fb[1] = c0.y; fb[2] = c0.z; fb[3] = c0.w; fb[4] = c1.x; fb[5] = c1.y; fb[6] = c1.z; fb[7] = c1.w;
+                        }
+                        __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                        for (int e = 0; e < 8; e += 2) {
+                            float y0 = fg[e] * ((v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e]) + fb[e];
+                            float y1 = fg[e + 1] * ((v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1]) + fb[e + 1];
+                            if (!out_live) { y0 = 0.f; y1 = 0.f; }
+                            o2[e / 2] = __floats2bfloat162_rn(y0, y1);
+                        }
+                        *reinterpret_cast<uint4*>(p.out + ((int64_t)kc * p.rows_phys + DX_HALO + so) * 8) = *reinterpret_cast<const uint4*>(o2);
                     }
-                    *reinterpret_cast<uint4*>(p.out + ((int64_t)kc * p.rows_phys + DX_HALO + so) * 8) = *reinterpret_cast<const uint4*>(o2);
                 }
             }
             ptx::tc_fence_before();
@@ -378,7 +391,7 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
     p.b1 = bw.b_c1; p.b2 = bw.b_c2; p.ln_g = bw.ln2_g; p.ln_b = bw.ln2_b;
     p.film = film; p.film_stride = film_stride; p.R = R;
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
-    int64_t tiles = (R.cap + FF_TILE - 1) / FF_TILE;
+    int64_t tiles = (R.cap + FF_OUT - 1) / FF_OUT;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
     ProfScope prof("tc_ffn_fused", s);
     ffn_tc_kernel<<<grid, FF_THREADS, FF_SMEM, s>>>(p);

@@ -6,29 +6,35 @@
 namespace dx {
 
 // ---------------------------------------------------------------------------------------------------------
-// build_rows: one CTA.  Replaces get_mask_from_lengths (model.py:14-24): every later kernel derives its pad
+// build_rows.  Replaces get_mask_from_lengths (model.py:14-24): every later kernel derives its pad
 // mask from (row_b, row_p, len).  No host sync: the total row count stays on the device (row_start[B]).
 // ---------------------------------------------------------------------------------------------------------
 __global__ void build_rows_kernel(const int64_t* __restrict__ lengths, int B, int n_max,
                                   int32_t* __restrict__ row_start, int32_t* __restrict__ row_b,
                                   int32_t* __restrict__ row_p, int64_t cap) {
     extern __shared__ int32_t s_start[];  // B + 1
-    if (threadIdx.x == 0) {
-        int32_t acc = 0;
-        for (int b = 0; b < B; ++b) {
-            s_start[b] = acc;
-            long long l = lengths[b];
-            if (l < 0) l = 0;
-            if (l > n_max) l = n_max;
-            acc += (int32_t)l + DX_GAP;
-        }
-        s_start[B] = acc;
+    // every CTA rebuilds the (tiny) prefix sum: parallel clamped loads, then one serial pass over shared memory
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        long long l = lengths[b];
+        if (l < 0) l = 0;
+        if (l > n_max) l = n_max;
+        s_start[b + 1] = (int32_t)l + DX_GAP;
     }
     __syncthreads();
-    for (int b = threadIdx.x; b <= B; b += blockDim.x) row_start[b] = s_start[b];
+    if (threadIdx.x == 0) {
+        int32_t acc = 0;
+        s_start[0] = 0;
+        for (int b = 1; b <= B; ++b) {
+            acc += s_start[b];
+            s_start[b] = acc;
+        }
+    }
+    __syncthreads();
+    if (blockIdx.x == 0)
+        for (int b = threadIdx.x; b <= B; b += blockDim.x) row_start[b] = s_start[b];
     const int32_t total = s_start[B];
     // fill (b, p) for every row: binary search of the owning utterance
-    for (int64_t r = threadIdx.x; r < cap; r += blockDim.x) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < cap; r += (int64_t)gridDim.x * blockDim.x) {
         if (r >= total) {
             row_b[r] = -1;
             row_p[r] = 0;
@@ -47,7 +53,10 @@ __global__ void build_rows_kernel(const int64_t* __restrict__ lengths, int B, in
 int build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int32_t* row_b, int32_t* row_p,
                int64_t cap, cudaStream_t s) {
     DX_REQUIRE(B >= 1 && B <= 8192, "build_rows: B=%d out of range", B);
-    build_rows_kernel<<<1, 1024, (B + 1) * sizeof(int32_t), s>>>(lengths, B, n_max, row_start, row_b, row_p, cap);
+    int grid = (int)((cap + 1023) / 1024);
+    if (grid > 148) grid = 148;
+    if (grid < 1) grid = 1;
+    build_rows_kernel<<<grid, 256, (B + 1) * sizeof(int32_t), s>>>(lengths, B, n_max, row_start, row_b, row_p, cap);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -181,7 +181,7 @@ class DaftExprt(nn.Module):
             setp(bw, "ln2_g", f32(sd[f + "layer_norm.weight"])); setp(bw, "ln2_b", f32(sd[f + "layer_norm.bias"]))
             setp(bw, "w_qkv_bf", packed(w_qkv, 128, 64)); setp(bw, "w_out_bf", packed(w_out, 128, 64))
             setp(bw, "w_c1_bf", packed(w_c1, 256, 32)); setp(bw, "w_c2_bf", packed(w_c2, 128, 64))
-            setp(bw, "w_ffn1_bf", packed(w_c1, 64, 128)); setp(bw, "w_ffn2_bf", packed(w_c2, 128, 64))
+            setp(bw, "w_ffn1_bf", packed(w_c1, 128, 64)); setp(bw, "w_ffn2_bf", packed(w_c2, 128, 64))
 
         p = "accent_encoder."
         for n in ("energy", "pitch"):
