@@ -1,0 +1,107 @@
+"""Host logic of the multi-GPU path: the shard plan and the sharded run, world_size 2 over
+``gloo`` on CPU.  The "model" here is the oracle port (tests may use it as the checker) or a cheap stand-in."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import _cases as C
+from daft_exprt_b200 import bulk, synthetic
+from oracle import daft_oracle as O
+
+
+def test_plan_is_a_partition_and_balanced():
+    hp = C.hparams()
+    in_lens, out_lens = synthetic.stream_lengths(hp, 1000, seed=43)
+    for world in (1, 2, 4, 8):
+        batches, mine = bulk.plan_shards(in_lens, out_lens, 64, world)
+        seen = sorted(i for b in batches for i in b)
+        assert seen == list(range(1000))                       # every utterance exactly once
+        assert sorted(k for m in mine for k in m) == list(range(len(batches)))
+        for b in batches:                                      # collate order: descending symbol count
+            assert [in_lens[i] for i in b] == sorted((in_lens[i] for i in b), reverse=True)
+        loads = [sum(bulk.batch_cost([in_lens[i] for i in batches[k]], [out_lens[i] for i in batches[k]]) for k in m)
+                 for m in mine]
+        assert max(loads) <= 1.25 * (sum(loads) / world) + 1e-9
+    # deterministic
+    assert bulk.plan_shards(in_lens, out_lens, 64, 4) == bulk.plan_shards(in_lens, out_lens, 64, 4)
+
+
+def test_collate_matches_forward_batch_contract():
+    hp = C.hparams()
+    stream = synthetic.UtteranceStream(hp, 10, seed=7, lmin=3, lmax=12)
+    in_lens, out_lens = stream.lengths()
+    batches = bulk.plan_batches(in_lens, out_lens, 4)
+    batch = bulk.collate(stream, batches[0])
+    assert len(batch) == 12
+    assert batch[5].tolist() == sorted(batch[5].tolist(), reverse=True)
+    assert torch.equal(batch[2].sum(dim=1), batch[9])           # data_loader.py:165-168 invariant
+    assert batch[8].shape == (4, 80, int(batch[9].max()))
+    for b in range(4):                                          # right-zero-padded
+        assert batch[0][b, int(batch[5][b]):].abs().sum() == 0
+        assert batch[8][b, :, int(batch[9][b]):].abs().sum() == 0
+
+
+class _OracleModel:
+    """Stand-in with the model's call signature, backed by the oracle port (CPU)."""
+
+    def __init__(self, hp, sd):
+        self.hp, self.sd = hp, sd
+        self.device = torch.device("cpu")
+
+    def __call__(self, batch):
+        return O.forward(self.sd, self.hp, tuple(t.clone() for t in batch))
+
+
+def _worker(rank, world, port, n_utt, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+    hp = C.hparams()
+    stream = synthetic.UtteranceStream(hp, n_utt, seed=11, lmin=3, lmax=10, dmax=3)
+    in_lens, out_lens = stream.lengths()
+    batches, mine = bulk.plan_shards(in_lens, out_lens, 3, world)
+    got = {}
+    runner = bulk.BulkRunner(_OracleModel(hp, C.state_dict()), sink=lambda i, mel: got.__setitem__(i, torch.from_numpy(mel.copy())))
+    frames = runner.run(stream, batches, mine[rank])
+    # no data-path collective: only the summary is gathered
+    tot = torch.tensor([frames], dtype=torch.long)
+    dist.all_reduce(tot)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, sorted(got))
+    if rank == 0:
+        ret["frames"] = int(tot)
+        ret["ids"] = gathered
+    ret[f"mels{rank}"] = {i: m for i, m in got.items()}
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_sharded_run_equals_single_process():
+    n_utt, world = 10, 2
+    port = 29500 + (os.getpid() % 2000)
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, port, n_utt, ret), nprocs=world, join=True)
+    hp = C.hparams()
+    stream = synthetic.UtteranceStream(hp, n_utt, seed=11, lmin=3, lmax=10, dmax=3)
+    in_lens, out_lens = stream.lengths()
+    assert ret["frames"] == sum(out_lens)
+    ids = ret["ids"]
+    assert sorted(ids[0] + ids[1]) == list(range(n_utt)) and not set(ids[0]) & set(ids[1])
+    # same batches on one process → identical mels (batch composition is part of the contract)
+    batches, _ = bulk.plan_shards(in_lens, out_lens, 3, 1)
+    single = {}
+    bulk.BulkRunner(_OracleModel(hp, C.state_dict()), sink=lambda i, mel: single.__setitem__(i, torch.from_numpy(mel.copy()))).run(
+        stream, batches, list(range(len(batches))))
+    merged = {}
+    merged.update(ret["mels0"]); merged.update(ret["mels1"])
+    for i in range(n_utt):
+        assert merged[i].shape == (80, out_lens[i])
+        # worker processes run the oracle with 2 intra-op threads, this process with the default: last-bit only
+        assert torch.allclose(merged[i], single[i], atol=1e-5, rtol=0)

@@ -204,3 +204,34 @@ def test_cfg2_full_size_properties(models, mode):
     ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))
     _check_mel(out[3][0], ref[3][0], out_len, mode)
     _check_weights(out[4], ref[4], in_len, out_len, mode)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_cfg4_long_form(models, mode):
+    """BASELINE config 4: 400 symbols, 2000 frames (attention-dominated regime; 16 KV tiles per query tile)."""
+    hp = C.hparams()
+    batch = C.synthetic.config_batch(hp, "cfg4_b1")
+    assert batch[8].shape[2] == 2000
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))
+    out = models[mode](tuple(t.cuda() for t in batch))
+    torch.cuda.synchronize()
+    _check_mel(out[3][0], ref[3][0], batch[9], mode)
+    _check_weights(out[4], ref[4], batch[5], batch[9], mode)
+
+
+def test_bulk_runner_matches_direct_forward(models):
+    """Config 3 plumbing on the device: pipelined H2D / forward / D2H + per-utterance crop == a direct call."""
+    from daft_exprt_b200 import bulk
+    hp = C.hparams()
+    m = models["bf16"]
+    stream = C.synthetic.UtteranceStream(hp, 24, seed=5, lmin=5, lmax=40)
+    in_lens, out_lens = stream.lengths()
+    batches, mine = bulk.plan_shards(in_lens, out_lens, 8, 1)
+    got = {}
+    frames = bulk.BulkRunner(m, sink=lambda i, mel: got.__setitem__(i, torch.from_numpy(mel.copy()))).run(stream, batches, mine[0])
+    assert frames == sum(out_lens) and sorted(got) == list(range(24))
+    for b in batches:
+        host = bulk.collate(stream, b)
+        mel = m(tuple(t.cuda() for t in host))[3][0].cpu()
+        for k, i in enumerate(b):
+            assert torch.equal(got[i], mel[k, :, :out_lens[i]])

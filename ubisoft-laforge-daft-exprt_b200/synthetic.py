@@ -79,3 +79,75 @@ CONFIGS = {
 
 def config_batch(hp, name):
     return forward_batch(hp, **CONFIGS[name])
+
+
+# ----------------------------------------------------------------------------------------------
+# utterance streams (BASELINE.json config 3: bulk generation over many utterances)
+# ----------------------------------------------------------------------------------------------
+def _utt_lengths(hp, index, seed, lmin, lmax, dmin, dmax):
+    g = torch.Generator().manual_seed(int(seed) + int(index))
+    L = int(torch.randint(lmin, lmax + 1, (1,), generator=g))
+    dint = torch.randint(dmin, dmax + 1, (L,), generator=g, dtype=torch.long)
+    return g, L, dint
+
+
+def stream_lengths(hp, n, seed=43, lmin=20, lmax=150, dmin=1, dmax=9):
+    """(in_lens, out_lens) lists of utterances 0..n-1 of the stream, without materialising them."""
+    in_lens, out_lens = [], []
+    for i in range(n):
+        _, L, dint = _utt_lengths(hp, i, seed, lmin, lmax, dmin, dmax)
+        in_lens.append(L)
+        out_lens.append(int(dint.sum()))
+    return in_lens, out_lens
+
+
+def utterance(hp, index, seed=43, lmin=20, lmax=150, dmin=1, dmax=9):
+    """One utterance of the stream in the reference's per-item layout (``data_loader.py:123-178``)."""
+    g, L, dint = _utt_lengths(hp, index, seed, lmin, lmax, dmin, dmax)
+    T = int(dint.sum())
+    return {
+        "symbols": torch.randint(1, hp.n_symbols, (L,), generator=g, dtype=torch.long),
+        "durations_int": dint,
+        "durations_float": dint.float() * (hp.hop_length / hp.sampling_rate),
+        "symbols_energy": torch.randn(L, generator=g),
+        "symbols_pitch": torch.randn(L, generator=g),
+        "frames_energy": torch.randn(T, generator=g).abs(),
+        "frames_pitch": torch.randn(T, generator=g).abs(),
+        "mel": torch.randn(hp.n_mel_channels, T, generator=g),
+        "speaker_id": torch.randint(0, hp.n_speakers, (), generator=g, dtype=torch.long),
+        "spk_emb": torch.randn(getattr(hp, "external_emb_dim", 192), generator=g),
+    }
+
+
+class UtteranceStream:
+    """Lazy dict-of-lists view over a synthetic stream: ``stream[field][i]`` builds utterance i on demand
+    (a small LRU keeps the ones of the batch being collated)."""
+
+    FIELDS = ("symbols", "durations_int", "durations_float", "symbols_energy", "symbols_pitch", "frames_energy",
+              "frames_pitch", "mel", "speaker_id", "spk_emb")
+
+    class _Field:
+        def __init__(self, owner, name):
+            self.owner, self.name = owner, name
+
+        def __getitem__(self, i):
+            return self.owner._get(i)[self.name]
+
+    def __init__(self, hp, n, seed=43, **kw):
+        self.hp, self.n, self.seed, self.kw = hp, n, seed, kw
+        self._cache = {}
+
+    def _get(self, i):
+        u = self._cache.get(i)
+        if u is None:
+            if len(self._cache) > 256:
+                self._cache.clear()
+            u = utterance(self.hp, i, self.seed, **self.kw)
+            self._cache[i] = u
+        return u
+
+    def __getitem__(self, name):
+        return UtteranceStream._Field(self, name)
+
+    def lengths(self):
+        return stream_lengths(self.hp, self.n, self.seed, **self.kw)
