@@ -154,7 +154,7 @@ def reference_arm(args):
                          "sample": f"16 of the 64 cfg2 utterances per step ({frames} valid frames), {args.steps} steps"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -166,7 +166,27 @@ def parse_profile(text):
     return out
 
 
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """Library chatter (e.g. NCCL's version banner) goes to stdout: keep the contract's ONE JSON line clean by
+    pointing fd 1 at stderr and writing the result line to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -347,7 +367,7 @@ def main():
             "kernels_ms_per_step": {k: round(v[1], 4) for k, v in sorted(prof.items())},
             "whole_model_tflops": batch_flops(host_batch, forward_flops) * world / (ms_res * 1e-3) / 1e12,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -40,6 +40,8 @@ struct AtcParams {
 
 __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcParams p) {
     extern __shared__ __align__(1024) uint8_t at_smem[];
+    ptx::griddep_wait();      // PDL: the lengths and QKV come from earlier kernels
+    ptx::griddep_launch();
     const int b = blockIdx.z, h = blockIdx.y;
     const int len = (int)min((long long)p.R.len[b], (long long)p.R.n_max);
     const int q0 = blockIdx.x * ATC_BQ;
@@ -264,6 +266,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
 // zero `n_rows` rows starting at the stream's total (tiles of the last utterance read a little past the end of
 // the stream; those rows must hold finite values because 0 * NaN would poison the P·V product)
 __global__ void zero_tail_rows_kernel(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, Rows R, int n_rows) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int64_t total = R.row_start[R.B];
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)nchunks * n_rows) return;
@@ -275,7 +279,7 @@ __global__ void zero_tail_rows_kernel(__nv_bfloat16* buf, int nchunks, int64_t r
 
 int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Rows& R, int n_rows, cudaStream_t s) {
     const int64_t n = (int64_t)nchunks * n_rows;
-    zero_tail_rows_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(buf, nchunks, rows_phys, R, n_rows);
+    DX_LAUNCH_PDL((zero_tail_rows_kernel), (int)((n + 255) / 256), 256, 0, s, buf, nchunks, rows_phys, R, n_rows);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -294,7 +298,7 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
     if (debug_knob(1)) { p.v_lbo = 2048; p.v_sbo = 128; }
     dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_tc", s);
-    attention_tc_kernel<<<grid, ATC_THREADS, smem, s>>>(p);
+    DX_LAUNCH_PDL((attention_tc_kernel), grid, ATC_THREADS, smem, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }

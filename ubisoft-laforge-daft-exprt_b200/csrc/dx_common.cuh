@@ -79,6 +79,32 @@ __device__ __forceinline__ bool row_live(const Rows& R, int64_t r, int ext) {
     return p < lim;
 }
 
+// Launch with programmatic stream serialization (PDL): the kernel may start while the previous kernel of the
+// stream drains; it must call ptx::griddep_wait() before touching anything that kernel wrote.  debug knob 5
+// switches the attribute off (plain stream order) for A/B measurements.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = debug_knob(5) ? 0 : 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define DX_LAUNCH_PDL(kernel, grid, block, smem, stream, ...)                                  \
+    do {                                                                                      \
+        cudaError_t _le = dx::launch_pdl(kernel, grid, block, smem, stream, __VA_ARGS__);     \
+        if (_le != cudaSuccess) {                                                             \
+            dx::set_error("%s:%d: launch of %s -> %s", __FILE__, __LINE__, #kernel, cudaGetErrorString(_le)); \
+            return 1;                                                                         \
+        }                                                                                     \
+    } while (0)
+
 static inline int64_t round_up(int64_t a, int64_t m) { return (a + m - 1) / m * m; }
 
 // ---- warp helpers ----------------------------------------------------------------------------------------

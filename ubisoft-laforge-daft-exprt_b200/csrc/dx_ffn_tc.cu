@@ -88,15 +88,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2)) ? p.trace : nullptr;
     if (warp == 1) FF_TRACE(0);
-    const int64_t total = p.R.row_start[p.R.B];
-    // Short streams (symbol side): when the 252-row tiles would leave more than half of the CTAs idle, every CTA
-    // takes ONE half (126 outputs) instead, which halves the kernel's critical path.  Decided on the device: the
-    // valid row count is only known there.
-    const int halves = ((total + FF_TILE - 1) / FF_TILE) * 2 <= (int64_t)gridDim.x ? 1 : 2;
-    const int tile_rows = FF_OUT * halves;
-    const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
-    const uint32_t x_chunk_bytes = halves == 2 ? 4096u : 2176u;      // 256 / 136 rows of one 8-channel chunk
 
+    // ---- prologue that does not depend on the previous kernel (PDL: overlaps its tail) ----
     for (int i = threadIdx.x; i < 1024; i += FF_THREADS) s_b1[i] = p.b1[i];
     if (threadIdx.x < 128) {
         s_b2[threadIdx.x] = p.b2[threadIdx.x];
@@ -110,6 +103,34 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     }
     if (threadIdx.x == 0) {
         for (int i = 0; i < FF_WSTAGES; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_ptr);
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+    // the first FF_WSTAGES weight stages are the same for every tile (W1 chunk 0): fetch them now
+    if (warp == 0 && ptx::elect_one()) {
+        for (int s0 = 0; s0 < FF_WSTAGES; ++s0) {
+            ptx::mbar_expect_tx(&w_full[s0], FF_W_BYTES);
+            ptx::bulk_g2s(sW + s0 * FF_W_BYTES, reinterpret_cast<const uint8_t*>(p.w1) + (size_t)s0 * FF_W_BYTES, FF_W_BYTES, &w_full[s0]);
+        }
+    }
+    __syncwarp();
+    ptx::griddep_launch();
+    ptx::griddep_wait();
+    // ---- from here on the previous kernel's output (row map, activations) may be read ----
+    const int64_t total = p.R.row_start[p.R.B];
+    // Short streams (symbol side): when the 252-row tiles would leave more than half of the CTAs idle, every CTA
+    // takes ONE half (126 outputs) instead, which halves the kernel's critical path.  Decided on the device: the
+    // valid row count is only known there.
+    const int halves = ((total + FF_TILE - 1) / FF_TILE) * 2 <= (int64_t)gridDim.x ? 1 : 2;
+    const int tile_rows = FF_OUT * halves;
+    const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
+    const uint32_t x_chunk_bytes = halves == 2 ? 4096u : 2176u;      // 256 / 136 rows of one 8-channel chunk
+    if (threadIdx.x == 0) {
         ptx::mbar_init(x_full, 1);
         ptx::mbar_init(x_empty, 4 * halves);
         ptx::mbar_init(d1_full, 1);
@@ -119,12 +140,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         ptx::mbar_init(d2_empty, 4 * halves);
         ptx::fence_barrier_init();
     }
-    if (warp == 1) ptx::tmem_alloc<512>(tmem_ptr);
-    ptx::fence_proxy_async();
-    ptx::tc_fence_before();
     __syncthreads();
-    ptx::tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
     // TMEM columns: D1[h] at 128 h, D2[h] at 256 + 128 h
     const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 256;
 
@@ -145,6 +161,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         if (cc < 0 || cc >= FF_NCH) continue;
                         const uint8_t* base = reinterpret_cast<const uint8_t*>(which == 0 ? p.w1 : p.w2) + (size_t)cc * 6 * FF_W_BYTES;
                         for (int st = 0; st < 6; ++st, ++wit) {
+                            if (wit < FF_WSTAGES) continue;          // fetched in the prologue
                             const int s = wit % FF_WSTAGES;
                             ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
                             ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
@@ -159,6 +176,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
         const uint32_t aX = ptx::smem_u32(sX), aHs = ptx::smem_u32(sHs), aW = ptx::smem_u32(sW);
         uint32_t wit = 0, tile_it = 0;
+        if ((int)blockIdx.x >= n_tiles)      // no tile: the prefetched weight stages must land before the CTA exits
+            for (int s0 = 0; s0 < FF_WSTAGES; ++s0) ptx::mbar_wait(&w_full[s0], 0);
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
             ptx::mbar_wait(x_full, tile_it & 1);
             if (tile_it == 0) FF_TRACE(1);
@@ -394,7 +413,7 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
     int64_t tiles = (R.cap + FF_OUT - 1) / FF_OUT;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
     ProfScope prof("tc_ffn_fused", s);
-    ffn_tc_kernel<<<grid, FF_THREADS, FF_SMEM, s>>>(p);
+    DX_LAUNCH_PDL((ffn_tc_kernel), grid, FF_THREADS, FF_SMEM, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }

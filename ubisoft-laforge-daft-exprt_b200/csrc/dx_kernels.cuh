@@ -88,6 +88,8 @@ struct TcGemmArgs {
     const char* tag;            // profiler tag (dx_profile_report)
 };
 int tc_gemm(const TcGemmArgs& g, const Rows& R, cudaStream_t s);
+// dx_tc_linear.cu: weight-resident variant for K = 128, taps = 1, N <= 384 (QKV / out-proj + LN / mel projection)
+int tc_linear(const TcGemmArgs& g, const Rows& R, cudaStream_t s);
 int tc_gemm_plain(const TcGemmArgs& g, int64_t M, cudaStream_t s);   // no row map: rows [0, M) all live
 int pack_weight_bf16(const float* w, int taps, int K, int N, int nt, int ks, __nv_bfloat16* out, cudaStream_t s);
 int64_t packed_weight_elems(int taps, int K, int N, int nt, int ks);

@@ -4,6 +4,7 @@
 // normalisation and the contraction stay fp32 in both arithmetic modes.
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
 
 namespace dx {
 
@@ -33,6 +34,8 @@ __global__ void lenreg_symbols_kernel(const float* __restrict__ x_f32, const __n
                                       int64_t rows_phys, Rows R, const float* __restrict__ dur,
                                       const float* __restrict__ energy, const float* __restrict__ pitch,
                                       DxModelWeights w, float* __restrict__ xs, float* __restrict__ sigma) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -73,9 +76,9 @@ int lenreg_symbols(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_p
                    float* sigma, cudaStream_t s) {
     int grid = (int)((RL.cap + 7) / 8);
     if (x_bf)
-        lenreg_symbols_kernel<true><<<grid, 256, 0, s>>>(nullptr, x_bf, rows_phys, RL, dur, energy, pitch, *w, xs, sigma);
+        DX_LAUNCH_PDL((lenreg_symbols_kernel<true>), grid, 256, 0, s, nullptr, x_bf, rows_phys, RL, dur, energy, pitch, *w, xs, sigma);
     else
-        lenreg_symbols_kernel<false><<<grid, 256, 0, s>>>(x_f32, nullptr, 0, RL, dur, energy, pitch, *w, xs, sigma);
+        DX_LAUNCH_PDL((lenreg_symbols_kernel<false>), grid, 256, 0, s, x_f32, nullptr, 0, RL, dur, energy, pitch, *w, xs, sigma);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -88,6 +91,8 @@ int lenreg_symbols(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_p
 __global__ void lenreg_scan_kernel(const int64_t* __restrict__ dint, int B, int L, int clamp_one,
                                    int64_t* __restrict__ cumsum, float* __restrict__ mu,
                                    int64_t* __restrict__ out_len, int64_t* __restrict__ two_mu) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
     const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (b >= B) return;
@@ -120,7 +125,7 @@ __global__ void lenreg_scan_kernel(const int64_t* __restrict__ dint, int B, int 
 
 int lenreg_scan(const int64_t* dint, int B, int L, bool clamp_one, int64_t* cumsum, float* mu, int64_t* out_len,
                 int64_t* two_mu, cudaStream_t s) {
-    lenreg_scan_kernel<<<(B + 7) / 8, 256, 0, s>>>(dint, B, L, clamp_one ? 1 : 0, cumsum, mu, out_len, two_mu);
+    DX_LAUNCH_PDL((lenreg_scan_kernel), (B + 7) / 8, 256, 0, s, dint, B, L, clamp_one ? 1 : 0, cumsum, mu, out_len, two_mu);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -177,6 +182,8 @@ lenreg_frames_kernel(const float* __restrict__ xs, Rows RL, Rows RT, const float
                      const float* __restrict__ sigma, const float* __restrict__ pos,
                      float* __restrict__ weights, float* __restrict__ xo_f32, __nv_bfloat16* __restrict__ xo_bf,
                      int64_t rows_phys_t) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     extern __shared__ __align__(16) float lr_smem[];
     const int L = RL.n_max, T = RT.n_max;
     const int Lp = (L + 3) & ~3;      // keep the float4-read tile below 16-byte aligned
@@ -280,9 +287,9 @@ int lenreg_frames(const float* xs, const Rows& RL, const Rows& RT, const float* 
     dim3 grid((unsigned)((RT.n_max + DX_GAP + LR_FT - 1) / LR_FT), (unsigned)RT.B);
     ProfScope prof("lenreg_frames", s);
     if (xo_bf)
-        lenreg_frames_kernel<true><<<grid, 256, smem, s>>>(xs, RL, RT, mu, sigma, pos, weights, nullptr, xo_bf, rows_phys_t);
+        DX_LAUNCH_PDL((lenreg_frames_kernel<true>), grid, 256, smem, s, xs, RL, RT, mu, sigma, pos, weights, nullptr, xo_bf, rows_phys_t);
     else
-        lenreg_frames_kernel<false><<<grid, 256, smem, s>>>(xs, RL, RT, mu, sigma, pos, weights, xo_f32, nullptr, 0);
+        DX_LAUNCH_PDL((lenreg_frames_kernel<false>), grid, 256, smem, s, xs, RL, RT, mu, sigma, pos, weights, xo_f32, nullptr, 0);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -100,6 +100,11 @@ static TcGemmArgs tc_args(const __nv_bfloat16* a, int64_t rp, int K, int N, int 
     return g;
 }
 
+// K = 128 linear layers go to the weight-resident kernel (debug knob 4: use the generic conv-GEMM kernel instead)
+static int linear_bf16(const TcGemmArgs& g, const Rows& R, cudaStream_t s) {
+    return debug_knob(4) ? tc_gemm(g, R, s) : tc_linear(g, R, s);
+}
+
 static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R, const float* film, int film_block,
                           cudaStream_t s) {
     const int64_t rp = p.rows_phys;
@@ -107,13 +112,13 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
     {   // QKV projection
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, 3 * DX_D, 1, bw.w_qkv_bf, 128, 64, bw.b_qkv, 0, TC_EPI_BF16, -1);
         g.out_bf = p.qkvb; g.tag = "tc_qkv";
-        DX_TRY(tc_gemm(g, R, s));
+        DX_TRY(linear_bf16(g, R, s));
     }
     DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
     {   // out-proj + residual + LN + mask
         TcGemmArgs g = tc_args(p.ob, rp, DX_D, DX_D, 1, bw.w_out_bf, 128, 64, bw.b_out, 0, TC_EPI_LN, 0);
         g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b; g.tag = "tc_outproj_ln";
-        DX_TRY(tc_gemm(g, R, s));
+        DX_TRY(linear_bf16(g, R, s));
     }
     if (!debug_knob(3))
         return ffn_bf16(p.yb, p.xb, rp, bw, film ? film + film_block * 256 : nullptr, 8 * 256, R, s);
@@ -248,7 +253,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
         DX_REQUIRE(w.mel_w_bf, "bf16 mode: packed mel projection missing");
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, DX_MEL, 1, w.mel_w_bf, 128, 64, w.mel_b, 0, TC_EPI_F32, -1);
         g.out_f32 = p.melo; g.tag = "tc_melproj";
-        DX_TRY(tc_gemm(g, RT, s));
+        DX_TRY(linear_bf16(g, RT, s));
     } else {
         DX_TRY(gemm_f32(p.x, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
     }

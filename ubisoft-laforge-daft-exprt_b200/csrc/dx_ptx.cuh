@@ -19,6 +19,15 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------------
+// griddep_launch: this CTA allows the next kernel in the stream to start launching (it fires once every CTA of
+// this grid has called it or exited, i.e. when no CTA of this grid is still waiting for an SM).
+// griddep_wait: returns when the previous kernel in the stream has completed and its writes are visible; a no-op
+// for a kernel launched without the programmatic-serialization attribute.  Every kernel of the pass calls it
+// before its first read of activations and before any global write, so completion stays transitive.
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- mbarrier ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

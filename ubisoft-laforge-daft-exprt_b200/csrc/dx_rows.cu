@@ -2,6 +2,7 @@
 // layouts ((B, C, T) / (B, L)) and the packed row stream.  All HBM-bound, coalesced kernels.
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
 
 namespace dx {
 
@@ -12,6 +13,8 @@ namespace dx {
 __global__ void build_rows_kernel(const int64_t* __restrict__ lengths, int B, int n_max,
                                   int32_t* __restrict__ row_start, int32_t* __restrict__ row_b,
                                   int32_t* __restrict__ row_p, int64_t cap) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     extern __shared__ int32_t s_start[];  // B + 1
     // every CTA rebuilds the (tiny) prefix sum: parallel clamped loads, then one serial pass over shared memory
     for (int b = threadIdx.x; b < B; b += blockDim.x) {
@@ -56,7 +59,7 @@ int build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int
     int grid = (int)((cap + 1023) / 1024);
     if (grid > 148) grid = 148;
     if (grid < 1) grid = 1;
-    build_rows_kernel<<<grid, 256, (B + 1) * sizeof(int32_t), s>>>(lengths, B, n_max, row_start, row_b, row_p, cap);
+    DX_LAUNCH_PDL((build_rows_kernel), grid, 256, (B + 1) * sizeof(int32_t), s, lengths, B, n_max, row_start, row_b, row_p, cap);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -70,6 +73,8 @@ int build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int
 template <bool OUT_BF16>
 __global__ void pack_mel_kernel(const float* __restrict__ mel, Rows R, int C, float* __restrict__ out_f32,
                                 __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ float tile[32][DX_MEL + 1];
     const int64_t r0 = (int64_t)blockIdx.x * 32;
     const int32_t total = R.row_start[R.B];
@@ -109,9 +114,9 @@ int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out
              cudaStream_t s) {
     int grid = (int)(R.cap / 32);
     if (out_bf)
-        pack_mel_kernel<true><<<grid, 256, 0, s>>>(mel, R, DX_MEL, nullptr, out_bf, rows_phys);
+        DX_LAUNCH_PDL((pack_mel_kernel<true>), grid, 256, 0, s, mel, R, DX_MEL, nullptr, out_bf, rows_phys);
     else
-        pack_mel_kernel<false><<<grid, 256, 0, s>>>(mel, R, DX_MEL, out_f32, nullptr, 0);
+        DX_LAUNCH_PDL((pack_mel_kernel<false>), grid, 256, 0, s, mel, R, DX_MEL, out_f32, nullptr, 0);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -121,6 +126,8 @@ int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out
 // model.py:562-563).  Every element of the output is written.
 // ---------------------------------------------------------------------------------------------------------
 __global__ void unpack_mel_kernel(const float* __restrict__ rows, Rows R, int C, float* __restrict__ mel) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ float tile[32][DX_MEL + 1];
     const int b = blockIdx.y;
     const int t0 = blockIdx.x * 32;
@@ -140,7 +147,7 @@ __global__ void unpack_mel_kernel(const float* __restrict__ rows, Rows R, int C,
 
 int unpack_mel(const float* rows, const Rows& R, float* mel, cudaStream_t s) {
     dim3 grid((R.n_max + 31) / 32, R.B);
-    unpack_mel_kernel<<<grid, 256, 0, s>>>(rows, R, DX_MEL, mel);
+    DX_LAUNCH_PDL((unpack_mel_kernel), grid, 256, 0, s, rows, R, DX_MEL, mel);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -154,6 +161,8 @@ __global__ void embed_symbols_kernel(const int64_t* __restrict__ symbols, const 
                                      int n_symbols, const float* __restrict__ pos, Rows R,
                                      float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_bf,
                                      int64_t rows_phys) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -185,9 +194,9 @@ int embed_symbols(const int64_t* symbols, const float* emb, int n_symbols, const
                   float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s) {
     int grid = (int)((R.cap + 7) / 8);
     if (out_bf)
-        embed_symbols_kernel<true><<<grid, 256, 0, s>>>(symbols, emb, n_symbols, pos, R, nullptr, out_bf, rows_phys);
+        DX_LAUNCH_PDL((embed_symbols_kernel<true>), grid, 256, 0, s, symbols, emb, n_symbols, pos, R, nullptr, out_bf, rows_phys);
     else
-        embed_symbols_kernel<false><<<grid, 256, 0, s>>>(symbols, emb, n_symbols, pos, R, out_f32, nullptr, 0);
+        DX_LAUNCH_PDL((embed_symbols_kernel<false>), grid, 256, 0, s, symbols, emb, n_symbols, pos, R, out_f32, nullptr, 0);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -222,6 +231,8 @@ __global__ void accent_input_kernel(const float* __restrict__ z2_f32, const __nv
                                     const float* __restrict__ pw, const float* __restrict__ pb,
                                     const float* __restrict__ pos, Rows R, float* __restrict__ out_f32,
                                     __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -262,10 +273,10 @@ int accent_input(const float* z2_f32, const __nv_bfloat16* z2_bf, const float* e
                  const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s) {
     int grid = (int)((R.cap + 7) / 8);
     if (out_bf)
-        accent_input_kernel<true><<<grid, 256, 0, s>>>(nullptr, z2_bf, energy, pitch, ew, eb, pw, pb, pos, R,
+        DX_LAUNCH_PDL((accent_input_kernel<true>), grid, 256, 0, s, nullptr, z2_bf, energy, pitch, ew, eb, pw, pb, pos, R,
                                                        nullptr, out_bf, rows_phys);
     else
-        accent_input_kernel<false><<<grid, 256, 0, s>>>(z2_f32, nullptr, energy, pitch, ew, eb, pw, pb, pos, R,
+        DX_LAUNCH_PDL((accent_input_kernel<false>), grid, 256, 0, s, z2_f32, nullptr, energy, pitch, ew, eb, pw, pb, pos, R,
                                                         out_f32, nullptr, 0);
     DX_CHECK_LAUNCH();
     return 0;
@@ -279,6 +290,8 @@ template <bool BF16>
 __global__ void __launch_bounds__(256)
 masked_mean_kernel(const float* __restrict__ x_f32, const __nv_bfloat16* __restrict__ x_bf,
                    int64_t rows_phys, Rows R, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ float s_part[8][8];
     const int b = blockIdx.x, c = blockIdx.y;   // chunk of 8 channels
     const int len = (int)min((long long)R.len[b], (long long)R.n_max);
@@ -318,9 +331,9 @@ int masked_mean(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys
                 cudaStream_t s) {
     ProfScope prof("masked_mean", s);
     if (x_bf)
-        masked_mean_kernel<true><<<dim3(R.B, 16), 256, 0, s>>>(nullptr, x_bf, rows_phys, R, out);
+        DX_LAUNCH_PDL((masked_mean_kernel<true>), dim3(R.B, 16), 256, 0, s, nullptr, x_bf, rows_phys, R, out);
     else
-        masked_mean_kernel<false><<<dim3(R.B, 16), 256, 0, s>>>(x_f32, nullptr, 0, R, out);
+        DX_LAUNCH_PDL((masked_mean_kernel<false>), dim3(R.B, 16), 256, 0, s, x_f32, nullptr, 0, R, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -328,6 +341,8 @@ int masked_mean(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys
 // rows [*][128] fp32 → padded (B, n_max, 128) with zeros at pads (debug / enc_out)
 __global__ void unpack_rows_kernel(const float* __restrict__ x_f32, const __nv_bfloat16* __restrict__ x_bf,
                                    int64_t rows_phys, Rows R, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
     const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= (int64_t)R.B * R.n_max) return;
@@ -351,7 +366,7 @@ __global__ void unpack_rows_kernel(const float* __restrict__ x_f32, const __nv_b
 int unpack_rows(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys, const Rows& R, float* out,
                 cudaStream_t s) {
     int64_t n = (int64_t)R.B * R.n_max;
-    unpack_rows_kernel<<<(int)((n + 7) / 8), 256, 0, s>>>(x_f32, x_bf, rows_phys, R, out);
+    DX_LAUNCH_PDL((unpack_rows_kernel), (int)((n + 7) / 8), 256, 0, s, x_f32, x_bf, rows_phys, R, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -362,6 +377,8 @@ int unpack_rows(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys
 // read as zeros (conv taps and tile overruns land there).  One launch for all buffers of a plan.
 // ---------------------------------------------------------------------------------------------------------
 __global__ void zero_halos_kernel(HaloList hl, int64_t rows_phys, int64_t cap) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int bi = blockIdx.y;
     if (bi >= hl.n) return;
     __nv_bfloat16* buf = hl.buf[bi];
@@ -380,7 +397,7 @@ __global__ void zero_halos_kernel(HaloList hl, int64_t rows_phys, int64_t cap) {
 int zero_halos(const HaloList& hl, int64_t rows_phys, int64_t cap, cudaStream_t s) {
     if (hl.n == 0) return 0;
     dim3 grid(8, hl.n);
-    zero_halos_kernel<<<grid, 256, 0, s>>>(hl, rows_phys, cap);
+    DX_LAUNCH_PDL((zero_halos_kernel), grid, 256, 0, s, hl, rows_phys, cap);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -393,6 +410,8 @@ int zero_halos(const HaloList& hl, int64_t rows_phys, int64_t cap, cudaStream_t 
 __global__ void ln_apply_bf16_kernel(__nv_bfloat16* __restrict__ x, int64_t rows_phys, int C,
                                      const float* __restrict__ stats, const float* __restrict__ g,
                                      const float* __restrict__ b, Rows R, int live_ext) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     const int64_t total = R.row_start[R.B];
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y;
@@ -427,7 +446,7 @@ int ln_apply_bf16(__nv_bfloat16* x, int64_t rows_phys, int C, const float* stats
                   const Rows& R, int live_ext, cudaStream_t s) {
     dim3 grid((unsigned)((R.cap + 255) / 256), (unsigned)(C / 8));
     ProfScope prof("ln_apply_bf16", s);
-    ln_apply_bf16_kernel<<<grid, 256, 0, s>>>(x, rows_phys, C, stats, g, b, R, live_ext);
+    DX_LAUNCH_PDL((ln_apply_bf16_kernel), grid, 256, 0, s, x, rows_phys, C, stats, g, b, R, live_ext);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -3,6 +3,7 @@
 // transforms (pitch shift / multiply, zero-duration masking).
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
 
 namespace dx {
 
@@ -21,6 +22,8 @@ __global__ void __launch_bounds__(256)
 style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_emb_in,
              const float* __restrict__ accent, DxModelWeights w, float* __restrict__ film,
              float* __restrict__ speaker_preds) {
+    ptx::griddep_wait();      // PDL: predecessor complete + visible
+    ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ __align__(16) float s_e[DX_SPK];
     __shared__ __align__(16) float s_c[DX_D];     // accent + spk
     __shared__ __align__(16) float s_a[DX_D];     // accent
@@ -109,7 +112,7 @@ int style(const DxModelWeights* w, int B, const float* spk_embs, const float* sp
           float* film, float* speaker_preds, cudaStream_t s) {
     DX_REQUIRE(spk_embs != nullptr || spk_emb_in != nullptr, "style: speaker embeddings required");
     ProfScope prof("style", s);
-    style_kernel<<<dim3(B, 9), 256, 0, s>>>(spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
+    DX_LAUNCH_PDL((style_kernel), dim3(B, 9), 256, 0, s, spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
     DX_CHECK_LAUNCH();
     return 0;
 }
