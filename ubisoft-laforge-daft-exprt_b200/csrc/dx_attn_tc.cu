@@ -4,27 +4,32 @@
 //   S_h = (Q_h · d^-0.5) K_h^T, -inf at padded keys, softmax over keys, O_h = A_h V_h.  The head-averaged
 //   weights torch also returns are discarded by FFTBlock (model.py:255) and never materialised here.
 //
-// One CTA = (utterance, head, 128-query tile).  K/V are streamed in 128-key tiles (2-stage ring, bulk copies).
-//   S  = Q K^T      : tcgen05.mma, A = Q [128 x 64] K-major, B = K tile [128 keys x 64] K-major → TMEM cols 0..127
-//   P  = softmax    : 4 warps, thread ↔ query row, online max/sum in fp32, P written to smem as the bf16 K-major
-//                     A operand of the next MMA
-//   PV = P V        : tcgen05.mma, B = V tile [64 dh x 128 keys] MN-major (the channel-interleaved global layout
-//                     IS that canonical layout) → TMEM cols 128..191 (fresh accumulator per tile)
-//   O  += corr * .. : the softmax threads keep O (64 fp32) in registers and fold each PV tile in with the
-//                     online-softmax correction, so no TMEM read-modify-write is needed.
-// All operand tiles use the no-swizzle canonical layouts, which are exactly what the channel-interleaved global
-// layout [chunk][row][8] gives per chunk, so every operand arrives by plain 2 KB bulk copies.
+// One CTA = (utterance, head, 128-query tile).  K/V are streamed in 64-key tiles (2-stage ring, bulk copies).
+//   S  = Q K^T      : tcgen05.mma 128x64x16 x4, A = Q K-major, B = K tile K-major → TMEM cols 0..63
+//   P  = softmax    : 4 warps, thread ↔ query row; S is read from TMEM once per tile (64 registers); the exponent
+//                     reference m_ref is only raised when the row maximum exceeds it by more than 8 (log2 units), so
+//                     P <= 256 and the rescale below is rare; P written to smem as the bf16 K-major A operand
+//   O += P V        : tcgen05.mma 128x64x16 x4, B = V tile MN-major (the channel-interleaved global layout IS that
+//                     canonical layout) → accumulates in TMEM cols 64..127 across all KV tiles
+//   rescale         : when a warp raises m_ref it multiplies its 32 O rows in TMEM (tcgen05.ld / st) before P is
+//                     handed to the MMA; s_full(j) already implies that P V of tile j-1 has completed.
+// Nothing of O lives in registers during the loop (v1 kept 64 fp32 per thread and folded every tile), so the
+// kernel fits 3 CTAs per SM (64 KB smem, 128 TMEM columns, <= 112 registers): the S → softmax → P·V chain of one
+// CTA is latency-bound (profiles/r01c_attention_tc_kernel_full.txt) and is hidden by the other two.
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
 
 namespace dx {
 
-constexpr int ATC_BQ = 128, ATC_BK = 128;
+constexpr int ATC_BQ = 128, ATC_BK = 64;
 constexpr int ATC_THREADS = 192;
-constexpr uint32_t ATC_TILE_BYTES = 8 * 128 * 16;      // one 128-row x 64-channel bf16 tile = 16 KB
-constexpr uint32_t ATC_P_BYTES = 16 * 128 * 16;        // P: 128 rows x 128 keys bf16 = 32 KB
-constexpr uint32_t ATC_TMEM_COLS = 256;
+constexpr uint32_t ATC_Q_BYTES = 8 * 128 * 16;         // 16 KB: [8 dh chunk][128 row][8]
+constexpr uint32_t ATC_K_BYTES = 8 * ATC_BK * 16;      // 8 KB:  [8 dh chunk][64 key][8]
+constexpr uint32_t ATC_P_BYTES = 8 * 128 * 16;         // 16 KB: [8 key chunk][128 row][8]
+constexpr uint32_t ATC_TMEM_COLS = 128;
+constexpr uint32_t ATC_SMEM = ATC_Q_BYTES + 4 * ATC_K_BYTES + ATC_P_BYTES + 8 * 8 + 16;
+constexpr float ATC_LAZY = 8.f;                        // raise the exponent reference only beyond this margin
 
 struct AtcParams {
     const __nv_bfloat16* qkv;   // [48][rows_phys][8]
@@ -34,11 +39,11 @@ struct AtcParams {
     uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
     long long* trace;           // bring-up: clock64 timeline of CTA (0,0,0) (dx_set_trace_buffer) or null
 };
-// timeline slots: [128] kernel start, [129] Q landed, [130] end; per KV step j (base 132 + 10 j):
-//   issuer +0 kv_full ok, +1 S issued, +2 p_full ok, +3 PV issued;  softmax +4 s_full ok, +5 pass A done, +6 P stored, +7 o_full ok, +8 folded
+// timeline slots: [128] kernel start, [129] Q landed, [130] end; per KV step j < 8 (base 132 + 10 j):
+//   issuer +0 kv_full ok, +1 S issued, +2 p_full ok, +3 PV issued;  softmax +4 s_full ok, +5 max done, +6 P stored
 #define AT_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
-__global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcParams p) {
+__global__ void __launch_bounds__(ATC_THREADS, 3) attention_tc_kernel(const AtcParams p) {
     extern __shared__ __align__(1024) uint8_t at_smem[];
     ptx::griddep_wait();      // PDL: the lengths and QKV come from earlier kernels
     ptx::griddep_launch();
@@ -50,15 +55,15 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
     const int n_kv = (len + ATC_BK - 1) / ATC_BK;
 
     uint8_t* sQ = at_smem;
-    uint8_t* sKV = sQ + ATC_TILE_BYTES;                 // 2 stages x (K | V)
-    uint8_t* sP = sKV + 4 * ATC_TILE_BYTES;
+    uint8_t* sKV = sQ + ATC_Q_BYTES;                    // 2 stages x (K | V)
+    uint8_t* sP = sKV + 4 * ATC_K_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + ATC_P_BYTES);
     uint64_t* q_full = bars;            // 1
     uint64_t* kv_full = bars + 1;       // 2
     uint64_t* kv_empty = bars + 3;      // 2
     uint64_t* s_full = bars + 5;
     uint64_t* p_full = bars + 6;
-    uint64_t* o_full = bars + 7;
+    uint64_t* o_done = bars + 7;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -70,7 +75,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
         ptx::mbar_init(s_full, 1);
         ptx::mbar_init(p_full, 4);
-        ptx::mbar_init(o_full, 1);
+        ptx::mbar_init(o_done, 1);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<ATC_TMEM_COLS>(tmem_ptr);
@@ -78,12 +83,11 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    const uint32_t tm_s = tmem_base, tm_o = tmem_base + 128;
+    const uint32_t tm_s = tmem_base, tm_o = tmem_base + 64;
 
     if (warp == 0) {
         if (ptx::elect_one()) {
-            // Q tile
-            ptx::mbar_expect_tx(q_full, ATC_TILE_BYTES);
+            ptx::mbar_expect_tx(q_full, ATC_Q_BYTES);
             for (int c = 0; c < 8; ++c) {
                 const __nv_bfloat16* src = p.qkv + ((int64_t)(h * 8 + c) * p.rows_phys + DX_HALO + rs + q0) * 8;
                 ptx::bulk_g2s(sQ + c * 2048, src, 2048, q_full);
@@ -92,167 +96,175 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                 const int st = j & 1;
                 const uint32_t ph = (j >> 1) & 1;
                 ptx::mbar_wait(&kv_empty[st], ph ^ 1);
-                uint8_t* sk = sKV + (size_t)st * 2 * ATC_TILE_BYTES;
-                uint8_t* sv = sk + ATC_TILE_BYTES;
-                ptx::mbar_expect_tx(&kv_full[st], 2 * ATC_TILE_BYTES);
+                uint8_t* sk = sKV + (size_t)st * 2 * ATC_K_BYTES;
+                uint8_t* sv = sk + ATC_K_BYTES;
+                ptx::mbar_expect_tx(&kv_full[st], 2 * ATC_K_BYTES);
                 const int64_t krow = DX_HALO + rs + (int64_t)j * ATC_BK;
                 for (int c = 0; c < 8; ++c) {
-                    ptx::bulk_g2s(sk + c * 2048, p.qkv + ((int64_t)(16 + h * 8 + c) * p.rows_phys + krow) * 8, 2048, &kv_full[st]);
-                    ptx::bulk_g2s(sv + c * 2048, p.qkv + ((int64_t)(32 + h * 8 + c) * p.rows_phys + krow) * 8, 2048, &kv_full[st]);
+                    ptx::bulk_g2s(sk + c * 1024, p.qkv + ((int64_t)(16 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &kv_full[st]);
+                    ptx::bulk_g2s(sv + c * 1024, p.qkv + ((int64_t)(32 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &kv_full[st]);
                 }
             }
         }
     } else if (warp == 1) {
-        // MMA issuer.  idesc_s: M=128, N=128, A/B K-major.  idesc_o: M=128, N=64, B MN-major (bit 16).
-        constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, 128);
+        // MMA issuer.  idesc_s: M=128, N=64, A/B K-major.  idesc_o: M=128, N=64, B MN-major (bit 16).
+        constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, 64);
         constexpr uint32_t idesc_o = ptx::make_idesc_bf16(128, 64) | (1u << 16);
-        ptx::mbar_wait(q_full, 0);
-        AT_TRACE(129);
-        const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
-        for (int j = 0; j < n_kv; ++j) {
+        const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP), aKV = ptx::smem_u32(sKV);
+        auto issue_s = [&](int j) {
             const int st = j & 1;
-            const uint32_t ph = (j >> 1) & 1;
-            ptx::mbar_wait(&kv_full[st], ph);
+            ptx::mbar_wait(&kv_full[st], (j >> 1) & 1);
             ptx::tc_fence_after();
             if (j < 8) AT_TRACE(132 + 10 * j + 0);
-            const uint32_t aK = ptx::smem_u32(sKV + (size_t)st * 2 * ATC_TILE_BYTES);
-            const uint32_t aV = aK + ATC_TILE_BYTES;
             if (ptx::elect_one()) {
+                const uint32_t aK = aKV + (uint32_t)st * 2 * ATC_K_BYTES;
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {   // dh = 64 = 4 x 16
                     const uint64_t da = ptx::make_desc(aQ + kk * 2 * 2048, 2048, 128);
-                    const uint64_t db = ptx::make_desc(aK + kk * 2 * 2048, 2048, 128);
+                    const uint64_t db = ptx::make_desc(aK + kk * 2 * 1024, 1024, 128);
                     ptx::mma_bf16(tm_s, da, db, idesc_s, kk != 0);
                 }
                 ptx::mma_commit(s_full);
             }
             __syncwarp();
             if (j < 8) AT_TRACE(132 + 10 * j + 1);
-            ptx::mbar_wait(p_full, j & 1);
+        };
+        ptx::mbar_wait(q_full, 0);
+        AT_TRACE(129);
+        issue_s(0);
+        for (int j = 0; j < n_kv; ++j) {
+            const int st = j & 1;
+            ptx::mbar_wait(p_full, j & 1);         // P_j in smem, S_j consumed, O rescaled if needed
             ptx::tc_fence_after();
             if (j < 8) AT_TRACE(132 + 10 * j + 2);
             if (ptx::elect_one()) {
+                const uint32_t aV = aKV + (uint32_t)st * 2 * ATC_K_BYTES + ATC_K_BYTES;
 #pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {   // 128 keys = 8 x 16
+                for (int kk = 0; kk < 4; ++kk) {   // 64 keys = 4 x 16
                     const uint64_t da = ptx::make_desc(aP + kk * 2 * 2048, 2048, 128);
                     const uint64_t db = ptx::make_desc(aV + kk * 256, p.v_lbo, p.v_sbo);
-                    ptx::mma_bf16(tm_o, da, db, idesc_o, kk != 0);
+                    ptx::mma_bf16(tm_o, da, db, idesc_o, (j | kk) != 0);
                 }
-                ptx::mma_commit(o_full);
                 ptx::mma_commit(&kv_empty[st]);
+                if (j == n_kv - 1) ptx::mma_commit(o_done);
             }
             __syncwarp();
             if (j < 8) AT_TRACE(132 + 10 * j + 3);
+            if (j + 1 < n_kv) issue_s(j + 1);      // queued behind P V_j: s_full(j+1) implies P V_j has completed
         }
     } else {
-        // softmax + output: thread ↔ query row
+        // softmax: thread ↔ query row
         const int lane_grp = warp & 3;
         const int row = lane_grp * 32 + lane;
         const uint32_t t_s = tm_s + ((uint32_t)(lane_grp * 32) << 16);
         const uint32_t t_o = tm_o + ((uint32_t)(lane_grp * 32) << 16);
         const float sl2 = 0.125f * 1.4426950408889634f;   // d^-0.5 * log2(e)
-        float o[64];
-#pragma unroll
-        for (int i = 0; i < 64; ++i) o[i] = 0.f;
-        float m = -INFINITY, l = 0.f;
+        float m_ref = -INFINITY, l = 0.f;
         for (int j = 0; j < n_kv; ++j) {
-            const int k0 = j * ATC_BK;
-            ptx::mbar_wait(s_full, j & 1);
+            const int nvalid = len - j * ATC_BK;               // keys of this tile that exist (>= 1)
+            const bool full = nvalid >= ATC_BK;
+            ptx::mbar_wait(s_full, j & 1);                     // also: P V_{j-1} complete → sP free, O stable
             ptx::tc_fence_after();
             if (j < 8) AT_TRACE(132 + 10 * j + 4);
-            // pass A: row max over valid keys (TMEM loads double-buffered: chunk q+1 is in flight while q is reduced)
-            const int nvalid = len - k0;                       // keys of this tile that exist (>= 1)
-            const bool full = nvalid >= ATC_BK;
-            float mx = -INFINITY;
+            // pass A: row maximum (S is read from TMEM twice, 32 columns at a time: holding all 64 scores across both
+            // passes costs registers that the third resident CTA needs)
+            float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
             {
                 float va[32], vb[32];
                 ptx::tmem_ld32(t_s, va);
+                ptx::tmem_ld32(t_s + 32, vb);
+                ptx::tmem_ld_wait_dep(va);
+                if (full) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    float* cur = (q & 1) ? vb : va;
-                    float* nxt = (q & 1) ? va : vb;
-                    ptx::tmem_ld_wait_dep(cur);
-                    if (q < 3) ptx::tmem_ld32(t_s + (q + 1) * 32, nxt);
-                    float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-                    if (full) {
-#pragma unroll
-                        for (int e = 0; e < 32; e += 4) {
-                            m0 = fmaxf(m0, cur[e]); m1 = fmaxf(m1, cur[e + 1]); m2 = fmaxf(m2, cur[e + 2]); m3 = fmaxf(m3, cur[e + 3]);
-                        }
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e)
-                            if (q * 32 + e < nvalid) m0 = fmaxf(m0, cur[e]);
+                    for (int e = 0; e < 32; e += 4) {
+                        m0 = fmaxf(m0, va[e]); m1 = fmaxf(m1, va[e + 1]); m2 = fmaxf(m2, va[e + 2]); m3 = fmaxf(m3, va[e + 3]);
                     }
-                    mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+#pragma unroll
+                    for (int e = 0; e < 32; e += 4) {
+                        m0 = fmaxf(m0, vb[e]); m1 = fmaxf(m1, vb[e + 1]); m2 = fmaxf(m2, vb[e + 2]); m3 = fmaxf(m3, vb[e + 3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        if (e < nvalid) m0 = fmaxf(m0, va[e]);
+                        if (32 + e < nvalid) m1 = fmaxf(m1, vb[e]);
+                    }
                 }
             }
+            const float mxs = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)) * sl2;
             if (j < 8) AT_TRACE(132 + 10 * j + 5);
-            const float m_new = fmaxf(m, mx * sl2);
-            const float corr = ptx::ex2_approx(m - m_new);     // m = -inf on the first tile → 0
+            // lazy reference update: keep m_ref while the new maximum stays within 2^ATC_LAZY of it
+            const bool raise = mxs > m_ref + ATC_LAZY;         // always true on the first tile (m_ref = -inf)
+            float corr = 1.f;
+            if (raise) {
+                corr = ptx::ex2_approx(m_ref - mxs);           // 0 on the first tile
+                m_ref = mxs;
+                l *= corr;
+            }
+            if (j > 0 && __any_sync(0xffffffffu, raise)) {
+                // rescale this warp's 32 rows of O in TMEM (lanes that keep their reference use corr = 1)
+                float o[32];
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    ptx::tmem_ld32(t_o + q * 32, o);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) o[e] *= corr;
+                    ptx::tmem_st32(t_o + q * 32, o);
+                }
+                ptx::tmem_st_wait();
+            }
             float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
-            // pass B: probabilities → bf16 P tile in smem (K-major, chunk = 8 keys)
-            {
-                float va[32], vb[32];
-                ptx::tmem_ld32(t_s, va);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    float* cur = (q & 1) ? vb : va;
-                    float* nxt = (q & 1) ? va : vb;
-                    ptx::tmem_ld_wait_dep(cur);
-                    if (q < 3) ptx::tmem_ld32(t_s + (q + 1) * 32, nxt);
+            for (int q = 0; q < 2; ++q) {
+                float v[32];
+                ptx::tmem_ld32(t_s + q * 32, v);
+                ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        __align__(16) __nv_bfloat162 o2[4];
-                        float pe[8];
+                for (int c = 0; c < 4; ++c) {
+                    __align__(16) __nv_bfloat162 o2[4];
+                    float pe[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            pe[e] = ptx::ex2_approx(fmaf(cur[c * 8 + e], sl2, -m_new));
-                            if (!full && q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
-                        }
-                        ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
-                        *reinterpret_cast<uint4*>(sP + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                    for (int e = 0; e < 8; ++e) {
+                        pe[e] = ptx::ex2_approx(fmaf(v[c * 8 + e], sl2, -m_ref));
+                        if (!full && q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
                     }
+                    ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
+                    *reinterpret_cast<uint4*>(sP + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
                 }
             }
-            const float ps = (ps0 + ps1) + (ps2 + ps3);
-            l = l * corr + ps;
-            m = m_new;
+            l += (ps0 + ps1) + (ps2 + ps3);
             // make the generic-proxy smem writes visible to the tensor core (async proxy), then signal
             ptx::fence_proxy_async();
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(p_full);
             if (j < 8) AT_TRACE(132 + 10 * j + 6);
-            // fold PV_j into the register accumulator
-            ptx::mbar_wait(o_full, j & 1);
-            ptx::tc_fence_after();
-            if (j < 8) AT_TRACE(132 + 10 * j + 7);
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                float v[32];
-                ptx::tmem_ld32(t_o + q * 32, v);
-                ptx::tmem_ld_wait();
-#pragma unroll
-                for (int e = 0; e < 32; ++e) o[q * 32 + e] = fmaf(o[q * 32 + e], corr, v[e]);
-            }
-            ptx::tc_fence_before();
-            if (j < 8) AT_TRACE(132 + 10 * j + 8);
         }
-        if (q0 + row < len) {
-            const float inv = 1.f / l;
-            const int64_t r = rs + q0 + row;
+        // O = (sum_j P_j V_j) / l
+        ptx::mbar_wait(o_done, 0);
+        ptx::tc_fence_after();
+        const float inv = 1.f / l;
+        const int64_t r = rs + q0 + row;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                __align__(16) __nv_bfloat162 o2[4];
+        for (int q = 0; q < 2; ++q) {
+            float o[32];
+            ptx::tmem_ld32(t_o + q * 32, o);
+            ptx::tmem_ld_wait();
+            if (q0 + row < len) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(o[c * 8 + 2 * e] * inv, o[c * 8 + 2 * e + 1] * inv);
-                *reinterpret_cast<uint4*>(p.out + ((int64_t)(h * 8 + c) * p.rows_phys + DX_HALO + r) * 8) =
-                    *reinterpret_cast<const uint4*>(o2);
+                for (int c = 0; c < 4; ++c) {
+                    __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(o[c * 8 + 2 * e] * inv, o[c * 8 + 2 * e + 1] * inv);
+                    *reinterpret_cast<uint4*>(p.out + ((int64_t)(h * 8 + q * 4 + c) * p.rows_phys + DX_HALO + r) * 8) =
+                        *reinterpret_cast<const uint4*>(o2);
+                }
             }
         }
+        ptx::tc_fence_before();
     }
     if (warp == 2) AT_TRACE(130);
     ptx::tc_fence_before();
@@ -285,7 +297,7 @@ int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Row
 }
 
 int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s) {
-    const size_t smem = ATC_TILE_BYTES * 5 + ATC_P_BYTES + 8 * sizeof(uint64_t) + 16;
+    const size_t smem = ATC_SMEM;
     static bool configured = false;
     if (!configured) {
         DX_CHECK_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -294,8 +306,8 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
     AtcParams p;
     p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R;
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
-    p.v_lbo = 128; p.v_sbo = 2048;
-    if (debug_knob(1)) { p.v_lbo = 2048; p.v_sbo = 128; }
+    p.v_lbo = 128; p.v_sbo = ATC_BK * 16;
+    if (debug_knob(1)) { p.v_lbo = ATC_BK * 16; p.v_sbo = 128; }
     dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_tc", s);
     DX_LAUNCH_PDL((attention_tc_kernel), grid, ATC_THREADS, smem, s, p);
