@@ -51,7 +51,8 @@ int64_t     dx_launch_count(void);
  * key 1: same for the MN-major V operand of attention; key 2: synchronise after every launch (fault location);
  * key 3: run the FFN as two GEMM launches instead of the fused kernel (A/B testing);
  * key 4: run the K = 128 linear layers in the generic conv-GEMM kernel instead of the weight-resident one;
- * key 5: launch without programmatic dependent launch (plain stream order between kernels). */
+ * key 5: launch without programmatic dependent launch (plain stream order between kernels);
+ * key 6: run attention + output projection + LayerNorm as ONE kernel (both heads per CTA; measured slower). */
 int         dx_set_debug(int key, int value);
 
 /* Bring-up: while a device buffer (>= 2 KB) is set, the fused FFN kernel writes a clock64 timeline of its CTA 0

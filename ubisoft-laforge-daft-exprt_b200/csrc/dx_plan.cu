@@ -114,11 +114,16 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
         g.out_bf = p.qkvb; g.tag = "tc_qkv";
         DX_TRY(linear_bf16(g, R, s));
     }
-    DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
-    {   // out-proj + residual + LN + mask
+    {   // attention, then out-proj + residual + LN + mask.  The single fused kernel (debug knob 6) is correct but
+        // slower at these sizes: both heads per CTA halves the CTA count and doubles the longest CTA.
         TcGemmArgs g = tc_args(p.ob, rp, DX_D, DX_D, 1, bw.w_out_bf, 128, 64, bw.b_out, 0, TC_EPI_LN, 0);
         g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b; g.tag = "tc_outproj_ln";
-        DX_TRY(linear_bf16(g, R, s));
+        if (!debug_knob(6)) {
+            DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
+            DX_TRY(linear_bf16(g, R, s));
+        } else {
+            DX_TRY(attention_block_bf16(p.qkvb, rp, g, R, s));
+        }
     }
     if (!debug_knob(3))
         return ffn_bf16(p.yb, p.xb, rp, bw, film ? film + film_block * 256 : nullptr, 8 * 256, R, s);

@@ -25,7 +25,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
         // accumulator is in registers: release TMEM early
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(tempty);
+        if (lane == 0 && tempty != nullptr) ptx::mbar_arrive(tempty);
         if (r < total) {
             float sum = 0.f;
 #pragma unroll
@@ -135,7 +135,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
             *reinterpret_cast<float2*>(g.row_stats + (r * TC_STAT_TILES + n_tile) * 2) = make_float2(ssum, ssq);
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(tempty);
+        if (lane == 0 && tempty != nullptr) ptx::mbar_arrive(tempty);
     }
 }
 

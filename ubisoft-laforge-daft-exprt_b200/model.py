@@ -76,6 +76,8 @@ class DaftExprt(nn.Module):
         # like the reference's FrameDecoder.__init__ (model.py:534)
         hparams.frame_decoder["hidden_embed_dim"] = self.hidden_embed_dim
         self._prepared = None        # (key, DxModelWeights, keep-alive tensors)
+        self.streams = 1             # utterance groups run concurrently per call (see _run)
+        self._side_streams = []
         self._workspaces = {}
         self._stats_table = None
 
@@ -225,15 +227,15 @@ class DaftExprt(nn.Module):
         self._prepared = (key, W, keep)
         return W
 
-    def _workspace(self, B, L_max, T_max):
+    def _workspace(self, B, L_max, T_max, slot=0):
         mode = _MODES[self.compute_mode]
-        key = (B, L_max, T_max, mode)
+        key = (B, L_max, T_max, mode, slot)
         ws = self._workspaces.get(key)
         if ws is None:
             n = _lib.load().dx_forward_workspace_bytes(B, L_max, T_max, mode)
             if n < 0:
                 _lib.check(1, "dx_forward_workspace_bytes")
-            if len(self._workspaces) >= 4:       # bounded cache
+            if len(self._workspaces) >= 8:       # bounded cache
                 self._workspaces.pop(next(iter(self._workspaces)))
             ws = torch.zeros(n, dtype=torch.uint8, device=self.device)
             self._workspaces[key] = ws
@@ -277,11 +279,17 @@ class DaftExprt(nn.Module):
     def _run(self, B, L_max, T_max, *, symbols, durations_float, durations_int, symbols_energy, symbols_pitch,
              input_lengths, frames_energy=None, frames_pitch=None, mel_specs=None, output_lengths=None,
              spk_embs=None, accent_emb_in=None, spk_emb_in=None, want_enc_out=False):
-        """One dx_forward call.  Returns dict of output tensors."""
+        """The whole pass = ``dx_forward``.  Returns dict of output tensors.
+
+        With ``self.streams > 1`` the batch is cut into that many contiguous groups of utterances which run as
+        independent ``dx_forward`` calls on separate CUDA streams (joined before returning).  Utterances are
+        independent given the padded widths ``L_max`` / ``T_max`` (they decide where the reference sees true
+        zero padding) and every group is given the full batch's widths, so the results are
+        bit-identical to the single call; the concurrency fills the tails of one group's kernels with the
+        other group's work."""
         W = self._prepare()
         lib = _lib.load()
         dev = self.device
-        ws = self._workspace(B, L_max, T_max)
         out = {
             "accent_emb": torch.empty(B, _lib.D, device=dev),
             "speaker_preds": torch.empty(B, self.n_speakers, device=dev),
@@ -291,20 +299,34 @@ class DaftExprt(nn.Module):
             "output_lengths": torch.empty(B, dtype=torch.long, device=dev),
             "enc_out": torch.empty(B, L_max, _lib.D, device=dev) if want_enc_out else None,
         }
-        a = _lib.DxForwardArgs()
-        a.B, a.L_max, a.T_max, a.mode = B, L_max, T_max, _MODES[self.compute_mode]
-        for name, t in (("symbols", symbols), ("durations_float", durations_float), ("durations_int", durations_int),
-                        ("symbols_energy", symbols_energy), ("symbols_pitch", symbols_pitch),
-                        ("input_lengths", input_lengths), ("frames_energy", frames_energy),
-                        ("frames_pitch", frames_pitch), ("mel_specs", mel_specs), ("output_lengths", output_lengths),
-                        ("spk_embs", spk_embs), ("accent_emb_in", accent_emb_in), ("spk_emb_in", spk_emb_in),
-                        ("accent_emb", out["accent_emb"]), ("speaker_preds", out["speaker_preds"]),
-                        ("film", out["film"]), ("enc_out", out["enc_out"]), ("mel_out", out["mel"]),
-                        ("weights_out", out["weights"]), ("output_lengths_out", out["output_lengths"]),
-                        ("workspace", ws)):
-            setattr(a, name, None if t is None else t.data_ptr())
-        a.workspace_bytes = ws.numel()
-        _lib.check(lib.dx_forward(C.byref(W), C.byref(a), _lib.stream_ptr()), "dx_forward")
+        tensors = (("symbols", symbols), ("durations_float", durations_float), ("durations_int", durations_int),
+                   ("symbols_energy", symbols_energy), ("symbols_pitch", symbols_pitch),
+                   ("input_lengths", input_lengths), ("frames_energy", frames_energy),
+                   ("frames_pitch", frames_pitch), ("mel_specs", mel_specs), ("output_lengths", output_lengths),
+                   ("spk_embs", spk_embs), ("accent_emb_in", accent_emb_in), ("spk_emb_in", spk_emb_in),
+                   ("accent_emb", out["accent_emb"]), ("speaker_preds", out["speaker_preds"]),
+                   ("film", out["film"]), ("enc_out", out["enc_out"]), ("mel_out", out["mel"]),
+                   ("weights_out", out["weights"]), ("output_lengths_out", out["output_lengths"]))
+        n = max(1, min(int(self.streams), B // 8)) if self.compute_mode == "bf16" else 1
+        bounds = [(B * i) // n for i in range(n + 1)]
+        cur = torch.cuda.current_stream(dev)
+        while len(self._side_streams) < n - 1:
+            self._side_streams.append(torch.cuda.Stream(dev))
+        fork = cur.record_event() if n > 1 else None
+        for i in range(n):
+            b0, b1 = bounds[i], bounds[i + 1]
+            stream = cur if i == 0 else self._side_streams[i - 1]
+            ws = self._workspace(b1 - b0, L_max, T_max, slot=i)
+            a = _lib.DxForwardArgs()
+            a.B, a.L_max, a.T_max, a.mode = b1 - b0, L_max, T_max, _MODES[self.compute_mode]
+            for name, t in tensors:
+                setattr(a, name, None if t is None else t[b0:b1].data_ptr())
+            a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+            if i > 0:
+                stream.wait_event(fork)
+            _lib.check(lib.dx_forward(C.byref(W), C.byref(a), C.c_void_p(stream.cuda_stream)), "dx_forward")
+        for i in range(1, n):
+            cur.wait_event(self._side_streams[i - 1].record_event())
         return out
 
     @torch.no_grad()
