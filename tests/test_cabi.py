@@ -40,7 +40,7 @@ def test_host_only_queries():
 
 
 def test_struct_sizes_match_header():
-    # 16 pointers per block; the model struct is pointers + 3 block arrays + 4 int32
+    # 18 pointers per block; the model struct is pointers + 3 block arrays + 4 int32
     import ctypes
     assert ctypes.sizeof(_lib.DxBlockWeights) == 18 * 8
     n_ptr = 19 + 14 + 8 + 4

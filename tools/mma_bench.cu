@@ -54,15 +54,17 @@ __device__ __forceinline__ uint32_t cluster_rank() {
 }
 
 // CG = 1: one CTA, M = 128.   CG = 2: CTA pair, M = 256 (128 rows per CTA), B split N/2 per CTA.
-template <int CG, int N, int AMODE, int BSW>
-__global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long long* out) {
+template <int CG, int N, int AMODE, int BSW, int CE = 0, int DSW = 0>
+__global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long long* out, int a_off, int a_lbo) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar;
+    __shared__ uint64_t dummy_bar[4];
     __shared__ uint32_t tmem_ptr;
     const int warp = threadIdx.x >> 5;
     const uint32_t rank = CG == 2 ? cluster_rank() : 0;
     if (threadIdx.x == 0) {
         ptx::mbar_init(&bar, 1);
+        for (int i = 0; i < 4; ++i) ptx::mbar_init(&dummy_bar[i], 1);
         ptx::fence_barrier_init();
     }
     if (warp == 0) {
@@ -79,7 +81,7 @@ __global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long lon
     ptx::tc_fence_after();
     const uint32_t tmem_base = tmem_ptr;
     const uint32_t sbase = ptx::smem_u32(smem);
-    const uint32_t sA = sbase, sB = sbase + 65536;     // A: 4 stages x 16 KB, B: 4 stages x 32 KB
+    const uint32_t sA = sbase + (uint32_t)a_off, sB = sbase + 65536 + 4096;     // A: 4 stages x 16 KB, B: 4 stages x 32 KB
     constexpr int NB = CG == 2 ? N / 2 : N;            // B rows held by this CTA
     constexpr uint32_t idesc = ptx::make_idesc_bf16(CG == 2 ? 256 : 128, N);
     constexpr uint32_t acc_stride = N <= 128 ? 128u : (AMODE == A_TMEM ? 0u : 256u);
@@ -93,13 +95,18 @@ __global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long lon
                 for (int i = 0; i < 16; ++i) {
                     const int k = i & 3, st = i >> 2;
                     uint64_t da, db;
-                    if (AMODE == A_SW128) da = desc_sw128(sA + st * 16384 + k * 32);
-                    else da = ptx::make_desc(sA + st * 16384 + k * 2 * 2048, 2048, 128);
+                    if (AMODE == A_SW128) da = desc_sw128(sA + st * 16384 + k * 32) | ((uint64_t)((a_off >> 7) & 7) << 49);
+                    else da = ptx::make_desc(sA + st * 16384 + k * 2 * a_lbo, a_lbo, 128);
                     if (BSW) db = desc_sw128(sB + st * 32768 + k * 32);
                     else db = ptx::make_desc(sB + st * 32768 + k * 2 * NB * 16, NB * 16, 128);
-                    if (CG == 2) mma_ss2(d, da, db, idesc, i != 0);
+                    const uint32_t dd = DSW ? d + (uint32_t)((i >> 2) & 1) * 256u : d;     // production: 4 MMAs per accumulator, then the other half's
+                    if (CG == 2) mma_ss2(dd, da, db, idesc, DSW ? (i & 3) != 0 || i > 7 : i != 0);
                     else if (AMODE == A_TMEM) mma_ts(d, tmem_base + 384 + k * 8, db, idesc, i != 0);
-                    else ptx::mma_bf16(d, da, db, idesc, i != 0);
+                    else ptx::mma_bf16(dd, da, db, idesc, DSW ? (i & 3) != 0 || i > 7 : i != 0);
+                    if (CE > 0 && (i + 1) % CE == 0) {
+                        if (CG == 2) commit2(&dummy_bar[(i / CE) & 3]);
+                        else ptx::mma_commit(&dummy_bar[(i / CE) & 3]);
+                    }
                 }
             }
             __syncwarp();
@@ -129,15 +136,15 @@ __global__ void __launch_bounds__(128, 1) mma_bench_kernel(int ngroups, long lon
     }
 }
 
-template <int CG, int N, int AMODE, int BSW>
-static void run(const char* name, int grid) {
+template <int CG, int N, int AMODE, int BSW, int CE = 0, int DSW = 0>
+static void run(const char* name, int grid, int a_off = 0, int a_lbo = 2048) {
     const int ngroups = 256, nmma = ngroups * 16;
     if (grid < CG) grid = CG;
     long long* d_out;
     CK(cudaMalloc(&d_out, grid * 2 * sizeof(long long)));
     CK(cudaMemset(d_out, 0, grid * 2 * sizeof(long long)));
     const size_t smem = 200 * 1024;
-    auto kern = mma_bench_kernel<CG, N, AMODE, BSW>;
+    auto kern = mma_bench_kernel<CG, N, AMODE, BSW, CE, DSW>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     for (int rep = 0; rep < 2; ++rep) {
         cudaLaunchConfig_t cfg{};
@@ -151,7 +158,7 @@ static void run(const char* name, int grid) {
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        CK(cudaLaunchKernelEx(&cfg, kern, ngroups, d_out));
+        CK(cudaLaunchKernelEx(&cfg, kern, ngroups, d_out, a_off, a_lbo));
         CK(cudaDeviceSynchronize());
     }
     std::vector<long long> h(grid * 2);
@@ -178,7 +185,42 @@ static void run_n(int grid) {
     run<2, N, A_SW128, 1>("cg2 SS  A SW128       B SW128      (M=256)", grid);
 }
 
-int main() {
+// conv taps are row shifts of the A operand: +16 B per row in the no-swizzle K-major layout (core matrices then straddle
+// 128-byte lines), +128 B per row in the SWIZZLE_128B layout (descriptor base_offset = row & 7)
+static void run_shift() {
+    char name[96];
+    for (int lbo : {2048, 4096})
+        for (int off : {0, 16, 32, 64, 112}) {
+            snprintf(name, sizeof name, "cg1 SS A no-swizzle +%3d B LBO %d", off, lbo);
+            run<1, 128, A_NOSW, 0>(name, 148, off, lbo);
+            snprintf(name, sizeof name, "cg2 SS A no-swizzle +%3d B LBO %d", off, lbo);
+            run<2, 128, A_NOSW, 0>(name, 148, off, lbo);
+        }
+    for (int off : {0, 128, 256, 896}) {
+        snprintf(name, sizeof name, "cg1 SS A SW128 +%3d B (row shift)", off);
+        run<1, 128, A_SW128, 1>(name, 148, off);
+        snprintf(name, sizeof name, "cg2 SS A SW128 +%3d B (row shift)", off);
+        run<2, 128, A_SW128, 1>(name, 148, off);
+    }
+}
+
+// production issue pattern: a tcgen05.commit after every stage (8 MMAs), accumulator switch every 4 MMAs
+template <int CE, int DSW>
+static void run_commit1() {
+    char name[96];
+    snprintf(name, sizeof name, "cg1 SS commit every %2d MMAs, D switch %d", CE, DSW);
+    run<1, 128, A_NOSW, 0, CE, DSW>(name, 148);
+    snprintf(name, sizeof name, "cg2 SS commit every %2d MMAs, D switch %d", CE, DSW);
+    run<2, 128, A_NOSW, 0, CE, DSW>(name, 148);
+}
+static void run_commit() {
+    run_commit1<0, 0>(); run_commit1<16, 0>(); run_commit1<8, 0>(); run_commit1<4, 0>(); run_commit1<2, 0>(); run_commit1<1, 0>();
+    run_commit1<0, 1>(); run_commit1<8, 1>(); run_commit1<4, 1>();
+}
+
+int main(int argc, char** argv) {
+    if (argc > 1 && argv[1][0] == 'c') { run_commit(); return 0; }
+    if (argc > 1) { run_shift(); return 0; }
     for (int grid : {2, 148}) {
         run_n<64>(grid);
         run_n<128>(grid);

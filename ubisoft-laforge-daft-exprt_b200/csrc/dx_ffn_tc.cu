@@ -16,19 +16,26 @@
 // Issue order G1(c), G2(c-1, 0), G2(c-1, 1): E1(c) runs under G2(c-1).
 //
 // Why these shapes (profiles/r01b_mma_bench.txt, r01b_ffn_trace_before.txt): a 128xNx16 SS MMA reads (128+N)*32 B
-// of shared memory in N/2 cycles, so N = 64 needs 192 B/clk against the SM's 128 B/clk; the first version of this
-// kernel (64-wide hidden chunks) was shared-memory-bandwidth bound at 49 % of the tensor peak, exactly the byte
-// count / 128.  N = 128 halves G1's operand traffic.  Every 16 KB weight stage is used by both halves.
-// Conv taps are +16 B shifts of the no-swizzle K-major descriptors (see dx_tc_gemm.cu).
-// Warps: 0 = bulk-copy producer, 1 = TMEM owner + MMA issuer, 2-5 = epilogue of half 0, 6-9 = epilogue of half 1
-// (warp w may only touch TMEM lanes 32 (w % 4) .. +31).
+// of shared memory in N/2 cycles, so N = 64 needs 192 B/clk against the SM's 128 B/clk; N = 128 runs at the
+// tensor-pipe rate.  Every 16 KB weight stage is used by both halves.  Conv taps are +16 B shifts of the
+// no-swizzle K-major descriptors (see dx_tc_gemm.cu; measured free, profiles/r01d_mma_ring_bench.txt).
+//
+// Why TWO MMA issuer warps (one per half): tcgen05.mma issue blocks while the tensor pipe's short queue is full, and
+// an mbarrier wait costs the issuing thread ~170 cycles even when the barrier has already completed, so a single
+// issuer leaves the pipe idle for ~180 cycles per weight stage (88-100 cycles per MMA instead of 64, whatever the
+// ring depth; tools/ring_bench.cu).  With one issuer per half the two halves are independent pipelines that share
+// only the X tile and the weight ring: while one warp sits in a barrier wait the other's MMAs keep the pipe busy
+// (72 cycles per MMA in the microbenchmark).  All D1 / Hs / D2 barriers are per half.
+// Warps: 0 = bulk-copy producer, 1 = TMEM owner + issuer of half 0, 2 = issuer of half 1, 3-6 = epilogue of half 0,
+// 7-10 = epilogue of half 1 (warp w may only touch TMEM lanes 32 (w % 4) .. +31).
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
+#include "dx_ffn_epilogue.cuh"
 
 namespace dx {
 
-constexpr int FF_THREADS = 320;
+constexpr int FF_THREADS = 352;
 constexpr int FF_OUT = 126;                 // outputs per half
 constexpr int FF_TILE = 2 * FF_OUT;         // outputs per CTA tile
 constexpr int FF_NCH = 8;                   // hidden chunks of 128 channels
@@ -42,7 +49,7 @@ constexpr uint32_t FF_OFF_W = FF_OFF_HS + 4 * FF_HS_BYTES;
 constexpr uint32_t FF_OFF_PAR = FF_OFF_W + FF_WSTAGES * FF_W_BYTES;
 constexpr uint32_t FF_PAR_FLOATS = 1024 + 128 + 128 + 128;          // b1, b2, gamma, beta
 constexpr uint32_t FF_OFF_BAR = FF_OFF_PAR + FF_PAR_FLOATS * 4;
-constexpr uint32_t FF_NBARS = 2 * FF_WSTAGES + 10;
+constexpr uint32_t FF_NBARS = 2 * FF_WSTAGES + 2 + 2 * 8;
 constexpr uint32_t FF_SMEM = FF_OFF_BAR + FF_NBARS * 8 + 16;
 
 struct FfnParams {
@@ -54,13 +61,15 @@ struct FfnParams {
     const float* film;          // pre-offset to the block, or null
     int film_stride;
     Rows R;
+    int dbg;                    // timing experiments (debug knob 8): bit 0 = weight stages are not copied (arrive only),
+                                // bit 1 = issue no MMAs, bit 2 = no Hs stores, bit 3 = no TMEM loads in E1 (results are wrong)
     long long* trace;           // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer) or null
 };
 
-// timeline slots (CTA 0 only): [0] kernel start, [1] X landed, then per chunk c (base 8 + 12 c):
+// timeline slots (CTA 0, half 0 only): [0] kernel start, [1] X landed, then per chunk c (base 8 + 12 c):
 //   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full[0] ok, +3 G2 issued (both subs), +4 first w_full wait of G1 done
 //   epilog  +6 d1_full ok, +7 TMEM loaded (sub 1), +8 hs_empty[1] ok, +9 Hs stored + fenced (sub 1)
-// [2] d2_full ok (E2 start), [3] E2 done
+// [2] d2_full ok (E2 start), [3] E2 done, [4] CTA done
 #define FF_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
@@ -73,20 +82,16 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     float* s_g = s_b2 + 128;
     float* s_be = s_g + 128;
     uint64_t* bars = reinterpret_cast<uint64_t*>(ff_smem + FF_OFF_BAR);
-    uint64_t* w_full = bars;                       // [S]
-    uint64_t* w_empty = bars + FF_WSTAGES;         // [S]
+    uint64_t* w_full = bars;                       // [S]   producer → both issuers
+    uint64_t* w_empty = bars + FF_WSTAGES;         // [S]   one commit per active issuer
     uint64_t* x_full = bars + 2 * FF_WSTAGES;
     uint64_t* x_empty = x_full + 1;
-    uint64_t* d1_full = x_full + 2;
-    uint64_t* d1_empty = x_full + 3;
-    uint64_t* hs_full = x_full + 4;                // [2] per sub
-    uint64_t* hs_empty = x_full + 6;               // [2]
-    uint64_t* d2_full = x_full + 8;
-    uint64_t* d2_empty = x_full + 9;
+    uint64_t* hb = x_full + 2;                     // per half h (8 barriers each):
+    // hb[8 h + 0] d1_full, +1 d1_empty, +2 hs_full[sub 0], +3 hs_full[sub 1], +4 hs_empty[0], +5 hs_empty[1], +6 d2_full, +7 d2_empty
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + FF_NBARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2)) ? p.trace : nullptr;
+    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 3)) ? p.trace : nullptr;
     if (warp == 1) FF_TRACE(0);
 
     // ---- prologue that does not depend on the previous kernel (PDL: overlaps its tail) ----
@@ -98,11 +103,11 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     }
     // rows 128..135 of the Hs buffers are read (taps of the two discarded output rows) but never written: zero once
     for (int i = threadIdx.x; i < 4 * 8 * 8; i += FF_THREADS) {
-        const int hb = i >> 6, kc = (i >> 3) & 7, rr = 128 + (i & 7);
-        *reinterpret_cast<uint4*>(sHs + hb * FF_HS_BYTES + kc * FF_HS_ROWS * 16 + rr * 16) = make_uint4(0u, 0u, 0u, 0u);
+        const int q = i >> 6, kc = (i >> 3) & 7, rr = 128 + (i & 7);
+        *reinterpret_cast<uint4*>(sHs + q * FF_HS_BYTES + kc * FF_HS_ROWS * 16 + rr * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
     if (threadIdx.x == 0) {
-        for (int i = 0; i < FF_WSTAGES; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
+        for (int i = 0; i < FF_WSTAGES; ++i) ptx::mbar_init(&w_full[i], 1);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<512>(tmem_ptr);
@@ -114,6 +119,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     // the first FF_WSTAGES weight stages are the same for every tile (W1 chunk 0): fetch them now
     if (warp == 0 && ptx::elect_one()) {
         for (int s0 = 0; s0 < FF_WSTAGES; ++s0) {
+            if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s0]); continue; }
             ptx::mbar_expect_tx(&w_full[s0], FF_W_BYTES);
             ptx::bulk_g2s(sW + s0 * FF_W_BYTES, reinterpret_cast<const uint8_t*>(p.w1) + (size_t)s0 * FF_W_BYTES, FF_W_BYTES, &w_full[s0]);
         }
@@ -131,13 +137,19 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
     const uint32_t x_chunk_bytes = halves == 2 ? 4096u : 2176u;      // 256 / 136 rows of one 8-channel chunk
     if (threadIdx.x == 0) {
+        for (int i = 0; i < FF_WSTAGES; ++i) ptx::mbar_init(&w_empty[i], halves);
         ptx::mbar_init(x_full, 1);
         ptx::mbar_init(x_empty, 4 * halves);
-        ptx::mbar_init(d1_full, 1);
-        ptx::mbar_init(d1_empty, 4 * halves);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&hs_full[i], 4 * halves); ptx::mbar_init(&hs_empty[i], 1); }
-        ptx::mbar_init(d2_full, 1);
-        ptx::mbar_init(d2_empty, 4 * halves);
+        for (int h = 0; h < 2; ++h) {
+            ptx::mbar_init(&hb[8 * h + 0], 1);          // d1_full
+            ptx::mbar_init(&hb[8 * h + 1], 4);          // d1_empty
+            ptx::mbar_init(&hb[8 * h + 2], 4);          // hs_full[0]
+            ptx::mbar_init(&hb[8 * h + 3], 4);          // hs_full[1]
+            ptx::mbar_init(&hb[8 * h + 4], 1);          // hs_empty[0]
+            ptx::mbar_init(&hb[8 * h + 5], 1);          // hs_empty[1]
+            ptx::mbar_init(&hb[8 * h + 6], 1);          // d2_full
+            ptx::mbar_init(&hb[8 * h + 7], 4);          // d2_empty
+        }
         ptx::fence_barrier_init();
     }
     __syncthreads();
@@ -164,6 +176,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                             if (wit < FF_WSTAGES) continue;          // fetched in the prologue
                             const int s = wit % FF_WSTAGES;
                             ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
+                            if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
                             ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
                             ptx::bulk_g2s(sW + s * FF_W_BYTES, base + (size_t)st * FF_W_BYTES, FF_W_BYTES, &w_full[s]);
                         }
@@ -171,93 +184,102 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
-        const uint32_t aX = ptx::smem_u32(sX), aHs = ptx::smem_u32(sHs), aW = ptx::smem_u32(sW);
-        uint32_t wit = 0, tile_it = 0;
-        if ((int)blockIdx.x >= n_tiles)      // no tile: the prefetched weight stages must land before the CTA exits
+    } else if (warp <= 2) {
+        // ===================== MMA issuers: warp 1 ↔ half 0, warp 2 ↔ half 1 =====================
+        const int h = warp - 1;
+        if ((int)blockIdx.x >= n_tiles && h == 0)      // no tile: the prefetched weight stages must land before the CTA exits
             for (int s0 = 0; s0 < FF_WSTAGES; ++s0) ptx::mbar_wait(&w_full[s0], 0);
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
-            ptx::mbar_wait(x_full, tile_it & 1);
-            if (tile_it == 0) FF_TRACE(1);
-            ptx::mbar_wait(d2_empty, (tile_it & 1) ^ 1);
-            ptx::tc_fence_after();
-            for (int c = 0; c <= FF_NCH; ++c) {
-                if (c < FF_NCH) {
-                    // ---- G1(c): D1[h] = X_h (*) W1[c]   (stage = (K half, tap): 64 input channels x 128 hidden)
-                    const uint32_t n = tile_it * FF_NCH + c;
-                    ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
-                    ptx::tc_fence_after();
-                    if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
-                    for (int st = 0; st < 6; ++st, ++wit) {
-                        const int kh = st / 3, tap = st % 3;
-                        const int s = wit % FF_WSTAGES;
-                        ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
+        if (h < halves) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
+            const uint32_t aX = ptx::smem_u32(sX) + FF_OUT * h * 16, aHs = ptx::smem_u32(sHs) + h * 2 * FF_HS_BYTES, aW = ptx::smem_u32(sW);
+            const uint32_t td1 = tm_d1 + 128 * h, td2 = tm_d2 + 128 * h;
+            uint64_t* d1_full = &hb[8 * h + 0];
+            uint64_t* d1_empty = &hb[8 * h + 1];
+            uint64_t* hs_full = &hb[8 * h + 2];
+            uint64_t* hs_empty = &hb[8 * h + 4];
+            uint64_t* d2_full = &hb[8 * h + 6];
+            uint64_t* d2_empty = &hb[8 * h + 7];
+            uint32_t wit = 0, tile_it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+                ptx::mbar_wait(x_full, tile_it & 1);
+                if (tile_it == 0) FF_TRACE(1);
+                ptx::mbar_wait(d2_empty, (tile_it & 1) ^ 1);
+                ptx::tc_fence_after();
+                for (int c = 0; c <= FF_NCH; ++c) {
+                    if (c < FF_NCH) {
+                        // ---- G1(c): D1[h] = X_h (*) W1[c]   (stage = (K half, tap): 64 input channels x 128 hidden)
+                        const uint32_t n = tile_it * FF_NCH + c;
+                        ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
                         ptx::tc_fence_after();
-                        if (tile_it == 0 && st == 0) FF_TRACE(8 + 12 * c + 4);
-                        if (ptx::elect_one()) {
-#pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                if (h >= halves) break;
-#pragma unroll
-                                for (int kk = 0; kk < 4; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aX + (kh * 8 + kk * 2) * 4096 + (FF_OUT * h + tap) * 16, 4096, 128);
-                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
-                                    ptx::mma_bf16(tm_d1 + 128 * h, da, db, idesc, (st | kk) != 0);
-                                }
-                            }
-                            ptx::mma_commit(&w_empty[s]);
-                            if (st == 5) ptx::mma_commit(d1_full);
-                        }
-                        __syncwarp();
-                    }
-                    if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
-                }
-                if (c >= 1) {
-                    // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
-                    const int cc = c - 1;
-                    const uint32_t k = tile_it * FF_NCH + cc;
-                    for (int st = 0; st < 6; ++st, ++wit) {
-                        const int sub = st / 3, tap = st % 3;
-                        if (tap == 0) {
-                            ptx::mbar_wait(&hs_full[sub], k & 1);
+                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
+                        for (int st = 0; st < 6; ++st, ++wit) {
+                            const int kh = st / 3, tap = st % 3;
+                            const int s = wit % FF_WSTAGES;
+                            ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
                             ptx::tc_fence_after();
-                            if (tile_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
-                        }
-                        const int s = wit % FF_WSTAGES;
-                        ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
-                        ptx::tc_fence_after();
-                        if (ptx::elect_one()) {
-#pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                if (h >= halves) break;
+                            if (tile_it == 0 && st == 0) FF_TRACE(8 + 12 * c + 4);
+                            if (ptx::elect_one()) {
 #pragma unroll
                                 for (int kk = 0; kk < 4; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aHs + (h * 2 + sub) * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16,
-                                                                       FF_HS_ROWS * 16, 128);
+                                    const uint64_t da = ptx::make_desc(aX + (kh * 8 + kk * 2) * 4096 + tap * 16, 4096, 128);
                                     const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
-                                    ptx::mma_bf16(tm_d2 + 128 * h, da, db, idesc, (cc | st | kk) != 0);
+                                    if (!(p.dbg & 2)) ptx::mma_bf16(td1, da, db, idesc, (st | kk) != 0);
+                                }
+                                ptx::mma_commit(&w_empty[s]);
+                                if (st == 5) ptx::mma_commit(d1_full);
+                            }
+                            __syncwarp();
+                        }
+                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
+                    }
+                    if (c >= 1) {
+                        // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
+                        const int cc = c - 1;
+                        const uint32_t k = tile_it * FF_NCH + cc;
+                        for (int st = 0; st < 6; ++st, ++wit) {
+                            const int sub = st / 3, tap = st % 3;
+                            if (tap == 0) {
+                                ptx::mbar_wait(&hs_full[sub], k & 1);
+                                ptx::tc_fence_after();
+                                if (tile_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
+                            }
+                            const int s = wit % FF_WSTAGES;
+                            ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
+                            ptx::tc_fence_after();
+                            if (ptx::elect_one()) {
+#pragma unroll
+                                for (int kk = 0; kk < 4; ++kk) {
+                                    const uint64_t da = ptx::make_desc(aHs + sub * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16, FF_HS_ROWS * 16, 128);
+                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
+                                    if (!(p.dbg & 2)) ptx::mma_bf16(td2, da, db, idesc, (cc | st | kk) != 0);
+                                }
+                                ptx::mma_commit(&w_empty[s]);
+                                if (tap == 2) {
+                                    ptx::mma_commit(&hs_empty[sub]);
+                                    if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
                                 }
                             }
-                            ptx::mma_commit(&w_empty[s]);
-                            if (tap == 2) {
-                                ptx::mma_commit(&hs_empty[sub]);
-                                if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
-                            }
+                            __syncwarp();
                         }
-                        __syncwarp();
+                        if (tile_it == 0) FF_TRACE(8 + 12 * cc + 3);
                     }
-                    if (tile_it == 0) FF_TRACE(8 + 12 * cc + 3);
                 }
             }
         }
-    } else if (((warp - 2) >> 2) < halves) {
-        // ===================== epilogue: warps 2-5 own half 0, warps 6-9 own half 1; thread ↔ row =====================
-        const int h = (warp - 2) >> 2;
+    } else if (((warp - 3) >> 2) < halves) {
+        // ===================== epilogue: warps 3-6 own half 0, warps 7-10 own half 1; thread ↔ row =====================
+        const int h = (warp - 3) >> 2;
         const int lane_grp = warp & 3;
         const int j = lane_grp * 32 + lane;                         // row inside the half
         const uint32_t lane_off = (uint32_t)(lane_grp * 32) << 16;
+        const uint32_t td1 = tm_d1 + 128 * h + lane_off, td2 = tm_d2 + 128 * h + lane_off;
+        uint64_t* d1_full = &hb[8 * h + 0];
+        uint64_t* d1_empty = &hb[8 * h + 1];
+        uint64_t* hs_full = &hb[8 * h + 2];
+        uint64_t* hs_empty = &hb[8 * h + 4];
+        uint64_t* d2_full = &hb[8 * h + 6];
+        uint64_t* d2_empty = &hb[8 * h + 7];
+        if (h != 0) tr = nullptr;
         uint32_t tile_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
             const int64_t R0 = (int64_t)tile * tile_rows;
@@ -276,9 +298,14 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
 #pragma unroll
                 for (int sub = 0; sub < 2; ++sub) {
                     float v[64];
-                    ptx::tmem_ld32(tm_d1 + lane_off + 128 * h + 64 * sub, v);
-                    ptx::tmem_ld32(tm_d1 + lane_off + 128 * h + 64 * sub + 32, v + 32);
-                    ptx::tmem_ld_wait();
+                    if (!(p.dbg & 8)) {
+                        ptx::tmem_ld32(td1 + 64 * sub, v);
+                        ptx::tmem_ld32(td1 + 64 * sub + 32, v + 32);
+                        ptx::tmem_ld_wait();
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 64; ++e) v[e] = (float)(e + j);
+                    }
                     if (sub == 1) {
                         // D1 is in registers: G1(c+1) may overwrite it
                         ptx::tc_fence_before();
@@ -288,23 +315,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                     }
                     ptx::mbar_wait(&hs_empty[sub], (n & 1) ^ 1);     // G2(c-1, sub) has finished reading this buffer
                     if (tile_it == 0 && sub == 1) FF_TRACE(8 + 12 * c + 8);
-                    uint8_t* dst = sHs + (h * 2 + sub) * FF_HS_BYTES + j * 16;
-                    const float* bias = s_b1 + c * 128 + sub * 64;
-#pragma unroll
-                    for (int kc = 0; kc < 8; ++kc) {
-                        const float4 ba = reinterpret_cast<const float4*>(bias)[kc * 2];
-                        const float4 bb = reinterpret_cast<const float4*>(bias)[kc * 2 + 1];
-                        const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-                        __align__(16) __nv_bfloat162 o2[4];
-#pragma unroll
-                        for (int e = 0; e < 8; e += 2) {
-                            float t0 = fmaxf(v[kc * 8 + e] + bz[e], 0.f);
-                            float t1 = fmaxf(v[kc * 8 + e + 1] + bz[e + 1], 0.f);
-                            if (!hid_live) { t0 = 0.f; t1 = 0.f; }
-                            o2[e / 2] = __floats2bfloat162_rn(t0, t1);
-                        }
-                        *reinterpret_cast<uint4*>(dst + kc * FF_HS_ROWS * 16) = *reinterpret_cast<const uint4*>(o2);
-                    }
+                    if (!(p.dbg & 4))
+                        ffn_e1_store(v, s_b1 + c * 128 + sub * 64, hid_live, sHs + (h * 2 + sub) * FF_HS_BYTES + j * 16, FF_HS_ROWS * 16);
                     ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
                     ptx::tc_fence_before();
                     __syncwarp();
@@ -319,59 +331,11 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             {
                 float v[128];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) ptx::tmem_ld32(tm_d2 + lane_off + 128 * h + q * 32, v + q * 32);
+                for (int q = 0; q < 4; ++q) ptx::tmem_ld32(td2 + q * 32, v + q * 32);
                 ptx::tmem_ld_wait();
-                if (out_write) {
-                    const uint8_t* xres = sX + (FF_OUT * h + j + 2) * 16;
-                    float sum = 0.f;
-#pragma unroll
-                    for (int kc = 0; kc < 16; ++kc) {
-                        const float4 ba = reinterpret_cast<const float4*>(s_b2)[kc * 2], bb = reinterpret_cast<const float4*>(s_b2)[kc * 2 + 1];
-                        const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-                        const uint4 pk = *reinterpret_cast<const uint4*>(xres + kc * 4096);
-                        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float t0 = v[kc * 8 + 2 * e] + bz[2 * e] + __low2float(h2[e]);
-                            const float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1] + __high2float(h2[e]);
-                            v[kc * 8 + 2 * e] = t0;
-                            v[kc * 8 + 2 * e + 1] = t1;
-                            sum += t0 + t1;
-                        }
-                    }
-                    const float mean = sum * (1.f / 128.f);
-                    float sq = 0.f;
-#pragma unroll
-                    for (int i = 0; i < 128; ++i) {
-                        const float d = v[i] - mean;
-                        sq = fmaf(d, d, sq);
-                    }
-                    const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
-                    const float* fp = p.film ? p.film + (int64_t)b_idx * p.film_stride : nullptr;
-#pragma unroll
-                    for (int kc = 0; kc < 16; ++kc) {
-                        const float4 g0 = reinterpret_cast<const float4*>(s_g)[kc * 2], g1 = reinterpret_cast<const float4*>(s_g)[kc * 2 + 1];
-                        const float4 e0 = reinterpret_cast<const float4*>(s_be)[kc * 2], e1 = reinterpret_cast<const float4*>(s_be)[kc * 2 + 1];
-                        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                        const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
-                        float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                        if (fp) {
-                            const float4 a0 = reinterpret_cast<const float4*>(fp)[kc * 2], a1 = reinterpret_cast<const float4*>(fp)[kc * 2 + 1];
-                            const float4 c0 = reinterpret_cast<const float4*>(fp + 128)[kc * 2], c1 = reinterpret_cast<const float4*>(fp + 128)[kc * 2 + 1];
-                            fg[0] = a0.x; fg[1] = a0.y; fg[2] = a0.z; fg[3] = a0.w; fg[4] = a1.x; fg[5] = a1.y; fg[6] = a1.z; fg[7] = a1.w;
-                            fb[0] = c0.x; fb[1] = c0.y; fb[2] = c0.z; fb[3] = c0.w; fb[4] = c1.x; fb[5] = c1.y; fb[6] = c1.z; fb[7] = c1.w;
-                        }
-                        __align__(16) __nv_bfloat162 o2[4];
-#pragma unroll
-                        for (int e = 0; e < 8; e += 2) {
-                            float y0 = fg[e] * ((v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e]) + fb[e];
-                            float y1 = fg[e + 1] * ((v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1]) + fb[e + 1];
-                            if (!out_live) { y0 = 0.f; y1 = 0.f; }
-                            o2[e / 2] = __floats2bfloat162_rn(y0, y1);
-                        }
-                        *reinterpret_cast<uint4*>(p.out + ((int64_t)kc * p.rows_phys + DX_HALO + so) * 8) = *reinterpret_cast<const uint4*>(o2);
-                    }
-                }
+                if (out_write)
+                    ffn_e2_store(v, sX + (FF_OUT * h + j + 2) * 16, s_b2, s_g, s_be, p.film ? p.film + (int64_t)b_idx * p.film_stride : nullptr,
+                                 out_live, p.out + (DX_HALO + so) * 8, p.rows_phys * 8);
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -385,6 +349,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) {
+        FF_TRACE(4);
         ptx::tc_fence_after();
         ptx::tmem_dealloc<512>(tmem_base);
     }
@@ -409,6 +374,7 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
     p.w2 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn2_bf);
     p.b1 = bw.b_c1; p.b2 = bw.b_c2; p.ln_g = bw.ln2_g; p.ln_b = bw.ln2_b;
     p.film = film; p.film_stride = film_stride; p.R = R;
+    p.dbg = debug_knob(8);
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
     int64_t tiles = (R.cap + FF_OUT - 1) / FF_OUT;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);

@@ -125,8 +125,10 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
             DX_TRY(attention_block_bf16(p.qkvb, rp, g, R, s));
         }
     }
-    if (!debug_knob(3))
-        return ffn_bf16(p.yb, p.xb, rp, bw, film ? film + film_block * 256 : nullptr, 8 * 256, R, s);
+    if (!debug_knob(3)) {
+        const float* fp = film ? film + film_block * 256 : nullptr;
+        return ffn_bf16(p.yb, p.xb, rp, bw, fp, 8 * 256, R, s);
+    }
     {   // conv1 + ReLU (hidden live one row past the utterance: H1)
         TcGemmArgs g = tc_args(p.yb, rp, DX_D, DX_C, DX_TAPS, bw.w_c1_bf, 256, 32, bw.b_c1, 1, TC_EPI_BF16, 1);
         g.out_bf = p.h1b; g.tag = "tc_ffn_conv1";
