@@ -235,3 +235,26 @@ def test_bulk_runner_matches_direct_forward(models):
         mel = m(tuple(t.cuda() for t in host))[3][0].cpu()
         for k, i in enumerate(b):
             assert torch.equal(got[i], mel[k, :, :out_lens[i]])
+
+
+@pytest.mark.parametrize("cfg", ["cfg2", "cfg4_b1"])
+def test_fused_block_tail_matches_four_launch_blocks(models, cfg):
+    """The fused block kernel (out-proj + LN1 + FFN + next QKV, two launches per FFT block) computes bit for bit what
+    the four-launch block (debug knob 9: QKV, attention, out-proj + LN1, FFN) computes: same bf16 rounding points,
+    same accumulation order.  cfg2 exercises two-half tiles (frames) and one-half tiles (symbols)."""
+    from daft_exprt_b200 import _lib
+    hp = C.hparams()
+    batch = tuple(t.cuda() for t in C.synthetic.config_batch(hp, cfg))
+    m = models["bf16"]
+    lib = _lib.load()
+    fused = m(batch)
+    torch.cuda.synchronize()
+    lib.dx_set_debug(9, 1)
+    try:
+        plain = m(batch)
+        torch.cuda.synchronize()
+    finally:
+        lib.dx_set_debug(9, 0)
+    assert torch.equal(fused[3][0], plain[3][0])          # mel
+    assert torch.equal(fused[4], plain[4])                # gaussian upsampling weights
+    assert torch.equal(fused[0], plain[0])                # accent embedding

@@ -29,7 +29,10 @@ torch.cuda.synchronize()
 lib.dx_set_trace_buffer(None, 0)
 t = buf.cpu().tolist()
 t0 = t[0]
-print(f"X landed        {t[1] - t0:8d}")
+if t[5]:
+    print(f"P0 A landed     {t[5] - t0:8d}")
+    print(f"P0 acc loaded   {t[6] - t0:8d}")
+print(f"X ready         {t[1] - t0:8d}")
 names = ["d1_empty", "G1_issued", "hs_full0", "G2_issued", "w_full0", "-", "d1_full", "tmem_ld1", "hs_empty1", "Hs_done1"]
 print("chunk " + " ".join(f"{n:>9s}" for n in names))
 for c in range(8):
@@ -37,6 +40,9 @@ for c in range(8):
     print(f"{c:5d} " + " ".join(f"{(v - t0) if v else 0:9d}" for v in row))
 print(f"E2 start        {t[2] - t0:8d}")
 print(f"E2 done         {t[3] - t0:8d}")
+if t[7]:
+    print(f"P3 done         {t[7] - t0:8d}")
+print(f"CTA done        {t[4] - t0:8d}")
 
 print("attention CTA (0,0,0) of the last launch (decoder block 3, longest utterance, head 0, q tile 0)")
 a0 = t[128]

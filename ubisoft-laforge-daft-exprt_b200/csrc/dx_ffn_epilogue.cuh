@@ -1,6 +1,12 @@
-// Per-row epilogue math of the fused FFN kernels (thread ↔ row; values come from TMEM in registers).
-//   ffn_e1_store: Hs = bf16(live ? ReLU(D1 + b1) : 0)                      PositionWiseConvFF model.py:228-229 (+ H1 live padding)
-//   ffn_e2_store: out = mask(FiLM(LN(D2 + b2 + x)))                        model.py:230-235, FFTBlock pad mask model.py:258
+// Per-row epilogue math of the fused FFT-block kernel (dx_ffn_tc.cu).  A row of 128 channels is owned by TWO threads
+// (same TMEM lane, two warps): "part" 0 holds channels 0-63, part 1 channels 64-127, each as 64 fp32 values read
+// from TMEM.  LayerNorm statistics are combined through shared memory as (part 0) + (part 1), each part summed in
+// channel order - the same order tc_epilogue_tile<128, TC_EPI_LN> uses, so fused and unfused blocks agree bit for bit.
+//   ffn_e1_store   Hs = bf16(live ? ReLU(D1 + b1) : 0)                 PositionWiseConvFF model.py:228-229 (+ H1 live padding)
+//   ffn_row_add    t = acc + bias + residual, partial sum              model.py:190 / :233 (residual)
+//   ffn_row_sq     partial sum of (t - mean)^2                         nn.LayerNorm model.py:191 / :234
+//   ffn_row_store  out = mask(FiLM(LN(t)))  → global and/or shared     model.py:235 (FiLM), :256 / :258 (pad mask)
+//   ffn_qkv_store  out = bf16(acc + bias)                              in_proj model.py:165,182
 #pragma once
 #include "dx_common.cuh"
 
@@ -25,38 +31,50 @@ __device__ __forceinline__ void ffn_e1_store(const float (&v)[64], const float* 
     }
 }
 
-// v: the row's 128 conv2 outputs (modified in place); xres: the row's residual in the X tile (chunk stride 4096 B);
-// fp: the utterance's FiLM vector [gamma 128 | beta 128] or null; out_row: &out[chunk 0][row][0], chunk stride out_chunk elements
-__device__ __forceinline__ void ffn_e2_store(float (&v)[128], const uint8_t* xres, const float* s_b2, const float* s_g, const float* s_be,
-                                             const float* fp, bool out_live, __nv_bfloat16* out_row, int64_t out_chunk) {
+// v[64] += bias[64] + residual (8 chunks of 8 bf16 at res + kc * res_stride bytes; shared or global memory);
+// returns the sum of the 64 results in channel order
+__device__ __forceinline__ float ffn_row_add(float (&v)[64], const float* bias, const uint8_t* res, int64_t res_stride) {
     float sum = 0.f;
 #pragma unroll
-    for (int kc = 0; kc < 16; ++kc) {
-        const float4 ba = reinterpret_cast<const float4*>(s_b2)[kc * 2], bb = reinterpret_cast<const float4*>(s_b2)[kc * 2 + 1];
+    for (int kc = 0; kc < 8; ++kc) {
+        const float4 ba = reinterpret_cast<const float4*>(bias)[kc * 2], bb = reinterpret_cast<const float4*>(bias)[kc * 2 + 1];
         const float bz[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-        const uint4 pk = *reinterpret_cast<const uint4*>(xres + kc * 4096);
+        const uint4 pk = *reinterpret_cast<const uint4*>(res + kc * res_stride);
         const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            const float t0 = v[kc * 8 + 2 * e] + bz[2 * e] + __low2float(h2[e]);
-            const float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1] + __high2float(h2[e]);
+            float t0 = v[kc * 8 + 2 * e] + bz[2 * e];
+            float t1 = v[kc * 8 + 2 * e + 1] + bz[2 * e + 1];
+            t0 += __low2float(h2[e]);
+            t1 += __high2float(h2[e]);
             v[kc * 8 + 2 * e] = t0;
             v[kc * 8 + 2 * e + 1] = t1;
-            sum += t0 + t1;
+            sum += t0;
+            sum += t1;
         }
     }
-    const float mean = sum * (1.f / 128.f);
+    return sum;
+}
+
+__device__ __forceinline__ float ffn_row_sq(const float (&v)[64], float mean) {
     float sq = 0.f;
 #pragma unroll
-    for (int i = 0; i < 128; ++i) {
+    for (int i = 0; i < 64; ++i) {
         const float d = v[i] - mean;
         sq = fmaf(d, d, sq);
     }
-    const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
+    return sq;
+}
+
+// g, be: LayerNorm gamma / beta of these 64 channels (shared memory); fp: FiLM [gamma 128 | beta 128] of the row's
+// utterance pre-offset to these 64 channels, or null; out_g: global &out[first chunk][row][0] or null (chunk stride
+// out_chunk elements); out_s: shared-memory copy or null (chunk stride smem_chunk bytes)
+__device__ __forceinline__ void ffn_row_store(const float (&v)[64], float mean, float rstd, const float* g, const float* be, const float* fp,
+                                              bool live, __nv_bfloat16* out_g, int64_t out_chunk, uint8_t* out_s, uint32_t smem_chunk) {
 #pragma unroll
-    for (int kc = 0; kc < 16; ++kc) {
-        const float4 g0 = reinterpret_cast<const float4*>(s_g)[kc * 2], g1 = reinterpret_cast<const float4*>(s_g)[kc * 2 + 1];
-        const float4 e0 = reinterpret_cast<const float4*>(s_be)[kc * 2], e1 = reinterpret_cast<const float4*>(s_be)[kc * 2 + 1];
+    for (int kc = 0; kc < 8; ++kc) {
+        const float4 g0 = reinterpret_cast<const float4*>(g)[kc * 2], g1 = reinterpret_cast<const float4*>(g)[kc * 2 + 1];
+        const float4 e0 = reinterpret_cast<const float4*>(be)[kc * 2], e1 = reinterpret_cast<const float4*>(be)[kc * 2 + 1];
         const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
         const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
         float fg[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f}, fb[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -69,10 +87,30 @@ __device__ __forceinline__ void ffn_e2_store(float (&v)[128], const uint8_t* xre
         __align__(16) __nv_bfloat162 o2[4];
 #pragma unroll
         for (int e = 0; e < 8; e += 2) {
-            float y0 = fg[e] * ((v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e]) + fb[e];
-            float y1 = fg[e + 1] * ((v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1]) + fb[e + 1];
-            if (!out_live) { y0 = 0.f; y1 = 0.f; }
+            float y0 = (v[kc * 8 + e] - mean) * rstd * gg[e] + ee[e];
+            float y1 = (v[kc * 8 + e + 1] - mean) * rstd * gg[e + 1] + ee[e + 1];
+            y0 = fg[e] * y0 + fb[e];
+            y1 = fg[e + 1] * y1 + fb[e + 1];
+            if (!live) { y0 = 0.f; y1 = 0.f; }
             o2[e / 2] = __floats2bfloat162_rn(y0, y1);
+        }
+        if (out_g != nullptr) *reinterpret_cast<uint4*>(out_g + kc * out_chunk) = *reinterpret_cast<const uint4*>(o2);
+        if (out_s != nullptr) *reinterpret_cast<uint4*>(out_s + kc * smem_chunk) = *reinterpret_cast<const uint4*>(o2);
+    }
+}
+
+// 64 columns of one 128-column tile of the next block's QKV projection
+__device__ __forceinline__ void ffn_qkv_store(const float (&v)[64], const float* bias, bool in_utt, __nv_bfloat16* out_row, int64_t out_chunk) {
+#pragma unroll
+    for (int kc = 0; kc < 8; ++kc) {
+        const float4 b0 = reinterpret_cast<const float4*>(bias)[kc * 2], b1 = reinterpret_cast<const float4*>(bias)[kc * 2 + 1];
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        __align__(16) __nv_bfloat162 o2[4];
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) {
+            float t0 = v[kc * 8 + e] + bb[e], t1 = v[kc * 8 + e + 1] + bb[e + 1];
+            if (!in_utt) { t0 = 0.f; t1 = 0.f; }
+            o2[e / 2] = __floats2bfloat162_rn(t0, t1);
         }
         *reinterpret_cast<uint4*>(out_row + kc * out_chunk) = *reinterpret_cast<const uint4*>(o2);
     }

@@ -1,19 +1,27 @@
-// Fused position-wise conv feed-forward for sm_100a (tcgen05 + TMEM + bulk-copy pipeline):
+// Fused tail of an FFT block for sm_100a (tcgen05 + TMEM + bulk-copy pipeline), one kernel for
 //
-//   y = mask( FiLM( LN( conv1d_{C→D,k3}( ReLU( conv1d_{D→C,k3}(x) + b1 ) ) + b2 + x ) ) )
+//   [P0]  x1 = mask( LN1( attn · W_out + b_out + x_in ) )                       MultiHeadAttention out_proj + residual
+//                                                                               + LayerNorm (model.py:187-191), pad mask (:256)
+//   [FFN] y  = mask( FiLM( LN2( conv1d_{C→D,k3}( ReLU( conv1d_{D→C,k3}(x1) + b1 ) ) + b2 + x1 ) ) )
+//                                                                               PositionWiseConvFF.forward (model.py:220-235), mask (:258)
+//   [P3]  qkv' = y · W_qkv' + b_qkv'                                            in_proj of the NEXT block (model.py:165,182)
 //
-// = PositionWiseConvFF.forward (model.py:220-235) + the FFTBlock pad mask (model.py:258), evaluated on the packed row
-// stream with the reference's "live padding" semantics (H1): the hidden activation of the first row after an
-// utterance is live, everything beyond is true zero padding.  The 1024-wide hidden activation never leaves the SM.
+// evaluated on the packed row stream with the reference's "live padding" semantics (H1): the hidden activation of
+// the first row after an utterance is live, everything beyond is true zero padding.  P0 and P3 are optional: without
+// P0 the kernel reads x1 from global memory; without P3 it stops after the FFN (last block of a stack).  Fusing them
+// removes two launches per block whose fixed cost (launch, prologue, tail: ~10 us each) exceeded their math (~1 us).
+// x1 and the 1024-wide hidden activation never leave the SM.
 //
 // One CTA = 252 output rows = two "halves" of 128 hidden rows (126 outputs each, 1 halo row per side).
-//   X   [16 chunk][256 row][8]  bf16  rows R0-2 .. R0+253, loaded once per tile by 16 bulk copies; also the residual
+//   X   [16 chunk][256 row][8]  bf16  rows R0-2 .. R0+253: written by the P0 epilogue (or 16 bulk copies); also the residual
+//   P0  A = attn rows R0-2 .. R0+253 (bulk-copied into the Hs region), D2[h] = A[128 h ..] · W_out, 8 MMAs per half
 //   for hidden chunk c (128 channels, 8 chunks):
 //     G1  D1[h] (128x128 fp32, TMEM) = sum_tap X_h[. + tap] · W1[c][tap]        24 MMAs (128x128x16) per half
 //     E1  Hs[h][sub] = bf16(live ? ReLU(D1[h][:, 64 sub ..] + b1) : 0)          sub = 0,1; thread ↔ row
 //     G2  D2[h] (128x128 fp32, TMEM) += sum_tap Hs[h][sub][. + tap] · W2[tap][c, sub]   12 MMAs per half and sub
-//   E2  out = mask(FiLM(LN(D2[h] + b2 + X_res)))                                 thread ↔ row, LN in registers
-// Issue order G1(c), G2(c-1, 0), G2(c-1, 1): E1(c) runs under G2(c-1).
+//   E2  y = mask(FiLM(LN2(D2[h] + b2 + X_res)))  → global, and → Y[h] (the Hs region of the half) as the A operand of P3
+//   P3  D1[h], D2[h], D1[h] = Y[h] · W_qkv'[:, 128 nt ..]   8 MMAs per 128-column tile; epilogue + bias → bf16 → global
+// Issue order G1(c), G2(c-1, 0), G2(c-1, 1): E1(c) runs under G2(c-1).  Short streams use ONE half per CTA.
 //
 // Why these shapes (profiles/r01b_mma_bench.txt, r01b_ffn_trace_before.txt): a 128xNx16 SS MMA reads (128+N)*32 B
 // of shared memory in N/2 cycles, so N = 64 needs 192 B/clk against the SM's 128 B/clk; N = 128 runs at the
@@ -26,8 +34,15 @@
 // ring depth; tools/ring_bench.cu).  With one issuer per half the two halves are independent pipelines that share
 // only the X tile and the weight ring: while one warp sits in a barrier wait the other's MMAs keep the pipe busy
 // (72 cycles per MMA in the microbenchmark).  All D1 / Hs / D2 barriers are per half.
-// Warps: 0 = bulk-copy producer, 1 = TMEM owner + issuer of half 0, 2 = issuer of half 1, 3-6 = epilogue of half 0,
-// 7-10 = epilogue of half 1 (warp w may only touch TMEM lanes 32 (w % 4) .. +31).
+// Warps: 0 = bulk-copy producer, 1 = TMEM owner + issuer of half 0, 2 = issuer of half 1, 3 idle, 4-11 = epilogue of
+// half 0, 12-19 = epilogue of half 1.  A warp may only touch TMEM lanes 32 (w % 4) .. +31, so every 32-row group
+// is served by TWO warps that split the 128 channels (E1: one 64-channel K sub-block of G2 each; the LayerNorm
+// epilogues exchange their partial sums through shared memory): the row epilogues were latency-bound with one
+// thread per row (P0 8 k cycles, E2 14 k cycles of a 108 k-cycle tile).
+//
+// TMEM accumulator protocol (per half): D1 is "used" 8 (+2 with P3) times per tile, D2 1 (+1 with P0, +1 with P3)
+// times; use number u: issuer waits empty (parity (u & 1) ^ 1), issues, commits full; epilogue waits full
+// (parity u & 1), loads the accumulator into registers, arrives on empty.
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
@@ -35,9 +50,11 @@
 
 namespace dx {
 
-constexpr int FF_THREADS = 352;
-constexpr int FF_OUT = 126;                 // outputs per half
-constexpr int FF_TILE = 2 * FF_OUT;         // outputs per CTA tile
+constexpr int FF_THREADS = 640;             // 20 warps: producer, 2 issuers, 1 idle, 16 epilogue
+constexpr int FF_EPI_WARP0 = 4;
+constexpr int FF_OUT = 126;                 // outputs per half (two-half tiles)
+constexpr int FF_OUT1 = 124;                // outputs of a one-half tile: its 128 X rows are exactly one P0 M tile
+constexpr int FF_TILE = 2 * FF_OUT;         // outputs per two-half CTA tile
 constexpr int FF_NCH = 8;                   // hidden chunks of 128 channels
 constexpr int FF_WSTAGES = 5;
 constexpr uint32_t FF_X_BYTES = 16 * 256 * 16;          // 65536
@@ -47,51 +64,83 @@ constexpr uint32_t FF_W_BYTES = 16384;
 constexpr uint32_t FF_OFF_HS = FF_X_BYTES;
 constexpr uint32_t FF_OFF_W = FF_OFF_HS + 4 * FF_HS_BYTES;
 constexpr uint32_t FF_OFF_PAR = FF_OFF_W + FF_WSTAGES * FF_W_BYTES;
-constexpr uint32_t FF_PAR_FLOATS = 1024 + 128 + 128 + 128;          // b1, b2, gamma, beta
+constexpr uint32_t FF_PAR_FLOATS = 1024 + 3 * 128 + 3 * 128 + 384 + 1024;   // b1 | b2, ln2 g, b | b_out, ln1 g, b | b_qkv' | LN exchange
 constexpr uint32_t FF_OFF_BAR = FF_OFF_PAR + FF_PAR_FLOATS * 4;
-constexpr uint32_t FF_NBARS = 2 * FF_WSTAGES + 2 + 2 * 8;
+constexpr uint32_t FF_NBARS = 2 * FF_WSTAGES + 3 + 2 * 9;
 constexpr uint32_t FF_SMEM = FF_OFF_BAR + FF_NBARS * 8 + 16;
+static_assert(FF_SMEM <= 232448, "fused FFN kernel: shared memory");
+static_assert(2 * FF_HS_BYTES >= 32768 && 4 * FF_HS_BYTES >= FF_X_BYTES, "Hs region must hold the P0 A tile and the P3 A tiles");
 
 struct FfnParams {
-    const __nv_bfloat16* x;     // [16][rows_phys][8] block input (also the residual)
+    const __nv_bfloat16* x;     // [16][rows_phys][8] x1 (FFN input and residual); unused with P0
     __nv_bfloat16* out;         // [16][rows_phys][8]
     int64_t rows_phys;
     const __nv_bfloat16 *w1, *w2;   // packed: W1 (taps 3, K 128, N 1024, nt 128, ks 64), W2 (taps 3, K 1024, N 128, nt 128, ks 64)
     const float *b1, *b2, *ln_g, *ln_b;
     const float* film;          // pre-offset to the block, or null
     int film_stride;
+    // P0 (attn != null): attention output, block input (residual), packed W_out (K 128, N 128, nt 128, ks 64)
+    const __nv_bfloat16 *attn, *x_in, *w_out;
+    const float *b_out, *ln1_g, *ln1_b;
+    // P3 (qkv_out != null): packed W_qkv of the next block (K 128, N 384, nt 128, ks 64), output [48][rows_phys][8]
+    const __nv_bfloat16* w_qkv;
+    const float* b_qkv;
+    __nv_bfloat16* qkv_out;
     Rows R;
     int dbg;                    // timing experiments (debug knob 8): bit 0 = weight stages are not copied (arrive only),
                                 // bit 1 = issue no MMAs, bit 2 = no Hs stores, bit 3 = no TMEM loads in E1 (results are wrong)
     long long* trace;           // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer) or null
 };
 
-// timeline slots (CTA 0, half 0 only): [0] kernel start, [1] X landed, then per chunk c (base 8 + 12 c):
+// timeline slots (CTA 0, half 0 only): [0] kernel start, [1] X ready, then per chunk c (base 8 + 12 c):
 //   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full[0] ok, +3 G2 issued (both subs), +4 first w_full wait of G1 done
 //   epilog  +6 d1_full ok, +7 TMEM loaded (sub 1), +8 hs_empty[1] ok, +9 Hs stored + fenced (sub 1)
-// [2] d2_full ok (E2 start), [3] E2 done, [4] CTA done
+// [2] d2_full ok (E2 start), [3] E2 done, [4] CTA done, [5] P0 A tile landed, [6] P0 accumulator ready, [7] P3 done
 #define FF_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
+
+// global source of weight stage q of a tile, in MMA issue order: [W_out k 0,1] G1(0) { G1(c) G2(c-1) } G2(7) [W_qkv' (nt, k)]
+__device__ __forceinline__ const uint8_t* ff_stage_src(const FfnParams& p, int q, int n_p0) {
+    if (q < n_p0) return reinterpret_cast<const uint8_t*>(p.w_out) + (size_t)q * FF_W_BYTES;
+    q -= n_p0;
+    if (q >= 12 * FF_NCH) return reinterpret_cast<const uint8_t*>(p.w_qkv) + (size_t)(q - 12 * FF_NCH) * FF_W_BYTES;
+    int c, w;            // c: loop iteration 0..8; w: 0..5 → G1(c), 6..11 → G2(c-1)
+    if (q < 6) { c = 0; w = q; }
+    else { c = 1 + (q - 6) / 12; w = (q - 6) % 12; if (c == FF_NCH) w += 6; }
+    if (w < 6) return reinterpret_cast<const uint8_t*>(p.w1) + ((size_t)c * 6 + w) * FF_W_BYTES;
+    return reinterpret_cast<const uint8_t*>(p.w2) + ((size_t)(c - 1) * 6 + (w - 6)) * FF_W_BYTES;
+}
 
 __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
     extern __shared__ __align__(1024) uint8_t ff_smem[];
     uint8_t* sX = ff_smem;
-    uint8_t* sHs = ff_smem + FF_OFF_HS;         // [half][sub]
+    uint8_t* sHs = ff_smem + FF_OFF_HS;         // [half][sub]; also the P0 A tile and the P3 A tiles
     uint8_t* sW = ff_smem + FF_OFF_W;
     float* s_b1 = reinterpret_cast<float*>(ff_smem + FF_OFF_PAR);
     float* s_b2 = s_b1 + 1024;
     float* s_g = s_b2 + 128;
     float* s_be = s_g + 128;
+    float* s_bo = s_be + 128;                   // P0: b_out, ln1 gamma, ln1 beta
+    float* s_g1 = s_bo + 128;
+    float* s_be1 = s_g1 + 128;
+    float* s_bq = s_be1 + 128;                  // P3: b_qkv' [384]
+    float* s_red = s_bq + 384;                  // LayerNorm partial sums [2 buf][2 half][2 part][128 row]
     uint64_t* bars = reinterpret_cast<uint64_t*>(ff_smem + FF_OFF_BAR);
     uint64_t* w_full = bars;                       // [S]   producer → both issuers
     uint64_t* w_empty = bars + FF_WSTAGES;         // [S]   one commit per active issuer
-    uint64_t* x_full = bars + 2 * FF_WSTAGES;
-    uint64_t* x_empty = x_full + 1;
-    uint64_t* hb = x_full + 2;                     // per half h (8 barriers each):
-    // hb[8 h + 0] d1_full, +1 d1_empty, +2 hs_full[sub 0], +3 hs_full[sub 1], +4 hs_empty[0], +5 hs_empty[1], +6 d2_full, +7 d2_empty
+    uint64_t* x_full = bars + 2 * FF_WSTAGES;      // bulk copies of the X tile (or of the P0 A tile) have landed
+    uint64_t* x_empty = x_full + 1;                // epilogue warps are done with the tile's shared memory
+    uint64_t* x_ready = x_full + 2;                // P0: the epilogue warps have written the X tile
+    uint64_t* hb = x_full + 3;                     // per half h (9 barriers each):
+    // hb[9 h + 0] d1_full, +1 d1_empty, +2 hs_full[sub 0], +3 hs_full[sub 1], +4 hs_empty[0], +5 hs_empty[1], +6 d2_full, +7 d2_empty,
+    // +8 y_full (P3: E2 has written the half's A tile)
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + FF_NBARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 3)) ? p.trace : nullptr;
+    const bool has_p0 = p.attn != nullptr, has_p3 = p.qkv_out != nullptr;
+    const int n_p0 = has_p0 ? 2 : 0;
+    const int stages_per_tile = n_p0 + 12 * FF_NCH + (has_p3 ? 6 : 0);
+    const uint32_t d1_uses = FF_NCH + (has_p3 ? 2 : 0), d2_uses = 1 + (has_p0 ? 1 : 0) + (has_p3 ? 1 : 0);
+    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == FF_EPI_WARP0)) ? p.trace : nullptr;
     if (warp == 1) FF_TRACE(0);
 
     // ---- prologue that does not depend on the previous kernel (PDL: overlaps its tail) ----
@@ -100,12 +149,22 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         s_b2[threadIdx.x] = p.b2[threadIdx.x];
         s_g[threadIdx.x] = p.ln_g[threadIdx.x];
         s_be[threadIdx.x] = p.ln_b[threadIdx.x];
+        if (has_p0) {
+            s_bo[threadIdx.x] = p.b_out[threadIdx.x];
+            s_g1[threadIdx.x] = p.ln1_g[threadIdx.x];
+            s_be1[threadIdx.x] = p.ln1_b[threadIdx.x];
+        }
     }
-    // rows 128..135 of the Hs buffers are read (taps of the two discarded output rows) but never written: zero once
+    if (has_p3)
+        for (int i = threadIdx.x; i < 384; i += FF_THREADS) s_bq[i] = p.b_qkv[i];
+    // rows 128..135 of the Hs buffers are read (taps of the two discarded output rows) but never written by E1: they
+    // only feed discarded rows, so any finite value will do (zero here; later whatever P0 / P3 left there)
     for (int i = threadIdx.x; i < 4 * 8 * 8; i += FF_THREADS) {
         const int q = i >> 6, kc = (i >> 3) & 7, rr = 128 + (i & 7);
         *reinterpret_cast<uint4*>(sHs + q * FF_HS_BYTES + kc * FF_HS_ROWS * 16 + rr * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
+    for (int i = threadIdx.x; i < 16 * 8; i += FF_THREADS)       // X rows 128..135: only written by two-half tiles
+        *reinterpret_cast<uint4*>(sX + (i >> 3) * 4096 + (128 + (i & 7)) * 16) = make_uint4(0u, 0u, 0u, 0u);
     if (threadIdx.x == 0) {
         for (int i = 0; i < FF_WSTAGES; ++i) ptx::mbar_init(&w_full[i], 1);
         ptx::fence_barrier_init();
@@ -116,12 +175,12 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    // the first FF_WSTAGES weight stages are the same for every tile (W1 chunk 0): fetch them now
+    // the first FF_WSTAGES weight stages are the same for every tile: fetch them now
     if (warp == 0 && ptx::elect_one()) {
         for (int s0 = 0; s0 < FF_WSTAGES; ++s0) {
             if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s0]); continue; }
             ptx::mbar_expect_tx(&w_full[s0], FF_W_BYTES);
-            ptx::bulk_g2s(sW + s0 * FF_W_BYTES, reinterpret_cast<const uint8_t*>(p.w1) + (size_t)s0 * FF_W_BYTES, FF_W_BYTES, &w_full[s0]);
+            ptx::bulk_g2s(sW + s0 * FF_W_BYTES, ff_stage_src(p, s0, n_p0), FF_W_BYTES, &w_full[s0]);
         }
     }
     __syncwarp();
@@ -130,25 +189,28 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     // ---- from here on the previous kernel's output (row map, activations) may be read ----
     const int64_t total = p.R.row_start[p.R.B];
     // Short streams (symbol side): when the 252-row tiles would leave more than half of the CTAs idle, every CTA
-    // takes ONE half (126 outputs) instead, which halves the kernel's critical path.  Decided on the device: the
-    // valid row count is only known there.
+    // takes ONE half instead, which halves the kernel's critical path.  Decided on the device: the valid row count
+    // is only known there.
     const int halves = ((total + FF_TILE - 1) / FF_TILE) * 2 <= (int64_t)gridDim.x ? 1 : 2;
-    const int tile_rows = FF_OUT * halves;
+    const int out_rows = halves == 2 ? FF_OUT : FF_OUT1;               // outputs per half
+    const int tile_rows = out_rows * halves;
     const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
-    const uint32_t x_chunk_bytes = halves == 2 ? 4096u : 2176u;      // 256 / 136 rows of one 8-channel chunk
+    const uint32_t x_chunk_bytes = halves == 2 ? 4096u : (has_p0 ? 2048u : 2176u);      // 256 / 128 / 136 rows of one 8-channel chunk
     if (threadIdx.x == 0) {
         for (int i = 0; i < FF_WSTAGES; ++i) ptx::mbar_init(&w_empty[i], halves);
         ptx::mbar_init(x_full, 1);
-        ptx::mbar_init(x_empty, 4 * halves);
+        ptx::mbar_init(x_empty, 8 * halves);
+        ptx::mbar_init(x_ready, 8 * halves);
         for (int h = 0; h < 2; ++h) {
-            ptx::mbar_init(&hb[8 * h + 0], 1);          // d1_full
-            ptx::mbar_init(&hb[8 * h + 1], 4);          // d1_empty
-            ptx::mbar_init(&hb[8 * h + 2], 4);          // hs_full[0]
-            ptx::mbar_init(&hb[8 * h + 3], 4);          // hs_full[1]
-            ptx::mbar_init(&hb[8 * h + 4], 1);          // hs_empty[0]
-            ptx::mbar_init(&hb[8 * h + 5], 1);          // hs_empty[1]
-            ptx::mbar_init(&hb[8 * h + 6], 1);          // d2_full
-            ptx::mbar_init(&hb[8 * h + 7], 4);          // d2_empty
+            ptx::mbar_init(&hb[9 * h + 0], 1);          // d1_full
+            ptx::mbar_init(&hb[9 * h + 1], 8);          // d1_empty
+            ptx::mbar_init(&hb[9 * h + 2], 4);          // hs_full[0]
+            ptx::mbar_init(&hb[9 * h + 3], 4);          // hs_full[1]
+            ptx::mbar_init(&hb[9 * h + 4], 1);          // hs_empty[0]
+            ptx::mbar_init(&hb[9 * h + 5], 1);          // hs_empty[1]
+            ptx::mbar_init(&hb[9 * h + 6], 1);          // d2_full
+            ptx::mbar_init(&hb[9 * h + 7], 8);          // d2_empty
+            ptx::mbar_init(&hb[9 * h + 8], 8);          // y_full
         }
         ptx::fence_barrier_init();
     }
@@ -157,30 +219,25 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 256;
 
     if (warp == 0) {
-        // ===================== producer: X tile + weight stages =====================
+        // ===================== producer: X tile (or P0 A tile) + weight stages =====================
         if (ptx::elect_one()) {
             uint32_t wit = 0, tile_it = 0;
+            const __nv_bfloat16* src = has_p0 ? p.attn : p.x;
+            uint8_t* dst = has_p0 ? sHs : sX;
+            const uint32_t dst_chunk = (has_p0 && halves == 1) ? 2048u : 4096u;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
                 const int64_t R0 = (int64_t)tile * tile_rows;
                 ptx::mbar_wait(x_empty, (tile_it & 1) ^ 1);
                 ptx::mbar_expect_tx(x_full, 16 * x_chunk_bytes);
                 for (int kc = 0; kc < 16; ++kc)
-                    ptx::bulk_g2s(sX + kc * 4096, p.x + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, x_chunk_bytes, x_full);
-                // weight order must match the MMA issue order: W1(c) [2 K halves x 3 taps], then W2(c-1) [2 subs x 3 taps]
-                for (int c = 0; c <= FF_NCH; ++c) {
-                    for (int which = 0; which < 2; ++which) {
-                        const int cc = which == 0 ? c : c - 1;
-                        if (cc < 0 || cc >= FF_NCH) continue;
-                        const uint8_t* base = reinterpret_cast<const uint8_t*>(which == 0 ? p.w1 : p.w2) + (size_t)cc * 6 * FF_W_BYTES;
-                        for (int st = 0; st < 6; ++st, ++wit) {
-                            if (wit < FF_WSTAGES) continue;          // fetched in the prologue
-                            const int s = wit % FF_WSTAGES;
-                            ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
-                            if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
-                            ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
-                            ptx::bulk_g2s(sW + s * FF_W_BYTES, base + (size_t)st * FF_W_BYTES, FF_W_BYTES, &w_full[s]);
-                        }
-                    }
+                    ptx::bulk_g2s(dst + kc * dst_chunk, src + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, x_chunk_bytes, x_full);
+                for (int q = 0; q < stages_per_tile; ++q, ++wit) {
+                    if (wit < FF_WSTAGES) continue;          // fetched in the prologue
+                    const int s = wit % FF_WSTAGES;
+                    ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
+                    if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
+                    ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
+                    ptx::bulk_g2s(sW + s * FF_W_BYTES, ff_stage_src(p, q, n_p0), FF_W_BYTES, &w_full[s]);
                 }
             }
         }
@@ -192,159 +249,232 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         if (h < halves) {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
             const uint32_t aX = ptx::smem_u32(sX) + FF_OUT * h * 16, aHs = ptx::smem_u32(sHs) + h * 2 * FF_HS_BYTES, aW = ptx::smem_u32(sW);
+            const uint32_t aP0 = ptx::smem_u32(sHs) + 128 * h * 16;          // P0 A tile: rows 128 h .. of [16][256 | 128 rows][16 B]
+            const uint32_t p0_lbo = halves == 2 ? 4096u : 2048u;
             const uint32_t td1 = tm_d1 + 128 * h, td2 = tm_d2 + 128 * h;
-            uint64_t* d1_full = &hb[8 * h + 0];
-            uint64_t* d1_empty = &hb[8 * h + 1];
-            uint64_t* hs_full = &hb[8 * h + 2];
-            uint64_t* hs_empty = &hb[8 * h + 4];
-            uint64_t* d2_full = &hb[8 * h + 6];
-            uint64_t* d2_empty = &hb[8 * h + 7];
+            uint64_t* d1_full = &hb[9 * h + 0];
+            uint64_t* d1_empty = &hb[9 * h + 1];
+            uint64_t* hs_full = &hb[9 * h + 2];
+            uint64_t* hs_empty = &hb[9 * h + 4];
+            uint64_t* d2_full = &hb[9 * h + 6];
+            uint64_t* d2_empty = &hb[9 * h + 7];
+            uint64_t* y_full = &hb[9 * h + 8];
             uint32_t wit = 0, tile_it = 0;
+            // one weight stage = 4 MMAs of this half: A at a_base + kk * a_step (K-major, LBO a_lbo), B = the stage
+#define FF_STAGE(a_base, a_step, a_lbo, d_tmem, acc_first, ...)                                                         \
+            do {                                                                                                        \
+                const int s = wit % FF_WSTAGES;                                                                         \
+                ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);                                                      \
+                ptx::tc_fence_after();                                                                                  \
+                if (ptx::elect_one()) {                                                                                 \
+                    _Pragma("unroll") for (int kk = 0; kk < 4; ++kk) {                                                  \
+                        const uint64_t da = ptx::make_desc((a_base) + kk * (a_step), (a_lbo), 128);                     \
+                        const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);             \
+                        if (!(p.dbg & 2)) ptx::mma_bf16((d_tmem), da, db, idesc, (acc_first) || kk != 0);               \
+                    }                                                                                                   \
+                    ptx::mma_commit(&w_empty[s]);                                                                       \
+                    __VA_ARGS__;                                                                                        \
+                }                                                                                                       \
+                __syncwarp();                                                                                           \
+                ++wit;                                                                                                  \
+            } while (0)
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+                uint32_t u1 = tile_it * d1_uses, u2 = tile_it * d2_uses;       // accumulator use counters
                 ptx::mbar_wait(x_full, tile_it & 1);
+                if (tile_it == 0 && has_p0) FF_TRACE(5);
+                if (has_p0) {
+                    // ---- P0: D2[h] = attn[128 h .. +127] · W_out   (stage = K half)
+                    ptx::mbar_wait(d2_empty, (u2 & 1) ^ 1);
+                    ptx::tc_fence_after();
+                    for (int ks = 0; ks < 2; ++ks)
+                        FF_STAGE(aP0 + ks * 8 * p0_lbo, 2 * p0_lbo, p0_lbo, td2, ks != 0, if (ks == 1) ptx::mma_commit(d2_full));
+                    ++u2;
+                    ptx::mbar_wait(x_ready, tile_it & 1);      // X tile written by the epilogue warps of both halves
+                    ptx::tc_fence_after();
+                }
                 if (tile_it == 0) FF_TRACE(1);
-                ptx::mbar_wait(d2_empty, (tile_it & 1) ^ 1);
+                ptx::mbar_wait(d2_empty, (u2 & 1) ^ 1);
                 ptx::tc_fence_after();
                 for (int c = 0; c <= FF_NCH; ++c) {
                     if (c < FF_NCH) {
                         // ---- G1(c): D1[h] = X_h (*) W1[c]   (stage = (K half, tap): 64 input channels x 128 hidden)
-                        const uint32_t n = tile_it * FF_NCH + c;
-                        ptx::mbar_wait(d1_empty, (n & 1) ^ 1);
+                        ptx::mbar_wait(d1_empty, (u1 & 1) ^ 1);
                         ptx::tc_fence_after();
                         if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
-                        for (int st = 0; st < 6; ++st, ++wit) {
+                        for (int st = 0; st < 6; ++st) {
                             const int kh = st / 3, tap = st % 3;
-                            const int s = wit % FF_WSTAGES;
-                            ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
-                            ptx::tc_fence_after();
-                            if (tile_it == 0 && st == 0) FF_TRACE(8 + 12 * c + 4);
-                            if (ptx::elect_one()) {
-#pragma unroll
-                                for (int kk = 0; kk < 4; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aX + (kh * 8 + kk * 2) * 4096 + tap * 16, 4096, 128);
-                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
-                                    if (!(p.dbg & 2)) ptx::mma_bf16(td1, da, db, idesc, (st | kk) != 0);
-                                }
-                                ptx::mma_commit(&w_empty[s]);
-                                if (st == 5) ptx::mma_commit(d1_full);
-                            }
-                            __syncwarp();
+                            FF_STAGE(aX + kh * 8 * 4096 + tap * 16, 2 * 4096, 4096, td1, st != 0, if (st == 5) ptx::mma_commit(d1_full));
                         }
+                        ++u1;
                         if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
                     }
                     if (c >= 1) {
                         // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
                         const int cc = c - 1;
                         const uint32_t k = tile_it * FF_NCH + cc;
-                        for (int st = 0; st < 6; ++st, ++wit) {
+                        for (int st = 0; st < 6; ++st) {
                             const int sub = st / 3, tap = st % 3;
                             if (tap == 0) {
                                 ptx::mbar_wait(&hs_full[sub], k & 1);
                                 ptx::tc_fence_after();
                                 if (tile_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
                             }
-                            const int s = wit % FF_WSTAGES;
-                            ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);
-                            ptx::tc_fence_after();
-                            if (ptx::elect_one()) {
-#pragma unroll
-                                for (int kk = 0; kk < 4; ++kk) {
-                                    const uint64_t da = ptx::make_desc(aHs + sub * FF_HS_BYTES + kk * 2 * FF_HS_ROWS * 16 + tap * 16, FF_HS_ROWS * 16, 128);
-                                    const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);
-                                    if (!(p.dbg & 2)) ptx::mma_bf16(td2, da, db, idesc, (cc | st | kk) != 0);
-                                }
-                                ptx::mma_commit(&w_empty[s]);
-                                if (tap == 2) {
-                                    ptx::mma_commit(&hs_empty[sub]);
-                                    if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
-                                }
-                            }
-                            __syncwarp();
+                            FF_STAGE(aHs + sub * FF_HS_BYTES + tap * 16, 2 * FF_HS_ROWS * 16, FF_HS_ROWS * 16, td2, (cc | st) != 0,
+                                     if (tap == 2) {
+                                         ptx::mma_commit(&hs_empty[sub]);
+                                         if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
+                                     });
                         }
                         if (tile_it == 0) FF_TRACE(8 + 12 * cc + 3);
                     }
                 }
+                ++u2;
+                if (has_p3) {
+                    // ---- P3: next block's QKV projection of this half's outputs: tiles 0, 2 → D1[h], tile 1 → D2[h]
+                    ptx::mbar_wait(y_full, tile_it & 1);
+                    ptx::tc_fence_after();
+                    for (int nt = 0; nt < 3; ++nt) {
+                        const bool on_d1 = nt != 1;
+                        ptx::mbar_wait(on_d1 ? d1_empty : d2_empty, ((on_d1 ? u1 : u2) & 1) ^ 1);
+                        ptx::tc_fence_after();
+                        for (int ks = 0; ks < 2; ++ks)
+                            FF_STAGE(aHs + ks * 8 * 2048, 2 * 2048, 2048, on_d1 ? td1 : td2, ks != 0,
+                                     if (ks == 1) ptx::mma_commit(on_d1 ? d1_full : d2_full));
+                        if (on_d1) ++u1; else ++u2;
+                    }
+                }
             }
+#undef FF_STAGE
         }
-    } else if (((warp - 3) >> 2) < halves) {
-        // ===================== epilogue: warps 3-6 own half 0, warps 7-10 own half 1; thread ↔ row =====================
-        const int h = (warp - 3) >> 2;
+    } else if (warp >= FF_EPI_WARP0 && ((warp - FF_EPI_WARP0) >> 3) < halves) {
+        // ===================== epilogue: 16 warps; (half, channel part, lane quadrant); thread ↔ (row, 64 channels) ==========
+        const int e = warp - FF_EPI_WARP0;
+        const int h = e >> 3;
+        const int part = (e >> 2) & 1;                               // channels 64 part .. +63 of the row
         const int lane_grp = warp & 3;
         const int j = lane_grp * 32 + lane;                         // row inside the half
         const uint32_t lane_off = (uint32_t)(lane_grp * 32) << 16;
-        const uint32_t td1 = tm_d1 + 128 * h + lane_off, td2 = tm_d2 + 128 * h + lane_off;
-        uint64_t* d1_full = &hb[8 * h + 0];
-        uint64_t* d1_empty = &hb[8 * h + 1];
-        uint64_t* hs_full = &hb[8 * h + 2];
-        uint64_t* hs_empty = &hb[8 * h + 4];
-        uint64_t* d2_full = &hb[8 * h + 6];
-        uint64_t* d2_empty = &hb[8 * h + 7];
-        if (h != 0) tr = nullptr;
+        const uint32_t td1 = tm_d1 + 128 * h + lane_off + 64 * part, td2 = tm_d2 + 128 * h + lane_off + 64 * part;
+        uint64_t* d1_full = &hb[9 * h + 0];
+        uint64_t* d1_empty = &hb[9 * h + 1];
+        uint64_t* hs_full = &hb[9 * h + 2];
+        uint64_t* hs_empty = &hb[9 * h + 4];
+        uint64_t* d2_full = &hb[9 * h + 6];
+        uint64_t* d2_empty = &hb[9 * h + 7];
+        uint64_t* y_full = &hb[9 * h + 8];
+        uint8_t* sY = sHs + h * 2 * FF_HS_BYTES;                     // P3 A tile of this half: [16 chunk][128 row][16 B]
+        // LayerNorm statistics exchange between the two threads of a row: red[buf][h][part][row]
+        float* my_red = s_red + (h * 2 + part) * 128 + j;
+        const float* peer_red = s_red + (h * 2 + (part ^ 1)) * 128 + j;
+        const int pair_bar = 1 + h * 4 + lane_grp;                   // named barrier of the two warps that share these 32 rows
+        if (h != 0 || part != 0) tr = nullptr;
         uint32_t tile_it = 0;
+        // this part's 64 accumulator columns → registers, then hand the accumulator back to the issuer
+#define FF_LOAD64(v, taddr, full_bar, empty_bar, use)                                                       \
+        do {                                                                                                \
+            ptx::mbar_wait((full_bar), (use) & 1);                                                          \
+            ptx::tc_fence_after();                                                                          \
+            ptx::tmem_ld32((taddr), (v));                                                                   \
+            ptx::tmem_ld32((taddr) + 32, (v) + 32);                                                         \
+            ptx::tmem_ld_wait();                                                                            \
+            ptx::tc_fence_before();                                                                         \
+            __syncwarp();                                                                                   \
+            if (lane == 0) ptx::mbar_arrive(empty_bar);                                                     \
+        } while (0)
+        // mean and 1/std of the row from the two parts' partial sums (combined as part 0 + part 1 by both threads)
+#define FF_ROW_STATS(v, part_sum, mean, rstd)                                                               \
+        do {                                                                                                \
+            my_red[0] = (part_sum);                                                                         \
+            ptx::named_bar_sync(pair_bar, 64);                                                              \
+            const float o_ = peer_red[0];                                                                   \
+            mean = (part == 0 ? (part_sum) + o_ : o_ + (part_sum)) * (1.f / 128.f);                         \
+            const float sq_ = ffn_row_sq((v), mean);                                                        \
+            my_red[512] = sq_;                                                                              \
+            ptx::named_bar_sync(pair_bar, 64);                                                              \
+            const float p_ = peer_red[512];                                                                 \
+            rstd = rsqrtf((part == 0 ? sq_ + p_ : p_ + sq_) * (1.f / 128.f) + 1e-5f);                       \
+        } while (0)
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+            uint32_t u1 = tile_it * d1_uses, u2 = tile_it * d2_uses;
             const int64_t R0 = (int64_t)tile * tile_rows;
             const int64_t sh = R0 + FF_OUT * h - 1 + j;             // stream row of hidden row j
             const bool hid_live = sh >= 0 && sh < total && row_live(p.R, sh, 1);
             const int64_t so = R0 + FF_OUT * h + j;                 // stream row of output row j
-            const bool out_write = j < FF_OUT && so < total;
+            const bool out_write = j < out_rows && so < total;
             const bool out_live = out_write && row_live(p.R, so, 0);
-            const int b_idx = out_write ? max(p.R.row_b[so], 0) : 0;
-            ptx::mbar_wait(x_full, tile_it & 1);                     // residual rows are read from sX in E2
-            for (int c = 0; c < FF_NCH; ++c) {
+            const int row_b = out_write ? p.R.row_b[so] : -1;
+            const int b_idx = max(row_b, 0);
+            if (has_p0) {
+                // ---- P0 epilogue: X row 128 h + j = mask(LN1(D2 + b_out + x_in)), stream row R0 - 2 + 128 h + j
+                const int64_t sx = R0 - 2 + 128 * h + j;
+                const bool x_live = sx >= 0 && sx < total && row_live(p.R, sx, 0);
+                float v[64];
+                FF_LOAD64(v, td2, d2_full, d2_empty, u2);
+                ++u2;
+                if (tile_it == 0) FF_TRACE(6);
+                float psum = 0.f, mean, rstd;
+                if (x_live)
+                    psum = ffn_row_add(v, s_bo + 64 * part, reinterpret_cast<const uint8_t*>(p.x_in + ((int64_t)8 * part * p.rows_phys + DX_HALO + sx) * 8),
+                                       p.rows_phys * 16);
+                FF_ROW_STATS(v, psum, mean, rstd);
+                ffn_row_store(v, mean, rstd, s_g1 + 64 * part, s_be1 + 64 * part, nullptr, x_live, nullptr, 0,
+                              sX + 8 * part * 4096 + (128 * h + j) * 16, 4096);
+                ptx::fence_proxy_async();        // X writes → visible to the tensor core's async proxy
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(x_ready);
+            } else {
+                ptx::mbar_wait(x_full, tile_it & 1);                 // residual rows are read from sX in E2
+            }
+            for (int c = 0; c < FF_NCH; ++c, ++u1) {
+                // ---- E1(c): this part's 64 hidden channels (= G2's K sub-block `part`)
                 const uint32_t n = tile_it * FF_NCH + c;
-                ptx::mbar_wait(d1_full, n & 1);
-                ptx::tc_fence_after();
+                float v[64];
                 if (tile_it == 0) FF_TRACE(8 + 12 * c + 6);
-#pragma unroll
-                for (int sub = 0; sub < 2; ++sub) {
+                FF_LOAD64(v, td1, d1_full, d1_empty, u1);            // D1 is in registers: G1(c+1) may overwrite it
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
+                ptx::mbar_wait(&hs_empty[part], (n & 1) ^ 1);        // G2(c-1, part) has finished reading this buffer
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 8);
+                if (!(p.dbg & 4))
+                    ffn_e1_store(v, s_b1 + c * 128 + part * 64, hid_live, sHs + (h * 2 + part) * FF_HS_BYTES + j * 16, FF_HS_ROWS * 16);
+                ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&hs_full[part]);
+                if (tile_it == 0) FF_TRACE(8 + 12 * c + 9);
+            }
+            {   // ---- E2: LN epilogue of this half (all G2 MMAs of the half have completed: its Hs buffers are free)
+                float v[64];
+                FF_LOAD64(v, td2, d2_full, d2_empty, u2);
+                ++u2;
+                if (tile_it == 0) FF_TRACE(2);
+                float mean, rstd;
+                const float psum = ffn_row_add(v, s_b2 + 64 * part, sX + 8 * part * 4096 + (FF_OUT * h + j + 2) * 16, 4096);
+                FF_ROW_STATS(v, psum, mean, rstd);
+                ffn_row_store(v, mean, rstd, s_g + 64 * part, s_be + 64 * part,
+                              p.film ? p.film + (int64_t)b_idx * p.film_stride + 64 * part : nullptr, out_live,
+                              out_write ? p.out + ((int64_t)8 * part * p.rows_phys + DX_HALO + so) * 8 : nullptr, p.rows_phys * 8,
+                              has_p3 ? sY + 8 * part * 2048 + j * 16 : nullptr, 2048);
+                if (tile_it == 0) FF_TRACE(3);
+            }
+            if (has_p3) {
+                ptx::fence_proxy_async();            // Y writes → async proxy
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(y_full);
+                const bool in_utt = row_b >= 0;
+                for (int nt = 0; nt < 3; ++nt) {
                     float v[64];
-                    if (!(p.dbg & 8)) {
-                        ptx::tmem_ld32(td1 + 64 * sub, v);
-                        ptx::tmem_ld32(td1 + 64 * sub + 32, v + 32);
-                        ptx::tmem_ld_wait();
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 64; ++e) v[e] = (float)(e + j);
-                    }
-                    if (sub == 1) {
-                        // D1 is in registers: G1(c+1) may overwrite it
-                        ptx::tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(d1_empty);
-                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
-                    }
-                    ptx::mbar_wait(&hs_empty[sub], (n & 1) ^ 1);     // G2(c-1, sub) has finished reading this buffer
-                    if (tile_it == 0 && sub == 1) FF_TRACE(8 + 12 * c + 8);
-                    if (!(p.dbg & 4))
-                        ffn_e1_store(v, s_b1 + c * 128 + sub * 64, hid_live, sHs + (h * 2 + sub) * FF_HS_BYTES + j * 16, FF_HS_ROWS * 16);
-                    ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
-                    ptx::tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(&hs_full[sub]);
-                    if (tile_it == 0 && sub == 1) FF_TRACE(8 + 12 * c + 9);
+                    if (nt != 1) { FF_LOAD64(v, td1, d1_full, d1_empty, u1); ++u1; }
+                    else { FF_LOAD64(v, td2, d2_full, d2_empty, u2); ++u2; }
+                    if (out_write)
+                        ffn_qkv_store(v, s_bq + nt * 128 + 64 * part, in_utt,
+                                      p.qkv_out + ((int64_t)(nt * 16 + 8 * part) * p.rows_phys + DX_HALO + so) * 8, p.rows_phys * 8);
                 }
+                if (tile_it == 0) FF_TRACE(7);
             }
-            // ---- E2: LN epilogue of this half
-            ptx::mbar_wait(d2_full, tile_it & 1);
-            ptx::tc_fence_after();
-            if (tile_it == 0) FF_TRACE(2);
-            {
-                float v[128];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) ptx::tmem_ld32(td2 + q * 32, v + q * 32);
-                ptx::tmem_ld_wait();
-                if (out_write)
-                    ffn_e2_store(v, sX + (FF_OUT * h + j + 2) * 16, s_b2, s_g, s_be, p.film ? p.film + (int64_t)b_idx * p.film_stride : nullptr,
-                                 out_live, p.out + (DX_HALO + so) * 8, p.rows_phys * 8);
-            }
-            ptx::tc_fence_before();
             __syncwarp();
-            if (tile_it == 0) FF_TRACE(3);
-            if (lane == 0) {
-                ptx::mbar_arrive(d2_empty);
-                ptx::mbar_arrive(x_empty);
-            }
+            if (lane == 0) ptx::mbar_arrive(x_empty);
         }
+#undef FF_LOAD64
+#undef FF_ROW_STATS
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -356,9 +486,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
 }
 
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
-             int film_stride, const Rows& R, cudaStream_t s) {
+             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse) {
     DX_REQUIRE(bw.w_ffn1_bf && bw.w_ffn2_bf, "ffn_bf16: fused-FFN packed weights missing");
-    DX_REQUIRE(x != out, "ffn_bf16: in-place operation is not supported (rows of neighbouring tiles are read as halos)");
     static int num_sms = 0;
     static bool configured = false;
     if (!configured) {
@@ -369,14 +498,30 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
         configured = true;
     }
     FfnParams p;
+    memset(&p, 0, sizeof(p));
     p.x = x; p.out = out; p.rows_phys = rows_phys;
     p.w1 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn1_bf);
     p.w2 = reinterpret_cast<const __nv_bfloat16*>(bw.w_ffn2_bf);
     p.b1 = bw.b_c1; p.b2 = bw.b_c2; p.ln_g = bw.ln2_g; p.ln_b = bw.ln2_b;
     p.film = film; p.film_stride = film_stride; p.R = R;
+    if (fuse != nullptr && fuse->attn != nullptr) {
+        DX_REQUIRE(fuse->x_in && bw.w_out_bf && bw.b_out && bw.ln1_g && bw.ln1_b, "ffn_bf16: fused out-proj needs x_in, W_out, b_out, LN1");
+        DX_REQUIRE(fuse->x_in != out && fuse->attn != out, "ffn_bf16: the output must not alias the block input or the attention output");
+        p.attn = fuse->attn; p.x_in = fuse->x_in;
+        p.w_out = reinterpret_cast<const __nv_bfloat16*>(bw.w_out_bf);
+        p.b_out = bw.b_out; p.ln1_g = bw.ln1_g; p.ln1_b = bw.ln1_b;
+    } else {
+        DX_REQUIRE(x != nullptr && x != out, "ffn_bf16: in-place operation is not supported (rows of neighbouring tiles are read as halos)");
+    }
+    if (fuse != nullptr && fuse->qkv_out != nullptr) {
+        DX_REQUIRE(fuse->next && fuse->next->w_qkv_bf && fuse->next->b_qkv, "ffn_bf16: fused QKV projection needs the next block's weights");
+        p.w_qkv = reinterpret_cast<const __nv_bfloat16*>(fuse->next->w_qkv_bf);
+        p.b_qkv = fuse->next->b_qkv;
+        p.qkv_out = fuse->qkv_out;
+    }
     p.dbg = debug_knob(8);
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
-    int64_t tiles = (R.cap + FF_OUT - 1) / FF_OUT;     // enough CTAs for the one-half-per-CTA mode of short streams
+    int64_t tiles = (R.cap + FF_OUT1 - 1) / FF_OUT1;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
     ProfScope prof("tc_ffn_fused", s);
     DX_LAUNCH_PDL((ffn_tc_kernel), grid, FF_THREADS, FF_SMEM, s, p);

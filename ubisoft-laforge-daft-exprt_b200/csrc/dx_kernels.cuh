@@ -32,9 +32,17 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
 struct TcGemmArgs;
 int attention_block_bf16(const __nv_bfloat16* qkv, int64_t rows_phys, const TcGemmArgs& g, const Rows& R, cudaStream_t s);
 
-// dx_ffn_tc.cu: fused conv1 + ReLU + conv2 + residual + LN + FiLM + mask
+// dx_ffn_tc.cu: fused conv1 + ReLU + conv2 + residual + LN + FiLM + mask; optionally with the attention output
+// projection + residual + LN1 in front (attn != null: x is ignored, x_in is the block input) and the next block's QKV
+// projection behind (qkv_out != null, next = that block's weights)
+struct FfnFuse {
+    const __nv_bfloat16* attn;
+    const __nv_bfloat16* x_in;
+    const DxBlockWeights* next;
+    __nv_bfloat16* qkv_out;
+};
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
-             int film_stride, const Rows& R, cudaStream_t s);
+             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse = nullptr);
 
 // dx_style.cu
 int style(const DxModelWeights* w, int B, const float* spk_embs, const float* spk_emb_in, const float* accent,

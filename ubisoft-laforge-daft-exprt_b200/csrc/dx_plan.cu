@@ -105,6 +105,7 @@ static int linear_bf16(const TcGemmArgs& g, const Rows& R, cudaStream_t s) {
     return debug_knob(4) ? tc_gemm(g, R, s) : tc_linear(g, R, s);
 }
 
+// One FFT block in four launches (debug knob 9; also the A/B reference of the fused stack below)
 static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R, const float* film, int film_block,
                           cudaStream_t s) {
     const int64_t rp = p.rows_phys;
@@ -140,6 +141,38 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
         g.film = film ? film + film_block * 256 : nullptr;
         g.film_stride = 8 * 256; g.tag = "tc_ffn_conv2_ln";
         DX_TRY(tc_gemm(g, R, s));
+    }
+    return 0;
+}
+
+// A stack of four FFT blocks (FFTBlock.forward x 4, model.py:249-259, called at :299-300 / :531-532 / :704-705) on the
+// row stream in p.xb, result back in p.xb.  Two launches per block: attention, then ONE kernel for out-proj + LN1 +
+// FFN + LN2/FiLM + the next block's QKV projection; the stack's first QKV projection is its own launch.  The block
+// input and output alternate between p.xb and p.yb (neighbouring tiles read the input rows as residual halos).
+static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Rows& R, const float* film, int film_block0,
+                          cudaStream_t s) {
+    if (debug_knob(9) || debug_knob(3) || debug_knob(6)) {
+        for (int i = 0; i < 4; ++i) DX_TRY(fft_block_bf16(blocks[i], p, R, film, film_block0 + i, s));
+        return 0;
+    }
+    const int64_t rp = p.rows_phys;
+    __nv_bfloat16 *cur = p.xb, *nxt = p.yb;
+    for (int i = 0; i < 4; ++i) {
+        const DxBlockWeights& bw = blocks[i];
+        DX_REQUIRE(bw.w_qkv_bf && bw.w_out_bf && bw.w_ffn1_bf && bw.w_ffn2_bf, "bf16 mode: packed weights missing (model not prepared for DX_MODE_BF16)");
+        if (i == 0) {
+            TcGemmArgs g = tc_args(cur, rp, DX_D, 3 * DX_D, 1, bw.w_qkv_bf, 128, 64, bw.b_qkv, 0, TC_EPI_BF16, -1);
+            g.out_bf = p.qkvb; g.tag = "tc_qkv";
+            DX_TRY(linear_bf16(g, R, s));
+        }
+        DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
+        FfnFuse f;
+        f.attn = p.ob; f.x_in = cur;
+        f.next = i < 3 ? &blocks[i + 1] : nullptr;
+        f.qkv_out = i < 3 ? p.qkvb : nullptr;
+        const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
+        DX_TRY(ffn_bf16(nullptr, nxt, rp, bw, fp, 8 * 256, R, s, &f));
+        __nv_bfloat16* t = cur; cur = nxt; nxt = t;
     }
     return 0;
 }
@@ -196,7 +229,7 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         }
         DX_TRY(accent_input(nullptr, p.ob, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
                             w.ae_pitch_b, w.pos_table, RT, nullptr, p.xb, rp, s));
-        for (int i = 0; i < 4; ++i) DX_TRY(fft_block_bf16(w.ae_blocks[i], p, RT, nullptr, 0, s));
+        DX_TRY(fft_stack_bf16(w.ae_blocks, p, RT, nullptr, 0, s));
         DX_TRY(masked_mean(nullptr, p.xb, rp, RT, accent_emb, s));
     }
     return 0;
@@ -241,10 +274,8 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     // 5. phoneme encoder
     DX_TRY(embed_symbols(a.symbols, w.symbols_embedding, w.n_symbols, w.pos_table, RL, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
-    for (int i = 0; i < 4; ++i) {
-        if (bf) DX_TRY(fft_block_bf16(w.pe_blocks[i], p, RL, a.film, i, s));
-        else DX_TRY(fft_block_f32(w.pe_blocks[i], p, RL, a.film, i, s));
-    }
+    if (bf) DX_TRY(fft_stack_bf16(w.pe_blocks, p, RL, a.film, 0, s));
+    else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.pe_blocks[i], p, RL, a.film, i, s));
     if (a.enc_out) DX_TRY(unpack_rows(bf ? nullptr : p.x, bf ? p.xb : nullptr, rp, RL, a.enc_out, s));
     // 6. length regulator → decoder input rows (x + P, masked)
     DX_TRY(lenreg_symbols(bf ? nullptr : p.x, bf ? p.xb : nullptr, rp, RL, a.durations_float, a.symbols_energy,
@@ -252,10 +283,8 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, a.weights_out, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
     // 7. frame decoder
-    for (int i = 0; i < 4; ++i) {
-        if (bf) DX_TRY(fft_block_bf16(w.fd_blocks[i], p, RT, a.film, 4 + i, s));
-        else DX_TRY(fft_block_f32(w.fd_blocks[i], p, RT, a.film, 4 + i, s));
-    }
+    if (bf) DX_TRY(fft_stack_bf16(w.fd_blocks, p, RT, a.film, 4, s));
+    else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.fd_blocks[i], p, RT, a.film, 4 + i, s));
     if (bf) {
         DX_REQUIRE(w.mel_w_bf, "bf16 mode: packed mel projection missing");
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, DX_MEL, 1, w.mel_w_bf, 128, 64, w.mel_b, 0, TC_EPI_F32, -1);

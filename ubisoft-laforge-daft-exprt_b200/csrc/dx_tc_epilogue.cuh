@@ -27,7 +27,9 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
         __syncwarp();
         if (lane == 0 && tempty != nullptr) ptx::mbar_arrive(tempty);
         if (r < total) {
-            float sum = 0.f;
+            // statistics are summed per 64-channel half and combined as (low + high): the order the fused block
+            // kernel uses (two threads per row), so both paths give identical bits
+            float sum_lo = 0.f, sum_hi = 0.f;
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
                 float4 b0 = reinterpret_cast<const float4*>(s_bias)[c * 2];
@@ -49,17 +51,19 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
                     if (g.relu) t = fmaxf(t, 0.f);
                     t += rr[e];
                     v[c * 8 + e] = t;
-                    sum += t;
+                    if (c < 8) sum_lo += t;
+                    else sum_hi += t;
                 }
             }
-            const float mean = sum * (1.f / 128.f);
-            float sq = 0.f;
+            const float mean = (sum_lo + sum_hi) * (1.f / 128.f);
+            float sq_lo = 0.f, sq_hi = 0.f;
 #pragma unroll
-            for (int i = 0; i < 128; ++i) {
-                const float d = v[i] - mean;
-                sq = fmaf(d, d, sq);
+            for (int i = 0; i < 64; ++i) {
+                const float d0 = v[i] - mean, d1 = v[64 + i] - mean;
+                sq_lo = fmaf(d0, d0, sq_lo);
+                sq_hi = fmaf(d1, d1, sq_hi);
             }
-            const float rstd = rsqrtf(sq * (1.f / 128.f) + 1e-5f);
+            const float rstd = rsqrtf((sq_lo + sq_hi) * (1.f / 128.f) + 1e-5f);
             const float* fp = g.film ? g.film + (int64_t)b_idx * g.film_stride : nullptr;
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
