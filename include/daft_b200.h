@@ -53,8 +53,7 @@ int64_t     dx_launch_count(void);
  * key 4: run the K = 128 linear layers in the generic conv-GEMM kernel instead of the weight-resident one;
  * key 5: launch without programmatic dependent launch (plain stream order between kernels);
  * key 6: run attention + output projection + LayerNorm as ONE kernel (both heads per CTA; measured slower);
- * key 8: timing experiments on the fused FFN kernel (bit 0 no weight copies, bit 1 no MMAs, bit 2 no Hs stores,
- *        bit 3 no TMEM loads; results are wrong, only the kernel time is meaningful). */
+ * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two. */
 int         dx_set_debug(int key, int value);
 
 /* Bring-up: while a device buffer (>= 2 KB) is set, the fused FFN kernel writes a clock64 timeline of its CTA 0

@@ -87,8 +87,6 @@ struct FfnParams {
     const float* b_qkv;
     __nv_bfloat16* qkv_out;
     Rows R;
-    int dbg;                    // timing experiments (debug knob 8): bit 0 = weight stages are not copied (arrive only),
-                                // bit 1 = issue no MMAs, bit 2 = no Hs stores, bit 3 = no TMEM loads in E1 (results are wrong)
     long long* trace;           // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer) or null
 };
 
@@ -97,6 +95,14 @@ struct FfnParams {
 //   epilog  +6 d1_full ok, +7 TMEM loaded (sub 1), +8 hs_empty[1] ok, +9 Hs stored + fenced (sub 1)
 // [2] d2_full ok (E2 start), [3] E2 done, [4] CTA done, [5] P0 A tile landed, [6] P0 accumulator ready, [7] P3 done
 #define FF_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
+
+// Timing experiments (results are wrong; only the kernel time is meaningful): compile with -DFF_EXPERIMENT=<bits>,
+// bit 0 = weight stages are not copied (arrive only), bit 1 = issue no MMAs, bit 2 = no Hs stores.  Compile time on
+// purpose: the MMA issuers are bound by the latency of their own instruction stream (tools/ring_bench.cu), so even a
+// uniform branch per MMA costs throughput.  profiles/r01d_ffn_timing_knobs.txt has the numbers.
+#ifndef FF_EXPERIMENT
+#define FF_EXPERIMENT 0
+#endif
 
 // global source of weight stage q of a tile, in MMA issue order: [W_out k 0,1] G1(0) { G1(c) G2(c-1) } G2(7) [W_qkv' (nt, k)]
 __device__ __forceinline__ const uint8_t* ff_stage_src(const FfnParams& p, int q, int n_p0) {
@@ -178,7 +184,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     // the first FF_WSTAGES weight stages are the same for every tile: fetch them now
     if (warp == 0 && ptx::elect_one()) {
         for (int s0 = 0; s0 < FF_WSTAGES; ++s0) {
-            if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s0]); continue; }
+            if (FF_EXPERIMENT & 1) { ptx::mbar_arrive(&w_full[s0]); continue; }
             ptx::mbar_expect_tx(&w_full[s0], FF_W_BYTES);
             ptx::bulk_g2s(sW + s0 * FF_W_BYTES, ff_stage_src(p, s0, n_p0), FF_W_BYTES, &w_full[s0]);
         }
@@ -235,7 +241,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                     if (wit < FF_WSTAGES) continue;          // fetched in the prologue
                     const int s = wit % FF_WSTAGES;
                     ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
-                    if (p.dbg & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
+                    if (FF_EXPERIMENT & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
                     ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
                     ptx::bulk_g2s(sW + s * FF_W_BYTES, ff_stage_src(p, q, n_p0), FF_W_BYTES, &w_full[s]);
                 }
@@ -259,24 +265,24 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             uint64_t* d2_full = &hb[9 * h + 6];
             uint64_t* d2_empty = &hb[9 * h + 7];
             uint64_t* y_full = &hb[9 * h + 8];
-            uint32_t wit = 0, tile_it = 0;
+            uint32_t tile_it = 0, w_phase = 0;
+            int s = 0;                                   // ring slot and phase of the next weight stage
             // one weight stage = 4 MMAs of this half: A at a_base + kk * a_step (K-major, LBO a_lbo), B = the stage
 #define FF_STAGE(a_base, a_step, a_lbo, d_tmem, acc_first, ...)                                                         \
             do {                                                                                                        \
-                const int s = wit % FF_WSTAGES;                                                                         \
-                ptx::mbar_wait(&w_full[s], (wit / FF_WSTAGES) & 1);                                                      \
+                ptx::mbar_wait(&w_full[s], w_phase);                                                                    \
                 ptx::tc_fence_after();                                                                                  \
                 if (ptx::elect_one()) {                                                                                 \
                     _Pragma("unroll") for (int kk = 0; kk < 4; ++kk) {                                                  \
                         const uint64_t da = ptx::make_desc((a_base) + kk * (a_step), (a_lbo), 128);                     \
                         const uint64_t db = ptx::make_desc(aW + s * FF_W_BYTES + kk * 2 * 2048, 2048, 128);             \
-                        if (!(p.dbg & 2)) ptx::mma_bf16((d_tmem), da, db, idesc, (acc_first) || kk != 0);               \
+                        if (!(FF_EXPERIMENT & 2)) ptx::mma_bf16((d_tmem), da, db, idesc, (acc_first) || kk != 0);     \
                     }                                                                                                   \
                     ptx::mma_commit(&w_empty[s]);                                                                       \
                     __VA_ARGS__;                                                                                        \
                 }                                                                                                       \
                 __syncwarp();                                                                                           \
-                ++wit;                                                                                                  \
+                if (++s == FF_WSTAGES) { s = 0; w_phase ^= 1; }                                                         \
             } while (0)
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
                 uint32_t u1 = tile_it * d1_uses, u2 = tile_it * d2_uses;       // accumulator use counters
@@ -301,6 +307,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         ptx::mbar_wait(d1_empty, (u1 & 1) ^ 1);
                         ptx::tc_fence_after();
                         if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
+#pragma unroll
                         for (int st = 0; st < 6; ++st) {
                             const int kh = st / 3, tap = st % 3;
                             FF_STAGE(aX + kh * 8 * 4096 + tap * 16, 2 * 4096, 4096, td1, st != 0, if (st == 5) ptx::mma_commit(d1_full));
@@ -312,6 +319,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
                         const int cc = c - 1;
                         const uint32_t k = tile_it * FF_NCH + cc;
+#pragma unroll
                         for (int st = 0; st < 6; ++st) {
                             const int sub = st / 3, tap = st % 3;
                             if (tap == 0) {
@@ -434,7 +442,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
                 ptx::mbar_wait(&hs_empty[part], (n & 1) ^ 1);        // G2(c-1, part) has finished reading this buffer
                 if (tile_it == 0) FF_TRACE(8 + 12 * c + 8);
-                if (!(p.dbg & 4))
+                if (!(FF_EXPERIMENT & 4))
                     ffn_e1_store(v, s_b1 + c * 128 + part * 64, hid_live, sHs + (h * 2 + part) * FF_HS_BYTES + j * 16, FF_HS_ROWS * 16);
                 ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
                 __syncwarp();
@@ -519,7 +527,6 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
         p.b_qkv = fuse->next->b_qkv;
         p.qkv_out = fuse->qkv_out;
     }
-    p.dbg = debug_knob(8);
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
     int64_t tiles = (R.cap + FF_OUT1 - 1) / FF_OUT1;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
