@@ -53,7 +53,8 @@ int64_t     dx_launch_count(void);
  * key 4: run the K = 128 linear layers in the generic conv-GEMM kernel instead of the weight-resident one;
  * key 5: launch without programmatic dependent launch (plain stream order between kernels);
  * key 6: run attention + output projection + LayerNorm as ONE kernel (both heads per CTA; measured slower);
- * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two. */
+ * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two;
+ * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch). */
 int         dx_set_debug(int key, int value);
 
 /* Bring-up: while a device buffer (>= 2 KB) is set, the fused FFN kernel writes a clock64 timeline of its CTA 0

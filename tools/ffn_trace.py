@@ -24,6 +24,8 @@ torch.cuda.synchronize()
 lib = _lib.load()
 buf = torch.zeros(256, dtype=torch.long, device="cuda")
 lib.dx_set_trace_buffer(buf.data_ptr(), buf.numel() * 8)
+if len(sys.argv) > 1:
+    lib.dx_set_debug(10, int(sys.argv[1]))      # which of the 12 block-tail launches (1-4 accent, 5-8 symbols, 9-12 decoder)
 model(batch)          # every FFN launch overwrites the trace: the last one (decoder block 3, frame stream) remains
 torch.cuda.synchronize()
 lib.dx_set_trace_buffer(None, 0)

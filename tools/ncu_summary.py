@@ -2,6 +2,7 @@
 
     python tools/ncu_summary.py launches gpurun_out/launches.csv  > profiles/rNN_launches.txt
     python tools/ncu_summary.py full gpurun_out/prof.ncu-rep      > profiles/rNN_<kernel>_full.txt
+    python tools/ncu_summary.py traffic gpurun_out/prof.ncu-rep profiles/rNN_<kernel>_full.txt   # updates profiles/ncu_traffic.json
 """
 import csv
 import subprocess
@@ -55,5 +56,24 @@ def full(path):
             print(f"{h:75s} {units[i]:14s} " + "  ".join(r[i] for r in data))
 
 
+def traffic(path, source):
+    """DRAM bytes per launch (read + write, averaged over the captured launches) → profiles/ncu_traffic.json,
+    which bench.py reports as roofline.traffic."""
+    import json
+    import os
+    txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(txt.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    ik, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = sum(float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]] for r in data)
+    name = data[0][ik].split("(")[0].replace("void ", "").split("<")[0].split("::")[-1]
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
+    cur = json.load(open(out)) if os.path.exists(out) else {}
+    cur[name] = {"dram_bytes_per_launch": tot / len(data), "captured_launches": len(data), "source": source}
+    json.dump(cur, open(out, "w"), indent=1, sort_keys=True)
+    print(name, cur[name])
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])

@@ -528,9 +528,13 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
         p.qkv_out = fuse->qkv_out;
     }
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
+    if (p.trace != nullptr && debug_knob(10) > 0) {       // knob 10 = n: trace only every n-th .. launch (n = 1..12 of a step)
+        static int n_traced = 0;
+        if ((n_traced++ % 12) + 1 != debug_knob(10)) p.trace = nullptr;
+    }
     int64_t tiles = (R.cap + FF_OUT1 - 1) / FF_OUT1;     // enough CTAs for the one-half-per-CTA mode of short streams
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
-    ProfScope prof("tc_ffn_fused", s);
+    ProfScope prof(fuse != nullptr && fuse->tag != nullptr ? fuse->tag : "tc_ffn_fused", s);
     DX_LAUNCH_PDL((ffn_tc_kernel), grid, FF_THREADS, FF_SMEM, s, p);
     DX_CHECK_LAUNCH();
     return 0;

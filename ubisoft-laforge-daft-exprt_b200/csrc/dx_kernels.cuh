@@ -40,6 +40,7 @@ struct FfnFuse {
     const __nv_bfloat16* x_in;
     const DxBlockWeights* next;
     __nv_bfloat16* qkv_out;
+    const char* tag;            // profiler tag (null: "tc_ffn_fused")
 };
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
              int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse = nullptr);

@@ -167,9 +167,13 @@ int frame2symbol(const int64_t* cumsum, const int64_t* in_len, const int64_t* ou
 // Pass 1 sums the column denominators; pass 2 recomputes p (cheaper than holding an L x 32 tile), writes the
 // weights coalesced along t and contracts in chunks of 32 symbols, skipping symbols whose 32 weights are all
 // exactly 0 (fp32 exp underflows beyond ~14.4 σ, so the contraction is banded without changing the result).
+// Symbols whose Gaussian cannot reach the tile at all (exponent below LR_ZERO_ARG at the nearest frame centre, where
+// expf returns exactly 0) are flagged once per tile: they cost no expf in either pass, and a 32-symbol chunk without
+// any flagged-in symbol only writes its zero weights (no barrier, no contraction).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int LR_FT = 32;
 constexpr float LR_LOG_SQRT_2PI = 0.91893853320467274178f;
+constexpr float LR_ZERO_ARG = -110.f;      // expf(x) == 0 exactly for x < -103.98; margin for rounding of the argument
 
 __device__ __forceinline__ float gauss_prob(float t_center, float mu, float sg, float log_sg) {
     const float d = t_center - mu;
@@ -194,6 +198,7 @@ lenreg_frames_kernel(const float* __restrict__ xs, Rows RL, Rows RT, const float
     float* s_den = s_part + 8 * LR_FT;  // [32]
     float* s_w = s_den + LR_FT;       // [32 l][32 t]
     int* s_any = reinterpret_cast<int*>(s_w + 32 * LR_FT);  // [32]
+    int* s_band = s_any + 32;         // [Lp + 32]: 1 = the symbol's Gaussian can be non-zero somewhere in this tile
 
     const int b = blockIdx.y;
     const int t0 = blockIdx.x * LR_FT;
@@ -205,12 +210,18 @@ lenreg_frames_kernel(const float* __restrict__ xs, Rows RL, Rows RT, const float
         s_mu[l] = mu[(int64_t)b * L + l];
         s_sg[l] = sg;
         s_lsg[l] = logf(sg);
+        // nearest frame centre of the tile to μ_l; the largest exponent any frame of the tile can see
+        const float m = s_mu[l];
+        const float dmin = fmaxf(fmaxf((float)t0 + 0.5f - m, m - ((float)t0 + (float)LR_FT - 0.5f)), 0.f);
+        s_band[l] = (-(dmin * dmin) / (2.f * sg * sg) - s_lsg[l] - LR_LOG_SQRT_2PI) >= LR_ZERO_ARG;
     }
+    for (int l = len_in + tid; l < Lp + 32; l += 256) s_band[l] = 0;
     __syncthreads();
     const float tc = (float)(t0 + lane) + 0.5f;
     // pass 1: denominators
     float part = 0.f;
-    for (int l = warp; l < len_in; l += 8) part += gauss_prob(tc, s_mu[l], s_sg[l], s_lsg[l]);
+    for (int l = warp; l < len_in; l += 8)
+        if (s_band[l]) part += gauss_prob(tc, s_mu[l], s_sg[l], s_lsg[l]);      // else exactly + 0.f
     s_part[warp * LR_FT + lane] = part;
     __syncthreads();
     if (tid < LR_FT) {
@@ -228,12 +239,21 @@ lenreg_frames_kernel(const float* __restrict__ xs, Rows RL, Rows RT, const float
     for (int i = 0; i < 16; ++i) acc[i] = 0.f;
     const int64_t rsL = RL.row_start[b];
     for (int l0 = 0; l0 < L; l0 += 32) {
+        if (__ballot_sync(0xffffffffu, s_band[l0 + lane]) == 0u) {
+            // no symbol of this chunk reaches the tile: its weights are exactly 0
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int l = l0 + warp * 4 + i;
+                if (l < L && t0 + lane < T) weights[((int64_t)b * L + l) * T + t0 + lane] = 0.f;
+            }
+            continue;
+        }
         // 8 warps x 4 symbols each: weights for (l, t0 + lane)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int ll = warp * 4 + i, l = l0 + ll;
             float wv = 0.f;
-            if (l < len_in) wv = gauss_prob(tc, s_mu[l], s_sg[l], s_lsg[l]) / den;
+            if (l < len_in && s_band[l]) wv = gauss_prob(tc, s_mu[l], s_sg[l], s_lsg[l]) / den;
             s_w[ll * LR_FT + lane] = wv;
             const int any = __any_sync(0xffffffffu, wv != 0.f);
             if (lane == 0) s_any[ll] = any;
@@ -276,7 +296,7 @@ int lenreg_frames(const float* xs, const Rows& RL, const Rows& RT, const float* 
                   const float* pos, float* weights, float* xo_f32, __nv_bfloat16* xo_bf, int64_t rows_phys_t,
                   cudaStream_t s) {
     const int L = RL.n_max;
-    const size_t smem = (size_t)(3 * ((L + 3) & ~3) + 8 * LR_FT + LR_FT + 32 * LR_FT) * sizeof(float) + 32 * sizeof(int);
+    const size_t smem = (size_t)(3 * ((L + 3) & ~3) + 8 * LR_FT + LR_FT + 32 * LR_FT) * sizeof(float) + (32 + ((L + 3) & ~3) + 32) * sizeof(int);
     DX_REQUIRE(smem <= 200 * 1024, "lenreg_frames: L_max=%d too large", L);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {

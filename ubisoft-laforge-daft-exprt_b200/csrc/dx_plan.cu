@@ -150,7 +150,7 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
 // FFN + LN2/FiLM + the next block's QKV projection; the stack's first QKV projection is its own launch.  The block
 // input and output alternate between p.xb and p.yb (neighbouring tiles read the input rows as residual halos).
 static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Rows& R, const float* film, int film_block0,
-                          cudaStream_t s) {
+                          const char* tag, cudaStream_t s) {
     if (debug_knob(9) || debug_knob(3) || debug_knob(6)) {
         for (int i = 0; i < 4; ++i) DX_TRY(fft_block_bf16(blocks[i], p, R, film, film_block0 + i, s));
         return 0;
@@ -170,6 +170,7 @@ static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Row
         f.attn = p.ob; f.x_in = cur;
         f.next = i < 3 ? &blocks[i + 1] : nullptr;
         f.qkv_out = i < 3 ? p.qkvb : nullptr;
+        f.tag = tag;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
         DX_TRY(ffn_bf16(nullptr, nxt, rp, bw, fp, 8 * 256, R, s, &f));
         __nv_bfloat16* t = cur; cur = nxt; nxt = t;
@@ -229,7 +230,7 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         }
         DX_TRY(accent_input(nullptr, p.ob, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
                             w.ae_pitch_b, w.pos_table, RT, nullptr, p.xb, rp, s));
-        DX_TRY(fft_stack_bf16(w.ae_blocks, p, RT, nullptr, 0, s));
+        DX_TRY(fft_stack_bf16(w.ae_blocks, p, RT, nullptr, 0, "tc_block_tail_frames", s));
         DX_TRY(masked_mean(nullptr, p.xb, rp, RT, accent_emb, s));
     }
     return 0;
@@ -274,7 +275,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     // 5. phoneme encoder
     DX_TRY(embed_symbols(a.symbols, w.symbols_embedding, w.n_symbols, w.pos_table, RL, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
-    if (bf) DX_TRY(fft_stack_bf16(w.pe_blocks, p, RL, a.film, 0, s));
+    if (bf) DX_TRY(fft_stack_bf16(w.pe_blocks, p, RL, a.film, 0, "tc_block_tail_symbols", s));
     else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.pe_blocks[i], p, RL, a.film, i, s));
     if (a.enc_out) DX_TRY(unpack_rows(bf ? nullptr : p.x, bf ? p.xb : nullptr, rp, RL, a.enc_out, s));
     // 6. length regulator → decoder input rows (x + P, masked)
@@ -283,7 +284,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, a.weights_out, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
     // 7. frame decoder
-    if (bf) DX_TRY(fft_stack_bf16(w.fd_blocks, p, RT, a.film, 4, s));
+    if (bf) DX_TRY(fft_stack_bf16(w.fd_blocks, p, RT, a.film, 4, "tc_block_tail_frames", s));
     else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.fd_blocks[i], p, RT, a.film, 4 + i, s));
     if (bf) {
         DX_REQUIRE(w.mel_w_bf, "bf16 mode: packed mel projection missing");

@@ -405,46 +405,58 @@ int zero_halos(const HaloList& hl, int64_t rows_phys, int64_t cap, cudaStream_t 
 // ---------------------------------------------------------------------------------------------------------
 // ln_apply_bf16: LayerNorm over C = 1024 channels of a channel-interleaved bf16 buffer, in place, using the per-row
 // sum / sum-of-squares the producing GEMM's epilogue accumulated (accent pre-net, model.py:655,662).
-// Thread ↔ (row, 8-channel chunk): 16-byte loads/stores, consecutive threads on consecutive rows.
+// Thread ↔ (row, LNA_CHUNKS consecutive 8-channel chunks): the row's liveness and statistics are loaded once and
+// reused for LNA_CHUNKS 16-byte loads/stores (all issued before the first use); consecutive threads on consecutive rows.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void ln_apply_bf16_kernel(__nv_bfloat16* __restrict__ x, int64_t rows_phys, int C,
-                                     const float* __restrict__ stats, const float* __restrict__ g,
-                                     const float* __restrict__ b, Rows R, int live_ext) {
+constexpr int LNA_CHUNKS = 16;
+
+__global__ void __launch_bounds__(256) ln_apply_bf16_kernel(__nv_bfloat16* __restrict__ x, int64_t rows_phys, int C,
+                                                            const float* __restrict__ stats, const float* __restrict__ g,
+                                                            const float* __restrict__ b, Rows R, int live_ext) {
     ptx::griddep_wait();      // PDL: predecessor complete + visible
     ptx::griddep_launch();    // let the next kernel start its prologue
     const int64_t total = R.row_start[R.B];
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int c = blockIdx.y;
+    const int c0 = blockIdx.y * LNA_CHUNKS;
     if (r >= total) return;
-    __nv_bfloat16* ptr = x + ((int64_t)c * rows_phys + DX_HALO + r) * 8;
+    __nv_bfloat16* ptr = x + ((int64_t)c0 * rows_phys + DX_HALO + r) * 8;
+    const int64_t cs = rows_phys * 8;
     if (!row_live(R, r, live_ext)) {
-        *reinterpret_cast<uint4*>(ptr) = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int i = 0; i < LNA_CHUNKS; ++i) *reinterpret_cast<uint4*>(ptr + i * cs) = make_uint4(0u, 0u, 0u, 0u);
         return;
     }
+    uint4 pk[LNA_CHUNKS];
+#pragma unroll
+    for (int i = 0; i < LNA_CHUNKS; ++i) pk[i] = *reinterpret_cast<const uint4*>(ptr + i * cs);
     const float4 s01 = reinterpret_cast<const float4*>(stats + r * (TC_STAT_TILES * 2))[0];
     const float4 s23 = reinterpret_cast<const float4*>(stats + r * (TC_STAT_TILES * 2))[1];
     const float mean = (((s01.x + s01.z) + s23.x) + s23.z) / (float)C;      // fixed summation order
     float var = (((s01.y + s01.w) + s23.y) + s23.w) / (float)C - mean * mean;
     var = fmaxf(var, 0.f);
     const float rstd = rsqrtf(var + 1e-5f);
-    uint4 pk = *reinterpret_cast<const uint4*>(ptr);
-    __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&pk);
-    const float4 g0 = reinterpret_cast<const float4*>(g)[c * 2], g1 = reinterpret_cast<const float4*>(g)[c * 2 + 1];
-    const float4 b0 = reinterpret_cast<const float4*>(b)[c * 2], b1 = reinterpret_cast<const float4*>(b)[c * 2 + 1];
-    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-        float v0 = (__low2float(h2[e]) - mean) * rstd * gg[2 * e] + bb[2 * e];
-        float v1 = (__high2float(h2[e]) - mean) * rstd * gg[2 * e + 1] + bb[2 * e + 1];
-        h2[e] = __floats2bfloat162_rn(v0, v1);
+    for (int i = 0; i < LNA_CHUNKS; ++i) {
+        const int c = c0 + i;
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&pk[i]);
+        const float4 g0 = reinterpret_cast<const float4*>(g)[c * 2], g1 = reinterpret_cast<const float4*>(g)[c * 2 + 1];
+        const float4 b0 = reinterpret_cast<const float4*>(b)[c * 2], b1 = reinterpret_cast<const float4*>(b)[c * 2 + 1];
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float v0 = (__low2float(h2[e]) - mean) * rstd * gg[2 * e] + bb[2 * e];
+            float v1 = (__high2float(h2[e]) - mean) * rstd * gg[2 * e + 1] + bb[2 * e + 1];
+            h2[e] = __floats2bfloat162_rn(v0, v1);
+        }
+        *reinterpret_cast<uint4*>(ptr + i * cs) = pk[i];
     }
-    *reinterpret_cast<uint4*>(ptr) = pk;
 }
 
 int ln_apply_bf16(__nv_bfloat16* x, int64_t rows_phys, int C, const float* stats, const float* g, const float* b,
                   const Rows& R, int live_ext, cudaStream_t s) {
-    dim3 grid((unsigned)((R.cap + 255) / 256), (unsigned)(C / 8));
+    DX_REQUIRE(C % (8 * LNA_CHUNKS) == 0, "ln_apply_bf16: C=%d must be a multiple of %d", C, 8 * LNA_CHUNKS);
+    dim3 grid((unsigned)((R.cap + 255) / 256), (unsigned)(C / (8 * LNA_CHUNKS)));
     ProfScope prof("ln_apply_bf16", s);
     DX_LAUNCH_PDL((ln_apply_bf16_kernel), grid, 256, 0, s, x, rows_phys, C, stats, g, b, R, live_ext);
     DX_CHECK_LAUNCH();
