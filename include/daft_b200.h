@@ -52,7 +52,6 @@ int64_t     dx_launch_count(void);
  * key 3: run the FFN as two GEMM launches instead of the fused kernel (A/B testing);
  * key 4: run the K = 128 linear layers in the generic conv-GEMM kernel instead of the weight-resident one;
  * key 5: launch without programmatic dependent launch (plain stream order between kernels);
- * key 6: run attention + output projection + LayerNorm as ONE kernel (both heads per CTA; measured slower);
  * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two;
  * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch). */
 int         dx_set_debug(int key, int value);

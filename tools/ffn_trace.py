@@ -23,6 +23,7 @@ for _ in range(3):
 torch.cuda.synchronize()
 lib = _lib.load()
 buf = torch.zeros(256, dtype=torch.long, device="cuda")
+buf[250] = -(1 << 62)
 lib.dx_set_trace_buffer(buf.data_ptr(), buf.numel() * 8)
 if len(sys.argv) > 1:
     lib.dx_set_debug(10, int(sys.argv[1]))      # which of the 12 block-tail launches (1-4 accent, 5-8 symbols, 9-12 decoder)
@@ -46,6 +47,8 @@ if t[7]:
     print(f"P3 done         {t[7] - t0:8d}")
 print(f"CTA done        {t[4] - t0:8d}")
 
+if t[251]:
+    print(f"attention kernel (last launch): first CTA start to last CTA end {(t[251] + t[250]) / 1000:.2f} us, {t[252]} working CTAs")
 print("attention CTA (0,0,0) of the last launch (decoder block 3, longest utterance, head 0, q tile 0)")
 a0 = t[128]
 print(f"Q landed {t[129] - a0}   end {t[130] - a0}")

@@ -115,16 +115,11 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
         g.out_bf = p.qkvb; g.tag = "tc_qkv";
         DX_TRY(linear_bf16(g, R, s));
     }
-    {   // attention, then out-proj + residual + LN + mask.  The single fused kernel (debug knob 6) is correct but
-        // slower at these sizes: both heads per CTA halves the CTA count and doubles the longest CTA.
+    {   // attention, then out-proj + residual + LN + mask
         TcGemmArgs g = tc_args(p.ob, rp, DX_D, DX_D, 1, bw.w_out_bf, 128, 64, bw.b_out, 0, TC_EPI_LN, 0);
         g.out_bf = p.yb; g.res = p.xb; g.ln_g = bw.ln1_g; g.ln_b = bw.ln1_b; g.tag = "tc_outproj_ln";
-        if (!debug_knob(6)) {
-            DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
-            DX_TRY(linear_bf16(g, R, s));
-        } else {
-            DX_TRY(attention_block_bf16(p.qkvb, rp, g, R, s));
-        }
+        DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
+        DX_TRY(linear_bf16(g, R, s));
     }
     if (!debug_knob(3)) {
         const float* fp = film ? film + film_block * 256 : nullptr;
@@ -151,7 +146,7 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
 // input and output alternate between p.xb and p.yb (neighbouring tiles read the input rows as residual halos).
 static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Rows& R, const float* film, int film_block0,
                           const char* tag, cudaStream_t s) {
-    if (debug_knob(9) || debug_knob(3) || debug_knob(6)) {
+    if (debug_knob(9) || debug_knob(3)) {
         for (int i = 0; i < 4; ++i) DX_TRY(fft_block_bf16(blocks[i], p, R, film, film_block0 + i, s));
         return 0;
     }
