@@ -65,3 +65,52 @@ def build_reference_model(hp, state_dict):
     model.load_state_dict(state_dict, strict=True)
     model.eval()
     return model
+
+
+def import_reference_generate():
+    """Return the reference's ``daft_exprt.generate`` module (the synthesis driver).
+
+    ``generate.py:17`` pulls in the text cleaners, whose third-party imports (``unidecode``, ``inflect``) are not installed
+    here and are not on the tensor path → stubbed like librosa above."""
+    import_reference_model()
+    import warnings
+    for name in ("unidecode", "inflect"):
+        try:
+            __import__(name)
+        except Exception:
+            m = _stub(name)
+            m.__getattr__ = lambda attr: (lambda *a, **k: None)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")          # the reference's regex literals raise SyntaxWarning on 3.12
+        import daft_exprt.generate as ref_generate
+    return ref_generate
+
+
+class _ZeroVocoder:
+    """Stands in for HiFi-GAN (no weights offline): ``generate.py:327`` only needs ``infer``."""
+
+    def infer(self, mel_spec):
+        import numpy as np
+        return np.zeros(mel_spec.shape[1] * 256, dtype=np.float32)
+
+
+def run_reference_generate(model, hp, output_dir, batch=None, **kw):
+    """Run the reference's ``generate_batch_mel_specs`` (``batch=True``) or ``generate_mel_specs`` on CPU.
+
+    The reference moves every tensor with ``.cuda(gpu, non_blocking=True)`` (``generate.py:205-210,273-278``); there is no
+    GPU here, so ``torch.Tensor.cuda`` is replaced by the identity for the duration of the call (the model is on the CPU).
+    Plotting (``generate.py:324-326``, matplotlib absent) is replaced by a no-op and the vocoder by zeros; neither touches
+    the returned predictions."""
+    import torch
+    G = import_reference_generate()
+    saved_cuda, saved_plot = torch.Tensor.cuda, G.plot_2d_data
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    G.plot_2d_data = lambda *a, **k: None
+    try:
+        with torch.no_grad():
+            if batch:
+                return G.generate_batch_mel_specs(model=model, output_dir=output_dir, hparams=hp, n_jobs=1,
+                                                  vocoder=_ZeroVocoder(), **kw)
+            return G.generate_mel_specs(model=model, output_dir=output_dir, hparams=hp, vocoder=_ZeroVocoder(), **kw)
+    finally:
+        torch.Tensor.cuda, G.plot_2d_data = saved_cuda, saved_plot

@@ -10,8 +10,21 @@ from types import SimpleNamespace
 import copy
 
 
+def english_symbols():
+    """The reference's English symbol table (``symbols.py:16-40``, selected at ``hparams.py:178-191``): pad, EOS, whitespace,
+    punctuation, then the stressed Arpabet inventory in alphabetical order of the base phone (vowels carry stress 0-2)."""
+    vowels = {"AA", "AE", "AH", "AO", "AW", "AY", "EH", "ER", "EY", "IH", "IY", "OW", "OY", "UH", "UW"}
+    consonants = {"B", "CH", "D", "DH", "F", "G", "HH", "JH", "K", "L", "M", "N", "NG", "P", "R", "S", "SH", "T", "TH", "V",
+                  "W", "Y", "Z", "ZH"}
+    phones = []
+    for base in sorted(vowels | consonants):
+        phones += [base + str(k) for k in range(3)] if base in vowels else [base]
+    return list("_~ ,.!?") + phones
+
+
 def default_hparams(**overrides):
     hp = SimpleNamespace(
+        symbols=english_symbols(),
         n_mel_channels=80,
         n_symbols=76,
         n_speakers=2,

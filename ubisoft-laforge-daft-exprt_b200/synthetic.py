@@ -151,3 +151,56 @@ class UtteranceStream:
 
     def lengths(self):
         return stream_lengths(self.hp, self.n, self.seed, **self.kw)
+
+
+# ----------------------------------------------------------------------------------------------
+# synthesis requests (the driver's inputs, reference generate.py:333-345)
+# ----------------------------------------------------------------------------------------------
+def synthesis_request(hp, n, lmin, lmax, seed, pitch_transform="add", with_factors=True, zero_frac=0.15):
+    """``n`` utterances in the form ``generate_mel_specs`` takes them: phonemised sentences (words = lists of phones,
+    boundaries = single symbols, EOS last; ``generate.py:60-77``), optional per-symbol factors, speaker ids, file names, the
+    external prosody entries (``generate.py:222-243``: symbols, durations in frames, raw energy / log-pitch with zeros for
+    silent / unvoiced symbols), ECAPA embeddings and accent embeddings.  Returned as keyword arguments of
+    ``generate_mel_specs`` (minus model / output_dir / hparams)."""
+    g = torch.Generator().manual_seed(int(seed))
+    phones = [s for s in hp.symbols[7:]]
+    sentences, prosody, dur_f, en_f, pi_f = [], [], [], [], []
+    for i in range(n):
+        L = int(torch.randint(lmin, lmax + 1, (1,), generator=g))
+        sent, flat = [], []
+        while len(flat) < L - 1:
+            w = min(int(torch.randint(1, 6, (1,), generator=g)), L - 1 - len(flat))
+            word = [phones[int(k)] for k in torch.randint(0, len(phones), (w,), generator=g)]
+            sent.append(word)
+            flat += word
+            if len(flat) < L - 1:
+                bound = " ,.!?"[int(torch.randint(0, 5, (1,), generator=g)) if int(torch.randint(0, 4, (1,), generator=g)) == 0 else 0]
+                sent.append(bound)
+                flat.append(bound)
+        sent.append("~")
+        flat.append("~")
+        L = len(flat)
+        silent = torch.tensor([s in " ,.!?~" for s in flat])
+        frames = torch.randint(1, 10, (L,), generator=g).float() + torch.rand(L, generator=g) * 0.4
+        drop = torch.rand(L, generator=g) < zero_frac
+        frames = torch.where(silent & drop, torch.zeros(L), frames)
+        energy = (torch.rand(L, generator=g) * 3.0 + 0.2) * (frames > 0)
+        pitch = (5.0 + 0.3 * torch.randn(L, generator=g)) * (frames > 0) * (~silent) * (torch.rand(L, generator=g) > zero_frac)
+        sentences.append(sent)
+        prosody.append({"symbols": flat, "durations_frames": frames.tolist(), "energy": energy.tolist(),
+                        "pitch": pitch.tolist()})
+        if with_factors and i % 2 == 0:
+            dur_f.append((0.8 + 0.4 * torch.rand(L, generator=g)).tolist())
+            en_f.append((0.9 + 0.2 * torch.rand(L, generator=g)).tolist())
+            pi_f.append(((torch.rand(L, generator=g) - 0.5) * 40.0).tolist() if pitch_transform == "add"
+                        else (0.9 + 0.2 * torch.rand(L, generator=g)).tolist())
+        else:
+            dur_f.append(None)
+            en_f.append(None)
+            pi_f.append(None)
+    return dict(
+        sentences=sentences, file_names=[f"utt{i:04d}" for i in range(n)],
+        speaker_ids=torch.randint(0, hp.n_speakers, (n,), generator=g).tolist(),
+        dur_factors=dur_f, energy_factors=en_f, pitch_factors=[pitch_transform, pi_f], external_prosody=prosody,
+        external_embeddings=torch.randn(n, getattr(hp, "external_emb_dim", 192), generator=g),
+        external_accent_emb=torch.randn(n, hp.phoneme_encoder["hidden_embed_dim"], generator=g))
