@@ -57,5 +57,5 @@ print(" step " + " ".join(f"{n:>9s}" for n in an))
 for j in range(8):
     row = [t[132 + 10 * j + i] for i in range(9)]
     if not any(row):
-        break
+        continue
     print(f"{j:5d} " + " ".join(f"{(v - a0) if v else 0:9d}" for v in row))

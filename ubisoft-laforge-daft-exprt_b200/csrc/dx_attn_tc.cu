@@ -27,14 +27,16 @@
 namespace dx {
 
 constexpr int ATC_BQ = 128, ATC_BK = 64;
-constexpr int ATC_THREADS = 320;                       // producer, issuer, 2 x 4 softmax warps
-constexpr int ATC_KV_STAGES = 3;                       // S runs two tiles ahead of P·V: tiles g, g+1, g+2 are live
+constexpr int ATC_THREADS = 352;                       // producer, 2 issuers (one per softmax group), 2 x 4 softmax warps
+constexpr int ATC_SM_WARP0 = 3;                        // first softmax warp
+constexpr int ATC_K_STAGES = 3;                        // K tile: live from its load to the end of its S MMAs (short)
+constexpr int ATC_V_STAGES = 4;                        // V tile: live until its P·V has completed; tiles g .. g+3 are in flight
 constexpr uint32_t ATC_Q_BYTES = 8 * 128 * 16;         // 16 KB: [8 dh chunk][128 row][8]
 constexpr uint32_t ATC_K_BYTES = 8 * ATC_BK * 16;      // 8 KB:  [8 dh chunk][64 key][8]
 constexpr uint32_t ATC_P_BYTES = 8 * 128 * 16;         // 16 KB: [8 key chunk][128 row][8]
 constexpr uint32_t ATC_TMEM_COLS = 256;                // S0 | S1 | O_A | O_B
-constexpr uint32_t ATC_NBARS = 1 + 2 * ATC_KV_STAGES + 2 + 2 + 2 + 1;
-constexpr uint32_t ATC_SMEM = ATC_Q_BYTES + ATC_KV_STAGES * 2 * ATC_K_BYTES + 2 * ATC_P_BYTES + 2 * 128 * 8 + ATC_NBARS * 8 + 16;
+constexpr uint32_t ATC_NBARS = 1 + 2 * ATC_K_STAGES + 2 * ATC_V_STAGES + 2 + 2 + 2 + 2 + 1;
+constexpr uint32_t ATC_SMEM = ATC_Q_BYTES + (ATC_K_STAGES + ATC_V_STAGES) * ATC_K_BYTES + 2 * ATC_P_BYTES + 2 * 128 * 8 + ATC_NBARS * 8 + 16;
 constexpr float ATC_LAZY = 8.f;                        // raise the exponent reference only beyond this margin
 
 struct AtcParams {
@@ -44,6 +46,7 @@ struct AtcParams {
     Rows R;
     uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
     long long* trace;           // bring-up: clock64 timeline of CTA (0,0,0) (dx_set_trace_buffer) or null
+    int trace_ctas;             // > 0: the buffer also holds [256 + 4 i ..] = (start ns, end ns, SM id, K/V tiles) of CTA i
 };
 // timeline slots: [128] kernel start, [129] Q landed, [130] end; per K/V tile g < 8 (base 132 + 10 g):
 // issuer +0 kv_full ok, +1 S issued, +2 p_full ok, +3 PV issued;  softmax +4 s_full ok, +5 max done, +6 P stored
@@ -62,33 +65,48 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         atomicMax(reinterpret_cast<long long*>(p.trace) + 250, -t);
         atomicAdd(reinterpret_cast<unsigned long long*>(p.trace) + 252, 1ull);
+        const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (cta < p.trace_ctas) {
+            uint32_t smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            p.trace[256 + 4 * cta] = t;
+            p.trace[256 + 4 * cta + 2] = smid;
+            p.trace[256 + 4 * cta + 3] = (len + ATC_BK - 1) / ATC_BK;
+        }
     }
     const int64_t rs = p.R.row_start[b];
     const int n_kv = (len + ATC_BK - 1) / ATC_BK;
     const int h = (int)blockIdx.y;
 
     uint8_t* sQ = at_smem;
-    uint8_t* sKV = sQ + ATC_Q_BYTES;                    // ATC_KV_STAGES x (K | V)
-    uint8_t* sP = sKV + ATC_KV_STAGES * 2 * ATC_K_BYTES;  // 2 buffers
+    uint8_t* sK = sQ + ATC_Q_BYTES;                     // K ring
+    uint8_t* sV = sK + ATC_K_STAGES * ATC_K_BYTES;      // V ring
+    uint8_t* sP = sV + ATC_V_STAGES * ATC_K_BYTES;      // 2 buffers
     float2* s_ml = reinterpret_cast<float2*>(sP + 2 * ATC_P_BYTES);      // [2 group][128 row] (m_ref, l) for the merge
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_ml + 2 * 128);
     uint64_t* q_full = bars;                            // 1
-    uint64_t* kv_full = bars + 1;                       // [ATC_KV_STAGES]
-    uint64_t* kv_empty = kv_full + ATC_KV_STAGES;       // [ATC_KV_STAGES]  P·V of the tile has completed
-    uint64_t* s_full = kv_empty + ATC_KV_STAGES;        // [2]  S buffer written
+    uint64_t* k_full = bars + 1;                        // [ATC_K_STAGES]
+    uint64_t* k_empty = k_full + ATC_K_STAGES;          // [ATC_K_STAGES]  S of the tile has completed
+    uint64_t* v_full = k_empty + ATC_K_STAGES;          // [ATC_V_STAGES]
+    uint64_t* v_empty = v_full + ATC_V_STAGES;          // [ATC_V_STAGES]  P·V of the tile has completed
+    uint64_t* s_full = v_empty + ATC_V_STAGES;          // [2]  S buffer written
     uint64_t* p_full = s_full + 2;                      // [2]  P buffer written (and S buffer consumed, O rescaled)
     uint64_t* pv_done = p_full + 2;                     // [2]  P·V reading P buffer has completed
-    uint64_t* o_done = pv_done + 2;
+    uint64_t* s_free = pv_done + 2;                     // [2]  the group holds S in registers: the next S may overwrite the buffer
+    uint64_t* o_done = s_free + 2;                      // both groups' last P·V have completed
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + ATC_NBARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp == 1 || warp == 2 || warp == 6)) ? p.trace : nullptr;
+    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && (warp == 1 || warp == ATC_SM_WARP0)) ? p.trace : nullptr;
     if (warp == 1) AT_TRACE(128);
     if (threadIdx.x == 0) {
         ptx::mbar_init(q_full, 1);
-        for (int i = 0; i < ATC_KV_STAGES; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 4); ptx::mbar_init(&pv_done[i], 1); }
-        ptx::mbar_init(o_done, 1);
+        for (int i = 0; i < ATC_K_STAGES; ++i) { ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&k_empty[i], 1); }
+        for (int i = 0; i < ATC_V_STAGES; ++i) { ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&v_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 4); ptx::mbar_init(&pv_done[i], 1); ptx::mbar_init(&s_free[i], 4);
+        }
+        ptx::mbar_init(o_done, 2);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<ATC_TMEM_COLS>(tmem_ptr);
@@ -104,82 +122,91 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
             ptx::mbar_expect_tx(q_full, ATC_Q_BYTES);
             for (int c = 0; c < 8; ++c)       // Q occupies qkv chunks 0..15: 0-7 = head 0, 8-15 = head 1
                 ptx::bulk_g2s(sQ + c * 2048, p.qkv + ((int64_t)(h * 8 + c) * p.rows_phys + DX_HALO + rs + q0) * 8, 2048, q_full);
-            int st = 0;
-            uint32_t ph = 0;
             for (int g = 0; g < n_kv; ++g) {
-                ptx::mbar_wait(&kv_empty[st], ph ^ 1);
-                uint8_t* sk = sKV + (size_t)st * 2 * ATC_K_BYTES;
-                uint8_t* sv = sk + ATC_K_BYTES;
-                ptx::mbar_expect_tx(&kv_full[st], 2 * ATC_K_BYTES);
+                const int ks = g % ATC_K_STAGES, vs = g % ATC_V_STAGES;
                 const int64_t krow = DX_HALO + rs + (int64_t)g * ATC_BK;
-                for (int c = 0; c < 8; ++c) {
-                    ptx::bulk_g2s(sk + c * 1024, p.qkv + ((int64_t)(16 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &kv_full[st]);
-                    ptx::bulk_g2s(sv + c * 1024, p.qkv + ((int64_t)(32 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &kv_full[st]);
-                }
-                if (++st == ATC_KV_STAGES) { st = 0; ph ^= 1; }
+                ptx::mbar_wait(&k_empty[ks], ((uint32_t)(g / ATC_K_STAGES) & 1) ^ 1);
+                ptx::mbar_expect_tx(&k_full[ks], ATC_K_BYTES);
+                for (int c = 0; c < 8; ++c)
+                    ptx::bulk_g2s(sK + (size_t)ks * ATC_K_BYTES + c * 1024, p.qkv + ((int64_t)(16 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &k_full[ks]);
+                ptx::mbar_wait(&v_empty[vs], ((uint32_t)(g / ATC_V_STAGES) & 1) ^ 1);
+                ptx::mbar_expect_tx(&v_full[vs], ATC_K_BYTES);
+                for (int c = 0; c < 8; ++c)
+                    ptx::bulk_g2s(sV + (size_t)vs * ATC_K_BYTES + c * 1024, p.qkv + ((int64_t)(32 + h * 8 + c) * p.rows_phys + krow) * 8, 1024, &v_full[vs]);
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer.  idesc_s: M=128, N=64, A/B K-major.  idesc_o: B MN-major (bit 16) ==========
+    } else if (warp <= 2) {
+        // ===================== MMA issuers, one per softmax group (warp 1: even tiles, warp 2: odd tiles) =============
+        // A single issuer thread needs ~1100 cycles per tile (mbarrier waits ~170 each, 8 MMAs + 4 commits) and was the
+        // CTA's bottleneck (profiles/r01f_attn_cta_times.txt); each group's chain S -> softmax -> P·V is private.
+        // idesc_s: M=128, N=64, A/B K-major.  idesc_o: B MN-major (bit 16)
+        const int grp = warp - 1;
         constexpr uint32_t idesc_s = ptx::make_idesc_bf16(128, 64);
         constexpr uint32_t idesc_o = ptx::make_idesc_bf16(128, 64) | (1u << 16);
-        const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP), aKV = ptx::smem_u32(sKV);
-        int st_s = 0;                       // ring stage of the next S tile
-        uint32_t ph_s = 0;
+        const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP) + grp * ATC_P_BYTES, aK0 = ptx::smem_u32(sK), aV0 = ptx::smem_u32(sV);
+        const uint32_t t_s = tm_s + 64 * grp, t_o = tm_o + 64 * grp;
         auto issue_s = [&](int g) {
-            ptx::mbar_wait(&kv_full[st_s], ph_s);
+            const int st = g % ATC_K_STAGES;
+            ptx::mbar_wait(&k_full[st], (uint32_t)(g / ATC_K_STAGES) & 1);
             ptx::tc_fence_after();
             if (g < 8) AT_TRACE(132 + 10 * g + 0);
             if (ptx::elect_one()) {
-                const uint32_t aK = aKV + (uint32_t)st_s * 2 * ATC_K_BYTES;
+                const uint32_t aK = aK0 + (uint32_t)st * ATC_K_BYTES;
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {   // dh = 64 = 4 x 16
                     const uint64_t da = ptx::make_desc(aQ + kk * 2 * 2048, 2048, 128);
                     const uint64_t db = ptx::make_desc(aK + kk * 2 * 1024, 1024, 128);
-                    ptx::mma_bf16(tm_s + 64 * (g & 1), da, db, idesc_s, kk != 0);
+                    ptx::mma_bf16(t_s, da, db, idesc_s, kk != 0);
                 }
-                ptx::mma_commit(&s_full[g & 1]);
+                ptx::mma_commit(&k_empty[st]);
+                ptx::mma_commit(&s_full[grp]);
             }
             __syncwarp();
             if (g < 8) AT_TRACE(132 + 10 * g + 1);
-            if (++st_s == ATC_KV_STAGES) { st_s = 0; ph_s ^= 1; }
         };
-        ptx::mbar_wait(q_full, 0);
-        AT_TRACE(129);
-        issue_s(0);
-        if (n_kv > 1) issue_s(1);
-        int st_v = 0;
-        for (int g = 0; g < n_kv; ++g) {
-            ptx::mbar_wait(&p_full[g & 1], (g >> 1) & 1);      // P_g in smem, S_g consumed, O rescaled if needed
-            ptx::tc_fence_after();
-            if (g < 8) AT_TRACE(132 + 10 * g + 2);
-            if (ptx::elect_one()) {
-                const uint32_t aV = aKV + (uint32_t)st_v * 2 * ATC_K_BYTES + ATC_K_BYTES;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {   // 64 keys = 4 x 16
-                    const uint64_t da = ptx::make_desc(aP + (g & 1) * ATC_P_BYTES + kk * 2 * 2048, 2048, 128);
-                    const uint64_t db = ptx::make_desc(aV + kk * 256, p.v_lbo, p.v_sbo);
-                    ptx::mma_bf16(tm_o + 64 * (g & 1), da, db, idesc_o, g >= 2 || kk != 0);
+        if (grp < n_kv) {
+            ptx::mbar_wait(q_full, 0);
+            AT_TRACE(129);
+            issue_s(grp);
+            uint32_t it = 0;
+            for (int g = grp; g < n_kv; g += 2, ++it) {
+                if (g + 2 < n_kv) {
+                    ptx::mbar_wait(&s_free[grp], it & 1);       // S_g is in the group's registers
+                    ptx::tc_fence_after();
+                    issue_s(g + 2);
                 }
-                ptx::mma_commit(&kv_empty[st_v]);
-                ptx::mma_commit(&pv_done[g & 1]);
-                if (g == n_kv - 1) ptx::mma_commit(o_done);
+                const int st = g % ATC_V_STAGES;
+                ptx::mbar_wait(&v_full[st], (uint32_t)(g / ATC_V_STAGES) & 1);
+                ptx::mbar_wait(&p_full[grp], it & 1);           // P_g in smem, O rescaled if needed
+                ptx::tc_fence_after();
+                if (g < 8) AT_TRACE(132 + 10 * g + 2);
+                if (ptx::elect_one()) {
+                    const uint32_t aV = aV0 + (uint32_t)st * ATC_K_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {   // 64 keys = 4 x 16
+                        const uint64_t da = ptx::make_desc(aP + kk * 2 * 2048, 2048, 128);
+                        const uint64_t db = ptx::make_desc(aV + kk * 256, p.v_lbo, p.v_sbo);
+                        ptx::mma_bf16(t_o, da, db, idesc_o, it != 0 || kk != 0);
+                    }
+                    ptx::mma_commit(&v_empty[st]);
+                    ptx::mma_commit(&pv_done[grp]);
+                    if (g + 2 >= n_kv) ptx::mma_commit(o_done);
+                }
+                __syncwarp();
+                if (g < 8) AT_TRACE(132 + 10 * g + 3);
             }
-            __syncwarp();
-            if (g < 8) AT_TRACE(132 + 10 * g + 3);
-            if (++st_v == ATC_KV_STAGES) st_v = 0;
-            if (g + 2 < n_kv) issue_s(g + 2);      // into the S buffer tile g has just released
+        } else if (lane == 0) {
+            ptx::mbar_arrive(o_done);                           // a group without tiles (n_kv == 1)
         }
     } else {
         // ===================== softmax: two groups of 4 warps on alternating tiles; thread ↔ query row ================
-        const int grp = (warp - 2) >> 2;                    // 0: tiles 0, 2, 4, ...   1: tiles 1, 3, 5, ...
+        const int grp = (warp - ATC_SM_WARP0) >> 2;         // 0: tiles 0, 2, 4, ...   1: tiles 1, 3, 5, ...
         const int lane_grp = warp & 3;
         const int row = lane_grp * 32 + lane;
         const uint32_t lane_off = (uint32_t)(lane_grp * 32) << 16;
         const uint32_t t_s = tm_s + 64 * grp + lane_off;
         const uint32_t t_o = tm_o + 64 * grp + lane_off;
         uint8_t* sPg = sP + grp * ATC_P_BYTES;
-        if (grp != 0 && warp != 6) tr = nullptr;
         const float sl2 = 0.125f * 1.4426950408889634f;   // d^-0.5 * log2(e)
         float m_ref = -INFINITY, l = 0.f;
         for (int g = grp; g < n_kv; g += 2) {
@@ -245,28 +272,48 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
             }
             float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
             {
-                // pass B: the second 32-column load is in flight while the first half is processed
+                // pass B: the second 32-column load is in flight while the first half is processed; once it has landed
+                // the S buffer is handed back to the issuer (S of the group's next tile overlaps the rest of this pass)
                 float va[32], vb[32];
                 ptx::tmem_ld32(t_s, va);
                 ptx::tmem_ld_wait_dep(va);
                 ptx::tmem_ld32(t_s + 32, vb);
 #pragma unroll
                 for (int q = 0; q < 2; ++q) {
-                    if (q == 1) ptx::tmem_ld_wait_dep(vb);
+                    if (q == 1) {
+                        ptx::tmem_ld_wait_dep(vb);
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(&s_free[grp]);
+                    }
                     const float* v = q == 0 ? va : vb;
+                    if (full) {
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        __align__(16) __nv_bfloat162 o2[4];
-                        float pe[8];
+                        for (int c = 0; c < 4; ++c) {
+                            __align__(16) __nv_bfloat162 o2[4];
+                            float pe[8];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            pe[e] = ptx::ex2_approx(fmaf(v[c * 8 + e], sl2, -m_ref));
-                            if (!full && q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
+                            for (int e = 0; e < 8; ++e) pe[e] = ptx::ex2_approx(fmaf(v[c * 8 + e], sl2, -m_ref));
+                            ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
+                            *reinterpret_cast<uint4*>(sPg + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
                         }
-                        ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+                    } else {
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
-                        *reinterpret_cast<uint4*>(sPg + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                        for (int c = 0; c < 4; ++c) {
+                            __align__(16) __nv_bfloat162 o2[4];
+                            float pe[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                pe[e] = ptx::ex2_approx(fmaf(v[c * 8 + e], sl2, -m_ref));
+                                if (q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
+                            }
+                            ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
+                            *reinterpret_cast<uint4*>(sPg + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
+                        }
                     }
                 }
             }
@@ -312,7 +359,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         }
         ptx::tc_fence_before();
     }
-    if (warp == 2) AT_TRACE(130);
+    if (warp == ATC_SM_WARP0) AT_TRACE(130);
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -323,6 +370,8 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         atomicMax(reinterpret_cast<long long*>(p.trace) + 251, t);
+        const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (cta < p.trace_ctas) p.trace[256 + 4 * cta + 1] = t;
     }
 }
 
@@ -362,9 +411,11 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
         static int n_traced = 0;
         if ((n_traced++ % 12) + 1 != debug_knob(10)) p.trace = nullptr;
     }
+    dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
+    const size_t n_cta = (size_t)grid.x * grid.y * grid.z;
+    p.trace_ctas = (p.trace != nullptr && trace_buffer((256 + 4 * n_cta) * sizeof(long long)) != nullptr) ? (int)n_cta : 0;
     p.v_lbo = 128; p.v_sbo = ATC_BK * 16;
     if (debug_knob(1)) { p.v_lbo = ATC_BK * 16; p.v_sbo = 128; }
-    dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_tc", s);
     DX_LAUNCH_PDL((attention_tc_kernel), grid, ATC_THREADS, ATC_SMEM, s, p);
     DX_CHECK_LAUNCH();
