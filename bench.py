@@ -414,7 +414,7 @@ def main():
         d_in = tuple(t.to(dev) for t in inp)
         ee_d, ae_d = ee.to(dev), ae.to(dev)
         lats = []
-        for i in range(60):
+        for i in range(1010):                   # median over >= 1000 single-utterance calls
             d_pros = {k: v.to(dev) for k, v in pros.items()}
             torch.cuda.synchronize()
             t0 = time.perf_counter()
@@ -480,6 +480,35 @@ def main():
                                                "what": "same GPU model; per-item collate / prosody loops, pageable H2D, 8 blocking .cpu() reads (oracle restatement of generate.py)"},
                   "timing": "host wall clock, median of 5 after 1 warm-up, cuda synchronize on both sides; results compared bit for bit"}
 
+    # ---- the like-for-like GPU bar: the oracle port = the reference's torch ops, run eagerly in fp32 on
+    # this same B200 (the reference itself cannot travel to the box; the port is pinned against it)
+    eager = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import daft_oracle as O
+        tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = False
+        sd_dev = {k: v.to(dev) for k, v in sd.items()}
+        with torch.device(dev), torch.no_grad():
+            for _ in range(2):
+                O.forward(sd_dev, hp, tuple(t.clone() for t in dev_batch))
+            torch.cuda.synchronize()
+            reps = 5
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                eo = O.forward(sd_dev, hp, tuple(t.clone() for t in dev_batch))
+            e1.record()
+            torch.cuda.synchronize()
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
+        ms_eager = e0.elapsed_time(e1) / reps
+        ours_mel = step_resident()[3][0]
+        valid = (torch.arange(T_max, device=dev)[None, :] < dev_batch[9][:, None])[:, None, :]
+        rel = float(((ours_mel - eo[3][0]).abs() * valid).sum() / ((eo[3][0].abs() * valid).sum()))
+        eager = {"value": frames / (ms_eager * 1e-3), "unit": UNIT, "ms_per_step": ms_eager,
+                 "what": "oracle port (the reference's torch ops) eager fp32 on this GPU, TF32 off, inputs resident, 5 calls after 2 warm-ups",
+                 "rel_l1_of_ours_vs_eager_mel": rel}
+
     # ---- CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -510,7 +539,7 @@ def main():
                     "how": f"{args.steps} steps as one timed region, {NSLOT} slots, copy streams overlap H2D / D2H with compute",
                     "serial_ms_per_step": ms_e2e, "serial_value": total_frames / (ms_e2e * 1e-3)},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
-            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver,
+            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver, "eager_gpu_baseline": eager,
             "kernels_ms_per_step": {k: round(v[1], 4) for k, v in sorted(prof.items())},
             "whole_model_tflops": batch_flops(host_batch, forward_flops) * world / (ms_res * 1e-3) / 1e12,
         }

@@ -39,7 +39,7 @@ _POS_CACHE = {}
 
 def pos_table(dim, max_len=5000, timestep=10000.0):
     """Sin/cos table, fp32, same op sequence as model.py:125-130 so it is bit-identical."""
-    key = (dim, max_len, timestep)
+    key = (dim, max_len, timestep, str(torch.empty(0).device))     # per default device (bench.py also runs the port on the GPU)
     if key not in _POS_CACHE:
         pos = torch.arange(0, max_len, dtype=torch.float).unsqueeze(1)
         div = torch.exp(torch.arange(0, dim, 2).float() * (-math.log(timestep) / dim))

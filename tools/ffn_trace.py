@@ -52,7 +52,7 @@ if t[251]:
 print("attention CTA (0,0,0) of the last launch (decoder block 3, longest utterance, head 0, q tile 0)")
 a0 = t[128]
 print(f"Q landed {t[129] - a0}   end {t[130] - a0}")
-an = ["kv_full", "S_issued", "p_full", "PV_issued", "s_full", "passA", "P_stored", "o_full", "folded"]
+an = ["k_full", "S_issued", "p_full", "PV_issued", "s_full", "passA", "P_stored", "K_loaded", "V_loaded"]
 print(" step " + " ".join(f"{n:>9s}" for n in an))
 for j in range(8):
     row = [t[132 + 10 * j + i] for i in range(9)]
