@@ -186,6 +186,54 @@ int dx_tc_gemm_test(const void* a_il, int64_t a_rows_phys, int M, int K, int N, 
 int dx_test_attention(int mode, const void* qkv, void* out, int64_t rows_phys, const int64_t* lengths, int B, int n_max,
                       int32_t* rowmap_scratch, int64_t row_cap, void* stream);
 
+/* ---- HiFi-GAN generator, batched -------------------------------------------------
+ * Replaces HiFiGANGenerator.forward (vocoder/hifigan.py:159-176) with ResBlock1 (hifigan.py:77-97) for a whole batch
+ * of utterances at once, each vocoded as if alone on its cropped mel (what HiFiGanVocoder.infer does one utterance
+ * at a time, hifigan.py:211-226).  Utterances are packed into one frame stream separated by DX_VC_GAP zero frames;
+ * at stage s every activation row is (frame, phase) at rate prod(up[0..s]).  Every convolution is one implicit-GEMM
+ * launch: out[r] = sum_tap A[r + (tap - taps/2) * dil] · W[tap]; transposed convolutions (kernel = 2 · stride) are
+ * their 3-tap polyphase form at the input rate with N = stride · C_out.  DX_MODE_F32: fp32 SIMT kernels;
+ * DX_MODE_BF16: bf16 operands on tcgen05 with fp32 accumulation, fp32 residual stream. */
+#define DX_VC_GAP 4          /* zero frames in front of, between and behind utterances in the packed frame stream  */
+#define DX_VC_HALO 32        /* rows in front of / behind every bf16 activation buffer (>= (taps/2) * dil)          */
+#define DX_VC_MAX_STAGES 4
+#define DX_VC_MAX_KERNELS 3
+#define DX_VC_MAX_LAYERS 3
+
+typedef struct {
+    const float* w;          /* fp32 [taps][K][N]                                                                  */
+    const void*  w_bf;       /* bf16 packed by dx_pack_weight_bf16 with the (nt, ks) of dx_vocoder_conv_tiling, or NULL */
+    const float* bias;       /* [C_out]                                                                            */
+    int32_t taps, dil, K, N; /* N = stride * C_out for the upsamplers                                              */
+} DxVcConv;
+
+typedef struct {
+    int32_t n_stages, n_kernels, n_layers, mel_channels;      /* 4, 3, 3, 80 in the reference's DEFAULT_CONFIG     */
+    int32_t up[DX_VC_MAX_STAGES];                             /* upsample_rates   (hifigan.py:30)                  */
+    int32_t channels[DX_VC_MAX_STAGES];                       /* C_out of stage s (hifigan.py:141)                 */
+    DxVcConv pre;                                             /* conv_pre   (hifigan.py:131)                       */
+    DxVcConv ups[DX_VC_MAX_STAGES];                           /* ups[s]     (hifigan.py:133-143), polyphase form   */
+    DxVcConv rb[DX_VC_MAX_STAGES][DX_VC_MAX_KERNELS][DX_VC_MAX_LAYERS][2];   /* convs1[l], convs2[l] (hifigan.py:80-87) */
+    DxVcConv post;                                            /* conv_post  (hifigan.py:152): w fp32 [taps][K], N = 1 */
+} DxVocoderWeights;
+
+typedef struct {
+    int32_t B, T_max, mode, pad_;
+    int64_t frame_cap;       /* >= dx_vocoder_frame_cap(B, sum of lengths)                                         */
+    const float* mel;        /* (B, mel_channels, T_max) fp32                                                      */
+    const int64_t* lengths;  /* (B,) frames per utterance, each <= T_max                                           */
+    float* audio;            /* (B, T_max * hop) fp32, zeros behind every utterance                                */
+    void* workspace;
+    int64_t workspace_bytes;
+} DxVocoderArgs;
+
+/* rows of the packed frame stream needed for `total_frames` valid frames in B utterances (multiple of 128) */
+int64_t dx_vocoder_frame_cap(int B, int64_t total_frames);
+/* tile width nt and channels per pipeline stage ks the tensor-core conv kernel uses for a (taps, dil, K, N) conv */
+int dx_vocoder_conv_tiling(int taps, int dil, int K, int N, int* nt, int* ks);
+int64_t dx_vocoder_workspace_bytes(const DxVocoderWeights* w, int B, int64_t frame_cap, int mode);
+int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

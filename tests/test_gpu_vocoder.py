@@ -1,0 +1,88 @@
+"""GPU: the batched HiFi-GAN generator (dx_vocoder_forward through the Python mirror) against golden vectors frozen
+from the live reference generator and against the CPU oracle.  Tolerances follow the north star's two modes:
+fp32 mode max-abs <= 1e-3, bf16 mode relative L1 <= 2e-2 (waveform samples, tanh range)."""
+import numpy as np
+import pytest
+import torch
+
+import _cases as C
+from oracle import hifigan_oracle as H
+import make_vocoder_golden as VG
+from daft_exprt_b200 import vocoder as V
+
+pytestmark = pytest.mark.gpu
+FP32_MAX_ABS = 1e-3
+BF16_REL_L1 = 2e-2
+
+
+def _generator(mode, seed=VG.WEIGHT_SEED):
+    gen = V.HiFiGANGenerator(V.DEFAULT_CONFIG)
+    gen.load_state_dict(H.make_state_dict(seed=seed))
+    return gen.cuda().eval().set_mode(mode)
+
+
+def _check(audio, ref, mode):
+    assert audio.shape == ref.shape
+    assert np.isfinite(audio).all()
+    if mode == "fp32":
+        assert np.abs(audio - ref).max() <= FP32_MAX_ABS, np.abs(audio - ref).max()
+    else:
+        rel = np.abs(audio - ref).sum() / np.abs(ref).sum()
+        assert rel <= BF16_REL_L1, rel
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", sorted(VG.VOCODER_CASES))
+def test_generator_matches_golden(name, mode):
+    g = C.load_golden(name)
+    mels, lengths = VG.vocoder_case(**VG.VOCODER_CASES[name])
+    gen = _generator(mode)
+    audio = gen(mels.cuda(), lengths)
+    torch.cuda.synchronize()
+    assert audio.shape == (mels.size(0), 1, mels.size(2) * 256)
+    _check(audio[:, 0].cpu().numpy(), g["audio"], mode)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_batch_equals_single_utterance_calls_bitwise(mode):
+    """An utterance's samples do not depend on its neighbours in the packed stream, on its position, or on how the
+    stream is tiled: the batched call and B single calls agree bit for bit, and so do two runs."""
+    lengths = [40, 3, 31, 1, 18]
+    mels, ln = VG.vocoder_case(lengths=lengths, seed=31)
+    gen = _generator(mode)
+    batch = gen(mels.cuda(), ln).cpu()
+    again = gen(mels.cuda(), ln.cuda(), total_frames=sum(lengths)).cpu()
+    assert torch.equal(batch, again)
+    for b, n in enumerate(lengths):
+        one = gen(mels[b : b + 1, :, :n].cuda()).cpu()          # lengths=None: the whole tensor, as the reference module
+        assert torch.equal(one[0, 0], batch[b, 0, : n * 256]), b
+        assert torch.count_nonzero(batch[b, 0, n * 256 :]) == 0
+
+
+def test_oracle_parity_on_a_wider_batch_bf16_and_fp32():
+    lengths = [120, 77, 64, 9]
+    mels, ln = VG.vocoder_case(lengths=lengths, seed=33)
+    sd = H.make_state_dict(seed=99)
+    ref = H.infer_batch(sd, mels, ln).numpy()
+    for mode in ("fp32", "bf16"):
+        gen = V.HiFiGANGenerator(V.DEFAULT_CONFIG)
+        gen.load_state_dict(H.fold_weight_norm(sd))              # plain-weight checkpoint form
+        gen.cuda().set_mode(mode)
+        audio = gen(mels.cuda(), ln)[:, 0].cpu().numpy()
+        _check(audio, ref, mode)
+
+
+def test_vocoder_wrapper_contract():
+    sd = H.make_state_dict(seed=VG.WEIGHT_SEED)
+    voc = V.HiFiGanVocoder(state_dict=sd, device="cuda", mode="fp32")
+    mels, ln = VG.vocoder_case(**VG.VOCODER_CASES["voc_ragged"])
+    g = C.load_golden("voc_ragged")
+    a = voc.infer(mels[1, :, :9].numpy())                        # numpy (80, T) in, clipped numpy out
+    assert isinstance(a, np.ndarray) and a.shape == (9 * 256,) and np.abs(a).max() <= 1.0
+    assert np.abs(a - g["audio"][1, : 9 * 256]).max() <= FP32_MAX_ABS
+    with pytest.raises(ValueError):
+        voc.infer(mels)                                          # batches are refused, as in the reference helper
+    outs = voc.infer_batch(mels, ln)
+    assert [o.shape[0] for o in outs] == [int(n) * 256 for n in ln]
+    for b, o in enumerate(outs):
+        assert np.abs(o - g["audio"][b, : o.shape[0]]).max() <= FP32_MAX_ABS

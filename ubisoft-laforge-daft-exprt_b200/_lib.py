@@ -54,6 +54,26 @@ class DxForwardArgs(C.Structure):
     )
 
 
+VC_GAP, VC_HALO = 4, 32
+
+
+class DxVcConv(C.Structure):
+    _fields_ = [("w", _p), ("w_bf", _p), ("bias", _p),
+                ("taps", C.c_int32), ("dil", C.c_int32), ("K", C.c_int32), ("N", C.c_int32)]
+
+
+class DxVocoderWeights(C.Structure):
+    _fields_ = [("n_stages", C.c_int32), ("n_kernels", C.c_int32), ("n_layers", C.c_int32), ("mel_channels", C.c_int32),
+                ("up", C.c_int32 * 4), ("channels", C.c_int32 * 4),
+                ("pre", DxVcConv), ("ups", DxVcConv * 4), ("rb", (((DxVcConv * 2) * 3) * 3) * 4), ("post", DxVcConv)]
+
+
+class DxVocoderArgs(C.Structure):
+    _fields_ = [("B", C.c_int32), ("T_max", C.c_int32), ("mode", C.c_int32), ("pad_", C.c_int32),
+                ("frame_cap", C.c_int64), ("mel", _p), ("lengths", _p), ("audio", _p), ("workspace", _p),
+                ("workspace_bytes", C.c_int64)]
+
+
 # name -> (restype, argtypes); must list every function include/daft_b200.h declares
 SIGNATURES = {
     "dx_version": (C.c_int, []),
@@ -76,6 +96,10 @@ SIGNATURES = {
     "dx_int_durations": (C.c_int, [_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p, _p]),
     "dx_prosody_transform": (C.c_int, [_p, _p, _p, _p, _p, _p, _p, C.c_int, C.c_int, C.c_int, _p]),
     "dx_tc_gemm_test": (C.c_int, [_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p, C.c_int, C.c_int, _p, _p]),
+    "dx_vocoder_frame_cap": (C.c_int64, [C.c_int, C.c_int64]),
+    "dx_vocoder_conv_tiling": (C.c_int, [C.c_int] * 4 + [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "dx_vocoder_workspace_bytes": (C.c_int64, [C.POINTER(DxVocoderWeights), C.c_int, C.c_int64, C.c_int]),
+    "dx_vocoder_forward": (C.c_int, [C.POINTER(DxVocoderWeights), C.POINTER(DxVocoderArgs), _p]),
     "dx_test_attention": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p, C.c_int64, _p]),
 }
 
