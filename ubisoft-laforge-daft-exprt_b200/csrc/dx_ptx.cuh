@@ -63,6 +63,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// Same, for waits that are usually long (a tile's copies, a whole accumulation): back off with nanosleep between
+// polls so that the spinning warp does not take issue slots from the single-thread producer / issuer chains of the
+// CTAs sharing its scheduler (measured on the vocoder conv kernel: 3 CTAs/SM, 54 M warp instructions per launch
+// of which < 10 % were useful).
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint32_t spins = 0;
+    do {
+        __nanosleep(ns);
+        if (++spins > (1u << 26)) {
+            printf("dx: mbarrier wait timeout (block %d thread %d parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, parity);
+            __trap();
+        }
+    } while (!mbar_try_wait(bar, parity));
+}
+
 // named barrier among `nthreads` threads of the CTA (id 1..15; 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

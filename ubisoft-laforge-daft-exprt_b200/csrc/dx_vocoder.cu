@@ -279,6 +279,7 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
         c.e.frame_utt = L.frame_utt;
         c.e.out_shift = ilog2(in_rate * up);
         c.e.res = res; c.e.x_out = x_out; c.e.xs = L.xs; c.e.xs_mode = xs_mode;
+        c.e.x_rows = cap * in_rate * up;
         c.e.n_kernels = (float)w->n_kernels;
         c.e.act = 1;
         c.e.act_out = act_out;

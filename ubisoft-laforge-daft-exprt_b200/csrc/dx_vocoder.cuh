@@ -16,9 +16,12 @@ struct VcEpi {
     int c_out, up;                   // column n = ph * c_out + co → output row r * up + ph
     const int32_t* frame_utt;
     int out_shift;                   // log2(rate of the output rows)
-    const float* res;                // fp32 [rows_out][c_out] or null
-    float* x_out;                    // fp32 [rows_out][c_out] or null
-    float* xs;                       // fp32 [rows_out][c_out] (xs_mode != 0)
+    // fp32 residual stream, "quad-interleaved" [c_out/4][x_rows][4]: lane ↔ row accesses are 16 B at consecutive
+    // addresses (one coalesced 512 B request per warp and 4-channel group)
+    const float* res;                // or null
+    float* x_out;                    // or null
+    float* xs;                       // (xs_mode != 0)
+    int64_t x_rows;                  // rows of the output-rate tensors
     int xs_mode;                     // 0 none, 1 xs = y, 2 xs += y, 3 y = (xs + y) / n_kernels
     float n_kernels;
     int act;                         // 1: leaky_relu on act_out, 0: identity
@@ -35,25 +38,26 @@ __device__ __forceinline__ void vc_epilogue(const VcEpi& e, int64_t r, int n, fl
     const int64_t ro = r * e.up + ph;
     const bool valid = e.frame_utt[ro >> e.out_shift] >= 0;
     if (valid) {
-        const int64_t off = ro * e.c_out + co;
+        const int64_t off = ((int64_t)(co >> 2) * e.x_rows + ro) * 4;   // 4-channel group co/4 of row ro
+        const int64_t gstride = e.x_rows * 4 - 4;                        // off + i + (i/4) * gstride = group (co + i)/4
 #pragma unroll
         for (int i = 0; i < NV; i += 4) {
             float4 y = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
             const float* bb = s_bias ? s_bias + n + i : e.bias + co + i;
             y.x += bb[0]; y.y += bb[1]; y.z += bb[2]; y.w += bb[3];
             if (e.res) {
-                const float4 rr = *reinterpret_cast<const float4*>(e.res + off + i);
+                const float4 rr = *reinterpret_cast<const float4*>(e.res + off + i + (i >> 2) * gstride);
                 y.x += rr.x; y.y += rr.y; y.z += rr.z; y.w += rr.w;
             }
             if (e.xs_mode == 1) {
-                *reinterpret_cast<float4*>(e.xs + off + i) = y;
+                *reinterpret_cast<float4*>(e.xs + off + i + (i >> 2) * gstride) = y;
             } else if (e.xs_mode >= 2) {
-                const float4 a = *reinterpret_cast<const float4*>(e.xs + off + i);
+                const float4 a = *reinterpret_cast<const float4*>(e.xs + off + i + (i >> 2) * gstride);
                 y.x += a.x; y.y += a.y; y.z += a.z; y.w += a.w;     // xs += resblock(x), hifigan.py:170
-                if (e.xs_mode == 2) *reinterpret_cast<float4*>(e.xs + off + i) = y;
+                if (e.xs_mode == 2) *reinterpret_cast<float4*>(e.xs + off + i + (i >> 2) * gstride) = y;
                 else { y.x /= e.n_kernels; y.y /= e.n_kernels; y.z /= e.n_kernels; y.w /= e.n_kernels; }   // :171
             }
-            if (e.x_out) *reinterpret_cast<float4*>(e.x_out + off + i) = y;
+            if (e.x_out) *reinterpret_cast<float4*>(e.x_out + off + i + (i >> 2) * gstride) = y;
             v[i] = y.x; v[i + 1] = y.y; v[i + 2] = y.z; v[i + 3] = y.w;
         }
     }
