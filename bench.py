@@ -509,6 +509,88 @@ def main():
                  "what": "oracle port (the reference's torch ops) eager fp32 on this GPU, TF32 off, inputs resident, 5 calls after 2 warm-ups",
                  "rel_l1_of_ours_vs_eager_mel": rel}
 
+    # ---- HiFi-GAN generator: the step after the path.  The mels this step produced (64 utterances,
+    # the step's valid frames) -> waveforms in one batched pass; device-resident timing, end to end with host buffers,
+    # per-kernel profile, parity + CPU time on one utterance against the oracle restatement of hifigan.py.
+    vocoder = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.mode == "bf16":
+        from daft_exprt_b200 import vocoder as VC
+        gen = VC.HiFiGANGenerator(VC.DEFAULT_CONFIG)
+        voc_sd = VC.synthetic_state_dict(seed=4321)
+        gen.load_state_dict(voc_sd)
+        gen.to(dev).eval().set_mode("bf16")
+        mel_dev = step_resident()[3][0].contiguous()
+        len_host = host_batch[9].clone()
+        len_dev = dev_batch[9]
+        v_frames = int(len_host.sum())
+        for _ in range(2):
+            gen(mel_dev, len_dev, total_frames=v_frames)
+        torch.cuda.synchronize()
+        reps = 5
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            audio = gen(mel_dev, len_dev, total_frames=v_frames)
+        e1.record()
+        torch.cuda.synchronize()
+        v_ms = e0.elapsed_time(e1) / reps
+        # host buffers: pinned mel H2D + lengths, one pass, audio D2H into pinned memory
+        mel_pin = mel_dev.cpu().pin_memory()
+        aud_pin = torch.empty(audio.shape, dtype=torch.float32).pin_memory()
+        ts = []
+        for _ in range(4):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            a_ = gen(mel_pin.to(dev, non_blocking=True), len_host)
+            aud_pin.copy_(a_, non_blocking=True)
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        v_e2e = statistics.median(ts[1:]) * 1e3
+        lib.dx_profile_enable(1)
+        gen(mel_dev, len_dev, total_frames=v_frames)
+        torch.cuda.synchronize()
+        buf = ctypes.create_string_buffer(1 << 16)
+        _lib.check(lib.dx_profile_report(buf, len(buf)), "dx_profile_report")
+        lib.dx_profile_enable(0)
+        vprof = parse_profile(buf.value.decode())
+        v_flops = VC.flops_per_frame() * v_frames
+        peaks_ = {}
+        try:
+            peaks_ = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        v_peak = peaks_.get("bf16_tflops_sustained", 1400.0)
+        conv_ms = sum(ms for k, (n, ms) in vprof.items() if k.startswith(("vc_s", "vc_up", "vc_pre")))
+        # parity + CPU time: the shortest utterance of the batch, alone, through the oracle
+        from oracle import hifigan_oracle as HO
+        b_min = int(torch.argmin(len_host))
+        n_min = int(len_host[b_min])
+        torch.set_num_threads(os.cpu_count() or 1)
+        mel_one = mel_pin[b_min, :, :n_min].clone()
+        HO.infer(voc_sd, mel_one[:, : min(16, n_min)])
+        t0 = time.perf_counter()
+        ref_audio = HO.infer(voc_sd, mel_one)
+        v_cpu = time.perf_counter() - t0
+        ours_one = audio[b_min, 0, : n_min * 256].clamp(-1, 1).cpu()
+        v_rel = float((ours_one - ref_audio).abs().sum() / ref_audio.abs().sum())
+        vocoder = {
+            "workload": f"HiFiGANGenerator (hifigan.py DEFAULT_CONFIG, random-init): the {B} mels of this step, {v_frames} valid frames -> {v_frames * 256} samples, one batched pass, bf16 mode",
+            "frames_per_s": v_frames / (v_ms * 1e-3), "samples_per_s": v_frames * 256 / (v_ms * 1e-3), "ms_per_batch": v_ms,
+            "x_realtime_22050Hz": v_frames * 256 / (v_ms * 1e-3) / 22050.0,
+            "e2e_ms_per_batch_host_buffers": v_e2e, "e2e_samples_per_s": v_frames * 256 / (v_e2e * 1e-3),
+            "h2d_bytes": mel_pin.numel() * 4, "d2h_bytes": aud_pin.numel() * 4,
+            "launches": int(sum(n for n, _ in vprof.values())),
+            "roofline": {"bound": "tensor", "kernel": "vc_conv_tc_kernel (all conv launches of one pass)",
+                         "achieved": v_flops / (conv_ms * 1e-3) / 1e12, "peak": v_peak, "unit": "TFLOP/s",
+                         "frac": v_flops / (conv_ms * 1e-3) / 1e12 / v_peak, "algorithmic_flops_per_frame": VC.flops_per_frame(),
+                         "conv_ms_per_batch": conv_ms},
+            "kernels_ms": {k: round(ms, 4) for k, (n, ms) in sorted(vprof.items()) if k.startswith("vc_")},
+            "rel_l1_vs_oracle": v_rel, "parity_sample": f"utterance {b_min} ({n_min} frames) vocoded alone by the CPU oracle",
+            "cpu_baseline": {"value": n_min / v_cpu, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": f"one utterance of {n_min} frames, 1 call after a 16-frame warm-up, {v_cpu:.2f} s"},
+        }
+        del gen, audio, mel_pin, aud_pin
+
     # ---- CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -539,7 +621,7 @@ def main():
                     "how": f"{args.steps} steps as one timed region, {NSLOT} slots, copy streams overlap H2D / D2H with compute",
                     "serial_ms_per_step": ms_e2e, "serial_value": total_frames / (ms_e2e * 1e-3)},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
-            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver, "eager_gpu_baseline": eager,
+            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver, "eager_gpu_baseline": eager, "vocoder": vocoder,
             "kernels_ms_per_step": {k: round(v[1], 4) for k, v in sorted(prof.items())},
             "whole_model_tflops": batch_flops(host_batch, forward_flops) * world / (ms_res * 1e-3) / 1e12,
         }

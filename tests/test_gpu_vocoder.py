@@ -86,3 +86,27 @@ def test_vocoder_wrapper_contract():
     assert [o.shape[0] for o in outs] == [int(n) * 256 for n in ln]
     for b, o in enumerate(outs):
         assert np.abs(o - g["audio"][b, : o.shape[0]]).max() <= FP32_MAX_ABS
+
+
+def test_synthesis_driver_writes_waves_through_the_batched_vocoder(tmp_path):
+    """generate_mel_specs (row N1) with the B200 vocoder (row N4): one generator pass per batch; the .wav files equal
+    the reference driver's per-utterance ``vocoder.infer`` conversion (generate.py:322-323) of the same mels."""
+    import copy
+    from scipy.io import wavfile
+    from daft_exprt_b200 import generate as G, synthetic
+    from daft_exprt_b200.model import DaftExprt
+    hp = C.hparams()
+    model = DaftExprt(hp).cuda()
+    model.load_state_dict(C.state_dict())
+    model.eval().set_mode("bf16")
+    voc = V.HiFiGanVocoder(state_dict=H.make_state_dict(seed=VG.WEIGHT_SEED), device="cuda", mode="bf16")
+    req = synthetic.synthesis_request(hp, 5, 4, 12, 21, "add")
+    preds = G.generate_mel_specs(model, output_dir=str(tmp_path), hparams=hp, vocoder=voc, batch_size=3,
+                                 alpha_dur=1.0, alpha_pitch=1.0, alpha_energy=1.0, **copy.deepcopy(req))
+    assert len(preds) == 5
+    for name, p in preds.items():
+        sr, wav = wavfile.read(str(tmp_path / f"{name}.wav"))
+        assert sr == hp.sampling_rate and wav.dtype == np.int16 and wav.shape[0] == p[4].shape[1] * 256
+        audio = voc.infer(p[4])
+        ref = (audio * 32767.5).clip(min=-32768, max=32767).astype(np.int16)
+        assert np.array_equal(wav, ref), name

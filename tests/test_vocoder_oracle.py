@@ -106,3 +106,9 @@ def test_vocoder_host_queries():
     assert nt.value == 32 and ks.value == 32
     assert ctypes.sizeof(_lib.DxVcConv) == 40
     assert ctypes.sizeof(_lib.DxVocoderWeights) == 48 + 40 * (1 + 4 + 72 + 1)
+
+
+def test_product_synthetic_checkpoint_equals_the_oracles():
+    a, b = V.synthetic_state_dict(seed=5), H.make_state_dict(seed=5)
+    assert list(a) == list(b) and all(torch.equal(a[k], b[k]) for k in a)
+    assert V.flops_per_frame() == 614_105_088

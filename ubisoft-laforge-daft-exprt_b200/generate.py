@@ -8,8 +8,8 @@ meaning, return values and error behaviour:
   generate_batch_mel_specs      generate.py:187-330   collate, external prosody tensors (:213-278), ``inference``, crops
   generate_mel_specs            generate.py:333-399   batches of ``batch_size`` utterances, optional RTF report
 
-Text front end (phonemiser, ``generate.py:27-101``), plotting (``:324-326``) and the HiFi-GAN vocoder itself
-(``vocoder/hifigan.py``; no weights offline) are outside this row; a vocoder object handed in by the caller is used exactly
+Text front end (phonemiser, ``generate.py:27-101``) and plotting (``:324-326``) are outside this row.  The HiFi-GAN
+vocoder is row N4 (``vocoder.py``); any vocoder object handed in by the caller is used exactly
 as the reference uses it (``:327-329``).
 
 What is different from the reference is how the bytes move (the results are identical, tests/test_generate.py):
@@ -417,8 +417,19 @@ def _write_batch(predictions, output_dir, hparams, vocoder):
             "Provide --vocoder_checkpoint in synthesize.py or load a vocoder before calling generate."
         )
     from scipy.io import wavfile
+    names = list(predictions)
+    audios = None
+    if hasattr(vocoder, "infer_batch") and len(names) > 1:
+        # ours (vocoder.HiFiGanVocoder): the whole batch in ONE generator pass over the packed frame stream, every
+        # utterance vocoded as if alone (bit-identical to per-utterance infer calls, tests/test_gpu_vocoder.py)
+        mels = [np.asarray(predictions[n][4], dtype=np.float32) for n in names]
+        lengths = [m.shape[1] for m in mels]
+        batch = np.zeros((len(mels), mels[0].shape[0], max(lengths)), dtype=np.float32)
+        for b, m in enumerate(mels):
+            batch[b, :, : m.shape[1]] = m
+        audios = dict(zip(names, vocoder.infer_batch(batch, lengths)))
     for file_name, (_, _, _, _, mel_spec, weight) in predictions.items():
-        audio = vocoder.infer(mel_spec)
+        audio = audios[file_name] if audios is not None else vocoder.infer(mel_spec)
         audio_int16 = (audio * 32767.5).clip(min=-32768, max=32767).astype(np.int16)
         wavfile.write(os.path.join(output_dir, f'{file_name}.wav'), hparams.sampling_rate, audio_int16)
 

@@ -56,6 +56,44 @@ def _conv_specs(config):
     return specs
 
 
+def synthetic_state_dict(config=None, seed=4321, weight_norm=True, gain=1.1):
+    """Seeded random generator checkpoint (there is no network for the reference's default download, hifigan.py:43-68)
+    in the reference's key layout, ``weight_g`` / ``weight_v`` form by default.  Layers have O(1) signal gain: the
+    reference's own init N(0, 0.01²) (hifigan.py:73-74) would make every activation vanish.  Same sequence of draws as
+    ``oracle/hifigan_oracle.make_state_dict`` (checked by tests/test_vocoder_oracle.py)."""
+    import math
+    config = DEFAULT_CONFIG if config is None else config
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    for name, kind, cin, cout, k, _ in _conv_specs(config):
+        std = gain / math.sqrt(cin * (k if kind == "conv" else 2))
+        shape = (cout, cin, k) if kind == "conv" else (cin, cout, k)
+        v = torch.randn(shape, generator=g) * std
+        b = torch.randn(cout, generator=g) * 0.1
+        if weight_norm:
+            norm = v.flatten(1).norm(dim=1).view(-1, 1, 1)
+            scale = 0.75 + 0.5 * torch.rand(shape[0], 1, 1, generator=g)
+            sd[name + ".weight_g"] = norm * scale
+            sd[name + ".weight_v"] = v
+        else:
+            sd[name + ".weight"] = v
+        sd[name + ".bias"] = b
+    return sd
+
+
+def flops_per_frame(config=None):
+    """Algorithmic FLOPs (2 · MAC) of the generator per mel frame: every Conv1d / ConvTranspose1d at its rate."""
+    config = DEFAULT_CONFIG if config is None else config
+    c0, rate, total = config['upsample_initial_channel'], 1, 2 * config['model_in_dim'] * config['upsample_initial_channel'] * 7
+    for i, (u, k) in enumerate(zip(config['upsample_rates'], config['upsample_kernel_sizes'])):
+        cin, cout = c0 // 2 ** i, c0 // 2 ** (i + 1)
+        rate *= u
+        total += 2 * cin * cout * (k // u) * rate                       # k / u taps reach one output sample
+        for rk, dils in zip(config['resblock_kernel_sizes'], config['resblock_dilation_sizes']):
+            total += 2 * cout * cout * rk * 2 * len(dils) * rate
+    return total + 2 * cout * 7 * rate
+
+
 def _check_config(config):
     if str(config.get('resblock', '1')) != '1':
         raise NotImplementedError("only ResBlock1 generators (config['resblock'] == '1', the reference default) are built")
