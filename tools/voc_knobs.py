@@ -15,7 +15,7 @@ def prof(tagfilter=("vc_s2", "vc_s3", "vc_s1", "vc_s0")):
     for l in buf.value.decode().strip().splitlines():
         t, n, ms = l.split(); d[t] = float(ms)
     return d
-for k in (0, 1, 2, 4, 6, 8, 9, 14, 15):
+for k in (0, 1, 2, 8, 16, 17, 24, 25, 27):
     lib.dx_set_debug(11, k)
     gen(mels, ln); torch.cuda.synchronize()
     d = prof()

@@ -290,6 +290,8 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
     };
     static const char* const kStageTags[4][3] = {{"vc_up0", "vc_s0_conv1", "vc_s0_conv2"}, {"vc_up1", "vc_s1_conv1", "vc_s1_conv2"},
                                                 {"vc_up2", "vc_s2_conv1", "vc_s2_conv2"}, {"vc_up3", "vc_s3_conv1", "vc_s3_conv2"}};
+    static const char* const kPairTags[4] = {"vc_s0_pair", "vc_s1_pair", "vc_s2_pair", "vc_s3_pair"};
+    const bool fuse_pairs = bf && !debug_knob(12);      // knob 12: every ResBlock layer as two launches (A/B, bit-identical)
     // conv_pre (hifigan.py:160); its only consumer is leaky_relu → ups[0] (hifigan.py:162-163)
     DX_TRY(conv(w->pre, L.melp, 1, w->pre.N, 1, nullptr, nullptr, 0, L.next, "vc_pre"));
     int rate = 1;
@@ -301,17 +303,46 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
         for (int j = 0; j < w->n_kernels; ++j) {
             for (int l = 0; l < w->n_layers; ++l) {
                 const bool last = l == w->n_layers - 1;
-                // xt = leaky_relu(convs1[l](leaky_relu(x)))  (hifigan.py:92-94)
-                DX_TRY(conv(w->rb[st][j][l][0], l == 0 ? L.a0 : L.ar, rate, C, 1, nullptr, nullptr, 0, L.h, kStageTags[st][1]));
-                // x = convs2[l](xt) + x (hifigan.py:95-96); the last layer feeds xs (hifigan.py:167-171)
                 const float* res = l == 0 ? L.x0 : L.xr;
-                if (!last) {
-                    DX_TRY(conv(w->rb[st][j][l][1], L.h, rate, C, 1, res, L.xr, 0, L.ar, kStageTags[st][2]));
-                } else {
-                    const bool fin = j == w->n_kernels - 1;
-                    const int xs_mode = fin ? (w->n_kernels == 1 ? 0 : 3) : (j == 0 ? 1 : 2);
-                    DX_TRY(conv(w->rb[st][j][l][1], L.h, rate, C, 1, res, nullptr, xs_mode, fin ? L.next : nullptr, kStageTags[st][2]));
+                const bool fin = last && j == w->n_kernels - 1;
+                const int xs_mode = !last ? 0 : (fin ? (w->n_kernels == 1 ? 0 : 3) : (j == 0 ? 1 : 2));
+                float* x_out = last ? nullptr : L.xr;
+                void* act_out = last ? (fin ? L.next : nullptr) : L.ar;
+                const void* in = l == 0 ? L.a0 : L.ar;
+                if (fuse_pairs && C <= (debug_knob(13) ? 128 : 64)) {
+                    // one launch: x = convs2[l](leaky_relu(convs1[l](leaky_relu(x)))) + x, hidden tile on chip.  The
+                    // operand it reads (with halo rows of neighbouring tiles) and the one it writes must differ:
+                    // ar and h (free in this mode) alternate
+                    void* pp[2] = {L.ar, L.h};
+                    const void* pin = l == 0 ? L.a0 : pp[(l - 1) & 1];
+                    void* pout = last ? act_out : pp[l & 1];
+                    const DxVcConv& c1 = w->rb[st][j][l][0];
+                    const DxVcConv& c2 = w->rb[st][j][l][1];
+                    DX_REQUIRE(c1.w_bf && c2.w_bf && c1.bias && c2.bias && c1.taps == c2.taps && c2.dil == 1 && c1.K == C && c1.N == C &&
+                                   c2.K == C && c2.N == C, "vocoder: ResBlock layer %d/%d/%d is not a fusable pair", st, j, l);
+                    VcPairArgs pa;
+                    pa.a = (const __nv_bfloat16*)pin;
+                    pa.a_rows_phys = cap * rate + 2 * DX_VC_HALO;
+                    pa.C = C; pa.taps = c1.taps; pa.dil = c1.dil;
+                    pa.w1_bf = (const __nv_bfloat16*)c1.w_bf; pa.w2_bf = (const __nv_bfloat16*)c2.w_bf;
+                    pa.bias1 = c1.bias; pa.bias2 = c2.bias;
+                    pa.total_frames = L.frame_start + a->B;
+                    pa.shift = ilog2(rate);
+                    pa.rows_bound = cap * rate;
+                    pa.e.bias = c2.bias; pa.e.c_out = C; pa.e.up = 1;
+                    pa.e.frame_utt = L.frame_utt; pa.e.out_shift = pa.shift;
+                    pa.e.res = res; pa.e.x_out = x_out; pa.e.xs = L.xs; pa.e.xs_mode = xs_mode;
+                    pa.e.x_rows = cap * rate;
+                    pa.e.n_kernels = (float)w->n_kernels;
+                    pa.e.act = 1; pa.e.act_out = pout; pa.e.act_rows_phys = cap * rate + 2 * DX_VC_HALO;
+                    pa.tag = kPairTags[st];
+                    DX_TRY(vc_pair_bf16(pa, s));
+                    continue;
                 }
+                // xt = leaky_relu(convs1[l](leaky_relu(x)))  (hifigan.py:92-94)
+                DX_TRY(conv(w->rb[st][j][l][0], in, rate, C, 1, nullptr, nullptr, 0, L.h, kStageTags[st][1]));
+                // x = convs2[l](xt) + x (hifigan.py:95-96); the last layer feeds xs (hifigan.py:167-171)
+                DX_TRY(conv(w->rb[st][j][l][1], L.h, rate, C, 1, res, x_out, xs_mode, act_out, kStageTags[st][2]));
             }
         }
     }

@@ -100,3 +100,21 @@ int vc_conv_f32(const VcConvArgs& c, cudaStream_t s);
 void vc_conv_tiling(int taps, int dil, int K, int N, int* nt, int* ks);
 
 }  // namespace dx
+
+namespace dx {
+// One ResBlock1 layer (hifigan.py:92-96) in ONE launch: x_new = convs2(leaky_relu(convs1_dilated(a))) + x, with the
+// hidden tile in shared memory (dx_vocoder_conv.cu, vc_pair_tc_kernel).  bf16 mode, C = K = N <= 128.
+struct VcPairArgs {
+    const __nv_bfloat16* a;          // leaky_relu(x), bf16 interleaved [C/8][a_rows_phys][8]
+    int64_t a_rows_phys;
+    int C, taps, dil;                // convs1: taps x dil; convs2: taps x 1
+    const __nv_bfloat16 *w1_bf, *w2_bf;
+    const float *bias1, *bias2;
+    const int32_t* total_frames;
+    int shift;                       // log2(rate)
+    int64_t rows_bound;
+    VcEpi e;                         // epilogue of convs2 (bias = bias2, up = 1)
+    const char* tag;
+};
+int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s);
+}  // namespace dx

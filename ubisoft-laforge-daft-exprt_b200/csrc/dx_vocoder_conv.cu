@@ -95,8 +95,13 @@ __device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, b
     }
 }
 
+// (8 epilogue warps for NT >= 64 - two per TMEM lane group, alternating 32-column groups - were measured slower:
+// 320 threads x 2 CTAs cap the kernel at 96 registers and the NT = 128 epilogue spills; stage 1 conv2 141 -> 157 us.)
 template <int NT>
 __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kernel(const VcTcParams p) {
+    constexpr int EW = 4;                            // epilogue warps: one per TMEM lane group
+    constexpr int QS = EW / 4;
+    constexpr int NTHREADS = 64 + EW * 32;
     extern __shared__ __align__(1024) uint8_t vc_smem[];
     const uint32_t stage_bytes = p.a_stage_bytes + p.w_stage_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(vc_smem + (size_t)p.nstages * stage_bytes);
@@ -107,7 +112,7 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
     float* s_bias = reinterpret_cast<float*>(vc_smem + p.par_off);   // [N]: bias of column n = bias[n % c_out]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < p.c.N; i += VC_THREADS) s_bias[i] = p.c.e.bias[i % p.c.e.c_out];
+    for (int i = threadIdx.x; i < p.c.N; i += NTHREADS) s_bias[i] = p.c.e.bias[i % p.c.e.c_out];
     if (threadIdx.x == 0) {
         for (int i = 0; i < p.nstages; ++i) {
             ptx::mbar_init(&full_bar[i], 1);
@@ -115,7 +120,7 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&tfull_bar[i], 1);
-            ptx::mbar_init(&tempty_bar[i], 4);
+            ptx::mbar_init(&tempty_bar[i], EW);
         }
         ptx::fence_barrier_init();
     }
@@ -190,8 +195,9 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
             }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int lane_grp = warp & 3;                 // TMEM lanes 32*lane_grp .. +31
+        // ===================== epilogue (warps 2 .. 2+EW-1) =====================
+        const int lane_grp = warp & 3;                 // TMEM lanes 32*lane_grp .. +31 (a warp may only touch lanes 32 * (warp % 4) ..)
+        const int qoff = (warp - 2) >> 2;              // this warp's 32-column groups: q = qoff, qoff + QS, ...
         uint32_t tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int m_tile = (int)(item / p.n_tiles), n_tile = (int)(item % p.n_tiles);
@@ -201,16 +207,16 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
             const bool inr = r < total;
             const bool valid = inr && p.c.e.frame_utt[r >> p.c.in_shift] >= 0;   // all phases of a row share its frame
             VcPre pre;
-            vc_tc_prefetch(p.c.e, r, n_tile * NT, valid, pre);
+            vc_tc_prefetch(p.c.e, r, n_tile * NT + qoff * 32, valid, pre);
             ptx::mbar_wait_sleep(&tfull_bar[acc], acc_ph, 100);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)acc * NT;
 #pragma unroll 1
-            for (int q = 0; q < NT / 32; ++q) {
+            for (int q = qoff; q < NT / 32; q += QS) {
                 float v[32];
                 ptx::tmem_ld32(taddr + q * 32, v);
                 const int n = n_tile * NT + q * 32;
-                if (q > 0) vc_tc_prefetch(p.c.e, r, n, valid, pre);
+                if (q > qoff) vc_tc_prefetch(p.c.e, r, n, valid, pre);
                 ptx::tmem_ld_wait();
                 if (inr && n < p.c.N && !(p.dbg & 1)) vc_tc_finish(p.c.e, r, n, valid, v, pre, s_bias + n);
             }
@@ -302,6 +308,336 @@ int vc_conv_bf16(const VcConvArgs& c, cudaStream_t s) {
     if (nt == 32) return vc_tc_launch<32>(p, smem, grid, s);
     DX_REQUIRE(false, "vc_conv: tile width %d", nt);
     return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// fused ResBlock layer: convs1 (dilated) → leaky_relu → convs2 → + x, hidden tile never leaves the SM
+// ---------------------------------------------------------------------------------------------------------
+// One tile = 128 hidden rows H0 .. H0+127 with H0 = t * VM - hk (hk = taps / 2, VM = 128 - 2 hk valid output rows).
+//   M1: D1[b] = convs1 over the staged A tile (rows H0 - hk*dil .. H0 + 127 + hk*dil)
+//   P1: D1[b] → + bias1, leaky_relu, zero outside the utterances (= convs2's zero padding) → bf16 → Hs[b] in shared
+//       memory, already in the K-major UMMA layout (chunk stride RH rows; rows 128.. stay zero)
+//   M2: D2[b] = convs2 with A = Hs[b] (tap = +16 B) and B = the streamed W2 stages
+//   P2: D2[b] → the usual epilogue (bias2 + residual, xs bookkeeping, x_out, act_out) for rows m < VM
+// Issue order M1(0 .. NB-2), { M1(i+NB-1), M2(i) }: P1(i) runs under the following M1s, P2(i) under the next ones; D1, D2
+// and Hs have NB buffers (NB tiles in flight per CTA: the per-tile chain copy → M1 → P1 → M2 → P2 is ~7 µs long, its
+// bare barrier skeleton alone 1.5 µs).  Warps: 0 producer, 1 issuer, then EW epilogue warps (4 per 32 columns pair-up: warp w handles TMEM lane
+// group w % 4 and the 32-column groups q ≡ w / 4 mod EW / 4).
+constexpr int VP_RH = 144;           // rows per chunk of the hidden tile in shared memory (128 + taps - 1 <= 144)
+
+struct VcPairParams {
+    VcPairArgs c;
+    int nks1, kc1, nks2, kc2, nstages, halo1, ra, hk, vm;
+    uint32_t a_stage_bytes, w1_stage_bytes, w2_stage_bytes, stage_bytes, hs_bytes, hs_off, bar_off, par_off;
+    int dbg;   // timing experiments (debug knob 11): 1 no P2 body, 2 no A copies, 8 no MMAs, 16 no P1 body
+    int wres;            // both weight sets stay in shared memory for the whole kernel (<= 50 KB): the ring carries A only
+    uint32_t w_off;
+};
+
+template <int C>
+__global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) vc_pair_tc_kernel(const VcPairParams p) {
+    constexpr int EW = C >= 64 ? 8 : 4;              // epilogue warps
+    constexpr int QS = EW / 4;                       // 32-column groups handled in parallel
+    constexpr int NTHREADS = 64 + EW * 32;
+    constexpr int NB = 2;              // tiles in flight per CTA: D1, D2 and Hs buffers (2 NB C TMEM columns)
+    extern __shared__ __align__(1024) uint8_t vp_smem[];
+    uint8_t* hs = vp_smem + p.hs_off;                // [NB][C/8][VP_RH][16 B]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(vp_smem + p.bar_off);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = full_bar + p.nstages;
+    uint64_t* d1_full = empty_bar + p.nstages;       // [NB] each below
+    uint64_t* d1_empty = d1_full + NB;
+    uint64_t* hs_full = d1_empty + NB;
+    uint64_t* hs_empty = hs_full + NB;
+    uint64_t* d2_full = hs_empty + NB;
+    uint64_t* d2_empty = d2_full + NB;
+    uint64_t* w_bar = d2_empty + NB;                 // resident weights have landed (p.wres)
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(w_bar + 1);
+    float* s_b1 = reinterpret_cast<float*>(vp_smem + p.par_off);
+    float* s_b2 = s_b1 + C;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < C; i += NTHREADS) {
+        s_b1[i] = p.c.bias1[i];
+        s_b2[i] = p.c.bias2[i];
+    }
+    for (uint32_t i = threadIdx.x; i < NB * p.hs_bytes / 16; i += NTHREADS) reinterpret_cast<uint4*>(hs)[i] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < p.nstages; ++i) {
+            ptx::mbar_init(&full_bar[i], 1);
+            ptx::mbar_init(&empty_bar[i], 1);
+        }
+        ptx::mbar_init(w_bar, 1);
+        for (int i = 0; i < NB; ++i) {
+            ptx::mbar_init(&d1_full[i], 1);
+            ptx::mbar_init(&d1_empty[i], EW);
+            ptx::mbar_init(&hs_full[i], EW);
+            ptx::mbar_init(&hs_empty[i], 1);
+            ptx::mbar_init(&d2_full[i], 1);
+            ptx::mbar_init(&d2_empty[i], EW);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<2 * NB * C>(tmem_ptr);
+    ptx::fence_proxy_async();                        // the zeroed pad rows of Hs are read by the MMA (async proxy)
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;            // columns: D1[0..NB) D2[0..NB)
+    if (p.wres && warp == 0 && ptx::elect_one()) {   // weights do not depend on the previous kernel: fetch them under its tail
+        const uint32_t b1 = (uint32_t)p.nks1 * p.w1_stage_bytes, b2 = (uint32_t)p.nks2 * p.w2_stage_bytes;
+        ptx::mbar_expect_tx(w_bar, b1 + b2);
+        ptx::bulk_g2s(vp_smem + p.w_off, p.c.w1_bf, b1, w_bar);
+        ptx::bulk_g2s(vp_smem + p.w_off + b1, p.c.w2_bf, b2, w_bar);
+    }
+    ptx::griddep_launch();
+    ptx::griddep_wait();
+    const int64_t total = (int64_t)(*p.c.total_frames) << p.c.shift;
+    const int64_t m_tiles = (total + p.vm - 1) / p.vm;
+    // tiles of this CTA: t = blockIdx.x + j * gridDim.x, j = 0 .. n_mine-1
+    const int64_t n_mine = m_tiles > blockIdx.x ? (m_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const uint32_t a_rows_bytes = (uint32_t)(VC_BM + 2 * p.halo1) * 16;
+
+    if (warp == 0) {
+        // ===================== producer: stages in the issuer's order M1(0), { M1(j+1), M2(j) } =====================
+        if (ptx::elect_one()) {
+            uint32_t it = 0;
+            auto load1 = [&](int64_t j) {
+                const int64_t h0 = (blockIdx.x + j * gridDim.x) * (int64_t)p.vm - p.hk;
+                for (int ksg = 0; ksg < p.nks1; ++ksg, ++it) {
+                    const int s = it % p.nstages;
+                    ptx::mbar_wait_sleep(&empty_bar[s], ((it / p.nstages) & 1) ^ 1, 64);
+                    uint8_t* sa = vp_smem + (size_t)s * p.stage_bytes;
+                    ptx::mbar_expect_tx(&full_bar[s], ((p.dbg & 2) ? 0u : (uint32_t)p.kc1 * a_rows_bytes) + (p.wres ? 0u : p.w1_stage_bytes));
+                    for (int c = 0; c < ((p.dbg & 2) ? 0 : p.kc1); ++c)
+                        ptx::bulk_g2s(sa + (size_t)c * p.ra * 16,
+                                      p.c.a + ((int64_t)(ksg * p.kc1 + c) * p.c.a_rows_phys + DX_VC_HALO + h0 - p.halo1) * 8,
+                                      a_rows_bytes, &full_bar[s]);
+                    if (!p.wres)
+                        ptx::bulk_g2s(sa + p.a_stage_bytes, reinterpret_cast<const uint8_t*>(p.c.w1_bf) + (int64_t)ksg * p.w1_stage_bytes,
+                                      p.w1_stage_bytes, &full_bar[s]);
+                }
+            };
+            auto load2 = [&]() {
+                for (int ksg = 0; ksg < (p.wres ? 0 : p.nks2); ++ksg, ++it) {
+                    const int s = it % p.nstages;
+                    ptx::mbar_wait_sleep(&empty_bar[s], ((it / p.nstages) & 1) ^ 1, 64);
+                    uint8_t* sa = vp_smem + (size_t)s * p.stage_bytes;
+                    ptx::mbar_expect_tx(&full_bar[s], p.w2_stage_bytes);
+                    ptx::bulk_g2s(sa + p.a_stage_bytes, reinterpret_cast<const uint8_t*>(p.c.w2_bf) + (int64_t)ksg * p.w2_stage_bytes,
+                                  p.w2_stage_bytes, &full_bar[s]);
+                }
+            };
+            for (int64_t j = 0; j < NB - 1 && j < n_mine; ++j) load1(j);
+            for (int64_t j = 0; j < n_mine; ++j) {
+                if (j + NB - 1 < n_mine) load1(j + NB - 1);
+                load2();
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = ptx::make_idesc_bf16(VC_BM, C);
+        const uint32_t a_lbo = (uint32_t)p.ra * 16, b_lbo = C * 16, h_lbo = VP_RH * 16;
+        uint32_t it = 0;
+        const uint32_t wres1 = ptx::smem_u32(vp_smem + p.w_off), wres2 = wres1 + (uint32_t)p.nks1 * p.w1_stage_bytes;
+        if (p.wres) ptx::mbar_wait_sleep(w_bar, 0, 32);
+        auto mma1 = [&](int64_t j) {
+            const int b = (int)(j % NB);
+            ptx::mbar_wait_sleep(&d1_empty[b], ((uint32_t)(j / NB) & 1) ^ 1, 64);
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)b * C;
+            for (int ksg = 0; ksg < p.nks1; ++ksg, ++it) {
+                const int s = it % p.nstages;
+                ptx::mbar_wait_sleep(&full_bar[s], (it / p.nstages) & 1, 32);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint32_t sa = ptx::smem_u32(vp_smem + (size_t)s * p.stage_bytes);
+                    const uint32_t sw = p.wres ? wres1 + (uint32_t)ksg * p.w1_stage_bytes : sa + p.a_stage_bytes;
+                    for (int tap = 0; tap < ((p.dbg & 8) ? 0 : p.c.taps); ++tap)
+                        for (int kk = 0; kk < p.kc1 / 2; ++kk)
+                            ptx::mma_bf16(d_tmem, ptx::make_desc(sa + (uint32_t)(tap * p.c.dil) * 16 + (uint32_t)kk * 2 * a_lbo, a_lbo, 128),
+                                          ptx::make_desc(sw + (uint32_t)(tap * p.kc1 + kk * 2) * b_lbo, b_lbo, 128), idesc, (ksg | tap | kk) != 0);
+                    ptx::mma_commit(&empty_bar[s]);
+                    if (ksg == p.nks1 - 1) ptx::mma_commit(&d1_full[b]);
+                }
+                __syncwarp();
+            }
+        };
+        auto mma2 = [&](int64_t j) {
+            const int b = (int)(j % NB);
+            const uint32_t ph = (uint32_t)(j / NB) & 1;
+            ptx::mbar_wait_sleep(&hs_full[b], ph, 32);
+            ptx::mbar_wait_sleep(&d2_empty[b], ph ^ 1, 64);
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(NB + b) * C;
+            const uint32_t sh = ptx::smem_u32(hs + (size_t)b * p.hs_bytes);
+            for (int ksg = 0; ksg < p.nks2; ++ksg) {
+                int s = 0;
+                if (!p.wres) {
+                    s = it % p.nstages;
+                    ptx::mbar_wait_sleep(&full_bar[s], (it / p.nstages) & 1, 32);
+                    ptx::tc_fence_after();
+                    ++it;
+                }
+                if (ptx::elect_one()) {
+                    const uint32_t sw = p.wres ? wres2 + (uint32_t)ksg * p.w2_stage_bytes
+                                               : ptx::smem_u32(vp_smem + (size_t)s * p.stage_bytes) + p.a_stage_bytes;
+                    for (int tap = 0; tap < ((p.dbg & 8) ? 0 : p.c.taps); ++tap)
+                        for (int kk = 0; kk < p.kc2 / 2; ++kk)
+                            ptx::mma_bf16(d_tmem, ptx::make_desc(sh + (uint32_t)tap * 16 + (uint32_t)(ksg * p.kc2 + kk * 2) * h_lbo, h_lbo, 128),
+                                          ptx::make_desc(sw + (uint32_t)(tap * p.kc2 + kk * 2) * b_lbo, b_lbo, 128), idesc, (ksg | tap | kk) != 0);
+                    if (!p.wres) ptx::mma_commit(&empty_bar[s]);
+                    if (ksg == p.nks2 - 1) {
+                        ptx::mma_commit(&d2_full[b]);
+                        ptx::mma_commit(&hs_empty[b]);
+                    }
+                }
+                __syncwarp();
+            }
+        };
+        for (int64_t j = 0; j < NB - 1 && j < n_mine; ++j) mma1(j);
+        for (int64_t j = 0; j < n_mine; ++j) {
+            if (j + NB - 1 < n_mine) mma1(j + NB - 1);
+            mma2(j);
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int ew = warp - 2;
+        const int lane_grp = warp & 3, qoff = ew >> 2;        // a warp may only touch TMEM lanes 32 * (warp % 4) .. +31
+        const int m = lane_grp * 32 + lane;                                   // tile row (TMEM lane)
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(lane_grp * 32) << 16);
+        auto p1 = [&](int64_t j) {
+            const int b = (int)(j % NB);
+            const uint32_t ph = (uint32_t)(j / NB) & 1;
+            const int64_t hr = (blockIdx.x + j * gridDim.x) * (int64_t)p.vm - p.hk + m;      // hidden row of this thread
+            const bool hv = hr >= 0 && hr < total && p.c.e.frame_utt[hr >> p.c.shift] >= 0;
+            ptx::mbar_wait_sleep(&d1_full[b], ph, 64);
+            ptx::tc_fence_after();
+            ptx::mbar_wait_sleep(&hs_empty[b], ph ^ 1, 64);                    // M2(j - 2) has finished reading Hs[b]
+            uint8_t* dst = hs + (size_t)b * p.hs_bytes + (size_t)m * 16;
+#pragma unroll 1
+            for (int q = qoff; q < ((p.dbg & 16) ? 0 : C / 32); q += QS) {
+                float v[32];
+                ptx::tmem_ld32(lane_addr + (uint32_t)b * C + q * 32, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 pk;
+                    uint32_t* w = reinterpret_cast<uint32_t*>(&pk);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float x0 = vc_lrelu(v[c * 8 + 2 * e] + s_b1[q * 32 + c * 8 + 2 * e]);
+                        const float x1 = vc_lrelu(v[c * 8 + 2 * e + 1] + s_b1[q * 32 + c * 8 + 2 * e + 1]);
+                        w[e] = hv ? vc_pack2(x0, x1) : 0u;
+                    }
+                    *reinterpret_cast<uint4*>(dst + (size_t)(q * 4 + c) * VP_RH * 16) = pk;
+                }
+            }
+            ptx::tc_fence_before();
+            ptx::fence_proxy_async();                                          // Hs stores → visible to the MMA
+            __syncwarp();
+            if (lane == 0) {
+                ptx::mbar_arrive(&d1_empty[b]);
+                ptx::mbar_arrive(&hs_full[b]);
+            }
+        };
+        auto p2 = [&](int64_t j) {
+            const int b = (int)(j % NB);
+            const uint32_t ph = (uint32_t)(j / NB) & 1;
+            const int64_t r = (blockIdx.x + j * gridDim.x) * (int64_t)p.vm + m;               // output row
+            const bool inr = m < p.vm && r < total;
+            const bool valid = inr && p.c.e.frame_utt[r >> p.c.shift] >= 0;
+            VcPre pre;
+            vc_tc_prefetch(p.c.e, r, qoff * 32, valid, pre);
+            ptx::mbar_wait_sleep(&d2_full[b], ph, 64);
+            ptx::tc_fence_after();
+#pragma unroll 1
+            for (int q = qoff; q < C / 32; q += QS) {
+                float v[32];
+                ptx::tmem_ld32(lane_addr + (uint32_t)(NB + b) * C + q * 32, v);
+                if (q > qoff) vc_tc_prefetch(p.c.e, r, q * 32, valid, pre);
+                ptx::tmem_ld_wait();
+                if (inr && !(p.dbg & 1)) vc_tc_finish(p.c.e, r, q * 32, valid, v, pre, s_b2 + q * 32);
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&d2_empty[b]);
+        };
+        for (int64_t j = 0; j < NB - 1 && j < n_mine; ++j) p1(j);
+        for (int64_t j = 0; j < n_mine; ++j) {
+            if (j + NB - 1 < n_mine) p1(j + NB - 1);
+            p2(j);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<2 * NB * C>(tmem_base);
+    }
+}
+
+template <int C>
+static int vc_pair_launch(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
+    static size_t configured = 0;
+    if (smem > configured) {
+        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    ProfScope prof(p.c.tag ? p.c.tag : "vc_pair", s);
+    DX_LAUNCH_PDL((vc_pair_tc_kernel<C>), grid, 64 + (C >= 64 ? 256 : 128), smem, s, p);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s) {
+    DX_REQUIRE(c.C == 32 || c.C == 64 || c.C == 128, "vc_pair: C=%d (32, 64 or 128)", c.C);
+    DX_REQUIRE(c.taps % 2 == 1 && c.taps <= 17 && (c.taps / 2) * c.dil <= DX_VC_HALO - c.taps / 2, "vc_pair: taps=%d dil=%d", c.taps, c.dil);
+    DX_REQUIRE(c.w1_bf && c.w2_bf && c.bias1 && c.bias2, "vc_pair: weights missing (tag %s)", c.tag ? c.tag : "?");
+    DX_REQUIRE(c.e.up == 1 && c.e.c_out == c.C, "vc_pair: epilogue must be up = 1, c_out = C");
+    if (g_vc_sms == 0) {
+        int dev = 0;
+        DX_CHECK_CUDA(cudaGetDevice(&dev));
+        DX_CHECK_CUDA(cudaDeviceGetAttribute(&g_vc_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    VcPairParams p;
+    p.c = c;
+    p.dbg = debug_knob(11);
+    int nt1, ks1, nt2, ks2;
+    vc_conv_tiling(c.taps, c.dil, c.C, c.C, &nt1, &ks1);      // how the weights were packed (vocoder.py)
+    vc_conv_tiling(c.taps, 1, c.C, c.C, &nt2, &ks2);
+    DX_REQUIRE(nt1 == c.C && nt2 == c.C, "vc_pair: tile width %d / %d != C", nt1, nt2);
+    p.nks1 = c.C / ks1; p.kc1 = ks1 / 8;
+    p.nks2 = c.C / ks2; p.kc2 = ks2 / 8;
+    p.hk = c.taps / 2;
+    p.vm = VC_BM - 2 * p.hk;
+    p.halo1 = p.hk * c.dil;
+    p.ra = (int)round_up(VC_BM + 2 * p.halo1, 8);
+    p.a_stage_bytes = (uint32_t)p.kc1 * p.ra * 16;
+    p.w1_stage_bytes = (uint32_t)c.taps * p.kc1 * c.C * 16;
+    p.w2_stage_bytes = (uint32_t)c.taps * p.kc2 * c.C * 16;
+    const uint32_t w_total = (uint32_t)p.nks1 * p.w1_stage_bytes + (uint32_t)p.nks2 * p.w2_stage_bytes;
+    p.wres = (w_total <= 50 * 1024 && !debug_knob(14)) ? 1 : 0;
+    p.stage_bytes = p.a_stage_bytes + (p.wres ? 0u : (p.w1_stage_bytes > p.w2_stage_bytes ? p.w1_stage_bytes : p.w2_stage_bytes));
+    p.hs_bytes = (uint32_t)(c.C / 8) * VP_RH * 16;
+    const int nb = 2;                                       // = NB of the kernel
+    const size_t budget = (c.C == 128 ? 216 : 112) * 1024 - nb * (size_t)p.hs_bytes - 2048 - (p.wres ? w_total : 0);
+    int nst = (int)(budget / p.stage_bytes);
+    if (nst > (p.wres ? 6 : 4)) nst = p.wres ? 6 : 4;
+    DX_REQUIRE(nst >= 2, "vc_pair: stage of %u bytes does not allow 2 stages", p.stage_bytes);
+    p.nstages = nst;
+    p.hs_off = (uint32_t)nst * p.stage_bytes;
+    p.w_off = p.hs_off + nb * p.hs_bytes;
+    p.bar_off = p.w_off + (p.wres ? w_total : 0);
+    p.par_off = (uint32_t)round_up((int64_t)(p.bar_off + (2 * nst + 6 * nb + 1) * sizeof(uint64_t) + 16), 16);
+    const size_t smem = p.par_off + 2 * (size_t)c.C * sizeof(float);
+    const int per_sm = c.C == 128 ? 1 : 2;
+    const int64_t items = (c.rows_bound + p.vm - 1) / p.vm;
+    int grid = (int)(items < (int64_t)g_vc_sms * per_sm ? items : (int64_t)g_vc_sms * per_sm);
+    if (grid < 1) grid = 1;
+    if (c.C == 128) return vc_pair_launch<128>(p, smem, grid, s);
+    if (c.C == 64) return vc_pair_launch<64>(p, smem, grid, s);
+    return vc_pair_launch<32>(p, smem, grid, s);
 }
 
 // ---------------------------------------------------------------------------------------------------------
