@@ -234,6 +234,17 @@ int dx_vocoder_conv_tiling(int taps, int dil, int K, int N, int* nt, int* ks);
 int64_t dx_vocoder_workspace_bytes(const DxVocoderWeights* w, int B, int64_t frame_cap, int mode);
 int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* stream);
 
+/* ---- host-side batch collation for bulk generation ---------------------------------
+ * The padded-batch assembly of DaftExprtDataCollate.__call__ (data_loader.py:214-263) as memcpy / memset into ONE
+ * (pinned) staging block, outside the Python GIL and on `threads` host threads.  All pointers are HOST pointers.
+ * ptrs_host[b * 10 + f]: field f of utterance b — 0 symbols i64 (L_b), 1 durations_float f32 (L_b), 2 durations_int
+ * i64 (L_b), 3 symbols_energy f32 (L_b), 4 symbols_pitch f32 (L_b), 5 frames_energy f32 (T_b), 6 frames_pitch f32
+ * (T_b), 7 mel f32 (M, T_b) row-major, 8 speaker_id i64 (1), 9 spk_emb f32 (E).  lens_host[2 b] = L_b, [2 b + 1] = T_b.
+ * offs_host[12]: byte offsets inside the block of the 12 tensors of DaftExprt.forward (model.py:893-896 order), each
+ * padded to (B, L) / (B, T) / (B, M, T) / (B,) / (B, E); pad regions are zeroed. */
+int dx_host_collate(int B, int L, int T, int M, int E, const void* const* ptrs_host, const int32_t* lens_host,
+                    void* block_host, const int64_t* offs_host, int threads);
+
 #ifdef __cplusplus
 }
 #endif

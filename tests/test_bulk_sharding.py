@@ -105,3 +105,41 @@ def test_two_rank_sharded_run_equals_single_process():
         assert merged[i].shape == (80, out_lens[i])
         # worker processes run the oracle with 2 intra-op threads, this process with the default: last-bit only
         assert torch.allclose(merged[i], single[i], atol=1e-5, rtol=0)
+
+
+def test_staged_block_collate_equals_plain_collate():
+    """The worker-thread collate (numpy copies into a reused staging block, pad tails zeroed) yields the tensors of
+    the plain collate, also when the block held a larger batch before."""
+    hp = C.hparams()
+    stream = synthetic.UtteranceStream(hp, 12, seed=7, lmin=3, lmax=14)
+    in_lens, out_lens = stream.lengths()
+    batches = bulk.plan_batches(in_lens, out_lens, 4)
+    block = torch.full((1 << 20,), 255, dtype=torch.uint8)          # dirty: nothing may leak into the pad regions
+    for idx in batches:
+        layout = bulk.fill_block(block, stream, idx)
+        got = bulk.block_views(block, layout)
+        ref = bulk.collate(stream, idx)
+        assert len(got) == len(ref) == 12
+        for g, r in zip(got, ref):
+            assert g.dtype == r.dtype and g.shape == r.shape and torch.equal(g, r)
+
+
+def test_native_collate_equals_plain_collate():
+    """dx_host_collate (memcpy / memset in the library, 1 and 3 host threads) against the plain collate, on a dirty
+    block; bad lengths are refused."""
+    import pytest as _pt
+    from daft_exprt_b200 import _lib
+    hp = C.hparams()
+    lazy = synthetic.UtteranceStream(hp, 11, seed=5, lmin=2, lmax=15)
+    stream = {f: [lazy[f][i] for i in range(11)] for f in synthetic.UtteranceStream.FIELDS}
+    in_lens, out_lens = lazy.lengths()
+    table = bulk.PointerTable(stream)
+    for threads in (1, 3):
+        block = torch.full((1 << 20,), 170, dtype=torch.uint8)
+        for idx in bulk.plan_batches(in_lens, out_lens, 4):
+            layout = table.fill(block, idx, threads)
+            for g, r in zip(bulk.block_views(block, layout), bulk.collate(stream, idx)):
+                assert g.dtype == r.dtype and g.shape == r.shape and torch.equal(g, r)
+    table.lens[3, 1] = -1
+    with _pt.raises(_lib.DxError):
+        table.fill(torch.zeros(1 << 20, dtype=torch.uint8), [3, 4], 1)

@@ -100,6 +100,7 @@ SIGNATURES = {
     "dx_vocoder_conv_tiling": (C.c_int, [C.c_int] * 4 + [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "dx_vocoder_workspace_bytes": (C.c_int64, [C.POINTER(DxVocoderWeights), C.c_int, C.c_int64, C.c_int]),
     "dx_vocoder_forward": (C.c_int, [C.POINTER(DxVocoderWeights), C.POINTER(DxVocoderArgs), _p]),
+    "dx_host_collate": (C.c_int, [C.c_int] * 5 + [_p, _p, _p, _p, C.c_int]),
     "dx_test_attention": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p, C.c_int64, _p]),
 }
 

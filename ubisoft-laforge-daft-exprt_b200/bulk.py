@@ -95,55 +95,231 @@ def collate(utterances, idx):
 
 
 # ----------------------------------------------------------------------------------------------
+# staged collation: one pinned block per batch, filled with numpy on worker threads
+# ----------------------------------------------------------------------------------------------
+_ALIGN = 256
+_FORWARD_ORDER = ("symbols", "durations_float", "durations_int", "symbols_energy", "symbols_pitch", "input_lengths",
+                  "frames_energy", "frames_pitch", "mel_specs", "output_lengths", "speaker_ids", "spk_embs")
+
+
+def block_layout(B, L, T, M, E):
+    """Byte layout of one batch inside a staging block (the plan of ``data_loader.DaftExprtDataCollate``):
+    ``{name: (offset, nbytes, torch dtype, shape)}`` and the total size."""
+    i8, f4 = torch.int64, torch.float32
+    plan = [("symbols", i8, (B, L)), ("durations_int", i8, (B, L)), ("input_lengths", i8, (B,)), ("output_lengths", i8, (B,)),
+            ("speaker_ids", i8, (B,)), ("durations_float", f4, (B, L)), ("symbols_energy", f4, (B, L)),
+            ("symbols_pitch", f4, (B, L)), ("frames_energy", f4, (B, T)), ("frames_pitch", f4, (B, T)),
+            ("mel_specs", f4, (B, M, T)), ("spk_embs", f4, (B, E))]
+    layout, off = {}, 0
+    for name, dt, shape in plan:
+        n = 1
+        for d in shape:
+            n *= d
+        nbytes = n * (8 if dt == i8 else 4)
+        layout[name] = (off, nbytes, dt, shape)
+        off += (nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+    return layout, max(off, _ALIGN)
+
+
+def fill_block(block, utterances, idx):
+    """Collate the utterances ``idx`` (descending symbol count) into the uint8 staging tensor ``block`` (reference
+    ``data_loader.py:214-263``: right zero padding).  numpy slice copies — they release the GIL for the large mel rows,
+    so several batches can be collated side by side — and only the pad tails are zeroed, not the whole block.
+    Returns the layout."""
+    import numpy as np
+    B = len(idx)
+    lens = [int(utterances["symbols"][i].shape[0]) for i in idx]
+    tlens = [int(utterances["mel"][i].shape[1]) for i in idx]
+    L, T = max(lens), max(tlens)
+    M = int(utterances["mel"][idx[0]].shape[0])
+    E = int(utterances["spk_emb"][idx[0]].shape[0])
+    layout, total = block_layout(B, L, T, M, E)
+    assert total <= block.numel(), (total, block.numel())
+    raw = block.numpy()
+    v = {}
+    for name, (off, nbytes, dt, shape) in layout.items():
+        v[name] = raw[off:off + nbytes].view(np.int64 if dt == torch.int64 else np.float32).reshape(shape)
+    per_l = (("symbols", "symbols"), ("durations_float", "durations_float"), ("durations_int", "durations_int"),
+             ("symbols_energy", "symbols_energy"), ("symbols_pitch", "symbols_pitch"))
+    for b, i in enumerate(idx):
+        l, t = lens[b], tlens[b]
+        for dst, src in per_l:
+            row = v[dst][b]
+            row[:l] = utterances[src][i].numpy()
+            row[l:] = 0
+        for dst, src in (("frames_energy", "frames_energy"), ("frames_pitch", "frames_pitch")):
+            row = v[dst][b]
+            row[:t] = utterances[src][i].numpy()
+            row[t:] = 0
+        mel = v["mel_specs"][b]
+        mel[:, :t] = utterances["mel"][i].numpy()
+        mel[:, t:] = 0
+        v["input_lengths"][b], v["output_lengths"][b] = l, t
+        v["speaker_ids"][b] = int(utterances["speaker_id"][i])
+        v["spk_embs"][b] = utterances["spk_emb"][i].numpy()
+    return layout
+
+
+class PointerTable:
+    """Host pointers and lengths of every utterance of an in-memory stream, gathered once, so that a batch is collated
+    by ONE native call (``dx_host_collate``: memcpy / memset outside the GIL, several host threads) instead of ~700
+    Python-level slice assignments.  ``utterances``: the dict of per-utterance lists ``collate`` takes; tensors must be
+    contiguous CPU tensors of the reference's dtypes (int64 / float32) and are kept alive by this object."""
+
+    _SRC = (("symbols", torch.int64), ("durations_float", torch.float32), ("durations_int", torch.int64),
+            ("symbols_energy", torch.float32), ("symbols_pitch", torch.float32), ("frames_energy", torch.float32),
+            ("frames_pitch", torch.float32), ("mel", torch.float32), ("speaker_id", torch.int64), ("spk_emb", torch.float32))
+
+    def __init__(self, utterances, n=None):
+        import numpy as np
+        n = len(utterances["symbols"]) if n is None else n
+        self.n = n
+        self.keep = []
+        self.ptrs = np.zeros((n, len(self._SRC)), dtype=np.uint64)
+        self.lens = np.zeros((n, 2), dtype=np.int32)
+        for i in range(n):
+            for f, (name, dt) in enumerate(self._SRC):
+                t = utterances[name][i]
+                if t.dtype != dt or not t.is_contiguous() or t.device.type != "cpu":
+                    t = t.to(device="cpu", dtype=dt).contiguous()
+                self.keep.append(t)
+                self.ptrs[i, f] = t.data_ptr()
+            self.lens[i, 0] = utterances["symbols"][i].shape[0]
+            self.lens[i, 1] = utterances["mel"][i].shape[1]
+        self.M = int(utterances["mel"][0].shape[0])
+        self.E = int(utterances["spk_emb"][0].numel())
+
+    def fill(self, block, idx, threads=1):
+        """Native collate of the utterances ``idx`` into the uint8 staging tensor ``block``; returns the layout."""
+        import ctypes
+        import numpy as np
+        from . import _lib
+        ids = np.asarray(idx, dtype=np.int64)
+        lens = np.ascontiguousarray(self.lens[ids])
+        ptrs = np.ascontiguousarray(self.ptrs[ids])
+        B, L, T = len(idx), int(lens[:, 0].max()), int(lens[:, 1].max())
+        layout, total = block_layout(B, L, T, self.M, self.E)
+        assert total <= block.numel(), (total, block.numel())
+        offs = np.array([layout[name][0] for name in _FORWARD_ORDER], dtype=np.int64)
+        _lib.check(_lib.load().dx_host_collate(B, L, T, self.M, self.E, ctypes.c_void_p(ptrs.ctypes.data),
+                                               ctypes.c_void_p(lens.ctypes.data), ctypes.c_void_p(block.data_ptr()),
+                                               ctypes.c_void_p(offs.ctypes.data), int(threads)), "dx_host_collate")
+        return layout
+
+
+def block_views(buf, layout):
+    """The 12 tensors of ``DaftExprt.forward`` as views of a staging block or of its device mirror."""
+    out = []
+    for name in _FORWARD_ORDER:
+        off, nbytes, dt, shape = layout[name]
+        out.append(buf[off:off + nbytes].view(dt).view(shape))
+    return tuple(out)
+
+
+# ----------------------------------------------------------------------------------------------
 # execution
 # ----------------------------------------------------------------------------------------------
 class BulkRunner:
-    """Runs ``forward`` over this rank's batches with a two-deep pipeline: while batch k computes,
-    batch k+1 is collated + copied H2D on a side stream and batch k-1's mel goes D2H into pinned
-    memory and is handed to ``sink(utt_id, mel (80, T_b) numpy view)`` on a writer thread — the
-    per-item crop of the reference (``fine_tune.py:77-80``) without its blocking ``.cpu()``."""
+    """Runs ``forward`` over this rank's batches as a pipeline (``fine_tune.py:62-129`` without its blocking steps):
 
-    def __init__(self, model, sink=None, device=None):
+    * ``workers`` threads collate the next batches into a ring of pinned staging blocks — natively
+      (``PointerTable.fill`` → ``dx_host_collate``, no GIL, ``collate_threads`` host threads per batch) when the
+      utterances are in memory, else ``fill_block``,
+    * the main thread sends a block H2D as ONE copy on a side stream and runs ``forward`` on views of its device mirror,
+    * batch k-1's mel goes D2H into pinned memory and a writer thread hands ``sink(utt_id, mel (80, T_b) numpy view)``
+      the per-item crops (the reference's ``fine_tune.py:77-80`` without its blocking ``.cpu()``).
+
+    On a CPU model (tests) the same plan runs unstaged."""
+
+    def __init__(self, model, sink=None, device=None, workers=2, slots=6, collate_threads=4):
         self.model = model
         self.sink = sink
         self.device = device if device is not None else model.device
         self.frames = 0
+        self.workers, self.slots, self.collate_threads = max(1, int(workers)), max(3, int(slots)), max(1, int(collate_threads))
 
     def run(self, utterances, batches, my_batch_ids):
+        if self.device.type != "cuda":
+            return self._run_unstaged(utterances, batches, my_batch_ids)
+        from concurrent.futures import ThreadPoolExecutor
         dev = self.device
-        use_cuda = dev.type == "cuda"
-        copy_stream = torch.cuda.Stream(dev) if use_cuda else None
+        if not my_batch_ids:
+            return self.frames
+        # in-memory streams (dict of lists / PointerTable) are collated natively; lazy streams fall back to numpy copies
+        table = utterances if isinstance(utterances, PointerTable) else None
+        if table is None and isinstance(utterances, dict) and isinstance(utterances.get("symbols"), (list, tuple)):
+            table = PointerTable(utterances)
+        # capacity of a staging block: the largest batch of this shard
+        cap = 0
+        for k in my_batch_ids:
+            idx = batches[k]
+            if table is not None:
+                L, T = int(table.lens[idx, 0].max()), int(table.lens[idx, 1].max())
+                M, E = table.M, table.E
+            else:
+                L = max(int(utterances["symbols"][i].shape[0]) for i in idx)
+                T = max(int(utterances["mel"][i].shape[1]) for i in idx)
+                M, E = int(utterances["mel"][idx[0]].shape[0]), int(utterances["spk_emb"][idx[0]].shape[0])
+            cap = max(cap, block_layout(len(idx), L, T, M, E)[1])
+        S = self.slots
+        blocks = [torch.empty(cap, dtype=torch.uint8, pin_memory=True) for _ in range(S)]
+        mirrors = [torch.empty(cap, dtype=torch.uint8, device=dev) for _ in range(S)]
+        h2d_done = [None] * S                 # the block may be refilled once its last H2D has completed
+        fwd_done = [None] * S                 # the mirror may be overwritten once the forward reading it has completed
+        copy_stream = torch.cuda.Stream(dev)
         q = queue.Queue(maxsize=4)
         writer = threading.Thread(target=self._writer, args=(q,), daemon=True)
         writer.start()
 
-        def stage(k):
-            host = collate(utterances, batches[k])
-            if not use_cuda:
-                return host, host, None
-            with torch.cuda.stream(copy_stream):
-                d = tuple(t.to(dev, non_blocking=True) for t in host)
-                ev = torch.cuda.Event()
-                ev.record(copy_stream)
-            return host, d, ev
+        def collate_into(pos):
+            s = pos % S
+            if h2d_done[s] is not None:
+                h2d_done[s].synchronize()
+            if table is not None:
+                return table.fill(blocks[s], batches[my_batch_ids[pos]], self.collate_threads)
+            return fill_block(blocks[s], utterances, batches[my_batch_ids[pos]])
 
-        nxt = stage(my_batch_ids[0]) if my_batch_ids else None
-        for pos, k in enumerate(my_batch_ids):
-            host, d, ev = nxt
-            if ev is not None:
-                torch.cuda.current_stream(dev).wait_event(ev)
-            out = self.model(d)
-            nxt = stage(my_batch_ids[pos + 1]) if pos + 1 < len(my_batch_ids) else None
-            mel = out[3][0]
-            if use_cuda:
+        n = len(my_batch_ids)
+        depth = min(S - 1, self.workers + 1)
+        with ThreadPoolExecutor(max_workers=self.workers) as pool:
+            futs = {pos: pool.submit(collate_into, pos) for pos in range(min(depth, n))}
+            for pos in range(n):
+                s = pos % S
+                layout = futs.pop(pos).result()
+                nbytes = max(o + b for o, b, _, _ in layout.values())
+                with torch.cuda.stream(copy_stream):
+                    if fwd_done[s] is not None:
+                        copy_stream.wait_event(fwd_done[s])
+                    mirrors[s][:nbytes].copy_(blocks[s][:nbytes], non_blocking=True)
+                    h2d_done[s] = torch.cuda.Event()
+                    h2d_done[s].record(copy_stream)
+                if pos + depth < n:           # its slot is the one whose H2D was enqueued an iteration ago at the latest
+                    futs[pos + depth] = pool.submit(collate_into, pos + depth)
+                torch.cuda.current_stream(dev).wait_event(h2d_done[s])
+                out = self.model(block_views(mirrors[s], layout))
+                fwd_done[s] = torch.cuda.Event()
+                fwd_done[s].record()
+                mel = out[3][0]
                 hmel = torch.empty(mel.shape, dtype=mel.dtype, pin_memory=True)
                 hmel.copy_(mel, non_blocking=True)
                 done = torch.cuda.Event()
                 done.record()
-            else:
-                hmel, done = mel, None
+                out_len = block_views(blocks[s], layout)[9].clone()
+                self.frames += int(out_len.sum())
+                q.put((batches[my_batch_ids[pos]], out_len, hmel, done))
+        q.put(None)
+        writer.join()
+        return self.frames
+
+    def _run_unstaged(self, utterances, batches, my_batch_ids):
+        q = queue.Queue(maxsize=4)
+        writer = threading.Thread(target=self._writer, args=(q,), daemon=True)
+        writer.start()
+        for k in my_batch_ids:
+            host = collate(utterances, batches[k])
+            out = self.model(host)
             self.frames += int(host[9].sum())
-            q.put((batches[k], host[9], hmel, done))
+            q.put((batches[k], host[9], out[3][0], None))
         q.put(None)
         writer.join()
         return self.frames
