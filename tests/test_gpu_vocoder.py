@@ -161,3 +161,14 @@ def test_long_form_utterance_properties():
     ref = H.infer(sd, mels[0, :, :96])[: 64 * 256].numpy()
     got = a[0, : 64 * 256].cpu().numpy()
     assert np.abs(got - ref).sum() / np.abs(ref).sum() <= BF16_REL_L1
+
+
+def test_multi_pass_batches_equal_one_pass():
+    """Batches above max_frames_per_pass are vocoded group by group: same bits as one pass."""
+    lengths = [30, 28, 20, 9, 3]
+    mels, ln = VG.vocoder_case(lengths=lengths, seed=51)
+    gen = _generator("bf16")
+    one = gen(mels.cuda(), ln).cpu()
+    gen.max_frames_per_pass = 50
+    many = gen(mels.cuda(), ln).cpu()
+    assert torch.equal(one, many)

@@ -95,7 +95,7 @@ __global__ void vc_pack_mel_kernel(const float* __restrict__ mel, int C, int T_m
 template <bool BF>
 __global__ void vc_post_kernel(const void* __restrict__ act, int64_t rows_phys, int C, int taps, const float* __restrict__ w,
                                const float* __restrict__ bias, const int32_t* __restrict__ frame_start,
-                               const int64_t* __restrict__ lengths, int hop_shift, int T_max, int B, float* __restrict__ audio) {
+                               int hop_shift, int T_max, int B, float* __restrict__ audio) {
     extern __shared__ float s_w[];                      // [taps][C]
     for (int i = threadIdx.x; i < taps * C; i += blockDim.x) s_w[i] = w[i];
     ptx::griddep_launch();
@@ -246,7 +246,7 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
     const int64_t cap = a->frame_cap;
     int hop = 1;
     for (int i = 0; i < w->n_stages; ++i) hop *= w->up[i];
-    DX_REQUIRE((cap * hop) < (1ll << 31) * 64, "dx_vocoder_forward: frame_cap too large");
+    DX_REQUIRE(cap < (1ll << 31) / hop * 128, "dx_vocoder_forward: frame_cap=%lld too large (row tiles are counted in int32)", (long long)cap);
     VcLayout L;
     vc_carve(w, a->B, cap, a->mode, a->workspace, &L);
     DX_REQUIRE(L.bytes <= a->workspace_bytes, "dx_vocoder_forward: workspace %lld < %lld bytes", (long long)a->workspace_bytes, (long long)L.bytes);
@@ -355,10 +355,10 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
         if (bf) {
             DX_LAUNCH_PDL(vc_post_kernel<true>, dim3((unsigned)((n + 255) / 256)), dim3(256), smem, s, (const void*)L.next,
                           cap * hop + 2 * DX_VC_HALO, w->post.K, w->post.taps, w->post.w, w->post.bias, (const int32_t*)L.frame_start,
-                          a->lengths, ilog2(hop), a->T_max, a->B, a->audio);
+                          ilog2(hop), a->T_max, a->B, a->audio);
         } else {
             DX_LAUNCH_PDL(vc_post_kernel<false>, dim3((unsigned)((n + 255) / 256)), dim3(256), smem, s, (const void*)L.next,
-                          (int64_t)0, w->post.K, w->post.taps, w->post.w, w->post.bias, (const int32_t*)L.frame_start, a->lengths,
+                          (int64_t)0, w->post.K, w->post.taps, w->post.w, w->post.bias, (const int32_t*)L.frame_start,
                           ilog2(hop), a->T_max, a->B, a->audio);
         }
         DX_CHECK_LAUNCH();

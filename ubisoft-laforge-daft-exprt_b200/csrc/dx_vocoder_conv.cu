@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
     } else {
         // ===================== epilogue (warps 2 .. 2+EW-1) =====================
         const int lane_grp = warp & 3;                 // TMEM lanes 32*lane_grp .. +31 (a warp may only touch lanes 32 * (warp % 4) ..)
-        const int qoff = (warp - 2) >> 2;              // this warp's 32-column groups: q = qoff, qoff + QS, ...
+        const int qoff = (warp - 2) >> 2;              // this warp's 32-column groups: q = qoff, qoff + QS, ... (0 with EW = 4)
         uint32_t tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int m_tile = (int)(item / p.n_tiles), n_tile = (int)(item % p.n_tiles);

@@ -147,6 +147,9 @@ class HiFiGANGenerator(torch.nn.Module):
             self.register_buffer(name.replace(".", "__") + "__bias", torch.zeros(cout))
         self._prepared = None
         self._ws = {}
+        # a pass needs ~160 KB of workspace per frame (bf16 mode; 4 bytes more per element in fp32 mode): larger
+        # batches are vocoded in several passes over groups of utterances (identical results, tests/test_gpu_vocoder.py)
+        self.max_frames_per_pass = 65536
 
     # ---- checkpoint -------------------------------------------------------------------------------------------
     def state_dict(self, *a, **k):
@@ -281,8 +284,10 @@ class HiFiGANGenerator(torch.nn.Module):
             raise RuntimeError(f"expected mel of shape (B, {self.config['model_in_dim']}, T), got {tuple(x.shape)}")
         x = x.to(device=dev, dtype=torch.float32).contiguous()
         B, _, T = x.shape
+        host = None
         if lengths is None:
             total = B * T
+            host = torch.full((B,), T, dtype=torch.int64)
             len_dev = torch.full((B,), T, dtype=torch.int64, device=dev)
         else:
             if torch.is_tensor(lengths) and lengths.is_cuda:
@@ -294,9 +299,25 @@ class HiFiGANGenerator(torch.nn.Module):
                     raise ValueError("lengths must hold one value in [0, T] per utterance")
                 total = int(host.sum())
                 len_dev = host.to(dev)
+        audio = torch.empty(B, 1, T * self.hop, device=dev)
+        if total > self.max_frames_per_pass and B > 1 and host is not None:
+            # groups of consecutive utterances with at most max_frames_per_pass frames each
+            b0 = 0
+            while b0 < B:
+                b1, acc = b0 + 1, int(host[b0])
+                while b1 < B and acc + int(host[b1]) <= self.max_frames_per_pass:
+                    acc += int(host[b1])
+                    b1 += 1
+                self._run(W, x[b0:b1], len_dev[b0:b1], b1 - b0, T, acc, audio[b0:b1])
+                b0 = b1
+        else:
+            self._run(W, x, len_dev, B, T, total, audio)
+        return audio
+
+    def _run(self, W, x, len_dev, B, T, total, audio):
+        lib = _lib.load()
         frame_cap = lib.dx_vocoder_frame_cap(B, total)
         ws = self._workspace(W, B, frame_cap)
-        audio = torch.empty(B, 1, T * self.hop, device=dev)
         a = _lib.DxVocoderArgs()
         a.B, a.T_max, a.mode, a.frame_cap = B, T, _MODES[self.compute_mode], frame_cap
         a.mel, a.lengths, a.audio = x.data_ptr(), len_dev.data_ptr(), audio.data_ptr()
