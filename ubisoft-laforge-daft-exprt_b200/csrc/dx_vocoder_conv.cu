@@ -323,6 +323,12 @@ int vc_conv_bf16(const VcConvArgs& c, cudaStream_t s) {
 // and Hs have NB buffers (NB tiles in flight per CTA: the per-tile chain copy → M1 → P1 → M2 → P2 is ~7 µs long, its
 // bare barrier skeleton alone 1.5 µs).  Warps: 0 producer, 1 issuer, then EW epilogue warps (4 per 32 columns pair-up: warp w handles TMEM lane
 // group w % 4 and the 32-column groups q ≡ w / 4 mod EW / 4).
+#define VP_TRACE(j, slot)                                                                            \
+    do {                                                                                             \
+        if constexpr (TR) {                                                                          \
+            if (blockIdx.x == 0 && (j) < 64) p.trace[8 + 16 * (j) + (slot)] = clock64();                 \
+        }                                                                                            \
+    } while (0)
 constexpr int VP_RH = 144;           // rows per chunk of the hidden tile in shared memory (128 + taps - 1 <= 144)
 
 struct VcPairParams {
@@ -330,13 +336,16 @@ struct VcPairParams {
     int nks1, kc1, nks2, kc2, nstages, halo1, ra, hk, vm;
     uint32_t a_stage_bytes, w1_stage_bytes, w2_stage_bytes, stage_bytes, hs_bytes, hs_off, bar_off, par_off;
     int dbg;   // timing experiments (debug knob 11): 1 no P2 body, 2 no A copies, 8 no MMAs, 16 no P1 body
+    long long* trace;    // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer): 16 slots per tile, see tools/voc_trace.py
     int wres;            // both weight sets stay in shared memory for the whole kernel (<= 50 KB): the ring carries A only
     uint32_t w_off;
 };
 
-template <int C>
-__global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) vc_pair_tc_kernel(const VcPairParams p) {
-    constexpr int EW = C >= 64 ? 8 : 4;              // epilogue warps
+// TR: with the clock64 timeline of CTA 0 (tools/voc_trace.py); a separate instantiation because the 96-register C = 64
+// variant pays ~8 % for the extra live state
+template <int C, bool TR>
+__global__ void __launch_bounds__(64 + (C >= 128 ? 256 : 128), C == 128 ? 1 : 2) vc_pair_tc_kernel(const VcPairParams p) {
+    constexpr int EW = C >= 128 ? 8 : 4;             // epilogue warps
     constexpr int QS = EW / 4;                       // 32-column groups handled in parallel
     constexpr int NTHREADS = 64 + EW * 32;
     constexpr int NB = 2;              // tiles in flight per CTA: D1, D2 and Hs buffers (2 NB C TMEM columns)
@@ -392,6 +401,7 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
     }
     ptx::griddep_launch();
     ptx::griddep_wait();
+    if (TR && blockIdx.x == 0 && threadIdx.x == 0) p.trace[0] = clock64();
     const int64_t total = (int64_t)(*p.c.total_frames) << p.c.shift;
     const int64_t m_tiles = (total + p.vm - 1) / p.vm;
     // tiles of this CTA: t = blockIdx.x + j * gridDim.x, j = 0 .. n_mine-1
@@ -407,6 +417,7 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
                 for (int ksg = 0; ksg < p.nks1; ++ksg, ++it) {
                     const int s = it % p.nstages;
                     ptx::mbar_wait_sleep(&empty_bar[s], ((it / p.nstages) & 1) ^ 1, 64);
+                    if (ksg == 0) VP_TRACE(j, 0);
                     uint8_t* sa = vp_smem + (size_t)s * p.stage_bytes;
                     ptx::mbar_expect_tx(&full_bar[s], ((p.dbg & 2) ? 0u : (uint32_t)p.kc1 * a_rows_bytes) + (p.wres ? 0u : p.w1_stage_bytes));
                     for (int c = 0; c < ((p.dbg & 2) ? 0 : p.kc1); ++c)
@@ -445,11 +456,13 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
             const int b = (int)(j % NB);
             ptx::mbar_wait_sleep(&d1_empty[b], ((uint32_t)(j / NB) & 1) ^ 1, 64);
             ptx::tc_fence_after();
+            if (lane == 0) VP_TRACE(j, 2);
             const uint32_t d_tmem = tmem_base + (uint32_t)b * C;
             for (int ksg = 0; ksg < p.nks1; ++ksg, ++it) {
                 const int s = it % p.nstages;
                 ptx::mbar_wait_sleep(&full_bar[s], (it / p.nstages) & 1, 32);
                 ptx::tc_fence_after();
+                if (ksg == 0 && lane == 0) VP_TRACE(j, 3);
                 if (ptx::elect_one()) {
                     const uint32_t sa = ptx::smem_u32(vp_smem + (size_t)s * p.stage_bytes);
                     const uint32_t sw = p.wres ? wres1 + (uint32_t)ksg * p.w1_stage_bytes : sa + p.a_stage_bytes;
@@ -462,13 +475,16 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
                 }
                 __syncwarp();
             }
+            if (lane == 0) VP_TRACE(j, 4);
         };
         auto mma2 = [&](int64_t j) {
             const int b = (int)(j % NB);
             const uint32_t ph = (uint32_t)(j / NB) & 1;
             ptx::mbar_wait_sleep(&hs_full[b], ph, 32);
+            if (lane == 0) VP_TRACE(j, 5);
             ptx::mbar_wait_sleep(&d2_empty[b], ph ^ 1, 64);
             ptx::tc_fence_after();
+            if (lane == 0) VP_TRACE(j, 6);
             const uint32_t d_tmem = tmem_base + (uint32_t)(NB + b) * C;
             const uint32_t sh = ptx::smem_u32(hs + (size_t)b * p.hs_bytes);
             for (int ksg = 0; ksg < p.nks2; ++ksg) {
@@ -494,6 +510,7 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
                 }
                 __syncwarp();
             }
+            if (lane == 0) VP_TRACE(j, 7);
         };
         for (int64_t j = 0; j < NB - 1 && j < n_mine; ++j) mma1(j);
         for (int64_t j = 0; j < n_mine; ++j) {
@@ -506,13 +523,19 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
         const int lane_grp = warp & 3, qoff = ew >> 2;        // a warp may only touch TMEM lanes 32 * (warp % 4) .. +31
         const int m = lane_grp * 32 + lane;                                   // tile row (TMEM lane)
         const uint32_t lane_addr = tmem_base + ((uint32_t)(lane_grp * 32) << 16);
-        auto p1 = [&](int64_t j) {
+        // row validity comes from frame_utt (a dependent global load, ~1 k cycles even on an L2 hit): every lookup is
+        // issued one loop iteration before it is needed
+        // (the looked-up utterance id stays an int until it is used: comparing it at once would wait for the load)
+        auto row_utt = [&](int64_t row) -> int { return (row >= 0 && row < total) ? p.c.e.frame_utt[row >> p.c.shift] : -1; };
+        auto hrow = [&](int64_t j) -> int64_t { return (blockIdx.x + j * gridDim.x) * (int64_t)p.vm - p.hk + m; };
+        auto orow = [&](int64_t j) -> int64_t { return (blockIdx.x + j * gridDim.x) * (int64_t)p.vm + m; };
+        auto p1 = [&](int64_t j, bool hv) {
             const int b = (int)(j % NB);
             const uint32_t ph = (uint32_t)(j / NB) & 1;
-            const int64_t hr = (blockIdx.x + j * gridDim.x) * (int64_t)p.vm - p.hk + m;      // hidden row of this thread
-            const bool hv = hr >= 0 && hr < total && p.c.e.frame_utt[hr >> p.c.shift] >= 0;
+            if (threadIdx.x == 64) VP_TRACE(j, 8);
             ptx::mbar_wait_sleep(&d1_full[b], ph, 64);
             ptx::tc_fence_after();
+            if (threadIdx.x == 64) VP_TRACE(j, 9);
             ptx::mbar_wait_sleep(&hs_empty[b], ph ^ 1, 64);                    // M2(j - 2) has finished reading Hs[b]
             uint8_t* dst = hs + (size_t)b * p.hs_bytes + (size_t)m * 16;
 #pragma unroll 1
@@ -540,17 +563,20 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
                 ptx::mbar_arrive(&d1_empty[b]);
                 ptx::mbar_arrive(&hs_full[b]);
             }
+            if (threadIdx.x == 64) VP_TRACE(j, 10);
         };
-        auto p2 = [&](int64_t j) {
+        // P2 in two parts: the residual loads of tile j are requested BEFORE P1(j + NB - 1) runs, so their DRAM latency
+        // (the timeline showed ~2.5 k of P2's 4.2 k cycles waiting for them) hides under that P1
+        VcPre pre;
+        auto p2 = [&](int64_t j, bool valid) {
             const int b = (int)(j % NB);
             const uint32_t ph = (uint32_t)(j / NB) & 1;
-            const int64_t r = (blockIdx.x + j * gridDim.x) * (int64_t)p.vm + m;               // output row
+            const int64_t r = orow(j);
             const bool inr = m < p.vm && r < total;
-            const bool valid = inr && p.c.e.frame_utt[r >> p.c.shift] >= 0;
-            VcPre pre;
-            vc_tc_prefetch(p.c.e, r, qoff * 32, valid, pre);
+            if (threadIdx.x == 64) VP_TRACE(j, 11);
             ptx::mbar_wait_sleep(&d2_full[b], ph, 64);
             ptx::tc_fence_after();
+            if (threadIdx.x == 64) VP_TRACE(j, 12);
 #pragma unroll 1
             for (int q = qoff; q < C / 32; q += QS) {
                 float v[32];
@@ -562,32 +588,64 @@ __global__ void __launch_bounds__(64 + (C >= 64 ? 256 : 128), C == 128 ? 1 : 2) 
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&d2_empty[b]);
+            if (threadIdx.x == 64) VP_TRACE(j, 13);
         };
-        for (int64_t j = 0; j < NB - 1 && j < n_mine; ++j) p1(j);
-        for (int64_t j = 0; j < n_mine; ++j) {
-            if (j + NB - 1 < n_mine) p1(j + NB - 1);
-            p2(j);
+        static_assert(NB == 2, "the epilogue loop below is written for two tiles in flight");
+        if constexpr (C <= 64) {
+            // software-pipelined epilogue (163 registers available at 192 threads x 2 CTAs): per iteration the residual of
+            // tile j and the validity lookups of the NEXT iteration are requested first, then P1(j + 1), then P2(j)
+            int hu_next = n_mine > 1 ? row_utt(hrow(1)) : -1;                      // for P1(1)
+            int vu_cur = n_mine > 0 ? row_utt(orow(0)) : -1;                       // for P2(0)
+            if (n_mine > 0) p1(0, row_utt(hrow(0)) >= 0);
+            for (int64_t j = 0; j < n_mine; ++j) {
+                const bool valid = m < p.vm && vu_cur >= 0;
+                vc_tc_prefetch(p.c.e, orow(j), qoff * 32, valid, pre);
+                const int hu_after = j + 2 < n_mine ? row_utt(hrow(j + 2)) : -1;   // consumed in the next iteration
+                const int vu_next = j + 1 < n_mine ? row_utt(orow(j + 1)) : -1;
+                if (j + 1 < n_mine) p1(j + 1, hu_next >= 0);
+                p2(j, valid);
+                hu_next = hu_after;
+                vu_cur = vu_next;
+            }
+        } else {
+            // (8 epilogue warps x 2 CTAs cap a kernel at 96 registers: the pipelined loop then spills and is slower;
+            // measured on the 64-channel variant, stage 2: 2.10 -> 2.32 ms)
+            if (n_mine > 0) p1(0, row_utt(hrow(0)) >= 0);
+            for (int64_t j = 0; j < n_mine; ++j) {
+                if (j + 1 < n_mine) p1(j + 1, row_utt(hrow(j + 1)) >= 0);
+                const bool valid = m < p.vm && row_utt(orow(j)) >= 0;
+                vc_tc_prefetch(p.c.e, orow(j), qoff * 32, valid, pre);
+                p2(j, valid);
+            }
         }
     }
     ptx::tc_fence_before();
     __syncthreads();
+    if (TR && blockIdx.x == 0 && threadIdx.x == 0) {
+        p.trace[1] = clock64();
+        p.trace[2] = n_mine;
+    }
     if (warp == 1) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc<2 * NB * C>(tmem_base);
     }
 }
 
-template <int C>
-static int vc_pair_launch(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
+template <int C, bool TR>
+static int vc_pair_launch2(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
     static size_t configured = 0;
     if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     ProfScope prof(p.c.tag ? p.c.tag : "vc_pair", s);
-    DX_LAUNCH_PDL((vc_pair_tc_kernel<C>), grid, 64 + (C >= 64 ? 256 : 128), smem, s, p);
+    DX_LAUNCH_PDL((vc_pair_tc_kernel<C, TR>), grid, 64 + (C >= 128 ? 256 : 128), smem, s, p);
     DX_CHECK_LAUNCH();
     return 0;
+}
+template <int C>
+static int vc_pair_launch(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
+    return p.trace != nullptr ? vc_pair_launch2<C, true>(p, smem, grid, s) : vc_pair_launch2<C, false>(p, smem, grid, s);
 }
 
 int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s) {
@@ -603,6 +661,8 @@ int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s) {
     VcPairParams p;
     p.c = c;
     p.dbg = debug_knob(11);
+    p.trace = reinterpret_cast<long long*>(trace_buffer((8 + 16 * 64) * sizeof(long long)));
+    if (debug_knob(10) != 0 && (debug_knob(10) != c.C || (debug_knob(15) != 0 && debug_knob(15) != c.taps))) p.trace = nullptr;   // trace filter: C, taps
     int nt1, ks1, nt2, ks2;
     vc_conv_tiling(c.taps, c.dil, c.C, c.C, &nt1, &ks1);      // how the weights were packed (vocoder.py)
     vc_conv_tiling(c.taps, 1, c.C, c.C, &nt2, &ks2);
