@@ -13,3 +13,5 @@ echo "ncu pair rc=$?"; tail -n 2 gpurun_out/ncu_voc_pair.log
 ncu --set full --clock-control none --import-source on -k regex:vc_conv_tc --launch-skip 26 --launch-count 4 -f -o gpurun_out/voc_s1 python tools/voc_one.py 400 16 1 > gpurun_out/ncu_voc_s1.log 2>&1
 echo "ncu s1 rc=$?"
 ls -la gpurun_out | head -30
+for a in "32 7" "64 7" "64 11"; do python tools/voc_trace.py $a > gpurun_out/trace_${a// /_}.txt 2>&1; done
+head -3 gpurun_out/trace_64_7.txt
