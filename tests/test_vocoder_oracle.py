@@ -112,3 +112,27 @@ def test_product_synthetic_checkpoint_equals_the_oracles():
     a, b = V.synthetic_state_dict(seed=5), H.make_state_dict(seed=5)
     assert list(a) == list(b) and all(torch.equal(a[k], b[k]) for k in a)
     assert V.flops_per_frame() == 614_105_088
+
+
+def test_vocoder_cabi_refuses_bad_arguments_without_a_gpu():
+    """Argument validation of dx_vocoder_forward / dx_vocoder_workspace_bytes happens before any CUDA call."""
+    import ctypes
+    lib = _lib.load()
+    W = _lib.DxVocoderWeights()
+    assert lib.dx_vocoder_workspace_bytes(ctypes.byref(W), 1, 128, _lib.MODE_BF16) == -1         # 0 stages
+    assert b"stages" in lib.dx_last_error_string()
+    W.n_stages, W.n_kernels, W.n_layers, W.mel_channels = 4, 3, 3, 80
+    for i, (u, c) in enumerate(zip((8, 8, 2, 2), (256, 128, 64, 32))):
+        W.up[i], W.channels[i] = u, c
+    W.pre.N = 512
+    assert lib.dx_vocoder_workspace_bytes(ctypes.byref(W), 1, 100, _lib.MODE_BF16) == -1         # frame_cap % 128
+    n_bf = lib.dx_vocoder_workspace_bytes(ctypes.byref(W), 2, 256, _lib.MODE_BF16)
+    n_f32 = lib.dx_vocoder_workspace_bytes(ctypes.byref(W), 2, 256, _lib.MODE_F32)
+    assert 0 < n_bf < n_f32                                                                       # bf16 operands are half the size
+    assert 256 * 150_000 < n_bf < 256 * 180_000                                                   # ~160 KB per frame (DESIGN.md)
+    W.up[2] = 3
+    assert lib.dx_vocoder_workspace_bytes(ctypes.byref(W), 2, 256, _lib.MODE_BF16) == -1         # not a power of two
+    W.up[2] = 2
+    a = _lib.DxVocoderArgs()
+    assert lib.dx_vocoder_forward(ctypes.byref(W), ctypes.byref(a), None) != 0                    # NULL tensors
+    assert b"NULL" in lib.dx_last_error_string()
