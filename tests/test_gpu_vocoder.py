@@ -172,3 +172,27 @@ def test_multi_pass_batches_equal_one_pass():
     gen.max_frames_per_pass = 50
     many = gen(mels.cuda(), ln).cpu()
     assert torch.equal(one, many)
+
+
+@pytest.mark.parametrize("seed", [101, 102, 103])
+def test_random_batch_compositions(seed):
+    """Property sweep: random batch sizes and lengths (including empty utterances and tile-boundary lengths around
+    118 / 122 / 126 = the fused kernel's valid rows per tile at 8x ... 256x the frame rate): fp32 mode against the
+    oracle, bf16 mode batched == single calls bitwise."""
+    g = torch.Generator().manual_seed(seed)
+    B = int(torch.randint(2, 9, (1,), generator=g))
+    lengths = [int(v) for v in torch.randint(0, 40, (B,), generator=g)]
+    lengths[0] = max(lengths[0], 1)
+    lengths[-1] = [15, 29, 59][seed % 3]            # 59 frames * 2 = 118 rows at the first fused stage's rate ... etc.
+    mels, ln = VG.vocoder_case(lengths=lengths, seed=seed)
+    sd = H.make_state_dict(seed=VG.WEIGHT_SEED)
+    ref = H.infer_batch(sd, mels, ln).numpy()
+    _check(_generator("fp32")(mels.cuda(), ln)[:, 0].cpu().numpy(), ref, "fp32")
+    gen = _generator("bf16")
+    batch = gen(mels.cuda(), ln).cpu()
+    _check(batch[:, 0].numpy(), ref, "bf16")
+    for b, n in enumerate(lengths):
+        if n > 0:
+            one = gen(mels[b : b + 1, :, :n].cuda()).cpu()
+            assert torch.equal(one[0, 0], batch[b, 0, : n * 256]), (b, n)
+        assert torch.count_nonzero(batch[b, 0, n * 256 :]) == 0
