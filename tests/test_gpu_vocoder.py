@@ -31,12 +31,14 @@ def _check(audio, ref, mode):
         assert rel <= BF16_REL_L1, rel
 
 
-@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("mode", ["fp32", "bf16", "bf16+fp32res"])
 @pytest.mark.parametrize("name", sorted(VG.VOCODER_CASES))
 def test_generator_matches_golden(name, mode):
+    """bf16 mode with its default bf16 residual stream and with the fp32 residual option (DX_VC_RESIDUAL_F32)."""
     g = C.load_golden(name)
     mels, lengths = VG.vocoder_case(**VG.VOCODER_CASES[name])
-    gen = _generator(mode)
+    gen = _generator(mode.split("+")[0]).set_residual("fp32" if mode.endswith("fp32res") else "bf16")
+    mode = mode.split("+")[0]
     audio = gen(mels.cuda(), lengths)
     torch.cuda.synchronize()
     assert audio.shape == (mels.size(0), 1, mels.size(2) * 256)
@@ -127,6 +129,14 @@ def test_fused_layers_equal_two_launch_layers_bitwise():
     finally:
         lib.dx_set_debug(12, 0)
     assert torch.equal(fused, plain)
+    gen.set_residual("fp32")                                    # same property with the fp32 residual stream
+    fused32 = gen(mels.cuda(), ln).cpu()
+    try:
+        lib.dx_set_debug(12, 1)
+        plain32 = gen(mels.cuda(), ln).cpu()
+    finally:
+        lib.dx_set_debug(12, 0)
+    assert torch.equal(fused32, plain32) and not torch.equal(fused32, fused)
 
 
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])

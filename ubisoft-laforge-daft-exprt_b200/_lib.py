@@ -54,7 +54,7 @@ class DxForwardArgs(C.Structure):
     )
 
 
-VC_GAP, VC_HALO = 4, 32
+VC_GAP, VC_HALO, VC_RESIDUAL_F32 = 4, 32, 1
 
 
 class DxVcConv(C.Structure):
@@ -69,7 +69,7 @@ class DxVocoderWeights(C.Structure):
 
 
 class DxVocoderArgs(C.Structure):
-    _fields_ = [("B", C.c_int32), ("T_max", C.c_int32), ("mode", C.c_int32), ("pad_", C.c_int32),
+    _fields_ = [("B", C.c_int32), ("T_max", C.c_int32), ("mode", C.c_int32), ("flags", C.c_int32),
                 ("frame_cap", C.c_int64), ("mel", _p), ("lengths", _p), ("audio", _p), ("workspace", _p),
                 ("workspace_bytes", C.c_int64)]
 

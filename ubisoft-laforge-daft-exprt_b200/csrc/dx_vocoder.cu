@@ -243,6 +243,7 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
     DX_REQUIRE(a->mode == DX_MODE_F32 || a->mode == DX_MODE_BF16, "dx_vocoder_forward: mode=%d", a->mode);
     DX_REQUIRE(a->frame_cap >= 128 && a->frame_cap % 128 == 0, "dx_vocoder_forward: frame_cap=%lld (multiple of 128)", (long long)a->frame_cap);
     const bool bf = a->mode == DX_MODE_BF16;
+    const int x_bf16 = bf && !(a->flags & DX_VC_RESIDUAL_F32) ? 1 : 0;     // residual stream x: bf16 [C/8][rows][8] or fp32 [C/4][rows][4]
     const int64_t cap = a->frame_cap;
     int hop = 1;
     for (int i = 0; i < w->n_stages; ++i) hop *= w->up[i];
@@ -280,6 +281,7 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
         c.e.out_shift = ilog2(in_rate * up);
         c.e.res = res; c.e.x_out = x_out; c.e.xs = L.xs; c.e.xs_mode = xs_mode;
         c.e.x_rows = cap * in_rate * up;
+        c.e.x_bf16 = x_bf16;
         c.e.n_kernels = (float)w->n_kernels;
         c.e.act = 1;
         c.e.act_out = act_out;
@@ -333,6 +335,7 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
                     pa.e.frame_utt = L.frame_utt; pa.e.out_shift = pa.shift;
                     pa.e.res = res; pa.e.x_out = x_out; pa.e.xs = L.xs; pa.e.xs_mode = xs_mode;
                     pa.e.x_rows = cap * rate;
+                    pa.e.x_bf16 = x_bf16;
                     pa.e.n_kernels = (float)w->n_kernels;
                     pa.e.act = 1; pa.e.act_out = pout; pa.e.act_rows_phys = cap * rate + 2 * DX_VC_HALO;
                     pa.tag = kPairTags[st];

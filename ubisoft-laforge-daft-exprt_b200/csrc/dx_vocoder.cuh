@@ -22,6 +22,7 @@ struct VcEpi {
     float* x_out;                    // or null
     float* xs;                       // (xs_mode != 0)
     int64_t x_rows;                  // rows of the output-rate tensors
+    int x_bf16;                      // res / x_out are bf16 [c_out/8][x_rows][8] (bf16 mode default) instead of fp32
     int xs_mode;                     // 0 none, 1 xs = y, 2 xs += y, 3 y = (xs + y) / n_kernels
     float n_kernels;
     int act;                         // 1: leaky_relu on act_out, 0: identity

@@ -28,8 +28,9 @@ struct VcTcParams {
 // does loads-then-math-then-stores in that program order (res / xs / x_out may alias, so the compiler cannot hoist a
 // load above a store by itself — interleaved, the 8 residual loads became 8 serialised DRAM round trips: 18 k cycles
 // per tile, 3x the rest of the kernel; knob-11 timing experiments).
+template <bool XBF>
 struct VcPre {
-    float4 res[8];
+    float4 res[XBF ? 4 : 8];         // one row's 32 residual channels: bf16 (4 x 16 B) or fp32 (8 x 16 B)
 };
 
 __device__ __forceinline__ uint32_t vc_pack2(float a, float b) {
@@ -37,15 +38,23 @@ __device__ __forceinline__ uint32_t vc_pack2(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
-__device__ __forceinline__ void vc_tc_prefetch(const VcEpi& e, int64_t r, int n, bool valid, VcPre& pre) {
+template <bool XBF>
+__device__ __forceinline__ void vc_tc_prefetch(const VcEpi& e, int64_t r, int n, bool valid, VcPre<XBF>& pre) {
     if (e.res == nullptr || !valid) return;
     const int ph = n / e.c_out, co = n - ph * e.c_out;
-    const float* src = e.res + ((int64_t)(co >> 2) * e.x_rows + r * e.up + ph) * 4;
+    if constexpr (XBF) {
+        const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(e.res) + ((int64_t)(co >> 3) * e.x_rows + r * e.up + ph) * 8;
 #pragma unroll
-    for (int g = 0; g < 8; ++g) pre.res[g] = *reinterpret_cast<const float4*>(src + (int64_t)g * e.x_rows * 4);
+        for (int g = 0; g < 4; ++g) pre.res[g] = *reinterpret_cast<const float4*>(src + (int64_t)g * e.x_rows * 8);
+    } else {
+        const float* src = e.res + ((int64_t)(co >> 2) * e.x_rows + r * e.up + ph) * 4;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) pre.res[g] = *reinterpret_cast<const float4*>(src + (int64_t)g * e.x_rows * 4);
+    }
 }
 
-__device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, bool valid, float* v, const VcPre& pre,
+template <bool XBF>
+__device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, bool valid, float* v, const VcPre<XBF>& pre,
                                              const float* s_bias_n) {
     const int ph = n / e.c_out, co = n - ph * e.c_out;
     const int64_t ro = r * e.up + ph;
@@ -61,7 +70,14 @@ __device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, b
         for (int g = 0; g < 8; ++g) {
             const float4 bb = *reinterpret_cast<const float4*>(s_bias_n + 4 * g);
             float4 y = make_float4(v[4 * g] + bb.x, v[4 * g + 1] + bb.y, v[4 * g + 2] + bb.z, v[4 * g + 3] + bb.w);
-            if (e.res) { y.x += pre.res[g].x; y.y += pre.res[g].y; y.z += pre.res[g].z; y.w += pre.res[g].w; }
+            if (e.res) {
+                if constexpr (XBF) {                                           // 8 bf16 per float4: group g = half (g & 1) of chunk g / 2
+                    const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pre.res[g >> 1]) + (g & 1) * 2;
+                    y.x += __low2float(h2[0]); y.y += __high2float(h2[0]); y.z += __low2float(h2[1]); y.w += __high2float(h2[1]);
+                } else {
+                    y.x += pre.res[g].x; y.y += pre.res[g].y; y.z += pre.res[g].z; y.w += pre.res[g].w;
+                }
+            }
             if (e.xs_mode >= 2) {                                              // xs += resblock(x), hifigan.py:170
                 y.x += xs[g].x; y.y += xs[g].y; y.z += xs[g].z; y.w += xs[g].w;
                 if (e.xs_mode == 3) { y.x /= e.n_kernels; y.y /= e.n_kernels; y.z /= e.n_kernels; y.w /= e.n_kernels; }   // :171
@@ -73,7 +89,16 @@ __device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, b
             for (int g = 0; g < 8; ++g)
                 *reinterpret_cast<float4*>(e.xs + off + g * gs) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
         }
-        if (e.x_out) {
+        if (e.x_out && XBF) {
+            __nv_bfloat16* xo = reinterpret_cast<__nv_bfloat16*>(e.x_out) + ((int64_t)(co >> 3) * e.x_rows + ro) * 8;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 pk;
+                pk.x = vc_pack2(v[8 * c], v[8 * c + 1]); pk.y = vc_pack2(v[8 * c + 2], v[8 * c + 3]);
+                pk.z = vc_pack2(v[8 * c + 4], v[8 * c + 5]); pk.w = vc_pack2(v[8 * c + 6], v[8 * c + 7]);
+                *reinterpret_cast<uint4*>(xo + (int64_t)c * e.x_rows * 8) = pk;
+            }
+        } else if (e.x_out) {
 #pragma unroll
             for (int g = 0; g < 8; ++g)
                 *reinterpret_cast<float4*>(e.x_out + off + g * gs) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
@@ -97,7 +122,7 @@ __device__ __forceinline__ void vc_tc_finish(const VcEpi& e, int64_t r, int n, b
 
 // (8 epilogue warps for NT >= 64 - two per TMEM lane group, alternating 32-column groups - were measured slower:
 // 320 threads x 2 CTAs cap the kernel at 96 registers and the NT = 128 epilogue spills; stage 1 conv2 141 -> 157 us.)
-template <int NT>
+template <int NT, bool XBF>
 __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kernel(const VcTcParams p) {
     constexpr int EW = 4;                            // epilogue warps: one per TMEM lane group
     constexpr int QS = EW / 4;
@@ -206,7 +231,7 @@ __global__ void __launch_bounds__(VC_THREADS, NT == 128 ? 2 : 3) vc_conv_tc_kern
             const int64_t r = (int64_t)m_tile * VC_BM + lane_grp * 32 + lane;
             const bool inr = r < total;
             const bool valid = inr && p.c.e.frame_utt[r >> p.c.in_shift] >= 0;   // all phases of a row share its frame
-            VcPre pre;
+            VcPre<XBF> pre;
             vc_tc_prefetch(p.c.e, r, n_tile * NT + qoff * 32, valid, pre);
             ptx::mbar_wait_sleep(&tfull_bar[acc], acc_ph, 100);
             ptx::tc_fence_after();
@@ -252,17 +277,21 @@ void vc_conv_tiling(int taps, int dil, int K, int N, int* nt, int* ks) {
 
 static int g_vc_sms = 0;
 
-template <int NT>
-static int vc_tc_launch(const VcTcParams& p, size_t smem, int grid, cudaStream_t s) {
+template <int NT, bool XBF>
+static int vc_tc_launch2(const VcTcParams& p, size_t smem, int grid, cudaStream_t s) {
     static size_t configured = 0;
     if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_conv_tc_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_conv_tc_kernel<NT, XBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     ProfScope prof(p.c.tag ? p.c.tag : "vc_conv", s);
-    DX_LAUNCH_PDL((vc_conv_tc_kernel<NT>), grid, VC_THREADS, smem, s, p);
+    DX_LAUNCH_PDL((vc_conv_tc_kernel<NT, XBF>), grid, VC_THREADS, smem, s, p);
     DX_CHECK_LAUNCH();
     return 0;
+}
+template <int NT>
+static int vc_tc_launch(const VcTcParams& p, size_t smem, int grid, cudaStream_t s) {
+    return p.c.e.x_bf16 ? vc_tc_launch2<NT, true>(p, smem, grid, s) : vc_tc_launch2<NT, false>(p, smem, grid, s);
 }
 
 int vc_conv_bf16(const VcConvArgs& c, cudaStream_t s) {
@@ -343,7 +372,7 @@ struct VcPairParams {
 
 // TR: with the clock64 timeline of CTA 0 (tools/voc_trace.py); a separate instantiation because the 96-register C = 64
 // variant pays ~8 % for the extra live state
-template <int C, bool TR>
+template <int C, bool TR, bool XBF>
 __global__ void __launch_bounds__(64 + (C >= 128 ? 256 : 128), C == 128 ? 1 : 2) vc_pair_tc_kernel(const VcPairParams p) {
     constexpr int EW = C >= 128 ? 8 : 4;             // epilogue warps
     constexpr int QS = EW / 4;                       // 32-column groups handled in parallel
@@ -567,7 +596,7 @@ __global__ void __launch_bounds__(64 + (C >= 128 ? 256 : 128), C == 128 ? 1 : 2)
         };
         // P2 in two parts: the residual loads of tile j are requested BEFORE P1(j + NB - 1) runs, so their DRAM latency
         // (the timeline showed ~2.5 k of P2's 4.2 k cycles waiting for them) hides under that P1
-        VcPre pre;
+        VcPre<XBF> pre;
         auto p2 = [&](int64_t j, bool valid) {
             const int b = (int)(j % NB);
             const uint32_t ph = (uint32_t)(j / NB) & 1;
@@ -631,21 +660,23 @@ __global__ void __launch_bounds__(64 + (C >= 128 ? 256 : 128), C == 128 ? 1 : 2)
     }
 }
 
-template <int C, bool TR>
-static int vc_pair_launch2(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
+template <int C, bool TR, bool XBF>
+static int vc_pair_launch3(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
     static size_t configured = 0;
     if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C, TR, XBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     ProfScope prof(p.c.tag ? p.c.tag : "vc_pair", s);
-    DX_LAUNCH_PDL((vc_pair_tc_kernel<C, TR>), grid, 64 + (C >= 128 ? 256 : 128), smem, s, p);
+    DX_LAUNCH_PDL((vc_pair_tc_kernel<C, TR, XBF>), grid, 64 + (C >= 128 ? 256 : 128), smem, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }
 template <int C>
 static int vc_pair_launch(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
-    return p.trace != nullptr ? vc_pair_launch2<C, true>(p, smem, grid, s) : vc_pair_launch2<C, false>(p, smem, grid, s);
+    if (p.trace != nullptr)
+        return p.c.e.x_bf16 ? vc_pair_launch3<C, true, true>(p, smem, grid, s) : vc_pair_launch3<C, true, false>(p, smem, grid, s);
+    return p.c.e.x_bf16 ? vc_pair_launch3<C, false, true>(p, smem, grid, s) : vc_pair_launch3<C, false, false>(p, smem, grid, s);
 }
 
 int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s) {

@@ -140,6 +140,7 @@ class HiFiGANGenerator(torch.nn.Module):
         self.num_upsamples = len(config['upsample_rates'])
         self.hop = int(np.prod(config['upsample_rates']))
         self.compute_mode = "bf16"
+        self.residual = "bf16"           # bf16 mode only: dtype of the residual stream x ("fp32": tighter, 8 % slower)
         # folded (weight-norm-free) parameters under the reference's names: <prefix>.weight / <prefix>.bias
         for name, kind, cin, cout, k, _ in _conv_specs(config):
             shape = (cout, cin, k) if kind == "conv" else (cin, cout, k)
@@ -197,6 +198,14 @@ class HiFiGANGenerator(torch.nn.Module):
         if mode != self.compute_mode:
             self.compute_mode = mode
             self._prepared = None
+        return self
+
+    def set_residual(self, dtype):
+        """bf16 mode: keep the residual stream in "bf16" (default; rel. L1 ≈ 1.2e-2 against the reference on the golden
+        cases) or "fp32" (≈ 1.06e-2, 8 % slower).  fp32 mode is fp32 throughout."""
+        if dtype not in ("bf16", "fp32"):
+            raise ValueError(f"residual {dtype!r}: expected 'bf16' or 'fp32'")
+        self.residual = dtype
         return self
 
     def _apply(self, fn, *a, **k):
@@ -320,6 +329,7 @@ class HiFiGANGenerator(torch.nn.Module):
         ws = self._workspace(W, B, frame_cap)
         a = _lib.DxVocoderArgs()
         a.B, a.T_max, a.mode, a.frame_cap = B, T, _MODES[self.compute_mode], frame_cap
+        a.flags = _lib.VC_RESIDUAL_F32 if self.residual == "fp32" else 0
         a.mel, a.lengths, a.audio = x.data_ptr(), len_dev.data_ptr(), audio.data_ptr()
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         _lib.check(lib.dx_vocoder_forward(C.byref(W), C.byref(a), _lib.stream_ptr()), "dx_vocoder_forward")
@@ -331,7 +341,7 @@ class HiFiGanVocoder:
     download its default checkpoint (hifigan.py:43-68); there is no network here, so a path or ``state_dict`` is
     required."""
 
-    def __init__(self, checkpoint_path=None, config=None, device='cuda', state_dict=None, mode="bf16"):
+    def __init__(self, checkpoint_path=None, config=None, device='cuda', state_dict=None, mode="bf16", residual="bf16"):
         self.device = torch.device(device)
         self.config = DEFAULT_CONFIG if config is None else config
         self.checkpoint_path = checkpoint_path
@@ -343,7 +353,7 @@ class HiFiGanVocoder:
             state_dict = checkpoint.get('generator', checkpoint.get('state_dict', checkpoint))     # hifigan.py:202
         self.generator = HiFiGANGenerator(self.config)
         self.generator.load_state_dict(state_dict)
-        self.generator.to(self.device).eval().set_mode(mode)
+        self.generator.to(self.device).eval().set_mode(mode).set_residual(residual)
 
     def infer(self, mel_spec):
         if isinstance(mel_spec, np.ndarray):
