@@ -87,8 +87,21 @@ class ClockSampler:
 
     def __init__(self, gpu_index):
         self.idx = gpu_index
-        self.lines = []
+        self.lines = []          # (arrival time, csv line)
         self.proc = None
+        self.t0 = self.t1 = None
+
+    def mark_start(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
+
+    def in_window(self):
+        if self.t0 is None:
+            return len(self.lines)
+        t1 = self.t1 if self.t1 is not None else float("inf")
+        return sum(1 for t, _ in self.lines if self.t0 <= t <= t1 + 0.12)
 
     def start(self):
         try:
@@ -100,7 +113,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
 
     def stop(self):
         if self.proc is None:
@@ -108,7 +121,10 @@ class ClockSampler:
         time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        t1 = self.t1 if self.t1 is not None else float("inf")
+        for t, ln in self.lines:
+            if self.t0 is not None and not (self.t0 <= t <= t1 + 0.12):      # only samples taken under the timed load
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -325,13 +341,16 @@ def main():
         torch.cuda.synchronize()
         return t0.elapsed_time(t1)
 
+    # nvidia-smi needs ~1 s to deliver its first sample (longer with 8 GPUs), the timed region is tens of ms: the sampler
+    # starts before the warm-up and only samples that arrive inside the timed window count
+    clocks = ClockSampler(local_rank)
+    clocks.start()
     for _ in range(args.warmup):
         step_resident()
         step_e2e()
     run_pipelined(max(args.warmup, NSLOT + 1))
     sync_all()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
+    clocks.mark_start()
     l0 = lib.dx_launch_count()
     t_res = timed(step_resident, args.steps)
     launches = (lib.dx_launch_count() - l0) // args.steps
@@ -339,6 +358,13 @@ def main():
     t_e2e = timed(step_e2e, args.steps)
     sync_all()
     ms_pipe = run_pipelined(args.steps) / args.steps
+    # a short timed region can fall between two 100 ms samples: keep the same step running (untimed) until at least
+    # three samples have been taken under this load, 4 s at most
+    t_keep = time.perf_counter()
+    while clocks.proc is not None and clocks.in_window() < 3 and time.perf_counter() - t_keep < 4.0:
+        step_resident()
+        torch.cuda.synchronize()
+    clocks.mark_end()
     sync_all()
     clk = clocks.stop()
     # the pipelined loop must produce what the direct call produces
