@@ -148,7 +148,20 @@ typedef struct {
     /* scratch: dx_forward_workspace_bytes(B, L_max, T_max, mode) bytes, 256-byte aligned */
     void    *workspace;
     int64_t  workspace_bytes;
+    /* DX_IO_* bits; 0 = the reference's padded layouts everywhere */
+    int32_t  io_flags, pad_;
 } DxForwardArgs;
+
+/* Packed frame-side I/O (bulk generation, fine_tune.py:62-129: only valid frames cross PCIe).  With
+ * fs[b] = sum of output_lengths[0..b-1] and T_b = output_lengths[b]:
+ *   DX_IO_PACKED_FRAMES  frames_energy / frames_pitch are float[sum T_b] (utterance b at fs[b]) and mel_specs is
+ *                        float[80 * sum T_b]: utterance b is the (80, T_b) row-major block at 80 * fs[b] - the layout of
+ *                        the per-utterance .npy files the reference's loader reads (data_loader.py:150-160).  Frames
+ *                        beyond T_b read as zeros, which is what the reference's collate pads with (data_loader.py:246-259).
+ *   DX_IO_PACKED_MEL_OUT mel_out is float[80 * sum T_b] in the same per-utterance (80, T_b) blocks - exactly the
+ *                        crop fine_tune.py:79 takes from the padded output; nothing is written for padded frames. */
+#define DX_IO_PACKED_FRAMES 1
+#define DX_IO_PACKED_MEL_OUT 2
 
 int64_t dx_forward_workspace_bytes(int B, int L_max, int T_max, int mode);
 int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream);
@@ -247,6 +260,11 @@ int dx_vocoder_forward(const DxVocoderWeights* w, const DxVocoderArgs* a, void* 
  * padded to (B, L) / (B, T) / (B, M, T) / (B,) / (B, E); pad regions are zeroed. */
 int dx_host_collate(int B, int L, int T, int M, int E, const void* const* ptrs_host, const int32_t* lens_host,
                     void* block_host, const int64_t* offs_host, int threads);
+/* Same, with the frame side in the DX_IO_PACKED_FRAMES layout: offs_host[6..8] are the offsets of float[sum T_b],
+ * float[sum T_b] and float[M * sum T_b]; every utterance's mel is one memcpy of its (M, T_b) array, nothing is padded.
+ * T is only the bound the lengths are checked against. */
+int dx_host_collate_packed(int B, int L, int T, int M, int E, const void* const* ptrs_host, const int32_t* lens_host,
+                           void* block_host, const int64_t* offs_host, int threads);
 
 #ifdef __cplusplus
 }

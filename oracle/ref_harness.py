@@ -1,9 +1,11 @@
-"""TEST INFRASTRUCTURE ONLY — imports the *real* reference from /root/reference (read-only).
+"""TEST INFRASTRUCTURE ONLY — imports the *real* reference: from /root/reference (read-only, build container) or,
+where that does not exist (the GPU box), from the byte-identical staged copy ``oracle/_ref`` that
+``oracle/make_ref.py`` makes (git-ignored, travels with the gpurun snapshot).
 
-This exists only in the build container: the GPU box has no /root/reference, so nothing in
-``-m gpu`` tests, ``smoke()`` or ``bench.py`` may call into this module.  It is used to
-(1) pin ``oracle/daft_oracle.py`` (our CPU restatement) against the live reference, and
-(2) generate the golden vectors under ``tests/golden/`` (``tests/golden/make_golden.py``).
+It is used to (1) pin ``oracle/daft_oracle.py`` (our CPU restatement) against the live reference,
+(2) generate the golden vectors under ``tests/golden/`` (``tests/golden/make_golden.py``), and
+(3) time the reference's own CPU forward in ``bench.py --impl reference`` / ``cpu_baseline``.
+Nothing in the product package may import it.
 
 Accommodations (none modify the reference):
   * ``librosa`` / ``matplotlib`` are not installed here and ``daft_exprt/model.py:11`` pulls them
@@ -15,11 +17,26 @@ import os
 import sys
 import types
 
-REFERENCE_SRC = "/root/reference/src"
+_LIVE_SRC = "/root/reference/src"
+_STAGED_SRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _pick_source():
+    # DX_REF_FORCE_STAGED=1: use the staged copy even where /root/reference exists (tests of the GPU-box situation)
+    if os.environ.get("DX_REF_FORCE_STAGED") != "1" and os.path.isfile(os.path.join(_LIVE_SRC, "daft_exprt", "model.py")):
+        return _LIVE_SRC, "/root/reference"
+    if os.path.isfile(os.path.join(_STAGED_SRC, "daft_exprt", "model.py")):
+        from oracle import make_ref
+        if make_ref.verify():
+            return _STAGED_SRC, "oracle/_ref (staged copy of the reference, sha256-verified)"
+    return None, None
+
+
+REFERENCE_SRC, REFERENCE_KIND = _pick_source()
 
 
 def reference_available():
-    return os.path.isfile(os.path.join(REFERENCE_SRC, "daft_exprt", "model.py"))
+    return REFERENCE_SRC is not None
 
 
 def _stub(name, **attrs):
@@ -35,7 +52,7 @@ def _stub(name, **attrs):
 def import_reference_model():
     """Return the reference's ``daft_exprt.model`` module."""
     if not reference_available():
-        raise RuntimeError("reference not present (expected only in the build container)")
+        raise RuntimeError("reference not present (neither /root/reference nor a verified oracle/_ref copy)")
     for name in ("librosa", "matplotlib", "soundfile"):
         try:
             __import__(name)

@@ -55,3 +55,24 @@ def inference_case(name):
 
 def t(a):
     return torch.from_numpy(np.asarray(a))
+
+
+_MEASURED = {}
+
+
+def record(key, value):
+    """Keep the measured error of a bf16 / fp32 comparison (worst value per key over the session) in
+    gpurun_out/parity_measured.json, so that the tolerances in the tests can be read against what the hardware produced."""
+    import json
+    value = float(value)
+    _MEASURED[key] = max(value, _MEASURED.get(key, value))
+    try:
+        d = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        path = os.path.join(d, "parity_measured.json")
+        old = json.load(open(path)) if os.path.isfile(path) else {}
+        for k, v in _MEASURED.items():
+            old[k] = max(v, old.get(k, v))
+        json.dump(old, open(path, "w"), indent=1, sort_keys=True)
+    except (OSError, ValueError):
+        pass

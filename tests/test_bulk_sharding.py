@@ -143,3 +143,59 @@ def test_native_collate_equals_plain_collate():
     table.lens[3, 1] = -1
     with _pt.raises(_lib.DxError):
         table.fill(torch.zeros(1 << 20, dtype=torch.uint8), [3, 4], 1)
+
+
+def test_packed_collate_equals_packed_padded_batch():
+    """dx_host_collate_packed / fill_block(packed=True): the frame side holds exactly the valid frames, per-utterance
+    (80, T_b) blocks, and equals layouts.pack_frames of the padded collate bit for bit; the symbol side is unchanged."""
+    from daft_exprt_b200 import layouts
+    hp = C.hparams()
+    lazy = synthetic.UtteranceStream(hp, 13, seed=6, lmin=2, lmax=15)
+    stream = {f: [lazy[f][i] for i in range(13)] for f in synthetic.UtteranceStream.FIELDS}
+    in_lens, out_lens = lazy.lengths()
+    table = bulk.PointerTable(stream)
+    for idx in bulk.plan_batches(in_lens, out_lens, 5):
+        ref = bulk.collate(stream, idx)
+        e, p, m = layouts.pack_frames(ref[6], ref[7], ref[8], ref[9])
+        for fill in (lambda blk: table.fill(blk, idx, 2, packed=True), lambda blk: bulk.fill_block(blk, stream, idx, packed=True)):
+            block = torch.full((1 << 20,), 85, dtype=torch.uint8)
+            got = bulk.block_views(block, fill(block))
+            for k in (0, 1, 2, 3, 4, 5, 9, 10, 11):
+                assert torch.equal(got[k], ref[k]), k
+            assert torch.equal(got[6], e) and torch.equal(got[7], p) and torch.equal(got[8], m)
+        # round trip of the helpers
+        assert torch.equal(layouts.unpack_mel(m, ref[9], ref[8].shape[2]), ref[8])
+        views = layouts.mel_views(m, ref[9])
+        for b, v in enumerate(views):
+            assert torch.equal(v, ref[8][b, :, :int(ref[9][b])])
+
+
+def test_failing_sink_is_reported_not_hung():
+    """an exception in sink() used to kill the writer thread silently and hang run() on the bounded queue."""
+    hp = C.hparams()
+    stream = synthetic.UtteranceStream(hp, 40, seed=8, lmin=2, lmax=6)
+    in_lens, out_lens = stream.lengths()
+    batches, mine = bulk.plan_shards(in_lens, out_lens, 2, 1)      # 20 batches > queue depth 4
+
+    class _Cheap:
+        device = torch.device("cpu")
+
+        def __call__(self, batch):
+            B, T = batch[8].shape[0], batch[8].shape[2]
+            return None, None, None, [torch.zeros(B, 80, T), batch[9]], None
+
+    calls = []
+
+    def sink(i, mel):
+        calls.append(i)
+        if len(calls) == 3:
+            raise OSError("disk full")
+
+    runner = bulk.BulkRunner(_Cheap(), sink=sink)
+    with pytest.raises(OSError, match="disk full"):
+        runner.run(stream, batches, mine[0])
+    assert len(calls) == 3                       # the sink is not called again after it failed
+    # the runner is reusable afterwards
+    calls.clear()
+    runner2 = bulk.BulkRunner(_Cheap(), sink=lambda i, mel: None)
+    assert runner2.run(stream, batches, mine[0]) == sum(out_lens)

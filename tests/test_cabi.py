@@ -45,7 +45,7 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(_lib.DxBlockWeights) == 18 * 8
     n_ptr = 19 + 14 + 8 + 4
     assert ctypes.sizeof(_lib.DxModelWeights) == n_ptr * 8 + 3 * 4 * 18 * 8 + 16
-    assert ctypes.sizeof(_lib.DxForwardArgs) == 16 + 21 * 8 + 8
+    assert ctypes.sizeof(_lib.DxForwardArgs) == 16 + 21 * 8 + 8 + 8
 
 
 def test_model_mirror_has_reference_layout_and_fails_loudly_on_cpu():

@@ -97,3 +97,33 @@ def test_to_device_feeds_forward_like_parse_batch():
         assert a.dtype == b.dtype and torch.equal(a, b)
     out_a, out_b = model(inputs), model(fast)
     assert torch.equal(out_a[3][0], out_b[3][0]) and torch.equal(out_a[4], out_b[4])
+
+
+def test_collated_batch_pickles_and_survives_dataloader_workers():
+    """ADVICE r1: the reference's prepare_data_loaders uses this collate with num_workers >= 1 (data_loader.py:290-330);
+    the tuple subclass must cross the worker queue and DataLoader's pin_memory re-wrap."""
+    import pickle
+    from torch.utils.data import DataLoader, Dataset
+    from daft_exprt_b200.data_loader import CollatedBatch
+    hp, items = _items(6, 41)
+    batch = DaftExprtDataCollate(hp, pinned=False)(items)
+    clone = pickle.loads(pickle.dumps(batch))
+    assert isinstance(clone, CollatedBatch) and clone.layout == batch.layout
+    _same(clone, batch)
+
+    class _DS(Dataset):
+        def __len__(self):
+            return len(items)
+
+        def __getitem__(self, i):
+            return items[i]
+
+    loader = DataLoader(_DS(), batch_size=3, shuffle=False, num_workers=1, collate_fn=DaftExprtDataCollate(hp))
+    got = list(loader)
+    assert len(got) == 2
+    _same(got[0], DaftExprtDataCollate(hp, pinned=False)(items[:3]))
+    _same(got[1], DaftExprtDataCollate(hp, pinned=False)(items[3:]))
+    # a batch rebuilt without its block (what DataLoader(pin_memory=True) does to sequences) still moves
+    bare = CollatedBatch(tuple(batch))
+    moved = bare.to_device("cpu")
+    assert len(moved) == 12 and torch.equal(moved[8], batch[8])

@@ -14,6 +14,14 @@ pytestmark = pytest.mark.gpu
 
 FP32_MAX_ABS = 1e-3
 BF16_REL_L1 = 2e-2
+# bf16 tolerances of the SECONDARY outputs (the north-star gate is the mel's relative L1 above): 2 x the worst value
+# measured on B200 over every case of this file and test_gpu_round2.py (gpurun_out/parity_measured.json, copied to
+# profiles/r02_parity_measured.json)
+W_BF16_MAX_ABS = 0.2
+W_BF16_MEAN_ABS = 2e-3
+FILM_BF16_MAX_ABS = 6e-2
+ENC_BF16_MAX_ABS = 0.15
+ACCENT_BF16_MAX_ABS = 3e-2
 
 
 @pytest.fixture(scope="module")
@@ -37,9 +45,11 @@ def _check_mel(mel, ref_mel, out_len, mode):
     assert torch.all(mel[~valid] == 0), "padded frames must be exactly zero (FrameDecoder mask, model.py:562)"
     diff = (mel - ref_mel).abs()
     if mode == "fp32":
+        C.record("mel_max_abs_fp32", diff[valid].max())
         assert diff[valid].max().item() <= FP32_MAX_ABS, f"fp32 mel max-abs {diff[valid].max().item():.3e}"
     else:
         rel = (diff[valid].sum() / ref_mel[valid].abs().sum()).item()
+        C.record("mel_rel_l1_bf16", rel)
         assert rel <= BF16_REL_L1, f"bf16 mel rel-L1 {rel:.3e}"
 
 
@@ -51,16 +61,19 @@ def _check_weights(w, ref_w, in_len, out_len, mode):
     valid = (lv & tv).expand_as(ref_w)
     # the bf16 gate of the north star is on the mel; the alignment is a softmax-like ratio that is steep where the
     # predicted range σ is small, so bf16 encoder outputs move it by several 1e-2 in places
-    tol = 1e-4 if mode == "fp32" else 0.2
+    tol = 1e-4 if mode == "fp32" else W_BF16_MAX_ABS
+    C.record(f"weights_max_abs_{mode}", (w - ref_w)[valid].abs().max())
+    C.record(f"weights_mean_abs_{mode}", (w - ref_w)[valid].abs().mean())
     assert (w - ref_w)[valid].abs().max().item() <= tol
     if mode == "bf16":
-        assert (w - ref_w)[valid].abs().mean().item() <= 2e-3
+        assert (w - ref_w)[valid].abs().mean().item() <= W_BF16_MEAN_ABS
     # padded symbols carry exactly zero weight (model.py:503)
     assert torch.all(w[(~lv).expand_as(w)] == 0)
     # column sums agree with the reference's (1 where any Gaussian reaches the frame; the reference's columns
     # underflow to 0 where every p[l, t] underflows, model.py:505)
     colsum, ref_colsum = (w * lv).sum(dim=1), (ref_w * lv).sum(dim=1)
-    assert (colsum - ref_colsum)[tv.squeeze(1)].abs().max().item() <= (1e-4 if mode == "fp32" else 0.2)
+    C.record(f"weights_colsum_max_abs_{mode}", (colsum - ref_colsum)[tv.squeeze(1)].abs().max())
+    assert (colsum - ref_colsum)[tv.squeeze(1)].abs().max().item() <= (1e-4 if mode == "fp32" else W_BF16_MAX_ABS)
 
 
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
@@ -74,13 +87,16 @@ def test_forward_vs_golden(models, mode, name):
     assert torch.equal(dec[1].cpu(), C.t(g["output_lengths"]))
     _check_mel(dec[0], C.t(g["mel"]), batch[9], mode)
     _check_weights(w, C.t(g["weights"]), batch[5], batch[9], mode)
-    tol = 1e-3 if mode == "fp32" else 6e-2
+    tol = 1e-3 if mode == "fp32" else FILM_BF16_MAX_ABS
+    C.record(f"film_dec_max_abs_{mode}", (film[3].cpu() - C.t(g["film_dec"])).abs().max())
+    C.record(f"speaker_preds_max_abs_{mode}", (spk.cpu() - C.t(g["speaker_preds"])).abs().max())
     assert (film[3].cpu() - C.t(g["film_dec"])).abs().max().item() <= tol
     assert (spk.cpu() - C.t(g["speaker_preds"])).abs().max().item() <= tol
     # the tuple carries the caller's own tensors through, like the reference (model.py:943-946)
     assert enc[0] is dev[1] and enc[3] is dev[5] and dec[1] is dev[9]
     acc = m.accent_encoder(dev[6], dev[7], dev[8], dev[9]).cpu()
-    assert (acc - C.t(g["accent_emb"])).abs().max().item() <= (1e-4 if mode == "fp32" else 3e-2)
+    C.record(f"accent_emb_max_abs_{mode}", (acc - C.t(g["accent_emb"])).abs().max())
+    assert (acc - C.t(g["accent_emb"])).abs().max().item() <= (1e-4 if mode == "fp32" else ACCENT_BF16_MAX_ABS)
 
 
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
@@ -126,7 +142,8 @@ def test_forward_vs_oracle(models, mode, kw):
     film = O.style_adapter(sd, hp, accent + O.speaker_projection(sd, batch[11]))
     enc_ref = O.phoneme_encoder(sd, hp, batch[0], film["phoneme_encoder"], batch[5])
     enc = m._last_debug["enc_out"].cpu()
-    tol = 1e-3 if mode == "fp32" else 0.15
+    tol = 1e-3 if mode == "fp32" else ENC_BF16_MAX_ABS
+    C.record(f"enc_out_max_abs_{mode}", (enc - enc_ref).abs().max())
     assert (enc - enc_ref).abs().max().item() <= tol
 
 

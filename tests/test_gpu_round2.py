@@ -1,0 +1,202 @@
+"""GPU parity cases added in round 2 (VERDICT r1 "what's weak" 1-2): inference() at cfg2 size against the oracle
+in both arithmetic modes and both pitch transforms, cfg4 B=8, parse_batch against the reference's golden, packed
+frame-side I/O against the padded call (bit for bit), the multi-stream path on a fresh shape, the shape contract and the
+unknown-speaker KeyError.  Every bf16 comparison records its measured error into gpurun_out/parity_measured.json so the
+tolerances below can be read against what the hardware actually produced."""
+import numpy as np
+import pytest
+import torch
+
+import _cases as C
+from daft_exprt_b200 import layouts
+from daft_exprt_b200.model import DaftExprt
+from oracle import daft_oracle as O
+from test_gpu_parity import _check_mel, _check_weights, _valid_mask, models  # noqa: F401  (fixture)
+
+pytestmark = pytest.mark.gpu
+
+_record = C.record
+
+
+def _rel_l1(a, b, valid):
+    return ((a - b).abs()[valid].sum() / b.abs()[valid].sum()).item()
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("pt", ["add", "multiply"])
+def test_inference_cfg2_size_vs_oracle(models, mode, pt):
+    """DaftExprt.inference (model.py:1026-1114) at BASELINE cfg2 size: 64 utterances of 20-150 symbols, external prosody,
+    factors != identity.  Integers bit-exact; mel under the mode's gate; H8 mutation kept."""
+    hp = C.hparams()
+    inputs, prosody, ee, ae = C.synthetic.inference_batch(hp, 64, 20, 150, 42, pt)
+    g = torch.Generator().manual_seed(5)
+    L = inputs[0].shape[1]
+    dur_f = 0.8 + 0.4 * torch.rand(64, L, generator=g)
+    en_f = 0.9 + 0.2 * torch.rand(64, L, generator=g)
+    pi_f = (torch.rand(64, L, generator=g) - 0.5) * 40.0 if pt == "add" else 0.9 + 0.2 * torch.rand(64, L, generator=g)
+    inputs = (inputs[0], dur_f, en_f, pi_f, inputs[4], inputs[5])
+    ref_enc, ref_dec, ref_w = O.inference(C.state_dict(), hp, tuple(t.clone() for t in inputs), pt,
+                                          {k: v.clone() for k, v in prosody.items()}, ee.clone(), ae.clone())
+    m = models[mode]
+    dev_pros = {k: v.clone().cuda() for k, v in prosody.items()}
+    enc, dec, w = m.inference(tuple(t.cuda() for t in inputs), pt, hp, dev_pros, ee.cuda(), ae.cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(enc[1].cpu(), ref_enc[1]), "durations_int must be bit-exact"
+    assert torch.equal(dec[1].cpu(), ref_dec[1]), "output_lengths must be bit-exact"
+    assert torch.equal(enc[0].cpu(), ref_enc[0])
+    assert (enc[2].cpu() - ref_enc[2]).abs().max().item() <= 1e-6
+    assert (enc[3].cpu() - ref_enc[3]).abs().max().item() <= 2e-5
+    assert torch.equal(dev_pros["pitch_preds"], enc[3])
+    _check_mel(dec[0], ref_dec[0], ref_dec[1], mode)
+    _check_weights(w, ref_w, inputs[4], ref_dec[1], mode)
+    valid = _valid_mask(ref_dec[1], ref_dec[0].shape[2]).unsqueeze(1).expand_as(ref_dec[0])
+    _record(f"inference_cfg2_{pt}_{mode}_mel_rel_l1", _rel_l1(dec[0].cpu(), ref_dec[0], valid))
+    _record(f"inference_cfg2_{pt}_{mode}_mel_max_abs", (dec[0].cpu() - ref_dec[0]).abs()[valid].max())
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_cfg4_b8_vs_oracle(models, mode):
+    """BASELINE config 4 at B = 8: 8 x 400 symbols -> 8 x 2000 frames (the attention-dominated regime)."""
+    hp = C.hparams()
+    batch = C.synthetic.config_batch(hp, "cfg4_b8")
+    assert batch[8].shape == (8, 80, 2000)
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch))
+    out = models[mode](tuple(t.cuda() for t in batch))
+    torch.cuda.synchronize()
+    _check_mel(out[3][0], ref[3][0], batch[9], mode)
+    _check_weights(out[4], ref[4], batch[5], batch[9], mode)
+    valid = _valid_mask(batch[9], 2000).unsqueeze(1).expand_as(ref[3][0])
+    _record(f"cfg4_b8_{mode}_mel_rel_l1", _rel_l1(out[3][0].cpu(), ref[3][0], valid))
+    _record(f"cfg4_b8_{mode}_weights_max_abs", (out[4].cpu() - ref[4]).abs().max())
+
+
+def test_parse_batch_vs_reference_golden():
+    """DaftExprt.parse_batch (model.py:858-887) on the device against the frozen output of the reference's own method:
+    same 12 + 6 tensors, same dtypes, same values (inputs with off-contract dtypes exercise every cast)."""
+    import make_parse_batch_golden as MP
+    hp, batch14 = MP.parse_batch_case()
+    g = C.load_golden("parse_batch")
+    m = DaftExprt(hp).cuda()
+    inputs, targets = m.parse_batch(0, batch14)
+    assert len(inputs) == 12 and len(targets) == 6
+    for n, t in zip(MP.NAMES_IN, inputs):
+        ref = torch.from_numpy(g["in_" + n])
+        assert t.device.type == "cuda" and t.dtype == ref.dtype and torch.equal(t.cpu(), ref), n
+    for n, t in zip(MP.NAMES_TGT, targets):
+        ref = torch.from_numpy(g["tgt_" + n])
+        assert t.dtype == ref.dtype and torch.equal(t.cpu(), ref), n
+    # targets alias the inputs like the reference's (model.py:884-885)
+    assert targets[0] is inputs[1] and targets[3] is inputs[8]
+    with pytest.raises(ValueError, match="14 elements"):
+        m.parse_batch(0, batch14[:13])
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("kw", [dict(batch=7, lmin=5, lmax=61, seed=33), dict(batch=64, lmin=20, lmax=150, seed=42),
+                                dict(batch=1, lmin=1, lmax=1, seed=31, const_dur=1)])
+def test_packed_io_equals_padded_call(models, mode, kw):
+    """forward(packed_io=...) (DX_IO_PACKED_*: only valid frames in and out) computes bit for bit what the padded call
+    computes - the reference's collate pads with zeros (data_loader.py:246-259), which is what the packed reader returns
+    beyond T_b."""
+    hp = C.hparams()
+    batch = C.synthetic.forward_batch(hp, **kw)
+    m = models[mode]
+    dev = tuple(t.cuda() for t in batch)
+    ref = m(dev)
+    e, p, mel = layouts.pack_frames(batch[6], batch[7], batch[8], batch[9])
+    T_max, total = int(batch[9].max()), int(batch[9].sum())
+    packed = dev[:6] + (e.cuda(), p.cuda(), mel.cuda()) + dev[9:]
+    out = m(packed, packed_io=(T_max, total))
+    torch.cuda.synchronize()
+    assert out[3][0].shape == (total * 80,)
+    for b, v in enumerate(layouts.mel_views(out[3][0], batch[9])):
+        assert torch.equal(v, ref[3][0][b, :, :int(batch[9][b])]), b
+    assert torch.equal(out[4], ref[4]) and torch.equal(out[0], ref[0]) and torch.equal(out[1][3], ref[1][3])
+    assert torch.equal(layouts.unpack_mel(out[3][0], batch[9], T_max), ref[3][0])
+    with pytest.raises(ValueError, match="packed"):
+        m(dev, packed_io=(T_max, total))
+
+
+def test_two_streams_on_a_fresh_shape_equal_one_stream():
+    """the multi-stream path raced on its workspaces on the first call of every new shape (a memset landing
+    under a running group, LRU eviction handing one block to two groups).  No warm-up on purpose."""
+    hp = C.hparams()
+    sd = C.state_dict()
+    outs = []
+    for streams in (1, 2, 3):
+        m = DaftExprt(hp, mode="bf16").cuda()
+        m.load_state_dict(sd)
+        m.streams = streams
+        shapes = []
+        for seed, (lo, hi) in ((61, (20, 90)), (62, (30, 140)), (63, (10, 40))):     # three fresh shapes in a row
+            batch = C.synthetic.forward_batch(hp, batch=32, lmin=lo, lmax=hi, seed=seed)
+            o = m(tuple(t.cuda() for t in batch))
+            shapes.append((o[3][0].clone(), o[4].clone()))
+        torch.cuda.synchronize()
+        outs.append(shapes)
+    for other in outs[1:]:
+        for (mel_a, w_a), (mel_b, w_b) in zip(outs[0], other):
+            assert torch.equal(mel_a, mel_b) and torch.equal(w_a, w_b)
+
+
+def test_shape_contract_and_unknown_speaker(models):
+    """tensors that do not fit raise ValueError instead of becoming out-of-bounds device reads; a (1, 128) /
+    (1, 192) embedding broadcasts over the batch like the reference's `accent_emb + spk_emb`; an unknown speaker id is the
+    reference's KeyError (model.py:984) and the caller's speaker_ids are left alone."""
+    hp = C.hparams()
+    m = models["fp32"]
+    batch = C.synthetic.forward_batch(hp, batch=3, lmin=6, lmax=14, seed=41)
+    dev = [t.cuda() for t in batch]
+    for k, bad in ((1, dev[1][:, :-1]), (5, dev[5][:2]), (6, dev[6][:, :-1]), (8, dev[8][:, :79]), (11, dev[11][:2])):
+        args = list(dev)
+        args[k] = bad.contiguous()
+        with pytest.raises((ValueError, RuntimeError)):
+            m(tuple(args))
+    g = torch.Generator().manual_seed(1)
+    acc1, spk1 = torch.randn(1, 128, generator=g), torch.randn(1, 128, generator=g)
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in batch), external_accent_emb=acc1.expand(3, 128),
+                    external_spk_emb=spk1.expand(3, 128))
+    out = m(tuple(dev), external_accent_emb=acc1.cuda(), external_spk_emb=spk1.cuda())
+    _check_mel(out[3][0], ref[3][0], batch[9], "fp32")
+    with pytest.raises(ValueError):
+        m(tuple(dev), external_accent_emb=torch.randn(2, 128).cuda())
+    inputs, prosody, ee, ae = C.synthetic.inference_batch(hp, 3, 5, 9, 1)
+    ids = torch.tensor([0, 7, 1]).cuda()                 # 7 has no entry in hp.stats
+    before = ids.clone()
+    dev_in = tuple(t.cuda() for t in inputs[:5]) + (ids,)
+    with pytest.raises(KeyError, match="spk 7"):
+        m.inference(dev_in, "add", hp, {k: v.cuda() for k, v in prosody.items()}, ee.cuda(), ae.cuda())
+    assert torch.equal(ids, before)
+    # 'multiply' does not look the statistics up (model.py:1084-1085)
+    inputs_m, prosody_m, ee_m, ae_m = C.synthetic.inference_batch(hp, 3, 5, 9, 1, "multiply")
+    m.inference(tuple(t.cuda() for t in inputs_m[:5]) + (ids,), "multiply", hp, {k: v.cuda() for k, v in prosody_m.items()},
+                ee_m.cuda(), ae_m.cuda())
+    with pytest.raises(ValueError):
+        m.inference(dev_in[:1] + (dev_in[1][:, :-1].contiguous(),) + dev_in[2:], "multiply", hp,
+                    {k: v.cuda() for k, v in prosody.items()}, ee.cuda(), ae.cuda())
+
+
+def test_bulk_runner_packed_equals_padded_and_direct(models):
+    """cfg3 plumbing with packed frame-side I/O: the crops the sink receives are bit-identical to the padded runner's and
+    to a direct forward on the collated batch."""
+    from daft_exprt_b200 import bulk
+    hp = C.hparams()
+    m = models["bf16"]
+    lazy = C.synthetic.UtteranceStream(hp, 40, seed=5, lmin=5, lmax=60)
+    stream = {f: [lazy[f][i] for i in range(40)] for f in C.synthetic.UtteranceStream.FIELDS}
+    in_lens, out_lens = lazy.lengths()
+    batches, mine = bulk.plan_shards(in_lens, out_lens, 8, 1)
+    got = {}
+    for packed in (True, False):
+        res = {}
+        frames = bulk.BulkRunner(m, sink=lambda i, mel: res.__setitem__(i, torch.from_numpy(np.array(mel))), packed=packed).run(
+            stream, batches, mine[0])
+        assert frames == sum(out_lens) and sorted(res) == list(range(40))
+        got[packed] = res
+    for i in range(40):
+        assert got[True][i].shape == (80, out_lens[i]) and torch.equal(got[True][i], got[False][i])
+    for b in batches:
+        host = bulk.collate(stream, b)
+        mel = m(tuple(t.cuda() for t in host))[3][0].cpu()
+        for k, i in enumerate(b):
+            assert torch.equal(got[True][i], mel[k, :, :out_lens[i]])

@@ -68,3 +68,20 @@ def test_errors_match_reference_contract():
         O.inference(sd, hp, inputs, "add", None, ext_emb, acc_emb)
     with pytest.raises(NotImplementedError):
         O.inference(sd, hp, inputs, "bogus", prosody, ext_emb, acc_emb)
+
+
+def test_parse_batch_mirror_equals_reference_golden_on_cpu():
+    """DaftExprt.parse_batch (model.py:858-887) is host logic + casts: the mirror on 'cpu' against the frozen output of the
+    reference's own method (tests/golden/make_parse_batch_golden.py)."""
+    import torch
+    import make_parse_batch_golden as MP
+    from daft_exprt_b200.model import DaftExprt
+    hp, batch14 = MP.parse_batch_case()
+    g = C.load_golden("parse_batch")
+    inputs, targets = DaftExprt(hp).parse_batch("cpu", batch14)
+    for n, t in zip(MP.NAMES_IN, inputs):
+        ref = torch.from_numpy(g["in_" + n])
+        assert t.dtype == ref.dtype and torch.equal(t, ref), n
+    for n, t in zip(MP.NAMES_TGT, targets):
+        ref = torch.from_numpy(g["tgt_" + n])
+        assert t.dtype == ref.dtype and torch.equal(t, ref), n

@@ -9,6 +9,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG_DIR, "libdaft_b200.so")
 
 MODE_F32, MODE_BF16 = 0, 1
+IO_PACKED_FRAMES, IO_PACKED_MEL_OUT = 1, 2
 GAP, HALO, TAIL = 3, 8, 264
 D, HEADS, DH, CCH, TAPS, MEL, MEL_PAD, SPK = 128, 2, 64, 1024, 3, 80, 96, 192
 
@@ -50,7 +51,7 @@ class DxForwardArgs(C.Structure):
                              "spk_embs", "accent_emb_in", "spk_emb_in",
                              "accent_emb", "speaker_preds", "film", "enc_out", "mel_out", "weights_out",
                              "output_lengths_out", "workspace")]
-        + [("workspace_bytes", C.c_int64)]
+        + [("workspace_bytes", C.c_int64), ("io_flags", C.c_int32), ("pad_", C.c_int32)]
     )
 
 
@@ -101,6 +102,7 @@ SIGNATURES = {
     "dx_vocoder_workspace_bytes": (C.c_int64, [C.POINTER(DxVocoderWeights), C.c_int, C.c_int64, C.c_int]),
     "dx_vocoder_forward": (C.c_int, [C.POINTER(DxVocoderWeights), C.POINTER(DxVocoderArgs), _p]),
     "dx_host_collate": (C.c_int, [C.c_int] * 5 + [_p, _p, _p, _p, C.c_int]),
+    "dx_host_collate_packed": (C.c_int, [C.c_int] * 5 + [_p, _p, _p, _p, C.c_int]),
     "dx_test_attention": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p, C.c_int64, _p]),
 }
 
@@ -143,6 +145,7 @@ def ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
-def stream_ptr():
+def stream_ptr(device=None):
+    """The current CUDA stream of ``device`` (default: the current device) as the C ABI's ``void* stream``."""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)

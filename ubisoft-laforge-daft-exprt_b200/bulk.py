@@ -102,14 +102,19 @@ _FORWARD_ORDER = ("symbols", "durations_float", "durations_int", "symbols_energy
                   "frames_energy", "frames_pitch", "mel_specs", "output_lengths", "speaker_ids", "spk_embs")
 
 
-def block_layout(B, L, T, M, E):
+def block_layout(B, L, T, M, E, total_frames=None):
     """Byte layout of one batch inside a staging block (the plan of ``data_loader.DaftExprtDataCollate``):
-    ``{name: (offset, nbytes, torch dtype, shape)}`` and the total size."""
+    ``{name: (offset, nbytes, torch dtype, shape)}`` and the total size.  ``total_frames`` (= Σ T_b): the frame side
+    is PACKED (``include/daft_b200.h`` DX_IO_PACKED_FRAMES) — only valid frames are staged and cross PCIe."""
     i8, f4 = torch.int64, torch.float32
+    if total_frames is None:
+        frame_side = [("frames_energy", f4, (B, T)), ("frames_pitch", f4, (B, T)), ("mel_specs", f4, (B, M, T))]
+    else:
+        frame_side = [("frames_energy", f4, (total_frames,)), ("frames_pitch", f4, (total_frames,)),
+                      ("mel_specs", f4, (total_frames * M,))]
     plan = [("symbols", i8, (B, L)), ("durations_int", i8, (B, L)), ("input_lengths", i8, (B,)), ("output_lengths", i8, (B,)),
             ("speaker_ids", i8, (B,)), ("durations_float", f4, (B, L)), ("symbols_energy", f4, (B, L)),
-            ("symbols_pitch", f4, (B, L)), ("frames_energy", f4, (B, T)), ("frames_pitch", f4, (B, T)),
-            ("mel_specs", f4, (B, M, T)), ("spk_embs", f4, (B, E))]
+            ("symbols_pitch", f4, (B, L))] + frame_side + [("spk_embs", f4, (B, E))]
     layout, off = {}, 0
     for name, dt, shape in plan:
         n = 1
@@ -121,11 +126,11 @@ def block_layout(B, L, T, M, E):
     return layout, max(off, _ALIGN)
 
 
-def fill_block(block, utterances, idx):
+def fill_block(block, utterances, idx, packed=False):
     """Collate the utterances ``idx`` (descending symbol count) into the uint8 staging tensor ``block`` (reference
     ``data_loader.py:214-263``: right zero padding).  numpy slice copies — they release the GIL for the large mel rows,
     so several batches can be collated side by side — and only the pad tails are zeroed, not the whole block.
-    Returns the layout."""
+    ``packed``: the frame side is packed (one copy per utterance, no padding).  Returns the layout."""
     import numpy as np
     B = len(idx)
     lens = [int(utterances["symbols"][i].shape[0]) for i in idx]
@@ -133,7 +138,7 @@ def fill_block(block, utterances, idx):
     L, T = max(lens), max(tlens)
     M = int(utterances["mel"][idx[0]].shape[0])
     E = int(utterances["spk_emb"][idx[0]].shape[0])
-    layout, total = block_layout(B, L, T, M, E)
+    layout, total = block_layout(B, L, T, M, E, sum(tlens) if packed else None)
     assert total <= block.numel(), (total, block.numel())
     raw = block.numpy()
     v = {}
@@ -147,13 +152,19 @@ def fill_block(block, utterances, idx):
             row = v[dst][b]
             row[:l] = utterances[src][i].numpy()
             row[l:] = 0
-        for dst, src in (("frames_energy", "frames_energy"), ("frames_pitch", "frames_pitch")):
-            row = v[dst][b]
-            row[:t] = utterances[src][i].numpy()
-            row[t:] = 0
-        mel = v["mel_specs"][b]
-        mel[:, :t] = utterances["mel"][i].numpy()
-        mel[:, t:] = 0
+        if packed:
+            f0 = sum(tlens[:b])
+            v["frames_energy"][f0:f0 + t] = utterances["frames_energy"][i].numpy()
+            v["frames_pitch"][f0:f0 + t] = utterances["frames_pitch"][i].numpy()
+            v["mel_specs"][M * f0:M * (f0 + t)] = utterances["mel"][i].numpy().reshape(-1)
+        else:
+            for dst, src in (("frames_energy", "frames_energy"), ("frames_pitch", "frames_pitch")):
+                row = v[dst][b]
+                row[:t] = utterances[src][i].numpy()
+                row[t:] = 0
+            mel = v["mel_specs"][b]
+            mel[:, :t] = utterances["mel"][i].numpy()
+            mel[:, t:] = 0
         v["input_lengths"][b], v["output_lengths"][b] = l, t
         v["speaker_ids"][b] = int(utterances["speaker_id"][i])
         v["spk_embs"][b] = utterances["spk_emb"][i].numpy()
@@ -189,8 +200,9 @@ class PointerTable:
         self.M = int(utterances["mel"][0].shape[0])
         self.E = int(utterances["spk_emb"][0].numel())
 
-    def fill(self, block, idx, threads=1):
-        """Native collate of the utterances ``idx`` into the uint8 staging tensor ``block``; returns the layout."""
+    def fill(self, block, idx, threads=1, packed=False):
+        """Native collate of the utterances ``idx`` into the uint8 staging tensor ``block``; returns the layout.
+        ``packed``: frame side in the DX_IO_PACKED_FRAMES layout (``dx_host_collate_packed``)."""
         import ctypes
         import numpy as np
         from . import _lib
@@ -198,12 +210,14 @@ class PointerTable:
         lens = np.ascontiguousarray(self.lens[ids])
         ptrs = np.ascontiguousarray(self.ptrs[ids])
         B, L, T = len(idx), int(lens[:, 0].max()), int(lens[:, 1].max())
-        layout, total = block_layout(B, L, T, self.M, self.E)
+        layout, total = block_layout(B, L, T, self.M, self.E, int(lens[:, 1].sum()) if packed else None)
         assert total <= block.numel(), (total, block.numel())
         offs = np.array([layout[name][0] for name in _FORWARD_ORDER], dtype=np.int64)
-        _lib.check(_lib.load().dx_host_collate(B, L, T, self.M, self.E, ctypes.c_void_p(ptrs.ctypes.data),
-                                               ctypes.c_void_p(lens.ctypes.data), ctypes.c_void_p(block.data_ptr()),
-                                               ctypes.c_void_p(offs.ctypes.data), int(threads)), "dx_host_collate")
+        lib = _lib.load()
+        fn = lib.dx_host_collate_packed if packed else lib.dx_host_collate
+        _lib.check(fn(B, L, T, self.M, self.E, ctypes.c_void_p(ptrs.ctypes.data), ctypes.c_void_p(lens.ctypes.data),
+                      ctypes.c_void_p(block.data_ptr()), ctypes.c_void_p(offs.ctypes.data), int(threads)),
+                   "dx_host_collate_packed" if packed else "dx_host_collate")
         return layout
 
 
@@ -231,11 +245,13 @@ class BulkRunner:
 
     On a CPU model (tests) the same plan runs unstaged."""
 
-    def __init__(self, model, sink=None, device=None, workers=2, slots=6, collate_threads=4):
+    def __init__(self, model, sink=None, device=None, workers=2, slots=6, collate_threads=4, packed=True):
         self.model = model
         self.sink = sink
+        self.packed = bool(packed)      # only valid frames are staged, copied H2D and copied back (DX_IO_PACKED_*)
         self.device = device if device is not None else model.device
         self.frames = 0
+        self._writer_error = None
         self.workers, self.slots, self.collate_threads = max(1, int(workers)), max(3, int(slots)), max(1, int(collate_threads))
 
     def run(self, utterances, batches, my_batch_ids):
@@ -260,7 +276,8 @@ class BulkRunner:
                 L = max(int(utterances["symbols"][i].shape[0]) for i in idx)
                 T = max(int(utterances["mel"][i].shape[1]) for i in idx)
                 M, E = int(utterances["mel"][idx[0]].shape[0]), int(utterances["spk_emb"][idx[0]].shape[0])
-            cap = max(cap, block_layout(len(idx), L, T, M, E)[1])
+            mel_channels = M
+            cap = max(cap, block_layout(len(idx), L, T, M, E)[1])      # padded layout: an upper bound for the packed one
         S = self.slots
         blocks = [torch.empty(cap, dtype=torch.uint8, pin_memory=True) for _ in range(S)]
         mirrors = [torch.empty(cap, dtype=torch.uint8, device=dev) for _ in range(S)]
@@ -271,68 +288,105 @@ class BulkRunner:
         writer = threading.Thread(target=self._writer, args=(q,), daemon=True)
         writer.start()
 
+        packed = self.packed
+
         def collate_into(pos):
             s = pos % S
             if h2d_done[s] is not None:
                 h2d_done[s].synchronize()
             if table is not None:
-                return table.fill(blocks[s], batches[my_batch_ids[pos]], self.collate_threads)
-            return fill_block(blocks[s], utterances, batches[my_batch_ids[pos]])
+                return table.fill(blocks[s], batches[my_batch_ids[pos]], self.collate_threads, packed)
+            return fill_block(blocks[s], utterances, batches[my_batch_ids[pos]], packed)
 
         n = len(my_batch_ids)
         depth = min(S - 1, self.workers + 1)
-        with ThreadPoolExecutor(max_workers=self.workers) as pool:
-            futs = {pos: pool.submit(collate_into, pos) for pos in range(min(depth, n))}
-            for pos in range(n):
-                s = pos % S
-                layout = futs.pop(pos).result()
-                nbytes = max(o + b for o, b, _, _ in layout.values())
-                with torch.cuda.stream(copy_stream):
-                    if fwd_done[s] is not None:
-                        copy_stream.wait_event(fwd_done[s])
-                    mirrors[s][:nbytes].copy_(blocks[s][:nbytes], non_blocking=True)
-                    h2d_done[s] = torch.cuda.Event()
-                    h2d_done[s].record(copy_stream)
-                if pos + depth < n:           # its slot is the one whose H2D was enqueued an iteration ago at the latest
-                    futs[pos + depth] = pool.submit(collate_into, pos + depth)
-                torch.cuda.current_stream(dev).wait_event(h2d_done[s])
-                out = self.model(block_views(mirrors[s], layout))
-                fwd_done[s] = torch.cuda.Event()
-                fwd_done[s].record()
-                mel = out[3][0]
-                hmel = torch.empty(mel.shape, dtype=mel.dtype, pin_memory=True)
-                hmel.copy_(mel, non_blocking=True)
-                done = torch.cuda.Event()
-                done.record()
-                out_len = block_views(blocks[s], layout)[9].clone()
-                self.frames += int(out_len.sum())
-                q.put((batches[my_batch_ids[pos]], out_len, hmel, done))
-        q.put(None)
-        writer.join()
+        try:
+            with ThreadPoolExecutor(max_workers=self.workers) as pool:
+                futs = {pos: pool.submit(collate_into, pos) for pos in range(min(depth, n))}
+                for pos in range(n):
+                    if self._writer_error is not None:       # the sink failed: stop producing, re-raised below
+                        break
+                    s = pos % S
+                    layout = futs.pop(pos).result()
+                    nbytes = max(o + b for o, b, _, _ in layout.values())
+                    with torch.cuda.stream(copy_stream):
+                        if fwd_done[s] is not None:
+                            copy_stream.wait_event(fwd_done[s])
+                        mirrors[s][:nbytes].copy_(blocks[s][:nbytes], non_blocking=True)
+                        h2d_done[s] = torch.cuda.Event()
+                        h2d_done[s].record(copy_stream)
+                    if pos + depth < n:       # its slot is the one whose H2D was enqueued an iteration ago at the latest
+                        futs[pos + depth] = pool.submit(collate_into, pos + depth)
+                    torch.cuda.current_stream(dev).wait_event(h2d_done[s])
+                    out_len = block_views(blocks[s], layout)[9].clone()
+                    views = block_views(mirrors[s], layout)
+                    if packed:
+                        T_max, total = int(out_len.max()), int(out_len.sum())
+                        out = self.model(views, packed_io=(T_max, total))
+                    else:
+                        out = self.model(views)
+                    fwd_done[s] = torch.cuda.Event()
+                    fwd_done[s].record()
+                    mel = out[3][0]
+                    hmel = torch.empty(mel.shape, dtype=mel.dtype, pin_memory=True)
+                    hmel.copy_(mel, non_blocking=True)
+                    done = torch.cuda.Event()
+                    done.record()
+                    self.frames += int(out_len.sum())
+                    if packed:               # per-utterance (80, T_b) numpy views of the pinned buffer: the crop is free
+                        from .layouts import mel_views
+                        hmel = [v.numpy() for v in mel_views(hmel, out_len, mel_channels)]
+                    q.put((batches[my_batch_ids[pos]], out_len, hmel, done))
+                for f in futs.values():       # a failed run must not leave collate jobs writing into freed blocks
+                    f.cancel()
+        finally:
+            self._finish_writer(q, writer)
         return self.frames
 
     def _run_unstaged(self, utterances, batches, my_batch_ids):
         q = queue.Queue(maxsize=4)
         writer = threading.Thread(target=self._writer, args=(q,), daemon=True)
         writer.start()
-        for k in my_batch_ids:
-            host = collate(utterances, batches[k])
-            out = self.model(host)
-            self.frames += int(host[9].sum())
-            q.put((batches[k], host[9], out[3][0], None))
-        q.put(None)
-        writer.join()
+        try:
+            for k in my_batch_ids:
+                if self._writer_error is not None:
+                    break
+                host = collate(utterances, batches[k])
+                out = self.model(host)
+                self.frames += int(host[9].sum())
+                q.put((batches[k], host[9], out[3][0], None))
+        finally:
+            self._finish_writer(q, writer)
         return self.frames
 
     def _writer(self, q):
+        """Writer thread: hands the per-utterance crops to ``sink``.  An exception from ``sink`` (disk full, bad path) is
+        kept in ``self._writer_error``; the thread keeps DRAINING the queue (without calling ``sink`` again) so that the
+        producer never blocks on a full queue, and ``run`` re-raises the error after ``join``."""
         while True:
             item = q.get()
             if item is None:
                 return
-            ids, out_len, hmel, done = item
-            if done is not None:
-                done.synchronize()
-            if self.sink is not None:
-                arr = hmel.numpy()
-                for b, i in enumerate(ids):
-                    self.sink(i, arr[b, :, :int(out_len[b])])
+            if self._writer_error is not None:
+                continue
+            try:
+                ids, out_len, hmel, done = item
+                if done is not None:
+                    done.synchronize()
+                if self.sink is not None:
+                    if isinstance(hmel, (list, tuple)):          # packed output: per-utterance (80, T_b) views
+                        for i, v in zip(ids, hmel):
+                            self.sink(i, v)
+                    else:
+                        arr = hmel.numpy()
+                        for b, i in enumerate(ids):
+                            self.sink(i, arr[b, :, :int(out_len[b])])
+            except BaseException as e:          # noqa: BLE001 - re-raised in run()
+                self._writer_error = e
+
+    def _finish_writer(self, q, writer):
+        q.put(None)
+        writer.join()
+        if self._writer_error is not None:
+            err, self._writer_error = self._writer_error, None
+            raise err

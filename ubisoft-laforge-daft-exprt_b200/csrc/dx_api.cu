@@ -50,6 +50,20 @@ ProfScope::~ProfScope() {
     if (slot >= 0) cudaEventRecord(g_prof[slot].b, s);
 }
 
+int device_sm_count(int* sms) {
+    static std::atomic<int> cache[DX_MAX_DEVICES];
+    int dev = 0;
+    DX_CHECK_CUDA(cudaGetDevice(&dev));
+    const bool cached = dev >= 0 && dev < DX_MAX_DEVICES;
+    int n = cached ? cache[dev].load(std::memory_order_acquire) : 0;
+    if (n == 0) {
+        DX_CHECK_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        if (cached) cache[dev].store(n, std::memory_order_release);
+    }
+    *sms = n;
+    return 0;
+}
+
 int64_t row_cap(int B, int n_max) { return round_up((int64_t)B * (n_max + DX_GAP), 256); }
 
 }  // namespace dx

@@ -398,11 +398,8 @@ int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Row
 
 // out [16][rows_phys][8] = concat_h softmax(Q_h K_h^T / 8) V_h
 int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATC_SMEM));
-        configured = true;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(attention_tc_kernel, ATC_SMEM, configured));
     AtcParams p;
     memset(&p, 0, sizeof(p));
     p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R;

@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <atomic>
 #include "../../include/daft_b200.h"
 
 namespace dx {
@@ -106,6 +107,27 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
     } while (0)
 
 static inline int64_t round_up(int64_t a, int64_t m) { return (a + m - 1) / m * m; }
+
+// ---- per-device one-time kernel configuration --------------------------------------------------------------
+// cudaFuncAttributeMaxDynamicSharedMemorySize and the SM count are PER DEVICE: a process that drives several GPUs
+// (or several host threads: bulk.BulkRunner, the writer) must not share one "configured" flag.  The caches are keyed by
+// cudaGetDevice(); entries are atomics, and two threads racing on the same entry only set the same attribute twice.
+constexpr int DX_MAX_DEVICES = 64;
+struct SmemConfigured {
+    std::atomic<size_t> bytes[DX_MAX_DEVICES];
+};
+int device_sm_count(int* sms);      // SM count of the current device (dx_api.cu)
+
+template <typename Kern>
+static inline int ensure_dyn_smem(Kern kernel, size_t smem, SmemConfigured& cache) {
+    int dev = 0;
+    DX_CHECK_CUDA(cudaGetDevice(&dev));
+    const bool cached = dev >= 0 && dev < DX_MAX_DEVICES;
+    if (cached && smem <= cache.bytes[dev].load(std::memory_order_acquire)) return 0;
+    DX_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (cached) cache.bytes[dev].store(smem, std::memory_order_release);
+    return 0;
+}
 
 // ---- warp helpers ----------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

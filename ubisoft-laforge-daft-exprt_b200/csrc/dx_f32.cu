@@ -332,11 +332,8 @@ attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ 
 static const int AT_SMEM = (64 * AT_Q + 64 * (AT_K + 1) + AT_K * DX_DH + AT_K * (AT_Q + 4)) * (int)sizeof(float);
 
 int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(attention_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
-        configured = true;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(attention_f32_kernel, (size_t)AT_SMEM, configured));
     dim3 grid((unsigned)((R.n_max + AT_Q - 1) / AT_Q), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_f32", s);
     attention_f32_kernel<<<grid, 256, AT_SMEM, s>>>(qkv, R, out);

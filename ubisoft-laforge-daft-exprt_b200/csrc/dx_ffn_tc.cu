@@ -496,15 +496,10 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
              int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse) {
     DX_REQUIRE(bw.w_ffn1_bf && bw.w_ffn2_bf, "ffn_bf16: fused-FFN packed weights missing");
-    static int num_sms = 0;
-    static bool configured = false;
-    if (!configured) {
-        int dev = 0;
-        DX_CHECK_CUDA(cudaGetDevice(&dev));
-        DX_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-        DX_CHECK_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FF_SMEM));
-        configured = true;
-    }
+    int num_sms = 0;
+    DX_TRY(device_sm_count(&num_sms));
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(ffn_tc_kernel, (size_t)FF_SMEM, configured));
     FfnParams p;
     memset(&p, 0, sizeof(p));
     p.x = x; p.out = out; p.rows_phys = rows_phys;

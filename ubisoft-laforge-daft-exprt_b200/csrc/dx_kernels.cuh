@@ -5,13 +5,14 @@
 namespace dx {
 
 // dx_rows.cu
-int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s);
-int unpack_mel(const float* rows, const Rows& R, float* mel, cudaStream_t s);
+// packed: the frame-side tensor is in the DX_IO_PACKED_* layout (per-utterance (80, T_b) blocks / float[sum T_b])
+int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s, bool packed = false);
+int unpack_mel(const float* rows, const Rows& R, float* mel, cudaStream_t s, bool packed = false);
 int embed_symbols(const int64_t* symbols, const float* emb, int n_symbols, const float* pos, const Rows& R,
                   float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s);
 int accent_input(const float* z2_f32, const __nv_bfloat16* z2_bf, const float* energy, const float* pitch,
                  const float* ew, const float* eb, const float* pw, const float* pb, const float* pos,
-                 const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s);
+                 const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s, bool packed = false);
 int masked_mean(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys, const Rows& R, float* out,
                 cudaStream_t s);
 int unpack_rows(const float* x_f32, const __nv_bfloat16* x_bf, int64_t rows_phys, const Rows& R, float* out,

@@ -298,11 +298,10 @@ int lenreg_frames(const float* xs, const Rows& RL, const Rows& RT, const float* 
     const int L = RL.n_max;
     const size_t smem = (size_t)(3 * ((L + 3) & ~3) + 8 * LR_FT + LR_FT + 32 * LR_FT) * sizeof(float) + (32 + ((L + 3) & ~3) + 32) * sizeof(int);
     DX_REQUIRE(smem <= 200 * 1024, "lenreg_frames: L_max=%d too large", L);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(lenreg_frames_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        DX_CHECK_CUDA(cudaFuncSetAttribute(lenreg_frames_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    static SmemConfigured configured_bf, configured_f32;
+    if (smem > 48 * 1024) {
+        DX_TRY(ensure_dyn_smem(lenreg_frames_kernel<true>, smem, configured_bf));
+        DX_TRY(ensure_dyn_smem(lenreg_frames_kernel<false>, smem, configured_f32));
     }
     dim3 grid((unsigned)((RT.n_max + DX_GAP + LR_FT - 1) / LR_FT), (unsigned)RT.B);
     ProfScope prof("lenreg_frames", s);

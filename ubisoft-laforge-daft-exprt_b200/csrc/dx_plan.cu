@@ -187,10 +187,11 @@ static int zero_plan_halos(const Plan& p, cudaStream_t s) {
 // AccentEncoder.forward (model.py:679-716)
 // ---------------------------------------------------------------------------------------------------------
 int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, const float* frames_energy,
-                       const float* frames_pitch, const float* mel_specs, float* accent_emb, cudaStream_t s) {
+                       const float* frames_pitch, const float* mel_specs, float* accent_emb, cudaStream_t s,
+                       bool packed_frames) {
     DX_REQUIRE(frames_energy && frames_pitch && mel_specs, "accent encoder: frames_energy / frames_pitch / mel_specs required");
     if (p.mode == DX_MODE_F32) {
-        DX_TRY(pack_mel(mel_specs, RT, p.melp, nullptr, 0, s));
+        DX_TRY(pack_mel(mel_specs, RT, p.melp, nullptr, 0, s, packed_frames));
         // pre-net: 3 x (conv k3 → ReLU → LN), evaluated on the padded layout: ghost rows live (H1)
         DX_TRY(gemm_f32(p.melp, DX_MEL, w.ae_c0_w, w.ae_c0_b, DX_C, DX_TAPS, true, RT, -1, p.h1, s));
         DX_TRY(ln_rows_f32(p.h1, nullptr, w.ae_ln0_g, w.ae_ln0_b, DX_C, nullptr, 0, RT, 2, p.h2, s));
@@ -199,13 +200,13 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         DX_TRY(gemm_f32(p.h2, DX_C, w.ae_c2_w, w.ae_c2_b, DX_D, DX_TAPS, true, RT, -1, p.tmp, s));
         DX_TRY(ln_rows_f32(p.tmp, nullptr, w.ae_ln2_g, w.ae_ln2_b, DX_D, nullptr, 0, RT, 0, p.o, s));
         DX_TRY(accent_input(p.o, nullptr, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
-                            w.ae_pitch_b, w.pos_table, RT, p.x, nullptr, 0, s));
+                            w.ae_pitch_b, w.pos_table, RT, p.x, nullptr, 0, s, packed_frames));
         for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.ae_blocks[i], p, RT, nullptr, 0, s));
         DX_TRY(masked_mean(p.x, nullptr, 0, RT, accent_emb, s));
     } else {
         const int64_t rp = p.rows_phys;
         DX_REQUIRE(w.ae_c0_w_bf && w.ae_c1_w_bf && w.ae_c2_w_bf, "bf16 mode: packed pre-net weights missing");
-        DX_TRY(pack_mel(mel_specs, RT, nullptr, p.melb, rp, s));
+        DX_TRY(pack_mel(mel_specs, RT, nullptr, p.melb, rp, s, packed_frames));
         {
             TcGemmArgs g = tc_args(p.melb, rp, DX_MEL_PAD, DX_C, DX_TAPS, w.ae_c0_w_bf, 256, 32, w.ae_c0_b, 1, TC_EPI_BF16, 2);
             g.out_bf = p.h1b; g.row_stats = p.row_stats; g.tag = "tc_prenet0";
@@ -224,7 +225,7 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
             DX_TRY(tc_gemm(g, RT, s));
         }
         DX_TRY(accent_input(nullptr, p.ob, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
-                            w.ae_pitch_b, w.pos_table, RT, nullptr, p.xb, rp, s));
+                            w.ae_pitch_b, w.pos_table, RT, nullptr, p.xb, rp, s, packed_frames));
         DX_TRY(fft_stack_bf16(w.ae_blocks, p, RT, nullptr, 0, "tc_block_tail_frames", s));
         DX_TRY(masked_mean(nullptr, p.xb, rp, RT, accent_emb, s));
     }
@@ -241,6 +242,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     DX_REQUIRE(a.symbols && a.durations_float && a.durations_int && a.symbols_energy && a.symbols_pitch && a.input_lengths,
                "dx_forward: symbol-side inputs required");
     DX_REQUIRE(a.film && a.mel_out && a.weights_out && a.output_lengths_out, "dx_forward: film / mel_out / weights_out / output_lengths_out required");
+    DX_REQUIRE((a.io_flags & ~(DX_IO_PACKED_FRAMES | DX_IO_PACKED_MEL_OUT)) == 0, "dx_forward: unknown io_flags 0x%x", a.io_flags);
     const bool bf = a.mode == DX_MODE_BF16;
     const int64_t rp = p.rows_phys;
     if (bf) DX_TRY(zero_plan_halos(p, s));
@@ -263,7 +265,8 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     if (a.accent_emb_in != nullptr) {
         DX_CHECK_CUDA(cudaMemcpyAsync(accent, a.accent_emb_in, (size_t)a.B * DX_D * sizeof(float), cudaMemcpyDeviceToDevice, s));
     } else {
-        DX_TRY(run_accent_encoder(w, p, RT, a.frames_energy, a.frames_pitch, a.mel_specs, accent, s));
+        DX_TRY(run_accent_encoder(w, p, RT, a.frames_energy, a.frames_pitch, a.mel_specs, accent, s,
+                                  (a.io_flags & DX_IO_PACKED_FRAMES) != 0));
     }
     // 3-4. speaker projection, classifier, FiLM table
     DX_TRY(style(&w, a.B, a.spk_embs, a.spk_emb_in, accent, a.film, a.speaker_preds, s));
@@ -289,7 +292,7 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     } else {
         DX_TRY(gemm_f32(p.x, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
     }
-    DX_TRY(unpack_mel(p.melo, RT, a.mel_out, s));
+    DX_TRY(unpack_mel(p.melo, RT, a.mel_out, s, (a.io_flags & DX_IO_PACKED_MEL_OUT) != 0));
     return 0;
 }
 

@@ -39,7 +39,8 @@ struct Plan {
 int plan_layout(Plan* p, int B, int L_max, int T_max, int mode, void* workspace, int64_t workspace_bytes);
 
 int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, const float* frames_energy,
-                       const float* frames_pitch, const float* mel_specs, float* accent_emb, cudaStream_t s);
+                       const float* frames_pitch, const float* mel_specs, float* accent_emb, cudaStream_t s,
+                       bool packed_frames = false);
 int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s);
 
 }  // namespace dx

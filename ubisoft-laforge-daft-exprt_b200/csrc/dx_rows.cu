@@ -70,9 +70,23 @@ int build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int
 // Tile transpose through smem: reads coalesced along T, writes coalesced along channels.
 // OUT_BF16: write the bf16 channel-interleaved layout [C/8][rows_phys][8] instead of fp32 [rows][C].
 // ---------------------------------------------------------------------------------------------------------
+// Frame-side source of utterance b: element (channel c, frame p) at base[c * stride + p], valid for p < n.
+// Padded (B, C, n_max) tensors: n = n_max (the caller's padding content is read like the reference's convs see it).
+// Packed (DX_IO_PACKED_FRAMES): per-utterance (C, T_b) blocks at C * fs[b], fs[b] = row_start[b] - b * DX_GAP; frames
+// beyond T_b read as zeros (= the reference collate's zero padding).
+struct FrameView {
+    int64_t base;
+    int stride, n;
+};
+__device__ __forceinline__ FrameView frame_view(const Rows& R, int b, int C, bool packed) {
+    if (!packed) return FrameView{(int64_t)b * C * R.n_max, R.n_max, R.n_max};
+    const int tb = (int)min((long long)R.len[b], (long long)R.n_max);
+    return FrameView{(int64_t)C * (R.row_start[b] - b * DX_GAP), tb, tb};
+}
+
 template <bool OUT_BF16>
 __global__ void pack_mel_kernel(const float* __restrict__ mel, Rows R, int C, float* __restrict__ out_f32,
-                                __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys) {
+                                __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys, bool packed) {
     ptx::griddep_wait();      // PDL: predecessor complete + visible
     ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ float tile[32][DX_MEL + 1];
@@ -85,9 +99,10 @@ __global__ void pack_mel_kernel(const float* __restrict__ mel, Rows R, int C, fl
         int64_t r = r0 + tx;
         int b = (r < total) ? R.row_b[r] : -1;
         int p = (b >= 0) ? R.row_p[r] : 0;
-        bool ok = (b >= 0) && (p < R.n_max);
+        FrameView fv = (b >= 0) ? frame_view(R, b, C, packed) : FrameView{0, 0, 0};
+        bool ok = (b >= 0) && (p < fv.n);
         for (int c = ty; c < C; c += 8)
-            tile[tx][c] = ok ? mel[((int64_t)b * C + c) * R.n_max + p] : 0.f;
+            tile[tx][c] = ok ? mel[fv.base + (int64_t)c * fv.stride + p] : 0.f;
     }
     __syncthreads();
     if (!OUT_BF16) {
@@ -111,12 +126,13 @@ __global__ void pack_mel_kernel(const float* __restrict__ mel, Rows R, int C, fl
 }
 
 int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys,
-             cudaStream_t s) {
+             cudaStream_t s, bool packed) {
     int grid = (int)(R.cap / 32);
+    ProfScope prof("pack_mel", s);
     if (out_bf)
-        DX_LAUNCH_PDL((pack_mel_kernel<true>), grid, 256, 0, s, mel, R, DX_MEL, nullptr, out_bf, rows_phys);
+        DX_LAUNCH_PDL((pack_mel_kernel<true>), grid, 256, 0, s, mel, R, DX_MEL, nullptr, out_bf, rows_phys, packed);
     else
-        DX_LAUNCH_PDL((pack_mel_kernel<false>), grid, 256, 0, s, mel, R, DX_MEL, out_f32, nullptr, 0);
+        DX_LAUNCH_PDL((pack_mel_kernel<false>), grid, 256, 0, s, mel, R, DX_MEL, out_f32, nullptr, 0, packed);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -125,7 +141,7 @@ int pack_mel(const float* mel, const Rows& R, float* out_f32, __nv_bfloat16* out
 // unpack_mel: rows [*][80] fp32 → (B, 80, T) with zeros at t >= len (FrameDecoder mask + transpose,
 // model.py:562-563).  Every element of the output is written.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void unpack_mel_kernel(const float* __restrict__ rows, Rows R, int C, float* __restrict__ mel) {
+__global__ void unpack_mel_kernel(const float* __restrict__ rows, Rows R, int C, float* __restrict__ mel, bool packed) {
     ptx::griddep_wait();      // PDL: predecessor complete + visible
     ptx::griddep_launch();    // let the next kernel start its prologue
     __shared__ float tile[32][DX_MEL + 1];
@@ -141,13 +157,15 @@ __global__ void unpack_mel_kernel(const float* __restrict__ rows, Rows R, int C,
     __syncthreads();
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     int t = t0 + tx;
-    if (t < R.n_max)
-        for (int c = ty; c < C; c += 8) mel[((int64_t)b * C + c) * R.n_max + t] = tile[tx][c];
+    const FrameView fv = frame_view(R, b, C, packed);      // packed: only the len valid frames exist in the output
+    if (t < fv.n)
+        for (int c = ty; c < C; c += 8) mel[fv.base + (int64_t)c * fv.stride + t] = tile[tx][c];
 }
 
-int unpack_mel(const float* rows, const Rows& R, float* mel, cudaStream_t s) {
+int unpack_mel(const float* rows, const Rows& R, float* mel, cudaStream_t s, bool packed) {
     dim3 grid((R.n_max + 31) / 32, R.B);
-    DX_LAUNCH_PDL((unpack_mel_kernel), grid, 256, 0, s, rows, R, DX_MEL, mel);
+    ProfScope prof("unpack_mel", s);
+    DX_LAUNCH_PDL((unpack_mel_kernel), grid, 256, 0, s, rows, R, DX_MEL, mel, packed);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -205,10 +223,9 @@ int embed_symbols(const int64_t* symbols, const float* emb, int n_symbols, const
 // scalar_conv3: y[c] = bias[c] + sum_j w[c][j] * x[b, p + j - 1]   (ConvNorm1D(1 → 128, k=3), model.py:640-646,
 // 402-410) evaluated straight from the padded (B, n_max) input.
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float4 scalar_conv3(const float* __restrict__ x, int b, int p, int n_max,
+__device__ __forceinline__ float4 scalar_conv3(const float* __restrict__ xr, int p, int n_max,
                                                const float* __restrict__ w, const float* __restrict__ bias,
                                                int lane) {
-    const float* xr = x + (int64_t)b * n_max;
     float xm = (p - 1 >= 0) ? xr[p - 1] : 0.f;
     float x0 = (p < n_max) ? xr[p] : 0.f;
     float xp = (p + 1 < n_max) ? xr[p + 1] : 0.f;
@@ -230,7 +247,7 @@ __global__ void accent_input_kernel(const float* __restrict__ z2_f32, const __nv
                                     const float* __restrict__ ew, const float* __restrict__ eb,
                                     const float* __restrict__ pw, const float* __restrict__ pb,
                                     const float* __restrict__ pos, Rows R, float* __restrict__ out_f32,
-                                    __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys) {
+                                    __nv_bfloat16* __restrict__ out_bf, int64_t rows_phys, bool packed) {
     ptx::griddep_wait();      // PDL: predecessor complete + visible
     ptx::griddep_launch();    // let the next kernel start its prologue
     const int lane = threadIdx.x & 31;
@@ -252,8 +269,9 @@ __global__ void accent_input_kernel(const float* __restrict__ z2_f32, const __nv
                 __nv_bfloat162 hi = *reinterpret_cast<__nv_bfloat162*>(&pk.y);
                 z = make_float4(__low2float(lo), __high2float(lo), __low2float(hi), __high2float(hi));
             }
-            float4 e = scalar_conv3(energy, b, p, R.n_max, ew, eb, lane);
-            float4 q = scalar_conv3(pitch, b, p, R.n_max, pw, pb, lane);
+            const FrameView fv = frame_view(R, b, 1, packed);
+            float4 e = scalar_conv3(energy + fv.base, p, fv.n, ew, eb, lane);
+            float4 q = scalar_conv3(pitch + fv.base, p, fv.n, pw, pb, lane);
             float4 ps = reinterpret_cast<const float4*>(pos + (int64_t)p * DX_D)[lane];
             v = make_float4(((z.x + e.x) + q.x) + ps.x, ((z.y + e.y) + q.y) + ps.y, ((z.z + e.z) + q.z) + ps.z,
                             ((z.w + e.w) + q.w) + ps.w);
@@ -270,14 +288,15 @@ __global__ void accent_input_kernel(const float* __restrict__ z2_f32, const __nv
 
 int accent_input(const float* z2_f32, const __nv_bfloat16* z2_bf, const float* energy, const float* pitch,
                  const float* ew, const float* eb, const float* pw, const float* pb, const float* pos,
-                 const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s) {
+                 const Rows& R, float* out_f32, __nv_bfloat16* out_bf, int64_t rows_phys, cudaStream_t s, bool packed) {
     int grid = (int)((R.cap + 7) / 8);
+    ProfScope prof("accent_input", s);
     if (out_bf)
         DX_LAUNCH_PDL((accent_input_kernel<true>), grid, 256, 0, s, nullptr, z2_bf, energy, pitch, ew, eb, pw, pb, pos, R,
-                                                       nullptr, out_bf, rows_phys);
+                                                       nullptr, out_bf, rows_phys, packed);
     else
         DX_LAUNCH_PDL((accent_input_kernel<false>), grid, 256, 0, s, z2_f32, nullptr, energy, pitch, ew, eb, pw, pb, pos, R,
-                                                        out_f32, nullptr, 0);
+                                                        out_f32, nullptr, 0, packed);
     DX_CHECK_LAUNCH();
     return 0;
 }

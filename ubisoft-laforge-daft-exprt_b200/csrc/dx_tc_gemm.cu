@@ -186,15 +186,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_gemm_kernel(const TcParams p
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
-static int g_num_sms = 0;
 
 template <int NT, int EPI>
 static int tc_launch(const TcParams& p, size_t smem, int grid, cudaStream_t s) {
-    static size_t configured = 0;
-    if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<NT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(tc_gemm_kernel<NT, EPI>, smem, configured));
     ProfScope prof(p.g.tag ? p.g.tag : "tc_gemm", s);
     DX_LAUNCH_PDL((tc_gemm_kernel<NT, EPI>), grid, TC_THREADS, smem, s, p);
     DX_CHECK_LAUNCH();
@@ -205,11 +201,8 @@ static int tc_gemm_impl(const TcGemmArgs& g, const Rows* R, int64_t M, cudaStrea
     DX_REQUIRE(g.nt == 128 || g.nt == 256, "tc_gemm: nt=%d (128 or 256)", g.nt);
     DX_REQUIRE(g.ks % 16 == 0 && g.K % g.ks == 0, "tc_gemm: K=%d must be a multiple of ks=%d (multiple of 16)", g.K, g.ks);
     DX_REQUIRE(g.taps == 1 || g.taps == 3, "tc_gemm: taps=%d", g.taps);
-    if (g_num_sms == 0) {
-        int dev = 0;
-        DX_CHECK_CUDA(cudaGetDevice(&dev));
-        DX_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int g_num_sms = 0;
+    DX_TRY(device_sm_count(&g_num_sms));
     TcParams p;
     p.g = g;
     if (R) {

@@ -154,11 +154,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tc_linear_kernel(const TlParams
 
 template <int EPI>
 static int tl_launch(const TlParams& p, size_t smem, int grid, cudaStream_t s) {
-    static size_t configured = 0;
-    if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(tc_linear_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(tc_linear_kernel<EPI>, smem, configured));
     ProfScope prof(p.g.tag ? p.g.tag : "tc_linear", s);
     DX_LAUNCH_PDL((tc_linear_kernel<EPI>), grid, TL_THREADS, smem, s, p);
     DX_CHECK_LAUNCH();
@@ -169,12 +166,8 @@ int tc_linear(const TcGemmArgs& g, const Rows& R, cudaStream_t s) {
     DX_REQUIRE(g.K == 128 && g.taps == 1 && g.nt == 128 && g.ks == 64, "tc_linear: needs K=128, taps=1, nt=128, ks=64 (K=%d taps=%d nt=%d ks=%d)",
                g.K, g.taps, g.nt, g.ks);
     DX_REQUIRE(g.row_stats == nullptr, "tc_linear: row_stats not supported");
-    static int num_sms = 0;
-    if (num_sms == 0) {
-        int dev = 0;
-        DX_CHECK_CUDA(cudaGetDevice(&dev));
-        DX_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int num_sms = 0;
+    DX_TRY(device_sm_count(&num_sms));
     TlParams p;
     p.g = g;
     p.R = R;

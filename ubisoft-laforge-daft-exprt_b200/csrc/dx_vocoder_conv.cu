@@ -275,15 +275,10 @@ void vc_conv_tiling(int taps, int dil, int K, int N, int* nt, int* ks) {
     *ks = k;
 }
 
-static int g_vc_sms = 0;
-
 template <int NT, bool XBF>
 static int vc_tc_launch2(const VcTcParams& p, size_t smem, int grid, cudaStream_t s) {
-    static size_t configured = 0;
-    if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_conv_tc_kernel<NT, XBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(vc_conv_tc_kernel<NT, XBF>, smem, configured));
     ProfScope prof(p.c.tag ? p.c.tag : "vc_conv", s);
     DX_LAUNCH_PDL((vc_conv_tc_kernel<NT, XBF>), grid, VC_THREADS, smem, s, p);
     DX_CHECK_LAUNCH();
@@ -299,11 +294,8 @@ int vc_conv_bf16(const VcConvArgs& c, cudaStream_t s) {
     DX_REQUIRE(c.taps % 2 == 1 && (c.taps / 2) * c.dil <= DX_VC_HALO, "vc_conv: taps=%d dil=%d exceed the %d-row halo", c.taps, c.dil, DX_VC_HALO);
     DX_REQUIRE(c.e.c_out % 32 == 0 && c.N == c.e.c_out * c.e.up, "vc_conv: N=%d != up=%d * c_out=%d", c.N, c.e.up, c.e.c_out);
     DX_REQUIRE(c.w_bf != nullptr, "vc_conv: packed bf16 weights missing (tag %s)", c.tag ? c.tag : "?");
-    if (g_vc_sms == 0) {
-        int dev = 0;
-        DX_CHECK_CUDA(cudaGetDevice(&dev));
-        DX_CHECK_CUDA(cudaDeviceGetAttribute(&g_vc_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int g_vc_sms = 0;
+    DX_TRY(device_sm_count(&g_vc_sms));
     VcTcParams p;
     p.c = c;
     p.dbg = debug_knob(11);
@@ -662,11 +654,8 @@ __global__ void __launch_bounds__(64 + (C >= 128 ? 256 : 128), C == 128 ? 1 : 2)
 
 template <int C, bool TR, bool XBF>
 static int vc_pair_launch3(const VcPairParams& p, size_t smem, int grid, cudaStream_t s) {
-    static size_t configured = 0;
-    if (smem > configured) {
-        DX_CHECK_CUDA(cudaFuncSetAttribute(vc_pair_tc_kernel<C, TR, XBF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    DX_TRY(ensure_dyn_smem(vc_pair_tc_kernel<C, TR, XBF>, smem, configured));
     ProfScope prof(p.c.tag ? p.c.tag : "vc_pair", s);
     DX_LAUNCH_PDL((vc_pair_tc_kernel<C, TR, XBF>), grid, 64 + (C >= 128 ? 256 : 128), smem, s, p);
     DX_CHECK_LAUNCH();
@@ -684,11 +673,8 @@ int vc_pair_bf16(const VcPairArgs& c, cudaStream_t s) {
     DX_REQUIRE(c.taps % 2 == 1 && c.taps <= 17 && (c.taps / 2) * c.dil <= DX_VC_HALO - c.taps / 2, "vc_pair: taps=%d dil=%d", c.taps, c.dil);
     DX_REQUIRE(c.w1_bf && c.w2_bf && c.bias1 && c.bias2, "vc_pair: weights missing (tag %s)", c.tag ? c.tag : "?");
     DX_REQUIRE(c.e.up == 1 && c.e.c_out == c.C, "vc_pair: epilogue must be up = 1, c_out = C");
-    if (g_vc_sms == 0) {
-        int dev = 0;
-        DX_CHECK_CUDA(cudaGetDevice(&dev));
-        DX_CHECK_CUDA(cudaDeviceGetAttribute(&g_vc_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int g_vc_sms = 0;
+    DX_TRY(device_sm_count(&g_vc_sms));
     VcPairParams p;
     p.c = c;
     p.dbg = debug_knob(11);

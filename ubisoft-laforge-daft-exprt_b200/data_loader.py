@@ -16,6 +16,7 @@ length-bucketed sampler.
 """
 import numpy as np
 import torch
+import torch.utils.data
 
 _ALIGN = 256
 
@@ -23,14 +24,22 @@ _ALIGN = 256
 class CollatedBatch(tuple):
     """The reference's 14-tuple, plus the staging block it is a view of (``.block``, ``.layout``)."""
 
-    def __new__(cls, items, block, layout):
+    def __new__(cls, items, block=None, layout=None):
         self = super().__new__(cls, items)
         self.block, self.layout = block, layout
         return self
 
+    def __reduce__(self):
+        # picklable (DataLoader workers send batches through a queue); the items are re-sent as plain tensors and the
+        # staging block with them, so a batch that crossed a process boundary still moves as one copy
+        return (CollatedBatch, (tuple(self), self.block, self.layout))
+
     def to_device(self, device, non_blocking=True):
         """One H2D copy of the staging block; returns the 12 tensors of ``DaftExprt.forward`` (``parse_batch`` order:
-        the reference's batch indices 0-10 and 13) as views of the device mirror."""
+        the reference's batch indices 0-10 and 13) as views of the device mirror.  A batch rebuilt without its block
+        (``DataLoader(pin_memory=True)`` re-wraps sequences as ``type(batch)(items)``) is moved tensor by tensor."""
+        if self.block is None or not self._views_alias_block():
+            return tuple(self[i].to(device, non_blocking=non_blocking) for i in (0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 13))
         mirror = torch.empty(self.block.numel(), dtype=torch.uint8, device=device)
         mirror.copy_(self.block, non_blocking=non_blocking)
         out = []
@@ -41,12 +50,29 @@ class CollatedBatch(tuple):
         return tuple(out)
 
 
+def _views_alias(block, t):
+    lo, hi = block.data_ptr(), block.data_ptr() + block.numel()
+    return lo <= t.data_ptr() < hi
+
+
+CollatedBatch._views_alias_block = lambda self: _views_alias(self.block, self[8])   # mel_specs: the bulk of the bytes
+
+
 class DaftExprtDataCollate():
     ''' Zero-pads model inputs and targets (reference data_loader.py:201-287) '''
 
     def __init__(self, hparams, pinned=None):
         self.hparams = hparams
-        self.pinned = torch.cuda.is_available() if pinned is None else bool(pinned)
+        self.pinned = pinned          # None: pinned when CUDA is there and this is not a (forked) DataLoader worker
+
+    def _use_pinned(self):
+        if self.pinned is not None:
+            return bool(self.pinned)
+        # pinning initialises CUDA, which a forked DataLoader worker cannot do ("cannot re-initialize CUDA in forked
+        # subprocess"): workers fill pageable blocks, the main process pins them (DataLoader(pin_memory=True)) or not
+        if torch.utils.data.get_worker_info() is not None:
+            return False
+        return torch.cuda.is_available()
 
     def __call__(self, batch):
         B = len(batch)
@@ -77,7 +103,7 @@ class DaftExprtDataCollate():
             nbytes = int(np.prod(shape)) * (8 if dt == i8 else 4)
             layout[name] = (off, nbytes, dt, shape)
             off += (nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
-        block = torch.zeros(max(off, _ALIGN), dtype=torch.uint8, pin_memory=self.pinned)
+        block = torch.zeros(max(off, _ALIGN), dtype=torch.uint8, pin_memory=self._use_pinned())
         t = {name: block[o:o + n].view(dt).view(shape) for name, (o, n, dt, shape) in layout.items()}
 
         t["input_lengths"].copy_(input_lengths)

@@ -41,3 +41,42 @@ def pack_rows(x_padded, lengths):
         acc += n + _lib.GAP
     starts.append(acc)
     return torch.cat(pieces, dim=0), starts
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# packed frame-side I/O (include/daft_b200.h DX_IO_PACKED_*; DaftExprt.forward(..., packed_io=(T_max, total)))
+# ----------------------------------------------------------------------------------------------------------------
+def frame_starts(output_lengths):
+    """Exclusive prefix sum of the frame counts: utterance b's frames start at ``fs[b]``; ``fs[B]`` = total."""
+    fs = [0]
+    for n in output_lengths.tolist() if hasattr(output_lengths, "tolist") else output_lengths:
+        fs.append(fs[-1] + int(n))
+    return fs
+
+
+def pack_frames(frames_energy, frames_pitch, mel_specs, output_lengths):
+    """Padded (B, T) / (B, T) / (B, 80, T) → packed float[ΣT], float[ΣT], float[80·ΣT]: utterance b's mel is the
+    ``(80, T_b)`` row-major block at ``80 · fs[b]`` (the layout of the reference's per-utterance ``.npy`` features,
+    ``data_loader.py:150-160``).  Host-side helper for tests and callers that start from padded tensors; a loader that
+    has the per-utterance arrays copies them straight into the packed staging block instead."""
+    lens = [int(n) for n in output_lengths.tolist()]
+    e = torch.cat([frames_energy[b, :n] for b, n in enumerate(lens)])
+    p = torch.cat([frames_pitch[b, :n] for b, n in enumerate(lens)])
+    m = torch.cat([mel_specs[b, :, :n].reshape(-1) for b, n in enumerate(lens)])
+    return e.contiguous(), p.contiguous(), m.contiguous()
+
+
+def mel_views(packed_mel, output_lengths, n_mel=80):
+    """Per-utterance ``(80, T_b)`` views of a packed mel (no copies) — the crop ``fine_tune.py:79`` takes."""
+    fs = frame_starts(output_lengths)
+    return [packed_mel[n_mel * fs[b]:n_mel * fs[b + 1]].view(n_mel, fs[b + 1] - fs[b]) for b in range(len(fs) - 1)]
+
+
+def unpack_mel(packed_mel, output_lengths, T_max=None, n_mel=80):
+    """Packed mel → the reference's padded (B, 80, T_max) tensor with zeros behind every utterance."""
+    views = mel_views(packed_mel, output_lengths, n_mel)
+    T_max = max(v.shape[1] for v in views) if T_max is None else T_max
+    out = packed_mel.new_zeros(len(views), n_mel, T_max)
+    for b, v in enumerate(views):
+        out[b, :, :v.shape[1]] = v
+    return out

@@ -159,8 +159,9 @@ class DaftExprt(nn.Module):
                 K = k_pad
             n = lib.dx_packed_weight_elems(taps, K, N, nt, ks)
             out = torch.empty(n, dtype=torch.bfloat16, device=dev)
-            _lib.check(lib.dx_pack_weight_bf16(_lib.ptr(w_gemm), taps, K, N, nt, ks, _lib.ptr(out), _lib.stream_ptr()),
-                       "dx_pack_weight_bf16")
+            with torch.cuda.device(dev):
+                _lib.check(lib.dx_pack_weight_bf16(_lib.ptr(w_gemm), taps, K, N, nt, ks, _lib.ptr(out), _lib.stream_ptr(dev)),
+                           "dx_pack_weight_bf16")
             keep.append(out)
             return out
 
@@ -228,17 +229,19 @@ class DaftExprt(nn.Module):
         return W
 
     def _workspace(self, B, L_max, T_max, slot=0):
+        """One grow-only scratch buffer per slot (= per concurrent ``dx_forward`` of a call), reused for every shape
+        that needs no more bytes.  ``torch.empty``: the kernels zero what they rely on (``zero_plan_halos``), and an
+        allocation never enqueues a memset that could land under a running group.  A buffer that has to grow is
+        replaced; the old block is returned to torch's caching allocator, which keeps it away from other streams
+        until the kernels already enqueued on this stream have passed it (stream-ordered reuse)."""
         mode = _MODES[self.compute_mode]
-        key = (B, L_max, T_max, mode, slot)
-        ws = self._workspaces.get(key)
-        if ws is None:
-            n = _lib.load().dx_forward_workspace_bytes(B, L_max, T_max, mode)
-            if n < 0:
-                _lib.check(1, "dx_forward_workspace_bytes")
-            if len(self._workspaces) >= 8:       # bounded cache
-                self._workspaces.pop(next(iter(self._workspaces)))
-            ws = torch.zeros(n, dtype=torch.uint8, device=self.device)
-            self._workspaces[key] = ws
+        n = _lib.load().dx_forward_workspace_bytes(B, L_max, T_max, mode)
+        if n < 0:
+            _lib.check(1, "dx_forward_workspace_bytes")
+        ws = self._workspaces.get(slot)
+        if ws is None or ws.numel() < n or ws.device != self.device:
+            ws = torch.empty(n, dtype=torch.uint8, device=self.device)
+            self._workspaces[slot] = ws
         return ws
 
     # ------------------------------------------------------------------------------------------
@@ -276,9 +279,26 @@ class DaftExprt(nn.Module):
             return None
         return t.to(device=self.device, dtype=dtype).contiguous()
 
+    @staticmethod
+    def _expect(name, t, shape):
+        """Shape contract of one argument (``None`` passes).  The reference fails with a torch shape error when a
+        tensor does not fit (or broadcasts a size-1 batch dimension); raw device pointers would read out of bounds."""
+        if t is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"{name}: expected shape {tuple(shape)}, got {tuple(t.shape)}")
+
+    def _batch_rows(self, name, t, B, width):
+        """(B, width) embedding; a (1, width) tensor is broadcast over the batch like the reference's
+        ``accent_emb + spk_emb`` does (model.py:919)."""
+        if t is None:
+            return None
+        if t.dim() == 2 and t.shape[0] == 1 and B > 1 and t.shape[1] == width:
+            t = t.expand(B, width)
+        self._expect(name, t, (B, width))
+        return t.contiguous()
+
     def _run(self, B, L_max, T_max, *, symbols, durations_float, durations_int, symbols_energy, symbols_pitch,
              input_lengths, frames_energy=None, frames_pitch=None, mel_specs=None, output_lengths=None,
-             spk_embs=None, accent_emb_in=None, spk_emb_in=None, want_enc_out=False):
+             spk_embs=None, accent_emb_in=None, spk_emb_in=None, want_enc_out=False, packed_frames=None):
         """The whole pass = ``dx_forward``.  Returns dict of output tensors.
 
         With ``self.streams > 1`` the batch is cut into that many contiguous groups of utterances which run as
@@ -290,11 +310,35 @@ class DaftExprt(nn.Module):
         W = self._prepare()
         lib = _lib.load()
         dev = self.device
+        for name, t in (("symbols", symbols), ("durations_float", durations_float), ("durations_int", durations_int),
+                        ("symbols_energy", symbols_energy), ("symbols_pitch", symbols_pitch)):
+            self._expect(name, t, (B, L_max))
+        self._expect("input_lengths", input_lengths, (B,))
+        self._expect("output_lengths", output_lengths, (B,))
+        spk_embs = self._batch_rows("spk_embs", spk_embs, B, _lib.SPK)
+        accent_emb_in = self._batch_rows("external_accent_emb", accent_emb_in, B, _lib.D)
+        spk_emb_in = self._batch_rows("external_spk_emb", spk_emb_in, B, _lib.D)
+        io_flags = 0
+        if packed_frames is None:
+            self._expect("frames_energy", frames_energy, (B, T_max))
+            self._expect("frames_pitch", frames_pitch, (B, T_max))
+            self._expect("mel_specs", mel_specs, (B, _lib.MEL, T_max))
+            mel_shape = (B, _lib.MEL, T_max)
+        else:
+            # packed frame-side I/O (include/daft_b200.h DX_IO_PACKED_*): only the valid frames exist
+            total = int(packed_frames)
+            io_flags = _lib.IO_PACKED_MEL_OUT
+            if mel_specs is not None:
+                io_flags |= _lib.IO_PACKED_FRAMES
+                self._expect("frames_energy (packed)", frames_energy, (total,))
+                self._expect("frames_pitch (packed)", frames_pitch, (total,))
+                self._expect("mel_specs (packed)", mel_specs, (total * _lib.MEL,))
+            mel_shape = (total * _lib.MEL,)
         out = {
             "accent_emb": torch.empty(B, _lib.D, device=dev),
             "speaker_preds": torch.empty(B, self.n_speakers, device=dev),
             "film": torch.empty(B, 8, 2 * _lib.D, device=dev),
-            "mel": torch.empty(B, _lib.MEL, T_max, device=dev),
+            "mel": torch.empty(mel_shape, device=dev),
             "weights": torch.empty(B, L_max, T_max, device=dev),
             "output_lengths": torch.empty(B, dtype=torch.long, device=dev),
             "enc_out": torch.empty(B, L_max, _lib.D, device=dev) if want_enc_out else None,
@@ -307,31 +351,43 @@ class DaftExprt(nn.Module):
                    ("accent_emb", out["accent_emb"]), ("speaker_preds", out["speaker_preds"]),
                    ("film", out["film"]), ("enc_out", out["enc_out"]), ("mel_out", out["mel"]),
                    ("weights_out", out["weights"]), ("output_lengths_out", out["output_lengths"]))
-        n = max(1, min(int(self.streams), B // 8)) if self.compute_mode == "bf16" else 1
+        n = max(1, min(int(self.streams), B // 8)) if (self.compute_mode == "bf16" and packed_frames is None) else 1
         bounds = [(B * i) // n for i in range(n + 1)]
         cur = torch.cuda.current_stream(dev)
         while len(self._side_streams) < n - 1:
             self._side_streams.append(torch.cuda.Stream(dev))
+        # every group's scratch exists BEFORE the fork event is recorded: nothing the allocator enqueues on the
+        # current stream can land under a group that is already running on a side stream
+        wss = [self._workspace(bounds[i + 1] - bounds[i], L_max, T_max, slot=i) for i in range(n)]
         fork = cur.record_event() if n > 1 else None
-        for i in range(n):
-            b0, b1 = bounds[i], bounds[i + 1]
-            stream = cur if i == 0 else self._side_streams[i - 1]
-            ws = self._workspace(b1 - b0, L_max, T_max, slot=i)
-            a = _lib.DxForwardArgs()
-            a.B, a.L_max, a.T_max, a.mode = b1 - b0, L_max, T_max, _MODES[self.compute_mode]
-            for name, t in tensors:
-                setattr(a, name, None if t is None else t[b0:b1].data_ptr())
-            a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
-            if i > 0:
-                stream.wait_event(fork)
-            _lib.check(lib.dx_forward(C.byref(W), C.byref(a), C.c_void_p(stream.cuda_stream)), "dx_forward")
+        with torch.cuda.device(dev):
+            for i in range(n):
+                b0, b1 = bounds[i], bounds[i + 1]
+                stream = cur if i == 0 else self._side_streams[i - 1]
+                ws = wss[i]
+                a = _lib.DxForwardArgs()
+                a.B, a.L_max, a.T_max, a.mode = b1 - b0, L_max, T_max, _MODES[self.compute_mode]
+                a.io_flags = io_flags
+                for name, t in tensors:
+                    setattr(a, name, None if t is None else (t.data_ptr() if n == 1 else t[b0:b1].data_ptr()))
+                a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+                if i > 0:
+                    stream.wait_event(fork)
+                    ws.record_stream(stream)
+                _lib.check(lib.dx_forward(C.byref(W), C.byref(a), C.c_void_p(stream.cuda_stream)), "dx_forward")
         for i in range(1, n):
             cur.wait_event(self._side_streams[i - 1].record_event())
         return out
 
     @torch.no_grad()
-    def forward(self, inputs, external_accent_emb=None, external_spk_emb=None, _want_enc_out=False):
-        """``DaftExprt.forward`` (reference model.py:889-948); same 5-tuple."""
+    def forward(self, inputs, external_accent_emb=None, external_spk_emb=None, _want_enc_out=False, packed_io=None):
+        """``DaftExprt.forward`` (reference model.py:889-948); same 5-tuple.
+
+        ``packed_io=(T_max, total_frames)`` (an extension for bulk generation, ``fine_tune.py:62-129``): the frame-side
+        inputs ``frames_energy`` / ``frames_pitch`` / ``mel_specs`` are the PACKED tensors of ``layouts.pack_frames``
+        (float[ΣT] / float[80·ΣT], per-utterance ``(80, T_b)`` blocks) and the returned mel is packed the same way
+        (``layouts.unpack_mel`` / ``layouts.mel_views`` give the per-utterance crops ``fine_tune.py:79`` takes), so
+        only valid frames cross PCIe.  Both numbers come from the host-side lengths the collate already has; no sync."""
         if len(inputs) != 12:
             raise ValueError(f"inputs must have 12 elements (including spk_embs). Got {len(inputs)}.")
         (symbols, durations_float, durations_int, symbols_energy, symbols_pitch, input_lengths,
@@ -341,7 +397,11 @@ class DaftExprt(nn.Module):
         B, L_max = symbols.shape
         # T_max: the reference sizes frames by max(cumsum(durations_int)) (model.py:497), which the data
         # contract ties to the mel width (data_loader.py:165-168); the tensor shape avoids a host sync.
-        T_max = mel_specs.shape[2] if mel_specs is not None else int(output_lengths.max())
+        if packed_io is not None:
+            T_max, total_frames = int(packed_io[0]), int(packed_io[1])
+        else:
+            T_max = mel_specs.shape[2] if mel_specs is not None else int(output_lengths.max())
+            total_frames = None
         fl, lg = torch.float32, torch.long
         out = self._run(
             B, L_max, T_max,
@@ -354,7 +414,7 @@ class DaftExprt(nn.Module):
             output_lengths=self._dev(output_lengths, lg),
             spk_embs=None if external_spk_emb is not None else self._dev(spk_embs, fl),
             accent_emb_in=self._dev(external_accent_emb, fl), spk_emb_in=self._dev(external_spk_emb, fl),
-            want_enc_out=_want_enc_out)
+            want_enc_out=_want_enc_out, packed_frames=total_frames)
         film_dec = out["film"][:, 4:8, :]
         film_params = [self.style_adapter.post_multipliers, None, None, film_dec]
         encoder_preds = [durations_float, symbols_energy, symbols_pitch, input_lengths]
@@ -368,15 +428,21 @@ class DaftExprt(nn.Module):
         """``AccentEncoder.forward`` (reference model.py:679-716) → (B, 128)."""
         W = self._prepare()
         lib = _lib.load()
+        if mel_specs.dim() != 3 or mel_specs.shape[1] != _lib.MEL:
+            raise ValueError(f"mel_specs: expected (B, {_lib.MEL}, T), got {tuple(mel_specs.shape)}")
         B, _, T_max = mel_specs.shape
+        self._expect("frames_energy", frames_energy, (B, T_max))
+        self._expect("frames_pitch", frames_pitch, (B, T_max))
+        self._expect("output_lengths", output_lengths, (B,))
         ws = self._workspace(B, 1, T_max)
         fl = torch.float32
         fe, fp, mel = self._dev(frames_energy, fl), self._dev(frames_pitch, fl), self._dev(mel_specs, fl)
         ol = self._dev(output_lengths, torch.long)
         acc = torch.empty(B, _lib.D, device=self.device)
-        _lib.check(lib.dx_accent_encoder(C.byref(W), _MODES[self.compute_mode], B, T_max, _lib.ptr(fe), _lib.ptr(fp),
-                                         _lib.ptr(mel), _lib.ptr(ol), _lib.ptr(acc), _lib.ptr(ws), ws.numel(),
-                                         _lib.stream_ptr()), "dx_accent_encoder")
+        with torch.cuda.device(self.device):
+            _lib.check(lib.dx_accent_encoder(C.byref(W), _MODES[self.compute_mode], B, T_max, _lib.ptr(fe), _lib.ptr(fp),
+                                             _lib.ptr(mel), _lib.ptr(ol), _lib.ptr(acc), _lib.ptr(ws), ws.numel(),
+                                             _lib.stream_ptr(self.device)), "dx_accent_encoder")
         return acc
 
     # ---- inference-side prosody plumbing (reference model.py:950-1024), on the device ----------------
@@ -390,10 +456,11 @@ class DaftExprt(nn.Module):
         B, L = duration_preds.shape
         dint = torch.empty(B, L, dtype=torch.long, device=self.device)
         status = torch.empty(B, dtype=torch.int32, device=self.device)
-        _lib.check(lib.dx_int_durations(_lib.ptr(duration_preds), B, L, int(hparams.sampling_rate),
-                                        int(hparams.filter_length), int(hparams.hop_length),
-                                        1 if hparams.centered else 0, _lib.ptr(dint), _lib.ptr(status),
-                                        _lib.stream_ptr()), "dx_int_durations")
+        with torch.cuda.device(self.device):
+            _lib.check(lib.dx_int_durations(_lib.ptr(duration_preds), B, L, int(hparams.sampling_rate),
+                                            int(hparams.filter_length), int(hparams.hop_length),
+                                            1 if hparams.centered else 0, _lib.ptr(dint), _lib.ptr(status),
+                                            _lib.stream_ptr(self.device)), "dx_int_durations")
         self._last_status = status
         return duration_preds, dint
 
@@ -409,15 +476,32 @@ class DaftExprt(nn.Module):
                 tab[i, 0], tab[i, 1] = st["mean"], st["std"]
             self._stats_table = (hparams.stats, tab.to(self.device))
         tab = self._stats_table[1]
-        sel = tab.index_select(0, speaker_ids.to(self.device).long().clamp_(0, tab.shape[0] - 1))
-        return sel[:, 0].contiguous(), sel[:, 1].contiguous()
+        ids = speaker_ids.to(self.device).long()
+        # an id without an entry in hparams.stats is a KeyError in the reference (model.py:984); here it is flagged on the
+        # device (out of range, or a NaN row of the table) and raised by the caller at its host sync.  The caller's
+        # tensor is never modified.
+        in_range = (ids >= 0) & (ids < tab.shape[0])
+        sel = tab.index_select(0, torch.where(in_range, ids, torch.zeros_like(ids)))
+        unknown = ~in_range | torch.isnan(sel[:, 0])
+        return sel[:, 0].contiguous(), sel[:, 1].contiguous(), unknown
+
+    @staticmethod
+    def _raise_unknown_speakers(speaker_ids, unknown_host):
+        if bool(unknown_host.any()):
+            first = int(torch.nonzero(unknown_host).flatten()[0])
+            raise KeyError(f"spk {int(speaker_ids[first])}")
 
     def _transform(self, energy, pitch, energy_factors, pitch_factors, durations_int, mean, std, transform):
         lib = _lib.load()
         B, L = pitch.shape
-        _lib.check(lib.dx_prosody_transform(_lib.ptr(energy), _lib.ptr(pitch), _lib.ptr(energy_factors),
-                                            _lib.ptr(pitch_factors), _lib.ptr(durations_int), _lib.ptr(mean),
-                                            _lib.ptr(std), B, L, transform, _lib.stream_ptr()), "dx_prosody_transform")
+        for name, t in (("energy", energy), ("energy_factors", energy_factors), ("pitch_factors", pitch_factors),
+                        ("durations_int", durations_int)):
+            self._expect(name, t, (B, L))
+        with torch.cuda.device(self.device):
+            _lib.check(lib.dx_prosody_transform(_lib.ptr(energy), _lib.ptr(pitch), _lib.ptr(energy_factors),
+                                                _lib.ptr(pitch_factors), _lib.ptr(durations_int), _lib.ptr(mean),
+                                                _lib.ptr(std), B, L, transform, _lib.stream_ptr(self.device)),
+                       "dx_prosody_transform")
 
     @torch.no_grad()
     def inference(self, inputs, pitch_transform, hparams, external_prosody=None, external_embeddings=None,
@@ -435,6 +519,13 @@ class DaftExprt(nn.Module):
             raise NotImplementedError
         fl, lg = torch.float32, torch.long
         B, L_max = symbols.shape
+        self._expect("input_lengths", input_lengths, (B,))
+        self._expect("speaker_ids", speaker_ids, (B,))
+        for name, t in (("dur_factors", dur_factors), ("energy_factors", energy_factors), ("pitch_factors", pitch_factors),
+                        ("external_prosody['duration_preds']", external_prosody["duration_preds"]),
+                        ("external_prosody['energy_preds']", external_prosody["energy_preds"]),
+                        ("external_prosody['pitch_preds']", external_prosody["pitch_preds"])):
+            self._expect(name, t, (B, L_max))
         symbols_d = self._dev(symbols, lg)
         in_len = self._dev(input_lengths, lg)
         # duration_preds * dur_factors is a fresh tensor in the reference too (model.py:1074)
@@ -446,14 +537,16 @@ class DaftExprt(nn.Module):
         if pitch_preds.data_ptr() != pitch_src.data_ptr():
             pitch_preds = pitch_preds.clone()
         if pitch_transform == "add":
-            mean, std = self._pitch_stats(hparams, speaker_ids)
+            mean, std, unknown = self._pitch_stats(hparams, speaker_ids)
         else:
             mean = std = torch.zeros(B, device=self.device)
+            unknown = torch.zeros(B, dtype=torch.bool, device=self.device)
         self._transform(energy_preds, pitch_preds, self._dev(energy_factors, fl), self._dev(pitch_factors, fl),
                         durations_int, mean, std, 0 if pitch_transform == "add" else 1)
         # the only host sync of the pass: frame count (the reference syncs on it too, model.py:497,1100)
         # and the per-utterance status of the integer conversion
-        host = torch.stack([durations_int.sum(dim=1), self._last_status.long()]).cpu()
+        host = torch.stack([durations_int.sum(dim=1), self._last_status.long(), unknown.long()]).cpu()
+        self._raise_unknown_speakers(speaker_ids, host[2] != 0)
         if bool((host[1] != 0).any()):
             bad = [int(i) for i in torch.nonzero(host[1]).flatten()]
             raise RuntimeError(f"get_int_durations: the reference's duration_to_integer fails for utterances {bad} "
@@ -473,7 +566,8 @@ class DaftExprt(nn.Module):
 
     def pitch_shift(self, pitch_preds, pitch_factors, hparams, speaker_ids):
         """``DaftExprt.pitch_shift`` (reference model.py:975-994), in place on a device tensor."""
-        mean, std = self._pitch_stats(hparams, speaker_ids)
+        mean, std, unknown = self._pitch_stats(hparams, speaker_ids)
+        self._raise_unknown_speakers(speaker_ids, unknown.cpu())
         B, L = pitch_preds.shape
         ones = torch.ones(B, L, device=self.device)
         dint = torch.ones(B, L, dtype=torch.long, device=self.device)
