@@ -9,20 +9,27 @@ batch (B=64, 20-150 symbols, 1-9 frames per symbol) — utteranc
 collective ("weak" scaling).  Prints ONE JSON line (rank 0).
 
   value     valid mel frames/s, inputs resident in HBM, CUDA events per step, L2 flushed between steps
-  e2e       same metric through the public API with HOST (pinned) buffers: every step copies its 12 inputs H2D and
-            its mel + output_lengths D2H inside the timed region.  The steps are pipelined the way bulk generation
-            runs them (daft_exprt_b200/bulk.py): copy streams move step i+1 in and step i-1 out while step i
-            computes; K steps are timed as ONE region (events at both ends).  "serial_ms_per_step" is the same
-            loop without overlap (copy in, forward, copy out, one stream).
+  e2e       same metric through the public API with HOST (pinned) buffers: every step moves ONE staging block H2D (symbol
+            side padded, frame side PACKED: only valid frames, DaftExprt.forward(packed_io=...)) and the packed mel +
+            output_lengths D2H inside the timed region.  The steps are pipelined the way bulk generation runs them
+            (daft_exprt_b200/bulk.py): copy streams move step i+1 in and step i-1 out while step i computes; K steps are
+            timed as ONE region.  "padded" repeats it with the reference's padded tensors (12 copies in, padded mel out),
+            "serial_ms_per_step" is the padded loop without overlap.  Each rank is bound to its own host cores (and to its
+            GPU's NUMA node when the box has several) before its pinned memory is first touched (hostbind.py).
   roofline  the dominant kernel (ffn_tc_kernel: out-proj + LN1 + conv FFN + LN2/FiLM + next QKV, 12 launches per
             step): its algorithmic FLOPs / its summed launch durations (events recorded around every launch by the
-            library's profiler in a separate, untimed pass); traffic = DRAM bytes per launch from the committed
-            ncu --set full capture (profiles/ncu_traffic.json).  "gemm_family" is the same ratio over all
-            tcgen05 conv / linear launches.
-  cpu_baseline  the oracle port (oracle/daft_oracle.py) timed on this box's host cores on a bounded sample
+            library's profiler in a separate, untimed pass).  frac is against the BURST peak when the clocks sampled
+            during the timed region sat at sm_max_mhz with no cap reason, else against the sustained peak; both are
+            given.  "kernels" holds one roofline row per kernel family (tensor or HBM bound).
+  configs   the other BASELINE.json configs at every N: cfg1 (B=1: forward ms, p50 latency, CPU frames/s), cfg4 (L=400,
+            T=2000 at B=1 and B=8 + the attention kernel's roofline there), cfg3 (bulk.BulkRunner over a fixed slice of
+            the 100 k-utterance stream, STRONG-scaled over the N ranks: host collate + H2D + forward + D2H + crop)
+  cpu_baseline  the reference's own DaftExprt.forward (oracle/_ref, staged copy of the unmodified reference) — or the
+            oracle port when that copy is absent — timed on this box's host cores on the full cfg2 batch
 
---impl reference: the reference's CPU path for the same config = the oracle port (the reference itself is Python
-and lives only in the build container; the port is bit-identical to it there, tests/test_oracle_vs_reference.py).
+--impl reference: the reference's CPU path for the same config: the live reference class from oracle/_ref
+(cpu_baseline.kind "reference"), else the oracle port ("port"; bit-identical to it in the build container,
+tests/test_oracle_vs_reference.py).  Same 64-utterance cfg2 batch as our arm, every step.
 """
 import argparse
 import json
@@ -143,8 +150,37 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------------------
+def workload_config(batch):
+    """The `config` object both arms print (identical by construction: same batch, same weights)."""
+    return {"workload": WORKLOAD, "batch_per_gpu": int(batch[0].shape[0]), "L_max": int(batch[0].shape[1]),
+            "T_max": int(batch[8].shape[2]), "valid_frames_per_gpu_step": int(batch[9].sum()),
+            "l2": "flushed between timed iterations (512 MiB memset) on the GPU arm", "weights": "random-init, seed 1234"}
+
+
+def cpu_forward_fn(hp, sd):
+    """The reference's CPU forward for the timed CPU legs: the live reference class (oracle/_ref or /root/reference,
+    unmodified) when present, else the oracle port.  Returns (callable(batch) -> outputs, kind, description)."""
+    import torch
+    try:
+        from oracle import ref_harness as R
+        if R.reference_available():
+            ref = R.build_reference_model(hp, sd)
+
+            def run(batch):
+                with torch.no_grad():
+                    return ref(tuple(t.clone() for t in batch))
+            return run, "reference", f"reference DaftExprt.forward (model.py:889-948) from {R.REFERENCE_KIND}, fp32 eval, no_grad"
+    except Exception as e:          # noqa: BLE001 - fall back to the port and say why
+        sys.stderr.write(f"bench: live reference unavailable ({type(e).__name__}: {e}); timing the oracle port\n")
+    from oracle import daft_oracle as O
+
+    def run_port(batch):
+        return O.forward(sd, hp, tuple(t.clone() for t in batch))
+    return run_port, "port", "oracle port (oracle/daft_oracle.py: the reference's torch ops restated), fp32"
+
+
 def reference_arm(args):
-    """--impl reference: the oracle port (the reference's algorithm, fp32, eval, no_grad) on the host cores."""
+    """--impl reference: the reference's own CPU forward on the host cores, on the SAME cfg2 batch as our arm."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -152,24 +188,18 @@ def reference_arm(args):
     from daft_exprt_b200.hparams import default_hparams
     from daft_exprt_b200.weights import make_state_dict
     from daft_exprt_b200 import synthetic
-    from oracle import daft_oracle as O
     torch.set_num_threads(os.cpu_count() or 1)
     hp = default_hparams()
     sd = make_state_dict(hp, 1234)
-    full = synthetic.config_batch(hp, "cfg2")
-    sample = tuple(t[::4].contiguous() for t in full)          # 16 of the 64 utterances, same length mix
-    # crop the padding to the sample's own maxima, as the reference's collate would (data_loader.py:219,246)
-    L, T = int(sample[5].max()), int(sample[9].max())
-    sample = (sample[0][:, :L], sample[1][:, :L], sample[2][:, :L], sample[3][:, :L], sample[4][:, :L], sample[5],
-              sample[6][:, :T], sample[7][:, :T], sample[8][:, :, :T], sample[9], sample[10], sample[11])
-    sample = tuple(t.contiguous() for t in sample)
-    frames = int(sample[9].sum())
+    batch = synthetic.config_batch(hp, "cfg2")          # rank 0's batch of our arm (seed 42)
+    frames = int(batch[9].sum())
+    run, kind, what = cpu_forward_fn(hp, sd)
     for _ in range(max(1, args.warmup)):
-        O.forward(sd, hp, sample)
+        run(batch)
     times = []
     for _ in range(args.steps):
         t0 = time.perf_counter()
-        O.forward(sd, hp, sample)
+        run(batch)
         times.append(time.perf_counter() - t0)
     ms = 1000 * sum(times) / len(times)
     value = frames / (ms / 1000)
@@ -177,9 +207,9 @@ def reference_arm(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": "every 4th utterance of the cfg2 batch (16 of 64)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"16 of the 64 cfg2 utterances per step ({frames} valid frames), {args.steps} steps"},
+        "dtype": "f32", "data": "synthetic", "config": workload_config(batch),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "what": what,
+                         "sample": f"the full cfg2 batch (64 utterances, {frames} valid frames) per step, {args.steps} steps"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -213,6 +243,180 @@ def emit(line):
     out.flush()
 
 
+def kernel_rooflines(prof, batch, tc_peak, hbm_peak, ms_step):
+    """One roofline row per kernel family of the cfg2 step (bf16 mode): algorithmic FLOPs or bytes of the family's
+    launches / their summed durations (per-launch CUDA events).  Algorithmic work: SURVEY.md §8(d) (valid rows only,
+    2 FLOPs per MAC; bytes = the tensors a launch must read + write once)."""
+    in_l, out_l = [int(x) for x in batch[5].tolist()], [int(x) for x in batch[9].tolist()]
+    B, L_max, T_max = batch[0].shape[0], batch[0].shape[1], batch[8].shape[2]
+    sT, sL = sum(out_l), sum(in_l)
+    rows = []
+
+    def tensor_row(name, tags, flops, note):
+        ms = sum(prof[t][1] for t in tags if t in prof)
+        n = sum(prof[t][0] for t in tags if t in prof)
+        if ms <= 0:
+            return
+        ach = flops / (ms * 1e-3) / 1e12
+        rows.append({"kernel": name, "bound": "tensor", "launches_per_step": n, "ms_per_step": ms, "achieved": ach, "peak": tc_peak,
+                     "unit": "TFLOP/s", "frac": ach / tc_peak, "share_of_step": ms / ms_step, "algorithmic": note})
+
+    def hbm_row(name, tags, nbytes, note):
+        ms = sum(prof[t][1] for t in tags if t in prof)
+        n = sum(prof[t][0] for t in tags if t in prof)
+        if ms <= 0:
+            return
+        ach = nbytes / (ms * 1e-3) / 1e9
+        rows.append({"kernel": name, "bound": "hbm", "launches_per_step": n, "ms_per_step": ms, "achieved": ach, "peak": hbm_peak,
+                     "unit": "GB/s", "frac": ach / hbm_peak, "share_of_step": ms / ms_step, "algorithmic": note})
+
+    attn = 8 * sum(4 * t * t * D for t in out_l) + 4 * sum(4 * l * l * D for l in in_l)
+    tensor_row("attention_tc_kernel", ["attn_tc"], attn, "4 N_b^2 D FLOP per (utterance, block): QK^T + PV over valid tokens, 12 blocks")
+    tensor_row("tc_gemm_kernel<256,1> (accent pre-net convs 80->1024, 1024->1024)", ["tc_prenet0", "tc_prenet1"],
+               2 * sT * KT * (M * CC + CC * CC), "2 T k (80*1024 + 1024*1024) FLOP per valid frame")
+    tensor_row("tc_gemm_kernel<128,2> (pre-net conv 1024->128 + LN)", ["tc_prenet2_ln"], 2 * sT * KT * CC * D, "2 T k 1024*128 FLOP")
+    tensor_row("tc_linear_kernel (first QKV of each stack, mel projection)", ["tc_qkv", "tc_melproj"],
+               6 * D * D * (2 * sT + sL) + 2 * sT * D * M, "6 D^2 per row (QKV) + 2 D 80 per frame (mel)")
+    hbm_row("ln_apply_bf16_kernel", ["ln_apply_bf16"], 2 * 2 * (sT + 2 * B) * CC * 2,
+            "2 launches x (read + write one bf16 row of 1024 channels per live row)")
+    hbm_row("lenreg_frames_kernel", ["lenreg_frames"], B * L_max * T_max * 4 + sT * D * 2 + sL * D * 4,
+            "writes the (B, L_max, T_max) fp32 alignment tensor of the return contract + one bf16 row per frame; reads xs")
+    hbm_row("unpack_mel_kernel", ["unpack_mel"], sT * M * 4 + B * M * T_max * 4, "reads 320 B per frame, writes the padded (B, 80, T_max) fp32 mel")
+    hbm_row("pack_mel_kernel", ["pack_mel"], sT * M * 4 + sT * 96 * 2, "reads 320 B per frame, writes 96 bf16 channels per row")
+    hbm_row("accent_input_kernel", ["accent_input"], sT * (2 * D * 2 + D * 4 + 8), "bf16 row in + out, positional row, energy / pitch")
+    return rows
+
+
+def run_configs(args, model, hp, sd, dev, rank, world, timed, profile_step, sync_all, tc_peak, lat_p50, dist):
+    """The BASELINE.json configs the headline line does not carry, measured at every N:
+    cfg1 (B=1, 60 symbols, 300 frames), cfg4 (400 symbols, 2000 frames, B=1 and B=8), cfg3 (bulk generation: a fixed
+    slice of the 100 k-utterance stream through bulk.plan_shards + bulk.BulkRunner, sharded over the N ranks = strong
+    scaling; per-rank seconds, max over ranks).  cfg1 / cfg4 are per-GPU figures measured on rank 0."""
+    import torch
+    from daft_exprt_b200 import synthetic, bulk
+    out = {}
+    if rank == 0:
+        # ---- cfg1
+        b1 = synthetic.config_batch(hp, "cfg1")
+        d1 = tuple(t.to(dev) for t in b1)
+        for _ in range(5):
+            model(d1)
+        t = timed(lambda: model(d1), 50)
+        c1 = {"workload": "cfg1: B=1, 60 symbols, 300 frames, DaftExprt.forward; inference() p50 incl. D2H of the mel",
+              "forward_ms": statistics.median(t), "frames": int(b1[9].sum()), "p50_ms": lat_p50,
+              "frames_s": int(b1[9].sum()) / (statistics.median(t) * 1e-3)}
+        if not args.no_cpu_baseline:
+            torch.set_num_threads(os.cpu_count() or 1)
+            run_cpu, kind, what = cpu_forward_fn(hp, sd)
+            for _ in range(2):
+                run_cpu(b1)
+            ts = []
+            for _ in range(10):
+                t0 = time.perf_counter()
+                run_cpu(b1)
+                ts.append(time.perf_counter() - t0)
+            c1["cpu"] = {"frames_s": int(b1[9].sum()) / statistics.median(ts), "ms_per_call": 1e3 * statistics.median(ts), "kind": kind,
+                         "cores": torch.get_num_threads(), "sample": "10 timed calls after 2 warm-ups, median", "what": what}
+        out["cfg1"] = c1
+        # ---- cfg4
+        c4 = {"workload": "cfg4: 400 symbols, 2000 frames per utterance, DaftExprt.forward, inputs resident"}
+        for name, key in (("cfg4_b1", "b1"), ("cfg4_b8", "b8")):
+            bb = synthetic.config_batch(hp, name)
+            dd = tuple(t.to(dev) for t in bb)
+            for _ in range(3):
+                model(dd)
+            t = timed(lambda: model(dd), 20)
+            c4[key + "_ms"] = statistics.median(t)
+            c4[key + "_frames_s"] = int(bb[9].sum()) / (statistics.median(t) * 1e-3)
+            if key == "b8":
+                pr = profile_step(lambda: model(dd), 3)
+                fl = 8 * sum(4 * int(n) * int(n) * D for n in bb[9].tolist()) + 4 * sum(4 * int(n) * int(n) * D for n in bb[5].tolist())
+                if "attn_tc" in pr and pr["attn_tc"][1] > 0:
+                    ach = fl / (pr["attn_tc"][1] * 1e-3) / 1e12
+                    c4["attention_roofline"] = {"kernel": "attention_tc_kernel", "bound": "tensor", "achieved": ach, "peak": tc_peak,
+                                                "unit": "TFLOP/s", "frac": ach / tc_peak, "ms_per_step": pr["attn_tc"][1],
+                                                "launches_per_step": pr["attn_tc"][0], "share_of_step": pr["attn_tc"][1] / statistics.median(t),
+                                                "algorithmic": "4 N^2 D FLOP per (utterance, block), N = 2000 (8 blocks) / 400 (4 blocks)"}
+                c4["b8_kernels_ms"] = {k: round(v[1], 4) for k, v in sorted(pr.items())}
+        c4["frames_s"] = c4["b8_frames_s"]
+        out["cfg4"] = c4
+        del d1, dd
+    # ---- cfg3: every rank takes its shard of the slice (no data-path collective)
+    n_utt = int(args.cfg3_utterances)
+    in_lens, out_lens = synthetic.stream_lengths(hp, n_utt, seed=43)
+    batches, mine = bulk.plan_shards(in_lens, out_lens, 64, world)
+    my = mine[rank]
+    ids = sorted({i for k in my for i in batches[k]})
+    loc = {g: j for j, g in enumerate(ids)}
+    utts = [synthetic.utterance(hp, g, seed=43) for g in ids]
+    stream = {f: [u[f] for u in utts] for f in synthetic.UtteranceStream.FIELDS}
+    local_batches = [[loc[g] for g in batches[k]] for k in my]
+    table = bulk.PointerTable(stream)
+    n_cpu = len(os.sched_getaffinity(0))
+    seen = [0]
+
+    def sink(i, mel):
+        seen[0] += mel.shape[1]
+
+    runner_kw = dict(workers=2, slots=6, collate_threads=max(1, min(4, n_cpu // 2)))
+    secs, dev_ms, got = [], [], 0
+    for it in range(2):                     # first pass warms the pinned-block cache; the second is reported
+        seen[0] = 0
+        runner = bulk.BulkRunner(model, sink=sink, **runner_kw)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        got = runner.run(table, local_batches, list(range(len(local_batches))))
+        e1.record()
+        torch.cuda.synchronize()
+        secs.append(time.perf_counter() - t0)
+        dev_ms.append(e0.elapsed_time(e1))
+    my_frames = sum(out_lens[g] for g in ids)
+    assert got == my_frames == seen[0], (got, my_frames, seen[0])
+    tt = torch.tensor([secs[-1], dev_ms[-1] * 1e-3, float(my_frames), float(len(ids))], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx, sm = tt.clone(), tt.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        gather = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(gather, tt)
+        wall, devs, tot_frames, tot_utts = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[3])
+        per_rank = [round(float(g[0]), 4) for g in gather]
+    else:
+        wall, devs, tot_frames, tot_utts = secs[-1], dev_ms[-1] * 1e-3, float(my_frames), float(len(ids))
+        per_rank = [round(secs[-1], 4)]
+    if rank == 0:
+        out["cfg3"] = {
+            "workload": f"cfg3 slice: utterances 0..{n_utt - 1} of the 100 k stream (seed 43 + index, 20-150 symbols), global length sort, "
+                        f"batches of 64, LPT-assigned to {world} rank(s) (bulk.plan_shards), bulk.BulkRunner: native packed collate -> one H2D "
+                        "block -> forward(packed_io) -> packed mel D2H -> per-utterance crop to the sink; utterances in host memory",
+            "scaling": "strong", "utterances": int(tot_utts), "frames": int(tot_frames), "batches": len(batches),
+            "seconds": wall, "frames_s": tot_frames / wall, "utterances_s": tot_utts / wall,
+            "device_seconds": devs, "per_rank_seconds": per_rank,
+            "timing": "host wall clock of runner.run() between barriers (the path is a host pipeline), max over ranks; second of two passes; "
+                      "device_seconds = CUDA events on the main stream around the same call, max over ranks",
+            "runner": runner_kw, "projected_100k_seconds": 100000.0 / (tot_utts / wall)}
+    return out if rank == 0 else None
+
+
+def pick_peak(peaks, clk):
+    """Roofline denominator: MEASURED_PEAKS.json's burst bf16 figure when the clocks sampled under the timed load sat
+    at sm_max_mhz (within 3 %) with no cap / slowdown reason — the kernel is timed per launch inside a ~1 ms step, not
+    inside a seconds-long power-capped run — else the sustained figure."""
+    burst, sus = peaks.get("bf16_tflops"), peaks.get("bf16_tflops_sustained")
+    if burst is None and sus is None:
+        return 1400.0, "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)", {"burst": None, "sustained": 1400.0}
+    at_max = (clk and clk.get("sm_mhz") and clk.get("sm_max_mhz") and clk["sm_mhz"] >= 0.97 * clk["sm_max_mhz"]
+              and not clk.get("reasons"))
+    both = {"burst": burst, "sustained": sus}
+    if at_max and burst is not None:
+        return burst, "MEASURED_PEAKS.json bf16_tflops (burst: clocks at sm_max_mhz, no cap reason during the timed region)", both
+    if sus is not None:
+        return sus, "MEASURED_PEAKS.json bf16_tflops_sustained (clocks below max or capped during the timed region)", both
+    return burst, "MEASURED_PEAKS.json bf16_tflops", both
+
+
 def main():
     _guard_stdout()
     ap = argparse.ArgumentParser()
@@ -222,6 +426,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg1 / cfg3 / cfg4 blocks")
+    ap.add_argument("--cfg3-utterances", type=int, default=16384)
+    ap.add_argument("--no-bind", action="store_true", help="leave the rank on the default CPU affinity")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -232,16 +439,19 @@ def main():
     import torch.distributed as dist
     from daft_exprt_b200.hparams import default_hparams
     from daft_exprt_b200.weights import make_state_dict
-    from daft_exprt_b200 import synthetic, _lib
+    from daft_exprt_b200 import synthetic, _lib, bulk, layouts, hostbind
     from daft_exprt_b200.model import DaftExprt
     import __graft_entry__ as entry
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
     if rank == 0:
         entry.build()
     torch.cuda.set_device(local_rank)
+    # host placement BEFORE the first pinned allocation (first touch decides the NUMA node of the staging memory)
+    binding = {"bound": False, "why": "--no-bind"} if args.no_bind else hostbind.bind_to_gpu(local_rank, local_rank, local_world)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
@@ -290,20 +500,33 @@ def main():
         host_len.copy_(out[3][1], non_blocking=True)
         return out
 
-    # pipelined e2e: NSLOT input / output slots; copy streams overlap H2D of step i+1 and D2H of step i-1 with step i
+    # ---- e2e pipelines: NSLOT input / output slots; copy streams overlap H2D of step i+1 and D2H of step i-1 with step i
     NSLOT = 3
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     main = torch.cuda.current_stream(dev)
-    dev_in = [tuple(torch.empty_like(t, device=dev) for t in host_batch) for _ in range(NSLOT)]
-    host_out = [(torch.empty(B, 80, T_max).pin_memory(), torch.empty(B, dtype=torch.long).pin_memory()) for _ in range(NSLOT)]
     ev_in = [torch.cuda.Event() for _ in range(NSLOT)]        # inputs of the slot have landed
     ev_free = [torch.cuda.Event() for _ in range(NSLOT)]      # forward has consumed the slot's inputs
     ev_done = [torch.cuda.Event() for _ in range(NSLOT)]      # forward has produced the slot's outputs
     ev_out = [torch.cuda.Event() for _ in range(NSLOT)]       # outputs of the slot are on the host
     keep = [None] * NSLOT
 
-    def run_pipelined(steps):
+    # (a) packed: ONE pinned staging block per step in (symbol side padded, frame side packed = only valid frames), the
+    #     packed mel + lengths out — what bulk.BulkRunner moves (DX_IO_PACKED_*)
+    layout, blk_bytes = bulk.block_layout(B, L_max, T_max, 80, host_batch[11].shape[1], total_frames=frames)
+    stage = torch.empty(blk_bytes, dtype=torch.uint8).pin_memory()
+    pe, pp, pm = layouts.pack_frames(host_batch[6], host_batch[7], host_batch[8], host_batch[9])
+    packed_host = host_batch[:6] + (pe, pp, pm) + host_batch[9:]
+    for dst, src in zip(bulk.block_views(stage, layout), packed_host):
+        dst.copy_(src)
+    mirrors = [torch.empty(blk_bytes, dtype=torch.uint8, device=dev) for _ in range(NSLOT)]
+    pk_out = [(torch.empty(frames * 80).pin_memory(), torch.empty(B, dtype=torch.long).pin_memory()) for _ in range(NSLOT)]
+    # (b) padded: the reference's 12 padded tensors in, the padded (B, 80, T_max) mel out (round-1 pipeline)
+    dev_in = [tuple(torch.empty_like(t, device=dev) for t in host_batch) for _ in range(NSLOT)]
+    pd_out = [(torch.empty(B, 80, T_max).pin_memory(), torch.empty(B, dtype=torch.long).pin_memory()) for _ in range(NSLOT)]
+
+    def run_pipelined(steps, packed):
         """steps x (H2D, forward, D2H); returns ms for the whole region (device events on the main stream)."""
+        host_out = pk_out if packed else pd_out
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         t0.record(main)
@@ -315,8 +538,11 @@ def main():
             with torch.cuda.stream(s_in):
                 if i >= NSLOT:
                     s_in.wait_event(ev_free[k])
-                for dst, src in zip(dev_in[k], host_batch):
-                    dst.copy_(src, non_blocking=True)
+                if packed:
+                    mirrors[k].copy_(stage, non_blocking=True)
+                else:
+                    for dst, src in zip(dev_in[k], host_batch):
+                        dst.copy_(src, non_blocking=True)
                 ev_in[k].record(s_in)
 
         copy_in(0)
@@ -327,7 +553,10 @@ def main():
             main.wait_event(ev_in[k])
             if i >= NSLOT:
                 main.wait_event(ev_out[k])            # the slot's previous outputs have left the device
-            out = model(dev_in[k])
+            if packed:
+                out = model(bulk.block_views(mirrors[k], layout), packed_io=(T_max, frames))
+            else:
+                out = model(dev_in[k])
             keep[k] = out
             ev_free[k].record(main)
             ev_done[k].record(main)
@@ -348,7 +577,8 @@ def main():
     for _ in range(args.warmup):
         step_resident()
         step_e2e()
-    run_pipelined(max(args.warmup, NSLOT + 1))
+    run_pipelined(max(args.warmup, NSLOT + 1), True)
+    run_pipelined(max(args.warmup, NSLOT + 1), False)
     sync_all()
     clocks.mark_start()
     l0 = lib.dx_launch_count()
@@ -357,7 +587,9 @@ def main():
     sync_all()
     t_e2e = timed(step_e2e, args.steps)
     sync_all()
-    ms_pipe = run_pipelined(args.steps) / args.steps
+    ms_pipe = run_pipelined(args.steps, True) / args.steps
+    sync_all()
+    ms_pipe_padded = run_pipelined(args.steps, False) / args.steps
     # a short timed region can fall between two 100 ms samples: keep the same step running (untimed) until at least
     # three samples have been taken under this load, 4 s at most
     t_keep = time.perf_counter()
@@ -367,42 +599,49 @@ def main():
     clocks.mark_end()
     sync_all()
     clk = clocks.stop()
-    # the pipelined loop must produce what the direct call produces
+    # both pipelines must produce what the direct call produces (the packed one: the same valid frames, bit for bit)
     ref_out = step_resident()
     torch.cuda.synchronize()
-    assert torch.equal(host_out[(args.steps - 1) % NSLOT][0], ref_out[3][0].cpu()), "pipelined e2e result differs from the direct call"
+    ref_mel = ref_out[3][0].cpu()
+    last = (args.steps - 1) % NSLOT
+    assert torch.equal(pd_out[last][0], ref_mel), "padded pipelined e2e result differs from the direct call"
+    assert torch.equal(layouts.unpack_mel(pk_out[last][0], host_batch[9], T_max), ref_mel), "packed pipelined e2e result differs from the direct call"
+    assert torch.equal(pk_out[last][1], host_batch[9])
 
     ms_res, ms_e2e = sum(t_res) / len(t_res), sum(t_e2e) / len(t_e2e)
-    tt = torch.tensor([ms_res, ms_e2e, float(frames), ms_pipe], dtype=torch.float64, device=dev)
+    tt = torch.tensor([ms_res, ms_e2e, float(frames), ms_pipe, ms_pipe_padded], dtype=torch.float64, device=dev)
     if world > 1:
         mx = tt.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = tt.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms_res, ms_e2e, total_frames, ms_pipe = float(mx[0]), float(mx[1]), float(sm[2]), float(mx[3])
+        ms_res, ms_e2e, total_frames, ms_pipe, ms_pipe_padded = float(mx[0]), float(mx[1]), float(sm[2]), float(mx[3]), float(mx[4])
     else:
         total_frames = float(frames)
 
     # ---- per-kernel timing pass (untimed for the headline): events around every launch of the main families
     prof = {}
     roofline = None
-    if rank == 0:
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak, peak_src, both_peaks = pick_peak(peaks, clk)
+    hbm_peak = peaks.get("hbm_gbs", 6500.0)
+
+    def profile_step(fn, nprof=5):
         lib.dx_profile_enable(1)
-        nprof = 5
         for _ in range(nprof):
             flush.zero_()
-            step_resident()
+            fn()
         buf = ctypes.create_string_buffer(1 << 16)
         _lib.check(lib.dx_profile_report(buf, len(buf)), "dx_profile_report")
         lib.dx_profile_enable(0)
-        prof = {k: (n // nprof, ms / nprof) for k, (n, ms) in parse_profile(buf.value.decode()).items()}
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = peaks.get("bf16_tflops_sustained", 1400.0)
-        peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained" if "bf16_tflops_sustained" in peaks else "fallback 1.4 PFLOP/s sustained"
+        return {k: (n // nprof, ms / nprof) for k, (n, ms) in parse_profile(buf.value.decode()).items()}
+
+    if rank == 0:
+        prof = profile_step(step_resident)
         gemm_tags = [k for k in prof if k.startswith("tc_")] if args.mode == "bf16" else [k for k in prof if k == "gemm_f32"]
         gemm_ms = sum(prof[k][1] for k in gemm_tags)
         gflop = batch_flops(host_batch, gemm_flops_forward)
@@ -427,11 +666,17 @@ def main():
                         "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
                         "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
                         "traffic_source": traffic_src, "peak_source": peak_src,
+                        "frac_of_burst": ach / both_peaks["burst"] if both_peaks.get("burst") else None,
+                        "frac_of_sustained": ach / both_peaks["sustained"] if both_peaks.get("sustained") else None,
                         "algorithmic_flops_per_launch": fl / n_l, "avg_launch_ms": ms / n_l, "launches_per_step": n_l,
-                        "share_of_step": ms / sum(v[1] for v in prof.values()), "gemm_family": family}
+                        "share_of_step": ms / ms_res,
+                        "share_note": "kernel ms per step (per-launch events, PDL overlap removed) / ms_per_step",
+                        "gemm_family": family}
         elif family is not None:
             roofline = {"bound": "tensor", "kernel": family["kernels"], "achieved": family["achieved"], "peak": peak,
                         "unit": "TFLOP/s", "frac": family["frac"], "traffic": None, "peak_source": peak_src, "gemm_family": family}
+        if roofline is not None and args.mode == "bf16":
+            roofline["kernels"] = kernel_rooflines(prof, host_batch, peak, hbm_peak, ms_res)
 
     # ---- p50 single-utterance latency (cfg1 shape, inference(), host sync per call)
     lat_p50 = None
@@ -617,37 +862,55 @@ def main():
         }
         del gen, audio, mel_pin, aud_pin
 
+    # ---- the other BASELINE.json configs (every N): cfg1 latency, cfg4 long form, cfg3 bulk generation strong-scaled
+    configs = None
+    if not args.no_configs and args.mode == "bf16":
+        configs = run_configs(args, model, hp, sd, dev, rank, world, timed, profile_step, sync_all, peak, lat_p50, dist)
+
     # ---- CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        from oracle import daft_oracle as O
         torch.set_num_threads(os.cpu_count() or 1)
+        try:
+            os.sched_setaffinity(0, range(os.cpu_count() or 1))      # the CPU legs use every core, like the reference arm
+        except OSError:
+            pass
+        run_cpu, cpu_kind, cpu_what = cpu_forward_fn(hp, sd)
         cpu_batch = tuple(t.clone() for t in host_batch)
-        O.forward(sd, hp, cpu_batch)                       # warm-up
+        run_cpu(cpu_batch)                                 # warm-up
         t0 = time.perf_counter()
         reps = 2
         for _ in range(reps):
-            O.forward(sd, hp, cpu_batch)
+            run_cpu(cpu_batch)
         dt = (time.perf_counter() - t0) / reps
-        cpu = {"value": frames / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+        cpu = {"value": frames / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": cpu_kind, "what": cpu_what,
                "sample": f"the full cfg2 batch (64 utterances, {frames} valid frames), {reps} timed calls after 1 warm-up, {dt:.2f} s/call"}
 
     if rank == 0:
         in_bytes = sum(t.numel() * t.element_size() for t in host_batch)
         out_bytes = host_mel.numel() * 4 + host_len.numel() * 8
+        value = total_frames / (ms_res * 1e-3)
+        cfg = workload_config(host_batch)
         line = {
-            "metric": METRIC, "value": total_frames / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.mode, "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "L_max": L_max, "T_max": T_max,
-                       "valid_frames_per_gpu_step": frames, "l2": "flushed between timed iterations (512 MiB memset)",
-                       "weights": "random-init, seed 1234"},
+            "config": cfg,
             "e2e": {"value": total_frames / (ms_pipe * 1e-3), "unit": UNIT, "ms_per_step": ms_pipe,
-                    "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
-                    "how": f"{args.steps} steps as one timed region, {NSLOT} slots, copy streams overlap H2D / D2H with compute",
-                    "serial_ms_per_step": ms_e2e, "serial_value": total_frames / (ms_e2e * 1e-3)},
+                    "h2d_bytes_per_step": int(blk_bytes), "d2h_bytes_per_step": int(frames * 80 * 4 + B * 8),
+                    "how": f"{args.steps} steps as one timed region, {NSLOT} slots, copy streams overlap H2D / D2H with compute; one pinned "
+                           "staging block in (frame side packed: valid frames only), packed mel + lengths out, "
+                           "DaftExprt.forward(packed_io=...); result checked bit for bit against the direct call",
+                    "padded": {"value": total_frames / (ms_pipe_padded * 1e-3), "ms_per_step": ms_pipe_padded,
+                               "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
+                               "how": "same pipeline with the reference's padded tensors (12 copies in, padded mel out)"},
+                    "serial_ms_per_step": ms_e2e, "serial_value": total_frames / (ms_e2e * 1e-3),
+                    "host_binding": binding},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
-            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver, "eager_gpu_baseline": eager, "vocoder": vocoder,
+            "eager_gpu_baseline": eager,
+            "vs_eager_gpu": (frames / (ms_res * 1e-3)) / eager["value"] if (eager and world == 1) else None,
+            "configs": configs,
+            "latency_ms_p50_single_utterance_inference": lat_p50, "synthesis_driver": driver, "vocoder": vocoder,
             "kernels_ms_per_step": {k: round(v[1], 4) for k, v in sorted(prof.items())},
             "whole_model_tflops": batch_flops(host_batch, forward_flops) * world / (ms_res * 1e-3) / 1e12,
         }

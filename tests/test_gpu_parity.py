@@ -17,11 +17,16 @@ BF16_REL_L1 = 2e-2
 # bf16 tolerances of the SECONDARY outputs (the north-star gate is the mel's relative L1 above): 2 x the worst value
 # measured on B200 over every case of this file and test_gpu_round2.py (gpurun_out/parity_measured.json, copied to
 # profiles/r02_parity_measured.json)
-W_BF16_MAX_ABS = 0.2
-W_BF16_MEAN_ABS = 2e-3
-FILM_BF16_MAX_ABS = 6e-2
-ENC_BF16_MAX_ABS = 0.15
-ACCENT_BF16_MAX_ABS = 3e-2
+# measured worst -> tolerance: film_dec 2.7e-3 -> 6e-3; speaker_preds 2.5e-3 -> 6e-3; enc_out 3.8e-2 -> 8e-2; accent_emb 1.0e-2
+# -> 2.1e-2; alignment weights: mean-abs 5.5e-4 -> 1.1e-3; the single worst element of the ~7 M valid ones at cfg2 size is 0.23
+# (a ratio of two Gaussians where the predicted range sigma is smallest) -> 0.35 on the maximum, and the 99.9th percentile
+# is gated separately (measured 2.2e-2 -> 4.5e-2)
+W_BF16_MAX_ABS = 0.35
+W_BF16_P999_ABS = 4.5e-2
+W_BF16_MEAN_ABS = 1.1e-3
+FILM_BF16_MAX_ABS = 6e-3
+ENC_BF16_MAX_ABS = 8e-2
+ACCENT_BF16_MAX_ABS = 2.1e-2
 
 
 @pytest.fixture(scope="module")
@@ -67,6 +72,10 @@ def _check_weights(w, ref_w, in_len, out_len, mode):
     assert (w - ref_w)[valid].abs().max().item() <= tol
     if mode == "bf16":
         assert (w - ref_w)[valid].abs().mean().item() <= W_BF16_MEAN_ABS
+        d = (w - ref_w)[valid].abs().flatten()
+        p999 = d.kthvalue(max(1, int(0.999 * d.numel()))).values.item()
+        C.record("weights_p999_abs_bf16", p999)
+        assert p999 <= W_BF16_P999_ABS
     # padded symbols carry exactly zero weight (model.py:503)
     assert torch.all(w[(~lv).expand_as(w)] == 0)
     # column sums agree with the reference's (1 where any Gaussian reaches the frame; the reference's columns

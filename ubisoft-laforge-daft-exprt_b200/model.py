@@ -477,19 +477,18 @@ class DaftExprt(nn.Module):
             self._stats_table = (hparams.stats, tab.to(self.device))
         tab = self._stats_table[1]
         ids = speaker_ids.to(self.device).long()
-        # an id without an entry in hparams.stats is a KeyError in the reference (model.py:984); here it is flagged on the
-        # device (out of range, or a NaN row of the table) and raised by the caller at its host sync.  The caller's
-        # tensor is never modified.
-        in_range = (ids >= 0) & (ids < tab.shape[0])
-        sel = tab.index_select(0, torch.where(in_range, ids, torch.zeros_like(ids)))
-        unknown = ~in_range | torch.isnan(sel[:, 0])
-        return sel[:, 0].contiguous(), sel[:, 1].contiguous(), unknown
+        # an id without an entry in hparams.stats is a KeyError in the reference (model.py:984).  The gather clamps a COPY of
+        # the ids (the caller's tensor is never modified); the caller checks the ids themselves on the host - for free when
+        # they are a CPU tensor, else folded into the host read it does anyway - with _raise_unknown_speakers.
+        sel = tab.index_select(0, ids.clamp(0, tab.shape[0] - 1))
+        return sel[:, 0].contiguous(), sel[:, 1].contiguous(), ids
 
     @staticmethod
-    def _raise_unknown_speakers(speaker_ids, unknown_host):
-        if bool(unknown_host.any()):
-            first = int(torch.nonzero(unknown_host).flatten()[0])
-            raise KeyError(f"spk {int(speaker_ids[first])}")
+    def _raise_unknown_speakers(hparams, ids_host):
+        known = hparams.stats
+        for i in ids_host.tolist():
+            if f"spk {int(i)}" not in known:
+                raise KeyError(f"spk {int(i)}")
 
     def _transform(self, energy, pitch, energy_factors, pitch_factors, durations_int, mean, std, transform):
         lib = _lib.load()
@@ -536,17 +535,23 @@ class DaftExprt(nn.Module):
         pitch_preds = self._dev(pitch_src, fl)
         if pitch_preds.data_ptr() != pitch_src.data_ptr():
             pitch_preds = pitch_preds.clone()
+        ids_dev = None
         if pitch_transform == "add":
-            mean, std, unknown = self._pitch_stats(hparams, speaker_ids)
+            if speaker_ids.device.type == "cpu":
+                self._raise_unknown_speakers(hparams, speaker_ids)          # host tensor: checked before any launch
+                mean, std, _ = self._pitch_stats(hparams, speaker_ids)
+            else:
+                mean, std, ids_dev = self._pitch_stats(hparams, speaker_ids)
         else:
             mean = std = torch.zeros(B, device=self.device)
-            unknown = torch.zeros(B, dtype=torch.bool, device=self.device)
         self._transform(energy_preds, pitch_preds, self._dev(energy_factors, fl), self._dev(pitch_factors, fl),
                         durations_int, mean, std, 0 if pitch_transform == "add" else 1)
         # the only host sync of the pass: frame count (the reference syncs on it too, model.py:497,1100)
         # and the per-utterance status of the integer conversion
-        host = torch.stack([durations_int.sum(dim=1), self._last_status.long(), unknown.long()]).cpu()
-        self._raise_unknown_speakers(speaker_ids, host[2] != 0)
+        rows = [durations_int.sum(dim=1), self._last_status.long()] + ([ids_dev] if ids_dev is not None else [])
+        host = torch.stack(rows).cpu()
+        if ids_dev is not None:
+            self._raise_unknown_speakers(hparams, host[2])
         if bool((host[1] != 0).any()):
             bad = [int(i) for i in torch.nonzero(host[1]).flatten()]
             raise RuntimeError(f"get_int_durations: the reference's duration_to_integer fails for utterances {bad} "
@@ -566,8 +571,8 @@ class DaftExprt(nn.Module):
 
     def pitch_shift(self, pitch_preds, pitch_factors, hparams, speaker_ids):
         """``DaftExprt.pitch_shift`` (reference model.py:975-994), in place on a device tensor."""
-        mean, std, unknown = self._pitch_stats(hparams, speaker_ids)
-        self._raise_unknown_speakers(speaker_ids, unknown.cpu())
+        self._raise_unknown_speakers(hparams, speaker_ids.cpu())
+        mean, std, _ = self._pitch_stats(hparams, speaker_ids)
         B, L = pitch_preds.shape
         ones = torch.ones(B, L, device=self.device)
         dint = torch.ones(B, L, dtype=torch.long, device=self.device)
