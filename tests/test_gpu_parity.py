@@ -18,11 +18,12 @@ BF16_REL_L1 = 2e-2
 # measured on B200 over every case of this file and test_gpu_round2.py (gpurun_out/parity_measured.json, copied to
 # profiles/r02_parity_measured.json)
 # measured worst -> tolerance: film_dec 2.7e-3 -> 6e-3; speaker_preds 2.5e-3 -> 6e-3; enc_out 3.8e-2 -> 8e-2; accent_emb 1.0e-2
-# -> 2.1e-2; alignment weights: mean-abs 5.5e-4 -> 1.1e-3; the single worst element of the ~7 M valid ones at cfg2 size is 0.23
-# (a ratio of two Gaussians where the predicted range sigma is smallest) -> 0.35 on the maximum, and the 99.9th percentile
-# is gated separately (measured 2.2e-2 -> 4.5e-2)
+# -> 2.1e-2; alignment weights: mean-abs 5.5e-4 -> 1.1e-3, 99.9th percentile 1.0e-2 -> 2e-2; the single worst element of the
+# ~7 M valid ones is 0.28 (cfg2-size inference; a ratio of two Gaussians where the predicted range sigma is smallest, so
+# the bf16 encoder output moves it most) -> 0.35 on the maximum (1.25 x: the maximum is one element, the percentile and the
+# mean carry the gate)
 W_BF16_MAX_ABS = 0.35
-W_BF16_P999_ABS = 4.5e-2
+W_BF16_P999_ABS = 2e-2
 W_BF16_MEAN_ABS = 1.1e-3
 FILM_BF16_MAX_ABS = 6e-3
 ENC_BF16_MAX_ABS = 8e-2
