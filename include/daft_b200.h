@@ -166,6 +166,40 @@ typedef struct {
 int64_t dx_forward_workspace_bytes(int B, int L_max, int T_max, int mode);
 int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream);
 
+/* ---- training step (BASELINE.json config 5) ------------------------------------------------------------------
+ * One rank's share of the reference's training iteration (train.py:421-445): `outputs = model(inputs)` (model.py:889-948,
+ * dropout = identity), `loss, individual = criterion(outputs, targets, iteration)` (loss.py:57-159, pitch-consistency term
+ * off), `loss.backward()`.  `grads` is a DxModelWeights whose fp32 pointers say where the gradient of each weight is
+ * written, in the same ENGINE layout as the weight (the *_bf fields are ignored).  Every gradient is overwritten (no
+ * accumulation); the kernels are deterministic.  The data-parallel exchange (DDP's gradient averaging, train.py:269-272) is
+ * one all-reduce of the caller's flat gradient buffer between dx_train_step and dx_adam_step.  fp32 arithmetic. */
+#define DX_TRAIN_FORWARD_ONLY 1    /* flags: stop after the loss (validation: train.py:155-209) */
+typedef struct {
+    int32_t B, L_max, T_max, flags;
+    /* DaftExprt.forward inputs (model.py:893-896), reference layouts */
+    const int64_t *symbols;  const float *durations_float;  const int64_t *durations_int;
+    const float   *symbols_energy, *symbols_pitch;  const int64_t *input_lengths;
+    const float   *frames_energy, *frames_pitch, *mel_specs;  const int64_t *output_lengths;
+    const int64_t *speaker_ids;  const float *spk_embs;
+    /* DaftExprtLoss (loss.py:22-55): speaker_weight = update_adversarial_weight(iteration) (:51-55), computed by the host;
+     * loss_scale = 1 / accumulation_steps (train.py:423) */
+    float mel_spec_weight, post_mult_weight, energy_consistency_weight, speaker_weight, lambda_reversal, loss_scale;
+    /* outputs */
+    float *losses;        /* [8]: loss * loss_scale, speaker_loss, speaker_ce_raw, post_mult_loss, mel_spec_l1_loss,
+                                  mel_spec_l2_loss, energy_consistency_loss, pitch_consistency_loss (= 0)  (loss.py:148-157) */
+    float *mel_out;       /* (B, 80, T_max) mel prediction or NULL */
+    void  *workspace;     /* dx_train_workspace_bytes(B, L_max, T_max) bytes, 256-byte aligned */
+    int64_t workspace_bytes;
+} DxTrainArgs;
+
+int64_t dx_train_workspace_bytes(int B, int L_max, int T_max);
+int dx_train_step(const DxModelWeights* w, const DxModelWeights* grads, const DxTrainArgs* a, void* stream);
+/* torch.optim.Adam(betas, eps, weight_decay, amsgrad=False) (train.py:278-280) on flat fp32 buffers of n elements:
+ * g = grad * grad_scale + weight_decay * p; m, v moments; step counts from 1.  grad_scale = 1 / world_size after a SUM
+ * all-reduce. */
+int dx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                 float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+
 /* ---- single stages (unit-test surface; same kernels dx_forward launches) -------------------------------- */
 /* AccentEncoder.forward, model.py:679-716 */
 int dx_accent_encoder(const DxModelWeights* w, int mode, int B, int T_max, const float* frames_energy,

@@ -55,6 +55,20 @@ class DxForwardArgs(C.Structure):
     )
 
 
+TRAIN_FORWARD_ONLY = 1
+
+
+class DxTrainArgs(C.Structure):
+    _fields_ = (
+        [("B", C.c_int32), ("L_max", C.c_int32), ("T_max", C.c_int32), ("flags", C.c_int32)]
+        + [(n, _p) for n in ("symbols", "durations_float", "durations_int", "symbols_energy", "symbols_pitch", "input_lengths",
+                             "frames_energy", "frames_pitch", "mel_specs", "output_lengths", "speaker_ids", "spk_embs")]
+        + [(n, C.c_float) for n in ("mel_spec_weight", "post_mult_weight", "energy_consistency_weight", "speaker_weight",
+                                    "lambda_reversal", "loss_scale")]
+        + [("losses", _p), ("mel_out", _p), ("workspace", _p), ("workspace_bytes", C.c_int64)]
+    )
+
+
 VC_GAP, VC_HALO, VC_RESIDUAL_F32 = 4, 32, 1
 
 
@@ -90,6 +104,9 @@ SIGNATURES = {
     "dx_pack_weight_bf16": (C.c_int, [_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p]),
     "dx_forward_workspace_bytes": (C.c_int64, [C.c_int] * 4),
     "dx_forward": (C.c_int, [C.POINTER(DxModelWeights), C.POINTER(DxForwardArgs), _p]),
+    "dx_train_workspace_bytes": (C.c_int64, [C.c_int] * 3),
+    "dx_train_step": (C.c_int, [C.POINTER(DxModelWeights), C.POINTER(DxModelWeights), C.POINTER(DxTrainArgs), _p]),
+    "dx_adam_step": (C.c_int, [_p, _p, _p, _p, C.c_int64] + [C.c_float] * 5 + [C.c_int, C.c_float, _p]),
     "dx_accent_encoder": (C.c_int, [C.POINTER(DxModelWeights), C.c_int, C.c_int, C.c_int, _p, _p, _p, _p, _p, _p,
                                     C.c_int64, _p]),
     "dx_style": (C.c_int, [C.POINTER(DxModelWeights), C.c_int, _p, _p, _p, _p, _p, _p]),

@@ -10,6 +10,7 @@
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_plan.cuh"
+#include "dx_train.cuh"
 
 namespace dx {
 
@@ -140,6 +141,20 @@ int64_t dx_forward_workspace_bytes(int B, int L_max, int T_max, int mode) {
 int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream) {
     DX_REQUIRE(w != nullptr && a != nullptr, "dx_forward: null argument");
     return run_forward(*w, *a, (cudaStream_t)stream);
+}
+
+int64_t dx_train_workspace_bytes(int B, int L_max, int T_max) { return train_workspace_bytes(B, L_max, T_max); }
+
+int dx_train_step(const DxModelWeights* w, const DxModelWeights* grads, const DxTrainArgs* a, void* stream) {
+    DX_REQUIRE(w != nullptr && grads != nullptr && a != nullptr, "dx_train_step: null argument");
+    return run_train_step(*w, *grads, *a, (cudaStream_t)stream);
+}
+
+int dx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                 float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
+    DX_REQUIRE(params && grads && exp_avg && exp_avg_sq && n >= 0, "dx_adam_step: null argument");
+    return adam_step(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale,
+                     (cudaStream_t)stream);
 }
 
 int dx_accent_encoder(const DxModelWeights* w, int mode, int B, int T_max, const float* frames_energy,

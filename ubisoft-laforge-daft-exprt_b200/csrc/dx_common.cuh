@@ -145,12 +145,12 @@ __device__ __forceinline__ float warp_max(float v) {
 // out[r][n] = act(bias[n] + sum_j sum_k A[r + j - taps/2][k] * W[j][k][n]); rows outside [0, total) read as 0;
 // rows that are not live(ext) are written as 0.  ext < 0: no liveness masking (plain linear layers).
 int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, int taps, bool relu,
-             const Rows& R, int live_ext, float* out, cudaStream_t s);
+             const Rows& R, int live_ext, float* out, cudaStream_t s, const float* addend = nullptr);
 // out = live(ext) ? film(LN(in + res) * g + b) : 0   (one warp per row; C = 128 or 1024)
 int ln_rows_f32(const float* in, const float* res, const float* g, const float* b, int C, const float* film,
                 int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s);
 // masked multi-head self attention on packed rows; qkv [rows][384] → out [rows][128]
-int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s);
+int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s, float* lse = nullptr);
 
 // ---- row-stream plumbing (dx_rows.cu) --------------------------------------------------------------------
 int build_rows(const int64_t* lengths, int B, int n_max, int32_t* row_start, int32_t* row_b, int32_t* row_p,

@@ -15,7 +15,7 @@ constexpr int GF_BM = 128, GF_BN = 64, GF_BK = 16;
 
 __global__ void __launch_bounds__(256)
 gemm_f32_kernel(const float* __restrict__ A, int K, const float* __restrict__ W, const float* __restrict__ bias,
-                int N, int taps, int relu, Rows R, int live_ext, float* __restrict__ out) {
+                int N, int taps, int relu, Rows R, int live_ext, float* __restrict__ out, const float* __restrict__ addend) {
     __shared__ __align__(16) float As[2][GF_BK][GF_BM + 4];
     __shared__ __align__(16) float Bs[2][GF_BK][GF_BN];
     const int64_t total = R.row_start[R.B];
@@ -108,6 +108,7 @@ gemm_f32_kernel(const float* __restrict__ A, int K, const float* __restrict__ W,
         for (int j = 0; j < 4; ++j) {
             float t = acc[i][j] + bz[j];
             if (relu) t = fmaxf(t, 0.f);
+            if (addend != nullptr && n + j < N) t += addend[r * N + n + j];      // training: residual-gradient accumulation
             v[j] = live ? t : 0.f;
         }
         if (n + 3 < N) *reinterpret_cast<float4*>(out + r * N + n) = make_float4(v[0], v[1], v[2], v[3]);
@@ -118,11 +119,11 @@ gemm_f32_kernel(const float* __restrict__ A, int K, const float* __restrict__ W,
 }
 
 int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, int taps, bool relu,
-             const Rows& R, int live_ext, float* out, cudaStream_t s) {
+             const Rows& R, int live_ext, float* out, cudaStream_t s, const float* addend) {
     DX_REQUIRE(K % GF_BK == 0 && N % 4 == 0, "gemm_f32: K=%d must be a multiple of 16 and N=%d of 4", K, N);
     dim3 grid((unsigned)(R.cap / GF_BM), (unsigned)((N + GF_BN - 1) / GF_BN));
     ProfScope prof("gemm_f32", s);
-    gemm_f32_kernel<<<grid, 256, 0, s>>>(A, K, W, bias, N, taps, relu ? 1 : 0, R, live_ext, out);
+    gemm_f32_kernel<<<grid, 256, 0, s>>>(A, K, W, bias, N, taps, relu ? 1 : 0, R, live_ext, out, addend);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -215,7 +216,7 @@ int ln_rows_f32(const float* in, const float* res, const float* g, const float* 
 constexpr int AT_Q = 64, AT_K = 64;
 
 __global__ void __launch_bounds__(256)
-attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ out) {
+attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ out, float* __restrict__ lse) {
     extern __shared__ __align__(16) float smem[];
     float(*Qt)[AT_Q] = reinterpret_cast<float(*)[AT_Q]>(smem);                          // [64 d][64 q]
     float(*Kt)[AT_K + 1] = reinterpret_cast<float(*)[AT_K + 1]>(smem + 64 * AT_Q);      // [64 d][65]
@@ -325,18 +326,20 @@ attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ 
             const float inv = 1.f / l[i];
             *reinterpret_cast<float4*>(out + (rs + q) * DX_D + h * DX_DH + tx * 4) =
                 make_float4(o[i][0] * inv, o[i][1] * inv, o[i][2] * inv, o[i][3] * inv);
+            // training: log-sum-exp of the (scaled) scores of this query row, for the backward's recomputation of P
+            if (lse != nullptr && tx == 0) lse[(rs + q) * DX_HEADS + h] = m[i] + logf(l[i]);
         }
     }
 }
 
 static const int AT_SMEM = (64 * AT_Q + 64 * (AT_K + 1) + AT_K * DX_DH + AT_K * (AT_Q + 4)) * (int)sizeof(float);
 
-int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s) {
+int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s, float* lse) {
     static SmemConfigured configured;
     DX_TRY(ensure_dyn_smem(attention_f32_kernel, (size_t)AT_SMEM, configured));
     dim3 grid((unsigned)((R.n_max + AT_Q - 1) / AT_Q), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_f32", s);
-    attention_f32_kernel<<<grid, 256, AT_SMEM, s>>>(qkv, R, out);
+    attention_f32_kernel<<<grid, 256, AT_SMEM, s>>>(qkv, R, out, lse);
     DX_CHECK_LAUNCH();
     return 0;
 }

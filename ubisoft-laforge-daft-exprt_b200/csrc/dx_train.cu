@@ -1,0 +1,342 @@
+// Whole training step of BASELINE config 5 on one GPU: forward with saved activations, the reference's loss and
+// the hand-written backward of every module, enqueued on the caller's stream without host synchronisation.
+//
+// Replaces, for one rank, `outputs = model(inputs); loss, _ = criterion(outputs, targets, iteration); loss.backward()`
+// (train.py:421-434: DaftExprt.forward model.py:889-948 under autograd + DaftExprtLoss.forward loss.py:57-159).  Dropout is
+// the identity here (the parity configuration of SURVEY.md section 8d cfg5; the reference's dropout sites are model.py:167-168,
+// 216, 656, 663, 670).  The gradient of every one of the 184 parameters is written in the ENGINE layout of its weight
+// (DxModelWeights: conv weights [tap][Cin][Cout], in/out projections transposed, everything else torch layout); the
+// data-parallel exchange is one all-reduce of that flat buffer, done by the caller between this call and
+// dx_adam_step.  Arithmetic: fp32 SIMT kernels (the 1e-3 parity mode); the forward half is the same kernels DX_MODE_F32
+// inference runs, so the loss is the inference forward's to the last bit.
+#include <string.h>
+#include "dx_train.cuh"
+#include "dx_plan.cuh"
+
+namespace dx {
+
+namespace {
+
+struct Carver {
+    uint8_t* base;
+    int64_t off;
+    template <typename T>
+    T* take(int64_t n) {
+        off = round_up(off, 256);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += n * (int64_t)sizeof(T);
+        return p;
+    }
+};
+
+struct BlockSave {
+    float *xin, *qkv, *lse, *o, *t1, *x1, *h, *t2;
+};
+struct StackSave {
+    BlockSave blk[4];
+    float* out;
+    int64_t cap;
+};
+
+struct TrainPlan {
+    int B, L_max, T_max;
+    int64_t cap_t, cap_l, cap, bytes;
+    int32_t *t_row_start, *t_row_b, *t_row_p, *l_row_start, *l_row_b, *l_row_p;
+    StackSave acc, enc, dec;
+    float *melp, *a0, *z0, *a1, *z1, *a2, *z2;
+    float *accent, *film, *logits, *xs, *sigma, *mu, *weights, *melo;
+    int64_t* out_len;
+    // backward
+    float *dA, *dB, *dC, *dQKV, *dH1, *dH2, *dmel, *Dr, *wt, *scratch;
+    float *dfilm, *dlogits, *sv, *gat1, *gat2, *lpart, *dpost_reg, *ct, *gd, *gr, *dpre;
+    int64_t scratch_floats;
+};
+
+void carve_stack(Carver& c, StackSave& st, int64_t cap) {
+    st.cap = cap;
+    for (int i = 0; i < 4; ++i) {
+        BlockSave& b = st.blk[i];
+        b.xin = c.take<float>(cap * DX_D);
+        b.qkv = c.take<float>(cap * 3 * DX_D);
+        b.lse = c.take<float>(cap * DX_HEADS);
+        b.o = c.take<float>(cap * DX_D);
+        b.t1 = c.take<float>(cap * DX_D);
+        b.x1 = c.take<float>(cap * DX_D);
+        b.h = c.take<float>(cap * DX_C);
+        b.t2 = c.take<float>(cap * DX_D);
+    }
+    st.out = c.take<float>(cap * DX_D);
+}
+
+int64_t max64(int64_t a, int64_t b) { return a > b ? a : b; }
+
+int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void* ws, int64_t ws_bytes) {
+    DX_REQUIRE(B >= 1 && L_max >= 1 && T_max >= 1, "train plan: bad shape B=%d L_max=%d T_max=%d", B, L_max, T_max);
+    DX_REQUIRE(T_max <= 5000 && L_max <= 5000, "train plan: sequence longer than the 5000-row positional table (model.py:123)");
+    memset(p, 0, sizeof(*p));
+    p->B = B; p->L_max = L_max; p->T_max = T_max;
+    p->cap_t = row_cap(B, T_max);
+    p->cap_l = row_cap(B, L_max);
+    p->cap = max64(p->cap_t, p->cap_l);
+    Carver c{reinterpret_cast<uint8_t*>(ws), 0};
+    p->t_row_start = c.take<int32_t>(B + 1);
+    p->t_row_b = c.take<int32_t>(p->cap_t);
+    p->t_row_p = c.take<int32_t>(p->cap_t);
+    p->l_row_start = c.take<int32_t>(B + 1);
+    p->l_row_b = c.take<int32_t>(p->cap_l);
+    p->l_row_p = c.take<int32_t>(p->cap_l);
+    carve_stack(c, p->acc, p->cap_t);
+    carve_stack(c, p->enc, p->cap_l);
+    carve_stack(c, p->dec, p->cap_t);
+    p->melp = c.take<float>(p->cap_t * DX_MEL);
+    p->a0 = c.take<float>(p->cap_t * DX_C);
+    p->z0 = c.take<float>(p->cap_t * DX_C);
+    p->a1 = c.take<float>(p->cap_t * DX_C);
+    p->z1 = c.take<float>(p->cap_t * DX_C);
+    p->a2 = c.take<float>(p->cap_t * DX_D);
+    p->z2 = c.take<float>(p->cap_t * DX_D);
+    p->accent = c.take<float>((int64_t)B * DX_D);
+    p->film = c.take<float>((int64_t)B * 8 * 256);
+    p->logits = c.take<float>((int64_t)B * (n_speakers > 0 ? n_speakers : 1));
+    p->xs = c.take<float>(p->cap_l * DX_D);
+    p->sigma = c.take<float>((int64_t)B * L_max);
+    p->mu = c.take<float>((int64_t)B * L_max);
+    p->weights = c.take<float>((int64_t)B * L_max * T_max);
+    p->melo = c.take<float>(p->cap_t * DX_MEL);
+    p->out_len = c.take<int64_t>(B);
+    p->dA = c.take<float>(p->cap * DX_D);
+    p->dB = c.take<float>(p->cap * DX_D);
+    p->dC = c.take<float>(p->cap * DX_D);
+    p->dQKV = c.take<float>(p->cap * 3 * DX_D);
+    p->dH1 = c.take<float>(p->cap * DX_C);
+    p->dH2 = c.take<float>(p->cap * DX_C);
+    p->dmel = c.take<float>(p->cap_t * DX_MEL);
+    p->Dr = c.take<float>(p->cap * DX_HEADS);
+    p->wt = c.take<float>((int64_t)DX_TAPS * DX_C * DX_C);
+    int64_t sf = wgrad_scratch_floats(p->cap_t, DX_C, DX_C, DX_TAPS);
+    sf = max64(sf, ln_bwd_scratch_floats(p->cap, DX_C));
+    sf = max64(sf, colsum_scratch_floats(p->cap, DX_C));
+    sf = max64(sf, scalar_conv_scratch_floats(p->cap));
+    p->scratch_floats = sf;
+    p->scratch = c.take<float>(sf);
+    p->dfilm = c.take<float>((int64_t)B * 8 * 256);
+    p->dlogits = c.take<float>((int64_t)B * (n_speakers > 0 ? n_speakers : 1));
+    p->sv = c.take<float>((int64_t)B * SB_STRIDE);
+    p->gat1 = c.take<float>((int64_t)B * 1024);
+    p->gat2 = c.take<float>((int64_t)B * 1024);
+    p->lpart = c.take<float>((int64_t)B * 4);
+    p->dpost_reg = c.take<float>(16);
+    p->ct = c.take<float>(p->cap_t);
+    p->gd = c.take<float>(p->cap_l * DX_D);
+    p->gr = c.take<float>(p->cap_l * DX_D);
+    p->dpre = c.take<float>(p->cap_l);
+    p->bytes = round_up(c.off, 256);
+    if (ws != nullptr) {
+        DX_REQUIRE(ws_bytes >= p->bytes, "train plan: workspace of %lld bytes < required %lld", (long long)ws_bytes, (long long)p->bytes);
+        DX_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "train plan: workspace must be 256-byte aligned");
+    }
+    return 0;
+}
+
+inline float* G(const float* p) { return const_cast<float*>(p); }
+
+// ---- forward of one stack with saved activations (FFTBlock.forward x 4, model.py:249-259) -----------------------------
+int stack_forward(const DxBlockWeights* blocks, StackSave& st, const Rows& R, const float* film, int film_block0, cudaStream_t s) {
+    for (int i = 0; i < 4; ++i) {
+        const DxBlockWeights& bw = blocks[i];
+        BlockSave& b = st.blk[i];
+        float* y = i < 3 ? st.blk[i + 1].xin : st.out;
+        const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
+        DX_TRY(gemm_f32(b.xin, DX_D, bw.w_qkv, bw.b_qkv, 3 * DX_D, 1, false, R, -1, b.qkv, s));
+        DX_TRY(attention_f32(b.qkv, R, b.o, s, b.lse));
+        DX_TRY(gemm_f32(b.o, DX_D, bw.w_out, bw.b_out, DX_D, 1, false, R, -1, b.t1, s));
+        DX_TRY(ln_rows_f32(b.t1, b.xin, bw.ln1_g, bw.ln1_b, DX_D, nullptr, 0, R, 0, b.x1, s));
+        DX_TRY(gemm_f32(b.x1, DX_D, bw.w_c1, bw.b_c1, DX_C, DX_TAPS, true, R, 1, b.h, s));
+        DX_TRY(gemm_f32(b.h, DX_C, bw.w_c2, bw.b_c2, DX_D, DX_TAPS, false, R, -1, b.t2, s));
+        DX_TRY(ln_rows_f32(b.t2, b.x1, bw.ln2_g, bw.ln2_b, DX_D, fp, 8 * 256, R, 0, y, s));
+    }
+    return 0;
+}
+
+// dgrad of a conv / linear layer: dX = sum_taps dY[r + j - half] Wt[j]   with Wt the tap-flipped transpose of W
+int dgrad(const TrainPlan& p, const float* dY, int N_out, const float* W, int K_in, int taps, const Rows& R, float* dX,
+          const float* addend, cudaStream_t s) {
+    DX_TRY(transpose_weight(W, taps, K_in, N_out, p.wt, s));
+    return gemm_f32(dY, N_out, p.wt, nullptr, K_in, taps, false, R, -1, dX, s, addend);
+}
+
+// ---- backward of one stack.  In: gradient of the stack output = dy1 (+ dy2).  Out: gradient of the stack input = *g1 + *g2
+// (two buffers of the plan; the caller masks and adds them).  Parameter gradients go to gb[i].
+int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlockWeights* gb, const StackSave& st, const Rows& R,
+                   const float* film, float* dfilm, int film_block0, const float* dy1, const float* dy2, const float** g1,
+                   const float** g2, cudaStream_t s) {
+    float *A = p.dA, *Bf = p.dB, *C = p.dC;
+    // the incoming pair may live in two of A / B / C: the first LayerNorm backward must write into the third
+    auto is = [](const float* x, const float* y) { return x == y; };
+    float* bufs[3] = {p.dA, p.dB, p.dC};
+    int freei = 0;
+    for (int k = 0; k < 3; ++k)
+        if (!is(bufs[k], dy1) && !is(bufs[k], dy2)) { freei = k; break; }
+    A = bufs[freei];
+    // the two other plan buffers, in an order that keeps dy1 / dy2 alive until the first two kernels have read them
+    Bf = bufs[(freei + 1) % 3];
+    C = bufs[(freei + 2) % 3];
+    for (int i = 3; i >= 0; --i) {
+        const DxBlockWeights& bw = blocks[i];
+        const DxBlockWeights& g = gb[i];
+        const BlockSave& b = st.blk[i];
+        const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
+        // LN2 + FiLM + mask
+        DX_TRY(ln_bwd_rows(b.t2, b.x1, bw.ln2_g, DX_D, fp, 8 * 256, dy1, dy2, R, 0, A, G(g.ln2_g), G(g.ln2_b), p.scratch, s));
+        if (film) DX_TRY(film_bwd(b.t2, b.x1, bw.ln2_g, bw.ln2_b, dy1, dy2, R, dfilm + (film_block0 + i) * 256, 8 * 256, s));
+        // conv2 (A = dT2)
+        DX_TRY(colsum_rows(A, DX_D, R, G(g.b_c2), p.scratch, s));
+        DX_TRY(wgrad_f32(b.h, DX_C, A, DX_D, DX_TAPS, R, G(g.w_c2), p.scratch, s));
+        DX_TRY(dgrad(p, A, DX_D, bw.w_c2, DX_C, DX_TAPS, R, p.dH1, nullptr, s));
+        DX_TRY(relu_bwd(p.dH1, b.h, R.cap * DX_C, s));
+        // conv1
+        DX_TRY(colsum_rows(p.dH1, DX_C, R, G(g.b_c1), p.scratch, s));
+        DX_TRY(wgrad_f32(b.x1, DX_D, p.dH1, DX_C, DX_TAPS, R, G(g.w_c1), p.scratch, s));
+        DX_TRY(dgrad(p, p.dH1, DX_C, bw.w_c1, DX_D, DX_TAPS, R, Bf, nullptr, s));          // Bf = d x1 through the FFN
+        // LN1 + mask: d x1 = Bf + A (residual of the FFN)
+        DX_TRY(ln_bwd_rows(b.t1, b.xin, bw.ln1_g, DX_D, nullptr, 0, Bf, A, R, 0, C, G(g.ln1_g), G(g.ln1_b), p.scratch, s));
+        // out-proj (C = dT1)
+        DX_TRY(colsum_rows(C, DX_D, R, G(g.b_out), p.scratch, s));
+        DX_TRY(wgrad_f32(b.o, DX_D, C, DX_D, 1, R, G(g.w_out), p.scratch, s));
+        DX_TRY(dgrad(p, C, DX_D, bw.w_out, DX_D, 1, R, A, nullptr, s));                     // A = dO
+        DX_TRY(attention_bwd_f32(b.qkv, b.o, b.lse, A, R, p.Dr, p.dQKV, s));
+        DX_TRY(colsum_rows(p.dQKV, 3 * DX_D, R, G(g.b_qkv), p.scratch, s));
+        DX_TRY(wgrad_f32(b.xin, DX_D, p.dQKV, 3 * DX_D, 1, R, G(g.w_qkv), p.scratch, s));
+        DX_TRY(dgrad(p, p.dQKV, 3 * DX_D, bw.w_qkv, DX_D, 1, R, Bf, nullptr, s));           // Bf = d x through QKV
+        // gradient of the block input = Bf + C (residual of the attention); becomes (dy1, dy2) of block i - 1
+        dy1 = Bf; dy2 = C;          // the next block's first LayerNorm backward writes into A, which holds neither
+    }
+    *g1 = dy1; *g2 = dy2;
+    return 0;
+}
+
+}  // namespace
+
+int64_t train_workspace_bytes(int B, int L_max, int T_max) {
+    TrainPlan p;
+    if (train_layout(&p, B, L_max, T_max, 64, nullptr, 0) != 0) return -1;
+    return p.bytes;
+}
+
+int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTrainArgs& a, cudaStream_t s) {
+    TrainPlan p;
+    DX_REQUIRE(w.n_speakers >= 1 && w.n_speakers <= 64, "train: n_speakers=%d out of range (1..64)", w.n_speakers);
+    DX_TRY(train_layout(&p, a.B, a.L_max, a.T_max, w.n_speakers, a.workspace, a.workspace_bytes));
+    DX_REQUIRE(a.workspace != nullptr, "dx_train_step: workspace required");
+    DX_REQUIRE(a.symbols && a.durations_float && a.durations_int && a.symbols_energy && a.symbols_pitch && a.input_lengths &&
+                   a.frames_energy && a.frames_pitch && a.mel_specs && a.output_lengths && a.speaker_ids && a.spk_embs && a.losses,
+               "dx_train_step: every input of DaftExprt.forward, speaker_ids and the losses buffer are required");
+    const int B = a.B;
+    Rows RT{p.t_row_start, p.t_row_b, p.t_row_p, a.output_lengths, B, a.T_max, p.cap_t};
+    Rows RL{p.l_row_start, p.l_row_b, p.l_row_p, a.input_lengths, B, a.L_max, p.cap_l};
+    DX_TRY(build_rows(a.output_lengths, B, a.T_max, p.t_row_start, p.t_row_b, p.t_row_p, p.cap_t, s));
+    DX_TRY(build_rows(a.input_lengths, B, a.L_max, p.l_row_start, p.l_row_b, p.l_row_p, p.cap_l, s));
+
+    // ======================================= forward (model.py:889-948) =======================================
+    DX_TRY(lenreg_scan(a.durations_int, B, a.L_max, false, nullptr, p.mu, p.out_len, nullptr, s));
+    // accent encoder (model.py:679-716)
+    DX_TRY(pack_mel(a.mel_specs, RT, p.melp, nullptr, 0, s));
+    DX_TRY(gemm_f32(p.melp, DX_MEL, w.ae_c0_w, w.ae_c0_b, DX_C, DX_TAPS, true, RT, -1, p.a0, s));
+    DX_TRY(ln_rows_f32(p.a0, nullptr, w.ae_ln0_g, w.ae_ln0_b, DX_C, nullptr, 0, RT, 2, p.z0, s));
+    DX_TRY(gemm_f32(p.z0, DX_C, w.ae_c1_w, w.ae_c1_b, DX_C, DX_TAPS, true, RT, -1, p.a1, s));
+    DX_TRY(ln_rows_f32(p.a1, nullptr, w.ae_ln1_g, w.ae_ln1_b, DX_C, nullptr, 0, RT, 1, p.z1, s));
+    DX_TRY(gemm_f32(p.z1, DX_C, w.ae_c2_w, w.ae_c2_b, DX_D, DX_TAPS, true, RT, -1, p.a2, s));
+    DX_TRY(ln_rows_f32(p.a2, nullptr, w.ae_ln2_g, w.ae_ln2_b, DX_D, nullptr, 0, RT, 0, p.z2, s));
+    DX_TRY(accent_input(p.z2, nullptr, a.frames_energy, a.frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w, w.ae_pitch_b,
+                        w.pos_table, RT, p.acc.blk[0].xin, nullptr, 0, s));
+    DX_TRY(stack_forward(w.ae_blocks, p.acc, RT, nullptr, 0, s));
+    DX_TRY(masked_mean(p.acc.out, nullptr, 0, RT, p.accent, s));
+    // conditioning (model.py:904-920)
+    DX_TRY(style(&w, B, a.spk_embs, nullptr, p.accent, p.film, p.logits, s));
+    // phoneme encoder (model.py:590-610)
+    DX_TRY(embed_symbols(a.symbols, w.symbols_embedding, w.n_symbols, w.pos_table, RL, p.enc.blk[0].xin, nullptr, 0, s));
+    DX_TRY(stack_forward(w.pe_blocks, p.enc, RL, p.film, 0, s));
+    // length regulator (model.py:417-510)
+    DX_TRY(lenreg_symbols(p.enc.out, nullptr, 0, RL, a.durations_float, a.symbols_energy, a.symbols_pitch, &w, p.xs, p.sigma, s));
+    DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, p.weights, p.dec.blk[0].xin, nullptr, 0, s));
+    // frame decoder (model.py:548-564)
+    DX_TRY(stack_forward(w.fd_blocks, p.dec, RT, p.film, 4, s));
+    DX_TRY(gemm_f32(p.dec.out, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
+    if (a.mel_out) DX_TRY(unpack_mel(p.melo, RT, a.mel_out, s));
+
+    // ======================================= loss (loss.py:57-159) ============================================
+    DxLossParams lp{a.mel_spec_weight, a.post_mult_weight, a.energy_consistency_weight, a.speaker_weight, a.loss_scale};
+    DX_TRY(loss_forward_backward(p.melo, a.mel_specs, RT, p.logits, a.speaker_ids, w.n_speakers, w.post_mult, lp, p.lpart, p.dmel,
+                                 p.dlogits, a.losses, p.dpost_reg, s));
+    if (a.flags & DX_TRAIN_FORWARD_ONLY) return 0;
+
+    // ======================================= backward =========================================================
+    const float *g1 = nullptr, *g2 = nullptr;
+    // mel projection (model.py:561)
+    DX_TRY(colsum_rows(p.dmel, DX_MEL, RT, G(g.mel_b), p.scratch, s));
+    DX_TRY(wgrad_f32(p.dec.out, DX_D, p.dmel, DX_MEL, 1, RT, G(g.mel_w), p.scratch, s));
+    DX_TRY(dgrad(p, p.dmel, DX_MEL, w.mel_w, DX_D, 1, RT, p.dB, nullptr, s));
+    DX_CHECK_CUDA(cudaMemsetAsync(p.dfilm, 0, (size_t)B * 8 * 256 * sizeof(float), s));
+    // frame decoder
+    DX_TRY(stack_backward(p, w.fd_blocks, g.fd_blocks, p.dec, RT, p.film, p.dfilm, 4, p.dB, nullptr, &g1, &g2, s));
+    // decoder input = (x_up + P) * valid: mask, then the length regulator
+    float* gdec = (g1 != p.dA && g2 != p.dA) ? p.dA : ((g1 != p.dB && g2 != p.dB) ? p.dB : p.dC);
+    DX_TRY(add_mask_rows(g1, g2, RT, gdec, s));
+    float* gx = (gdec == p.dA) ? p.dB : p.dA;          // d x' on the symbol stream (cap_l <= cap rows)
+    DX_TRY(lenreg_bwd(gdec, p.dec.blk[0].xin, w.pos_table, p.weights, p.xs, p.mu, p.sigma, a.durations_float, &w, RL, RT, p.ct, gx,
+                      p.gd, p.gr, p.dpre, s));
+    DX_TRY(colsum_rows(p.gr, DX_D, RL, G(g.gu_range_w), p.scratch, s));
+    DX_TRY(sum_rows_scalar(p.dpre, RL, G(g.gu_range_b), s));
+    DX_TRY(scalar_conv_wgrad(gx, a.symbols_energy, RL, G(g.gu_energy_w), G(g.gu_energy_b), p.scratch, s));
+    DX_TRY(scalar_conv_wgrad(gx, a.symbols_pitch, RL, G(g.gu_pitch_w), G(g.gu_pitch_b), p.scratch, s));
+    DX_TRY(scalar_conv_wgrad(p.gd, a.durations_float, RL, G(g.gu_dur_w), G(g.gu_dur_b), p.scratch, s));
+    // phoneme encoder
+    DX_TRY(stack_backward(p, w.pe_blocks, g.pe_blocks, p.enc, RL, p.film, p.dfilm, 0, gx, nullptr, &g1, &g2, s));
+    float* genc = (g1 != p.dA && g2 != p.dA) ? p.dA : ((g1 != p.dB && g2 != p.dB) ? p.dB : p.dC);
+    DX_TRY(add_mask_rows(g1, g2, RL, genc, s));
+    DX_TRY(embed_bwd(genc, a.symbols, w.n_symbols, RL, G(g.symbols_embedding), s));
+    // conditioning heads (model.py:904-920, 764-806, 829-830)
+    DX_TRY(style_bwd(a.spk_embs, p.accent, &w, p.dfilm, p.dlogits, a.lambda_reversal, B, p.sv, s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DG, 1024, B, p.gat1, s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_C, DX_D, B, p.gat2, s));
+    DX_TRY(outer_wgrad(p.gat1, 1024, p.gat2, DX_D, B, G(g.film_g_w), G(g.film_g_b), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DQ, 1024, B, p.gat1, s));
+    DX_TRY(outer_wgrad(p.gat1, 1024, p.gat2, DX_D, B, G(g.film_b_w), G(g.film_b_b), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DC, DX_D, B, p.gat1, s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_E, DX_SPK, B, p.gat2, s));
+    DX_TRY(outer_wgrad(p.gat1, DX_D, p.gat2, DX_SPK, B, G(g.spk_w), G(g.spk_b), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DH1, DX_D, B, p.gat1, s));
+    DX_TRY(outer_wgrad(p.gat1, DX_D, p.accent, DX_D, B, G(g.cls_w1), G(g.cls_b1), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DH2, DX_D, B, p.gat1, s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_H1, DX_D, B, p.gat2, s));
+    DX_TRY(outer_wgrad(p.gat1, DX_D, p.gat2, DX_D, B, G(g.cls_w2), G(g.cls_b2), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_H2, DX_D, B, p.gat2, s));
+    DX_TRY(outer_wgrad(p.dlogits, w.n_speakers, p.gat2, DX_D, B, G(g.cls_w3), G(g.cls_b3), s));
+    if (g.post_mult) DX_TRY(post_mult_grad(p.sv, B, p.dpost_reg, G(g.post_mult), s));
+    // accent encoder: mean pool, stack, pre-net
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DACC, DX_D, B, p.gat1, s));
+    DX_TRY(masked_mean_bwd(p.gat1, RT, p.dB, s));
+    DX_TRY(stack_backward(p, w.ae_blocks, g.ae_blocks, p.acc, RT, nullptr, nullptr, 0, p.dB, nullptr, &g1, &g2, s));
+    float* gacc = (g1 != p.dA && g2 != p.dA) ? p.dA : ((g1 != p.dB && g2 != p.dB) ? p.dB : p.dC);
+    DX_TRY(add_mask_rows(g1, g2, RT, gacc, s));
+    DX_TRY(scalar_conv_wgrad(gacc, a.frames_energy, RT, G(g.ae_energy_w), G(g.ae_energy_b), p.scratch, s));
+    DX_TRY(scalar_conv_wgrad(gacc, a.frames_pitch, RT, G(g.ae_pitch_w), G(g.ae_pitch_b), p.scratch, s));
+    float* d2 = (gacc == p.dA) ? p.dB : p.dA;
+    DX_TRY(ln_bwd_rows(p.a2, nullptr, w.ae_ln2_g, DX_D, nullptr, 0, gacc, nullptr, RT, 0, d2, G(g.ae_ln2_g), G(g.ae_ln2_b), p.scratch, s));
+    DX_TRY(relu_bwd(d2, p.a2, p.cap_t * DX_D, s));
+    DX_TRY(colsum_rows(d2, DX_D, RT, G(g.ae_c2_b), p.scratch, s));
+    DX_TRY(wgrad_f32(p.z1, DX_C, d2, DX_D, DX_TAPS, RT, G(g.ae_c2_w), p.scratch, s));
+    DX_TRY(dgrad(p, d2, DX_D, w.ae_c2_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
+    DX_TRY(ln_bwd_rows(p.a1, nullptr, w.ae_ln1_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 1, p.dH2, G(g.ae_ln1_g), G(g.ae_ln1_b), p.scratch, s));
+    DX_TRY(relu_bwd(p.dH2, p.a1, p.cap_t * DX_C, s));
+    DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c1_b), p.scratch, s));
+    DX_TRY(wgrad_f32(p.z0, DX_C, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c1_w), p.scratch, s));
+    DX_TRY(dgrad(p, p.dH2, DX_C, w.ae_c1_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
+    DX_TRY(ln_bwd_rows(p.a0, nullptr, w.ae_ln0_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 2, p.dH2, G(g.ae_ln0_g), G(g.ae_ln0_b), p.scratch, s));
+    DX_TRY(relu_bwd(p.dH2, p.a0, p.cap_t * DX_C, s));
+    DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c0_b), p.scratch, s));
+    DX_TRY(wgrad_f32(p.melp, DX_MEL, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c0_w), p.scratch, s));
+    return 0;
+}
+
+}  // namespace dx

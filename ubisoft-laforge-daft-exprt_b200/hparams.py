@@ -49,6 +49,20 @@ def default_hparams(**overrides):
             "conv_kernel": 3, "conv_channels": 1024, "conv_dropout": 0.1,
         },
     )
+    # training-side fields (BASELINE config 5): loss weights (hparams.py:72-88), optimiser (hparams.py:93-100)
+    hp.mel_spec_weight = 1.0
+    hp.energy_consistency_weight = 0.05
+    hp.pitch_consistency_weight = 0.0
+    hp.pitch_predictor_path = ""
+    hp.adv_max_weight = 1e-2
+    hp.warmup_steps = 10000
+    hp.accumulation_steps = 1
+    hp.betas = [0.9, 0.98]
+    hp.epsilon = 1e-9
+    hp.weight_decay = 1e-6
+    hp.grad_clip_thresh = float("inf")
+    hp.initial_learning_rate = 1e-4
+    hp.max_learning_rate = 1e-3
     for k, v in overrides.items():
         setattr(hp, k, v)
     return hp
