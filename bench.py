@@ -400,6 +400,103 @@ def run_configs(args, model, hp, sd, dev, rank, world, timed, profile_step, sync
     return out if rank == 0 else None
 
 
+def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
+    """BASELINE config 5: the training step (forward + loss + backward, gradient all-reduce over NCCL, Adam) at B = 32
+    utterances per GPU drawn as cfg2; weak scaling (each rank its own batch), K steps timed as one region with CUDA
+    events on the launching stream, max over ranks.  fp32 arithmetic (train.TrainEngine)."""
+    import torch
+    from daft_exprt_b200 import synthetic
+    from daft_exprt_b200.train import TrainEngine, flops_per_step, loss_dict
+    batch = synthetic.forward_batch(hp, batch=32, lmin=20, lmax=150, seed=42 + 1000 * rank)
+    d = tuple(t.to(dev) for t in batch)
+    frames = int(batch[9].sum())
+    eng = TrainEngine(hp, sd, device=dev)
+    steps, warm = max(5, min(args.steps, 10)), 3
+    for it in range(1, warm + 1):
+        eng.step(d, iteration=it)
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for it in range(warm + 1, warm + 1 + steps):
+        eng.step(d, iteration=it)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    # the pieces, on rank 0's clock: forward + backward, all-reduce, Adam
+    def span(fn, n=3):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+    ms_fb = span(lambda: eng.forward_backward(d, iteration=100))
+    ms_ar = span(eng.all_reduce_grads) if world > 1 else 0.0
+    ms_fwd = span(lambda: eng.forward_backward(d, iteration=100, forward_only=True))
+    losses = loss_dict(eng.losses)
+    tt = torch.tensor([ms, float(frames)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx, sm = tt.clone(), tt.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms, tot = float(mx[0]), float(sm[1])
+    else:
+        tot = float(frames)
+    if rank != 0:
+        return None
+    out = {"workload": "cfg5: training step, B=32 per GPU drawn as cfg2 (20-150 symbols), DaftExprt.forward + DaftExprtLoss (energy "
+                       "consistency 0.05, pitch consistency off) + backward, dropout = identity, one SUM all-reduce of the flat fp32 "
+                       "gradient buffer over NCCL, Adam(0.9, 0.98, eps 1e-9, wd 1e-6)",
+           "scaling": "weak", "dtype": "f32", "step_ms": ms, "frames_s": tot / (ms * 1e-3), "steps": steps, "warmup": warm,
+           "forward_backward_ms": ms_fb, "forward_loss_ms": ms_fwd, "all_reduce_ms": ms_ar, "all_reduce_bytes": int(eng.numel * 4),
+           "tflops_algorithmic": flops_per_step(batch[5].tolist(), batch[9].tolist()) * world / (ms * 1e-3) / 1e12,
+           "loss_after": losses["loss"], "timing": "CUDA events around the timed steps on the launching stream, max over ranks"}
+    if world == 1 and not args.no_cpu_baseline:
+        # the unmodified reference on this GPU (eager fp32, TF32 off) and on the host cores: forward + loss + backward + Adam
+        try:
+            import copy
+            from oracle import ref_harness as R
+            from oracle import train_oracle as TO
+            if R.reference_available():
+                ref = R.build_reference_model(hp, sd).to(dev)
+                import daft_exprt.loss as ref_loss
+                crit = ref_loss.DaftExprtLoss(str(dev), copy.deepcopy(hp))
+                opt = torch.optim.Adam(ref.parameters(), betas=tuple(hp.betas), eps=hp.epsilon, weight_decay=hp.weight_decay)
+                tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+                torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = False
+
+                def ref_step(it):
+                    inputs = tuple(t.clone() for t in d)
+                    opt.zero_grad(set_to_none=True)
+                    loss, _ = crit(ref(inputs), (inputs[1], inputs[3], inputs[4], inputs[8], inputs[9], inputs[10]), it)
+                    loss.backward()
+                    opt.step()
+                for it in (1, 2):
+                    ref_step(it)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for it in (3, 4, 5):
+                    ref_step(it)
+                torch.cuda.synchronize()
+                g_ms = (time.perf_counter() - t0) / 3 * 1e3
+                torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
+                out["eager_gpu_reference"] = {"step_ms": g_ms, "frames_s": frames / (g_ms * 1e-3), "speedup": g_ms / ms,
+                                              "what": "unmodified reference classes (oracle/_ref) eager fp32 on this GPU, eval mode, TF32 off: "
+                                                      "forward + DaftExprtLoss + backward + torch Adam, 3 steps after 2 warm-ups"}
+                del ref, opt
+                torch.set_num_threads(os.cpu_count() or 1)
+                t0 = time.perf_counter()
+                TO.reference_step(hp, sd, batch, 5)
+                c_s = time.perf_counter() - t0
+                out["cpu_reference"] = {"step_s": c_s, "frames_s": frames / c_s, "cores": torch.get_num_threads(), "kind": "reference",
+                                        "sample": "one forward + loss + backward of the same B=32 batch on the host cores (no optimiser step)"}
+        except Exception as e:          # noqa: BLE001
+            out["eager_gpu_reference"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
+
+
 def pick_peak(peaks, clk):
     """Roofline denominator: MEASURED_PEAKS.json's burst bf16 figure when the clocks sampled under the timed load sat
     at sm_max_mhz (within 3 %) with no cap / slowdown reason — the kernel is timed per launch inside a ~1 ms step, not
@@ -866,6 +963,9 @@ def main():
     configs = None
     if not args.no_configs and args.mode == "bf16":
         configs = run_configs(args, model, hp, sd, dev, rank, world, timed, profile_step, sync_all, peak, lat_p50, dist)
+        c5 = run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist)
+        if rank == 0:
+            configs["cfg5"] = c5
 
     # ---- CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
     cpu = None

@@ -1,0 +1,124 @@
+"""GPU: the training step of BASELINE config 5 (dx_train_step / dx_adam_step through train.TrainEngine) against the
+reference's own iteration run on the CPU (oracle/train_oracle.py: the unmodified reference classes under autograd).
+
+Gates (fp32 mode): loss terms within 1e-5 relative; every one of the 184 gradients within 1e-3 max-abs AND 2e-3 relative
+L1 of the reference's; an Adam step equal to torch.optim.Adam's on the same gradients; bit-identical repeat."""
+import pytest
+import torch
+
+import _cases as C
+from daft_exprt_b200.train import TrainEngine, loss_dict, update_learning_rate
+from oracle import ref_harness as R
+from oracle import train_oracle as TO
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not R.reference_available(), reason="reference (oracle/_ref) not present")]
+
+GRAD_MAX_ABS = 1e-3
+GRAD_REL_L1 = 2e-3
+LOSS_REL = 1e-5
+
+
+def _check_step(batch, iteration, hp=None):
+    hp = hp or C.hparams()
+    sd = C.state_dict()
+    ref_loss, ref_ind, ref_grads = TO.reference_step(hp, sd, batch, iteration)
+    eng = TrainEngine(hp, sd)
+    losses = loss_dict(eng.forward_backward(tuple(t.cuda() for t in batch), iteration=iteration))
+    assert abs(losses["loss"] - ref_loss) <= LOSS_REL * abs(ref_loss), (losses["loss"], ref_loss)
+    for k, v in ref_ind.items():
+        assert abs(losses[k] - v) <= LOSS_REL * max(abs(v), 1e-3), (k, losses[k], v)
+    grads = eng.grads_state_dict()
+    assert sorted(grads) == sorted(ref_grads) and len(grads) == 184
+    worst_abs = worst_rel = 0.0
+    for name, r in ref_grads.items():
+        o = grads[name].cpu()
+        assert o.shape == r.shape, name
+        d = (o - r).abs()
+        rel = d.sum().item() / max(r.abs().sum().item(), 1e-12)
+        worst_abs, worst_rel = max(worst_abs, d.max().item()), max(worst_rel, rel)
+        assert d.max().item() <= GRAD_MAX_ABS, f"{name}: max-abs {d.max().item():.3e}"
+        assert rel <= GRAD_REL_L1 or r.abs().sum().item() < 1e-6, f"{name}: rel-L1 {rel:.3e}"
+    return eng, worst_abs, worst_rel
+
+
+@pytest.mark.parametrize("kw,iteration", [
+    (dict(batch=4, lmin=5, lmax=30, seed=17), 1234),          # ragged, warm-up phase of the adversarial weight
+    (dict(batch=3, lmin=12, lmax=12, seed=18, const_dur=3), 20000),   # no padding anywhere (true zero padding at the ends)
+    (dict(batch=2, lmin=1, lmax=2, seed=19), 1),               # 1- and 2-symbol utterances
+])
+def test_gradients_match_reference_autograd(kw, iteration):
+    batch = C.synthetic.forward_batch(C.hparams(), **kw)
+    _, worst_abs, worst_rel = _check_step(batch, iteration)
+    C.record(f"train_grad_max_abs_B{kw['batch']}", worst_abs)
+    C.record(f"train_grad_rel_l1_B{kw['batch']}", worst_rel)
+
+
+def test_gradients_match_reference_autograd_cfg5_size():
+    """BASELINE config 5's per-GPU batch: 32 utterances drawn as cfg2 (20-150 symbols, 1-9 frames per symbol)."""
+    batch = C.synthetic.forward_batch(C.hparams(), batch=32, lmin=20, lmax=150, seed=42)
+    _, worst_abs, worst_rel = _check_step(batch, 5000)
+    C.record("train_grad_max_abs_B32", worst_abs)
+    C.record("train_grad_rel_l1_B32", worst_rel)
+
+
+def test_no_post_multipliers_and_no_energy_term():
+    """post_mult_weight = 0 removes the (2, 8) parameter (model.py:760-761, loss.py:92-95); energy_consistency_weight = 0
+    removes that term (loss.py:113)."""
+    hp = C.hparams()
+    hp.post_mult_weight = 0.0
+    hp.energy_consistency_weight = 0.0
+    sd = {k: v for k, v in C.state_dict().items() if k != "style_adapter.post_multipliers"}
+    batch = C.synthetic.forward_batch(hp, batch=3, lmin=4, lmax=20, seed=23)
+    ref_loss, ref_ind, ref_grads = TO.reference_step(hp, sd, batch, 77)
+    eng = TrainEngine(hp, sd)
+    losses = loss_dict(eng.forward_backward(tuple(t.cuda() for t in batch), iteration=77))
+    assert abs(losses["loss"] - ref_loss) <= LOSS_REL * abs(ref_loss)
+    assert losses["energy_consistency_loss"] == 0.0 and losses["post_mult_loss"] == 0.0
+    grads = eng.grads_state_dict()
+    assert len(grads) == 183
+    for name, r in ref_grads.items():
+        assert (grads[name].cpu() - r).abs().max().item() <= GRAD_MAX_ABS, name
+
+
+def test_step_is_deterministic_and_adam_equals_torch():
+    hp = C.hparams()
+    sd = C.state_dict()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=4, lmin=5, lmax=30, seed=17))
+    eng = TrainEngine(hp, sd)
+    eng.forward_backward(batch, iteration=10)
+    g1 = eng.grads.clone()
+    eng.forward_backward(batch, iteration=10)
+    assert torch.equal(g1, eng.grads), "two identical steps must give bit-identical gradients (no atomics)"
+    # three Adam steps on the flat buffers against torch.optim.Adam with the reference's settings (train.py:278-280)
+    p_ref = eng.params.clone().requires_grad_(True)
+    opt = torch.optim.Adam([p_ref], betas=tuple(hp.betas), eps=hp.epsilon, weight_decay=hp.weight_decay, amsgrad=False)
+    for it in (1, 2, 3):
+        lr = update_learning_rate(hp, it)
+        eng.forward_backward(batch, iteration=it)
+        for grp in opt.param_groups:
+            grp["lr"] = lr
+        p_ref.grad = eng.grads.clone()
+        opt.step()
+        eng.adam(lr)
+        assert (eng.params - p_ref.detach()).abs().max().item() <= 1e-7
+    # the updated weights still export in checkpoint layout and load into the inference mirror
+    from daft_exprt_b200.model import DaftExprt
+    m = DaftExprt(hp, mode="fp32").cuda()
+    m.load_state_dict(eng.state_dict())
+    losses_fwd = loss_dict(eng.forward_backward(batch, iteration=4, forward_only=True)).copy()
+    _, mel = eng.forward_backward(batch, iteration=4, forward_only=True, want_mel=True)
+    assert torch.equal(m(batch)[3][0], mel), "training forward and DX_MODE_F32 inference forward are the same kernels"
+    assert losses_fwd["loss"] > 0
+
+
+def test_loss_goes_down():
+    """Ten iterations on one batch at a fixed learning rate: the loss the step reports must fall (end-to-end sanity of
+    gradient signs, layouts and the optimiser)."""
+    hp = C.hparams()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=8, lmin=10, lmax=40, seed=29))
+    eng = TrainEngine(hp, C.state_dict())
+    first = None
+    for it in range(1, 11):
+        v = float(eng.step(batch, iteration=it, lr=2e-4)[0])
+        first = v if first is None else first
+    assert v < 0.97 * first, (first, v)        # measured: 4.51 -> 4.18
