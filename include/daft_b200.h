@@ -233,6 +233,19 @@ int dx_tc_gemm_test(const void* a_il, int64_t a_rows_phys, int M, int K, int N, 
 int dx_test_attention(int mode, const void* qkv, void* out, int64_t rows_phys, const int64_t* lengths, int B, int n_max,
                       int32_t* rowmap_scratch, int64_t row_cap, void* stream);
 
+/* Allocation-free variant of dx_test_attention.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same kernels, same arguments and results, but the int32 row map lives in a
+ * file-scope __device__ array inside the library (257 KB, held by every GPU that loads the library until exit)
+ * instead of caller scratch; the call performs no cudaMalloc / cudaFree / allocating library routine.
+ * Limits: 1 <= B <= 255 and dx_row_cap(B, n_max) <= DX_ATTENTION_STATIC_MAX_ROWS, else status 2 and a message.
+ * All calls on one device share the array (it keeps the last call's contents; every entry a call reads is rewritten
+ * by that call first, nothing needs to start at zero): calls that overlap on the GPU race — serialise them. */
+#define DX_ATTENTION_STATIC_MAX_ROWS 32768
+int64_t dx_attention_static_max_rows(void);
+int dx_attention_static(int mode, const void* qkv, void* out, int64_t rows_phys, const int64_t* lengths, int B, int n_max,
+                        void* stream);
+
 /* ---- HiFi-GAN generator, batched -------------------------------------------------
  * Replaces HiFiGANGenerator.forward (vocoder/hifigan.py:159-176) with ResBlock1 (hifigan.py:77-97) for a whole batch
  * of utterances at once, each vocoded as if alone on its cropped mel (what HiFiGanVocoder.infer does one utterance

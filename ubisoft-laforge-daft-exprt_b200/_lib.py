@@ -121,6 +121,8 @@ SIGNATURES = {
     "dx_host_collate": (C.c_int, [C.c_int] * 5 + [_p, _p, _p, _p, C.c_int]),
     "dx_host_collate_packed": (C.c_int, [C.c_int] * 5 + [_p, _p, _p, _p, C.c_int]),
     "dx_test_attention": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p, C.c_int64, _p]),
+    "dx_attention_static_max_rows": (C.c_int64, []),
+    "dx_attention_static": (C.c_int, [C.c_int, _p, _p, C.c_int64, _p, C.c_int, C.c_int, _p]),
 }
 
 _LIB = None
