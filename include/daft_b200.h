@@ -52,8 +52,13 @@ int64_t     dx_launch_count(void);
  * key 3: run the FFN as two GEMM launches instead of the fused kernel (A/B testing);
  * key 4: run the K = 128 linear layers in the generic conv-GEMM kernel instead of the weight-resident one;
  * key 5: launch without programmatic dependent launch (plain stream order between kernels);
+ * key 6: fused block kernel: never split a tile's hidden dimension across CTAs (whole tiles per CTA);
+ * key 7: its fewest hidden chunks per CTA when it splits (default 0 = 2 or 4 by the stream's size);
+ * key 8: it splits when whole tiles would occupy at most this percentage of the grid (default 0 = 35; 1000 = always);
+ * key 15: its timing experiments (wrong results; bit 0 no E2 stores, 1 no P3 stores, 2 no P0 residual, 3 no FiLM);
  * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two;
- * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch). */
+ * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch);
+ *         + 100: trace the last working CTA (always a tile owner) instead of CTA 0. */
 int         dx_set_debug(int key, int value);
 
 /* Bring-up: while a device buffer (>= 2 KB) is set, the fused FFN kernel writes a clock64 timeline of its CTA 0

@@ -285,3 +285,49 @@ def test_fused_block_tail_matches_four_launch_blocks(models, cfg):
     assert torch.equal(fused[3][0], plain[3][0])          # mel
     assert torch.equal(fused[4], plain[4])                # gaussian upsampling weights
     assert torch.equal(fused[0], plain[0])                # accent embedding
+
+
+@pytest.mark.parametrize("cfg", ["cfg1", "cfg2", "cfg4_b1"])
+def test_hidden_dimension_split_of_the_fused_block_kernel(models, cfg):
+    """The fused block kernel splits the 1024-wide hidden dimension of a tile across CTAs (stream-K; partial fp32 sums
+    meet in the tile's owner in a fixed order).  Against whole tiles per CTA (debug knob 6) only the fp32 summation
+    order of conv2 changes: the mel agrees to bf16 rounding, both stay inside the north-star gate against the oracle,
+    and the split path is deterministic run to run.  The split is on by default for short streams only; knob 8 = 1000
+    forces it for every stream (cfg2 frames: segments that span two tiles), knob 7 = 1 the deepest split (8 CTAs per
+    tile)."""
+    from daft_exprt_b200 import _lib
+    hp = C.hparams()
+    host = C.synthetic.config_batch(hp, cfg)
+    batch = tuple(t.cuda() for t in host)
+    ref = O.forward(C.state_dict(), hp, tuple(t.clone() for t in host)) if cfg != "cfg2" else None
+    m = models["bf16"]
+    lib = _lib.load()
+    split = m(batch)
+    split = (split[3][0].clone(), split[4].clone(), split[0].clone())
+    again = m(batch)
+    torch.cuda.synchronize()
+    assert torch.equal(split[0], again[3][0]) and torch.equal(split[1], again[4]) and torch.equal(split[2], again[0])
+    lib.dx_set_debug(6, 1)
+    try:
+        whole = m(batch)
+        whole = (whole[3][0].clone(), whole[4].clone())
+        torch.cuda.synchronize()
+    finally:
+        lib.dx_set_debug(6, 0)
+    lib.dx_set_debug(8, 1000)
+    try:
+        forced = m(batch)
+        forced = (forced[3][0].clone(), forced[4].clone())
+        lib.dx_set_debug(7, 1)
+        deep = m(batch)
+        deep = (deep[3][0].clone(), deep[4].clone())
+        torch.cuda.synchronize()
+    finally:
+        lib.dx_set_debug(7, 0)
+        lib.dx_set_debug(8, 0)
+    for other in (whole, forced, deep):
+        rel = ((split[0] - other[0]).abs().sum() / other[0].abs().sum()).item()
+        assert rel <= 1e-2, rel
+    if ref is not None:
+        for got in (split, whole, forced, deep):
+            _check_mel(got[0], ref[3][0], host[9], "bf16")

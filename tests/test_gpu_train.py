@@ -122,3 +122,20 @@ def test_loss_goes_down():
         v = float(eng.step(batch, iteration=it, lr=2e-4)[0])
         first = v if first is None else first
     assert v < 0.97 * first, (first, v)        # measured: 4.51 -> 4.18
+
+
+def test_step_does_not_depend_on_what_the_workspace_held():
+    """The workspace is caller memory with arbitrary contents: a step on a workspace full of NaN bit patterns gives the
+    same loss and bit-identical gradients as on a zeroed one (0 x stale-NaN would poison a weight gradient; found on
+    out_proj.weight, whose operand rows between utterances were never written)."""
+    hp = C.hparams()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=8, lmin=10, lmax=40, seed=29))
+    got = []
+    for fill in (0x00, 0xFF):
+        eng = TrainEngine(hp, C.state_dict())
+        eng._workspace(batch[0].shape[0], batch[0].shape[1], batch[8].shape[2]).fill_(fill)
+        losses = eng.forward_backward(batch, iteration=1).clone()
+        torch.cuda.synchronize()
+        got.append((losses, eng.grads.clone()))
+    assert torch.isfinite(got[1][1]).all()
+    assert torch.equal(got[0][0], got[1][0]) and torch.equal(got[0][1], got[1][1])

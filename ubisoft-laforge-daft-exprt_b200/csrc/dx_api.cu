@@ -165,6 +165,7 @@ int dx_accent_encoder(const DxModelWeights* w, int mode, int B, int T_max, const
     DX_TRY(plan_layout(&p, B, 1, T_max, mode, workspace, workspace_bytes));
     cudaStream_t s = (cudaStream_t)stream;
     Rows RT = p.rows_t(output_lengths);
+    if (mode == DX_MODE_BF16) DX_TRY(zero_plan_halos(p, s));
     DX_TRY(build_rows(output_lengths, B, T_max, p.t_row_start, p.t_row_b, p.t_row_p, p.cap_t, s));
     return run_accent_encoder(*w, p, RT, frames_energy, frames_pitch, mel_specs, accent_emb, s);
 }

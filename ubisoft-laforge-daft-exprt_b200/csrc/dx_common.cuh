@@ -141,6 +141,13 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// LayerNorm affine + FiLM of one value with the rounding points pinned (no compiler-chosen contraction), so that every
+// kernel that finishes a row this way (fused block kernel, tc_gemm / tc_linear LN epilogue) produces the same bits
+__device__ __forceinline__ float ln_film(float v, float mean, float rstd, float g, float be, float fg, float fb) {
+    const float y = __fmaf_rn(__fmul_rn(__fsub_rn(v, mean), rstd), g, be);
+    return __fmaf_rn(fg, y, fb);
+}
+
 // ---- fp32 path (dx_f32.cu) -------------------------------------------------------------------------------
 // out[r][n] = act(bias[n] + sum_j sum_k A[r + j - taps/2][k] * W[j][k][n]); rows outside [0, total) read as 0;
 // rows that are not live(ext) are written as 0.  ext < 0: no liveness masking (plain linear layers).

@@ -330,6 +330,13 @@ attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ 
             if (lse != nullptr && tx == 0) lse[(rs + q) * DX_HEADS + h] = m[i] + logf(l[i]);
         }
     }
+    // the utterance's gap rows get zeros: the training step's weight gradients run over every row of the stream
+    // (d out_proj.weight = O^T dT1 with dT1 = 0 there), and 0 x <whatever the workspace held> must stay 0
+    if (blockIdx.x == 0 && tid < DX_GAP * 16) {
+        const int64_t r = rs + len + tid / 16;
+        *reinterpret_cast<float4*>(out + r * DX_D + h * DX_DH + (tid & 15) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lse != nullptr && (tid & 15) == 0) lse[r * DX_HEADS + h] = 0.f;
+    }
 }
 
 static const int AT_SMEM = (64 * AT_Q + 64 * (AT_K + 1) + AT_K * DX_DH + AT_K * (AT_Q + 4)) * (int)sizeof(float);

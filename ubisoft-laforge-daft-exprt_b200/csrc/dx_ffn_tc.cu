@@ -40,9 +40,31 @@
 // epilogues exchange their partial sums through shared memory): the row epilogues were latency-bound with one
 // thread per row (P0 8 k cycles, E2 14 k cycles of a 108 k-cycle tile).
 //
-// TMEM accumulator protocol (per half): D1 is "used" 8 (+2 with P3) times per tile, D2 1 (+1 with P0, +1 with P3)
-// times; use number u: issuer waits empty (parity (u & 1) ^ 1), issues, commits full; epilogue waits full
-// (parity u & 1), loads the accumulator into registers, arrives on empty.
+// TMEM accumulator protocol (per half): D1 is "used" once per hidden chunk (+2 with P3), D2 once per segment (+1 with
+// P0, +1 with P3); use number u (a running count kept identically by issuer and epilogue): issuer waits empty (parity
+// (u & 1) ^ 1), issues, commits full; epilogue waits full (parity u & 1), loads the accumulator into registers, arrives
+// on empty.
+//
+// Work split (stream-K over the hidden dimension) for SHORT streams.  One tile is ~50 us of serial work; a cfg2 symbol
+// stream has 46 tiles for 148 SMs and a single utterance 3, so whole tiles per CTA leave most of the GPU idle and set the
+// latency floor of a launch.  When whole tiles would occupy about a third of the grid or less (decided on the device), the
+// unit of work becomes ONE HIDDEN CHUNK OF ONE 124-ROW TILE (8 units per tile): CTA i takes the contiguous unit range
+// [i U / G', (i + 1) U / G'), G' = min(grid, U / min_units), and walks it tile by tile ("segments", chunks a..b of a tile).
+// Every segment needs the tile's x1 (P0 is recomputed: 16 of a tile's 784 MMAs).  The segment that holds chunk 7 OWNS the
+// tile: it adds the partial D2 sums of the tile's other segments (fp32, written to global memory = L2 by their CTAs, one
+// slot per CTA, published with a release store of the launch's epoch into flags[cta]) to its own accumulator, in
+// descending CTA order - a fixed order, so results are deterministic for a given (row count, grid) - and runs E2 / P3.  A
+// CTA walks its range from the TOP: its only possible non-owner segment (the head of a tile whose tail belongs to CTA
+// i + 1) comes first and waits for nothing, so an owner only ever waits for CTAs with a LOWER index that are already past
+// their publishing point (no deadlock as long as CTAs are dispatched in index order, also next to another stream's
+// kernels; every wait is bounded and traps).  Longer streams keep whole tiles: there each extra segment costs more (P0 +
+// partial exchange, ~20 k cycles) than the chunks it takes over (~7 k each); measured, cfg2 frame stream: 0.489 -> 0.548 ms.
+// Without a partial buffer (debug knob 6) units are always whole tiles.  The split is a function of (row count, grid)
+// only, so the fused and the four-launch block (knob 9) split alike and stay bit-identical.
+//
+// Code size matters here: the once-per-tile epilogues are straight-line code that is fetched from L2 each time (ncu:
+// stall_no_inst was their top stall reason).  The mbarrier time-out report is one out-of-line function (it was 40 KB of
+// inlined printf set-up), and the E2 / P3 / dump epilogues keep the row in TMEM and loop over 16-column groups.
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
@@ -57,6 +79,7 @@ constexpr int FF_OUT1 = 124;                // outputs of a one-half tile: its 1
 constexpr int FF_TILE = 2 * FF_OUT;         // outputs per two-half CTA tile
 constexpr int FF_NCH = 8;                   // hidden chunks of 128 channels
 constexpr int FF_WSTAGES = 5;
+constexpr int FF_PARTIAL_FLOATS = 2 * 2 * 64 * 128;     // one CTA's partial D2 of a tile: [half][part][col 64][row 128] fp32 = 128 KB
 constexpr uint32_t FF_X_BYTES = 16 * 256 * 16;          // 65536
 constexpr uint32_t FF_HS_ROWS = 136;
 constexpr uint32_t FF_HS_BYTES = 8 * FF_HS_ROWS * 16;   // 17408 per (half, sub)
@@ -87,8 +110,51 @@ struct FfnParams {
     const float* b_qkv;
     __nv_bfloat16* qkv_out;
     Rows R;
-    long long* trace;           // bring-up: clock64 timeline of CTA 0 (dx_set_trace_buffer) or null
+    // split over the hidden dimension (null: whole tiles per CTA)
+    float* partial;             // [FF_MAX_CTAS][FF_PARTIAL_FLOATS]
+    uint32_t* flags;            // [FF_MAX_CTAS]: flags[i] == epoch once CTA i's partial of THIS launch is complete
+    uint32_t epoch;
+    int min_units;              // fewest hidden chunks per CTA; 0 = 4 when there are >= 2 chunks per CTA, else 2
+    int split_pct;              // split when whole tiles would occupy at most this percentage of the grid
+    long long* trace;           // bring-up: clock64 timeline of one CTA (dx_set_trace_buffer) or null
+    int trace_last;             // trace the last working CTA (always a tile owner) instead of CTA 0
+    int exp;                    // timing experiments (debug knob 15; results are wrong): bit 0 no E2 global stores, bit 1 no P3
+                                // global stores, bit 2 no P0 residual loads, bit 3 no FiLM loads, bit 4 no FiLM L1 prefetch
 };
+
+__device__ __forceinline__ uint32_t ff_ld_acquire(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ff_st_release(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// bounded: a protocol bug must trap, not hang the box
+__device__ __forceinline__ void ff_wait_flag(const uint32_t* p, uint32_t epoch) {
+    uint32_t spins = 0;
+    while (ff_ld_acquire(p) != epoch) {
+        __nanosleep(100);
+        if (++spins > (1u << 24)) {
+            printf("dx: ffn partial-sum flag timeout (block %d waits for epoch %u)\n", (int)blockIdx.x, epoch);
+            __trap();
+        }
+    }
+}
+
+// Segment walk shared by the three roles: the CTA's unit range [w_lo, w_hi) from the top; per segment: tile, chunks
+// a..b, t0 = first unit of the tile, owner = holds chunk 7.
+#define FF_SEG_BEGIN                                                                                        \
+    for (int64_t u_hi = w_hi; u_hi > w_lo;) {                                                               \
+        const int tile = (int)((u_hi - 1) / FF_NCH);                                                        \
+        const int64_t t0 = (int64_t)tile * FF_NCH;                                                          \
+        const int b = (int)(u_hi - 1 - t0);                                                                 \
+        const int a = (int)((w_lo > t0 ? w_lo : t0) - t0);                                                  \
+        const bool owner = b == FF_NCH - 1;                                                                 \
+        const bool seg_p3 = has_p3 && owner;
+#define FF_SEG_END                                                                                          \
+        u_hi = t0 + a;                                                                                      \
+    }
 
 // timeline slots (CTA 0, half 0 only): [0] kernel start, [1] X ready, then per chunk c (base 8 + 12 c):
 //   issuer  +0 d1_empty ok, +1 G1 issued, +2 hs_full[0] ok, +3 G2 issued (both subs), +4 first w_full wait of G1 done
@@ -103,18 +169,6 @@ struct FfnParams {
 #ifndef FF_EXPERIMENT
 #define FF_EXPERIMENT 0
 #endif
-
-// global source of weight stage q of a tile, in MMA issue order: [W_out k 0,1] G1(0) { G1(c) G2(c-1) } G2(7) [W_qkv' (nt, k)]
-__device__ __forceinline__ const uint8_t* ff_stage_src(const FfnParams& p, int q, int n_p0) {
-    if (q < n_p0) return reinterpret_cast<const uint8_t*>(p.w_out) + (size_t)q * FF_W_BYTES;
-    q -= n_p0;
-    if (q >= 12 * FF_NCH) return reinterpret_cast<const uint8_t*>(p.w_qkv) + (size_t)(q - 12 * FF_NCH) * FF_W_BYTES;
-    int c, w;            // c: loop iteration 0..8; w: 0..5 → G1(c), 6..11 → G2(c-1)
-    if (q < 6) { c = 0; w = q; }
-    else { c = 1 + (q - 6) / 12; w = (q - 6) % 12; if (c == FF_NCH) w += 6; }
-    if (w < 6) return reinterpret_cast<const uint8_t*>(p.w1) + ((size_t)c * 6 + w) * FF_W_BYTES;
-    return reinterpret_cast<const uint8_t*>(p.w2) + ((size_t)(c - 1) * 6 + (w - 6)) * FF_W_BYTES;
-}
 
 __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p) {
     extern __shared__ __align__(1024) uint8_t ff_smem[];
@@ -134,7 +188,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     uint64_t* w_full = bars;                       // [S]   producer → both issuers
     uint64_t* w_empty = bars + FF_WSTAGES;         // [S]   one commit per active issuer
     uint64_t* x_full = bars + 2 * FF_WSTAGES;      // bulk copies of the X tile (or of the P0 A tile) have landed
-    uint64_t* x_empty = x_full + 1;                // epilogue warps are done with the tile's shared memory
+    uint64_t* x_empty = x_full + 1;                // epilogue warps are done with the segment's shared memory
     uint64_t* x_ready = x_full + 2;                // P0: the epilogue warps have written the X tile
     uint64_t* hb = x_full + 3;                     // per half h (9 barriers each):
     // hb[9 h + 0] d1_full, +1 d1_empty, +2 hs_full[sub 0], +3 hs_full[sub 1], +4 hs_empty[0], +5 hs_empty[1], +6 d2_full, +7 d2_empty,
@@ -143,11 +197,9 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool has_p0 = p.attn != nullptr, has_p3 = p.qkv_out != nullptr;
-    const int n_p0 = has_p0 ? 2 : 0;
-    const int stages_per_tile = n_p0 + 12 * FF_NCH + (has_p3 ? 6 : 0);
-    const uint32_t d1_uses = FF_NCH + (has_p3 ? 2 : 0), d2_uses = 1 + (has_p0 ? 1 : 0) + (has_p3 ? 1 : 0);
-    long long* tr = (p.trace != nullptr && blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == FF_EPI_WARP0)) ? p.trace : nullptr;
-    if (warp == 1) FF_TRACE(0);
+    const int n_pre = has_p0 ? 2 : 0;              // weight stages every segment starts with (W_out): fetched before the PDL wait
+    long long* tr = nullptr;
+    const long long t_start = p.trace != nullptr ? clock64() : 0;
 
     // ---- prologue that does not depend on the previous kernel (PDL: overlaps its tail) ----
     for (int i = threadIdx.x; i < 1024; i += FF_THREADS) s_b1[i] = p.b1[i];
@@ -181,12 +233,12 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    // the first FF_WSTAGES weight stages are the same for every tile: fetch them now
+    // the W_out stages are the same for every segment: fetch them now
     if (warp == 0 && ptx::elect_one()) {
-        for (int s0 = 0; s0 < FF_WSTAGES; ++s0) {
+        for (int s0 = 0; s0 < n_pre; ++s0) {
             if (FF_EXPERIMENT & 1) { ptx::mbar_arrive(&w_full[s0]); continue; }
             ptx::mbar_expect_tx(&w_full[s0], FF_W_BYTES);
-            ptx::bulk_g2s(sW + s0 * FF_W_BYTES, ff_stage_src(p, s0, n_p0), FF_W_BYTES, &w_full[s0]);
+            ptx::bulk_g2s(sW + s0 * FF_W_BYTES, reinterpret_cast<const uint8_t*>(p.w_out) + (size_t)s0 * FF_W_BYTES, FF_W_BYTES, &w_full[s0]);
         }
     }
     __syncwarp();
@@ -194,14 +246,36 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     ptx::griddep_wait();
     // ---- from here on the previous kernel's output (row map, activations) may be read ----
     const int64_t total = p.R.row_start[p.R.B];
-    // Short streams (symbol side): when the 252-row tiles would leave more than half of the CTAs idle, every CTA
-    // takes ONE half instead, which halves the kernel's critical path.  Decided on the device: the valid row count
-    // is only known there.
-    const int halves = ((total + FF_TILE - 1) / FF_TILE) * 2 <= (int64_t)gridDim.x ? 1 : 2;
+    const int64_t n252 = (total + FF_TILE - 1) / FF_TILE;
+    // Short streams: 124-row tiles (ONE half per CTA) shorten the critical path when 252-row tiles would leave more than
+    // half of the CTAs idle.  Decided on the device: the valid row count is only known there.
+    const int halves_whole = n252 * 2 <= (int64_t)gridDim.x ? 1 : 2;
+    const int64_t tiles_whole = halves_whole == 2 ? n252 : (total + FF_OUT1 - 1) / FF_OUT1;
+    // Split the hidden dimension only when whole tiles would use about a third of the grid or less (measured on B200:
+    // cfg2 symbol stream, 46 tiles: 0.180 -> 0.161 ms per stack; one utterance, 3 tiles: 0.343 -> 0.283 ms; cfg2 frame
+    // stream, 109 tiles: 0.489 -> 0.548 ms - every extra segment repeats P0 and the partial-sum exchange, ~20 k cycles
+    // against ~7 k per chunk)
+    const bool split = p.partial != nullptr && tiles_whole * 100 <= (int64_t)p.split_pct * gridDim.x;
+    const int halves = split ? 1 : halves_whole;
     const int out_rows = halves == 2 ? FF_OUT : FF_OUT1;               // outputs per half
     const int tile_rows = out_rows * halves;
     const int n_tiles = (int)((total + tile_rows - 1) / tile_rows);
+    // this CTA's unit range (unit = one hidden chunk of one tile; whole tiles without the split)
+    const int gran = split ? 1 : FF_NCH;
+    const int64_t n_groups = (int64_t)n_tiles * (FF_NCH / gran);
+    const int min_units = p.min_units > 0 ? p.min_units : (n_groups >= 2 * (int64_t)gridDim.x ? 4 : 2);
+    int64_t ctas = split ? n_groups / min_units : n_groups;
+    if (ctas > (int64_t)gridDim.x) ctas = gridDim.x;
+    if (ctas < 1) ctas = 1;
+    const bool has_work = (int64_t)blockIdx.x < ctas;
+    const int64_t w_lo = has_work ? (int64_t)blockIdx.x * n_groups / ctas * gran : 0;
+    const int64_t w_hi = has_work ? ((int64_t)blockIdx.x + 1) * n_groups / ctas * gran : 0;
     const uint32_t x_chunk_bytes = halves == 2 ? 4096u : (has_p0 ? 2048u : 2176u);      // 256 / 128 / 136 rows of one 8-channel chunk
+    if (p.trace != nullptr && lane == 0 && (warp == 1 || warp == FF_EPI_WARP0) &&
+        (int64_t)blockIdx.x == (p.trace_last ? (n_groups > 0 ? ctas - 1 : 0) : 0)) {
+        tr = p.trace;
+        if (warp == 1) tr[0] = t_start;
+    }
     if (threadIdx.x == 0) {
         for (int i = 0; i < FF_WSTAGES; ++i) ptx::mbar_init(&w_empty[i], halves);
         ptx::mbar_init(x_full, 1);
@@ -224,34 +298,52 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
     // TMEM columns: D1[h] at 128 h, D2[h] at 256 + 128 h
     const uint32_t tm_d1 = tmem_base, tm_d2 = tmem_base + 256;
 
+    if (warp < FF_EPI_WARP0) {
     if (warp == 0) {
         // ===================== producer: X tile (or P0 A tile) + weight stages =====================
         if (ptx::elect_one()) {
-            uint32_t wit = 0, tile_it = 0;
+            uint32_t wit = 0, seg_it = 0;
             const __nv_bfloat16* src = has_p0 ? p.attn : p.x;
             uint8_t* dst = has_p0 ? sHs : sX;
             const uint32_t dst_chunk = (has_p0 && halves == 1) ? 2048u : 4096u;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
+            // weight stages in MMA issue order: [W_out k 0,1]  G1(a)  { G1(c) G2(c-1) }  G2(b)  [W_qkv' (nt, k)]
+#define FF_EMIT(srcptr)                                                                                     \
+            do {                                                                                            \
+                if ((int)wit >= n_pre) {                 /* the first n_pre stages were fetched in the prologue */ \
+                    const int s_ = wit % FF_WSTAGES;                                                        \
+                    ptx::mbar_wait(&w_empty[s_], ((wit / FF_WSTAGES) & 1) ^ 1);                             \
+                    if (FF_EXPERIMENT & 1) ptx::mbar_arrive(&w_full[s_]);                                   \
+                    else {                                                                                  \
+                        ptx::mbar_expect_tx(&w_full[s_], FF_W_BYTES);                                       \
+                        ptx::bulk_g2s(sW + s_ * FF_W_BYTES, (srcptr), FF_W_BYTES, &w_full[s_]);             \
+                    }                                                                                       \
+                }                                                                                           \
+                ++wit;                                                                                      \
+            } while (0)
+            FF_SEG_BEGIN
                 const int64_t R0 = (int64_t)tile * tile_rows;
-                ptx::mbar_wait(x_empty, (tile_it & 1) ^ 1);
+                ptx::mbar_wait(x_empty, (seg_it & 1) ^ 1);
                 ptx::mbar_expect_tx(x_full, 16 * x_chunk_bytes);
                 for (int kc = 0; kc < 16; ++kc)
                     ptx::bulk_g2s(dst + kc * dst_chunk, src + ((int64_t)kc * p.rows_phys + DX_HALO + R0 - 2) * 8, x_chunk_bytes, x_full);
-                for (int q = 0; q < stages_per_tile; ++q, ++wit) {
-                    if (wit < FF_WSTAGES) continue;          // fetched in the prologue
-                    const int s = wit % FF_WSTAGES;
-                    ptx::mbar_wait(&w_empty[s], ((wit / FF_WSTAGES) & 1) ^ 1);
-                    if (FF_EXPERIMENT & 1) { ptx::mbar_arrive(&w_full[s]); continue; }
-                    ptx::mbar_expect_tx(&w_full[s], FF_W_BYTES);
-                    ptx::bulk_g2s(sW + s * FF_W_BYTES, ff_stage_src(p, q, n_p0), FF_W_BYTES, &w_full[s]);
+                for (int q = 0; q < n_pre; ++q) FF_EMIT(reinterpret_cast<const uint8_t*>(p.w_out) + (size_t)q * FF_W_BYTES);
+                for (int c = a; c <= b + 1; ++c) {
+                    if (c <= b)
+                        for (int q = 0; q < 6; ++q) FF_EMIT(reinterpret_cast<const uint8_t*>(p.w1) + ((size_t)c * 6 + q) * FF_W_BYTES);
+                    if (c > a)
+                        for (int q = 0; q < 6; ++q) FF_EMIT(reinterpret_cast<const uint8_t*>(p.w2) + ((size_t)(c - 1) * 6 + q) * FF_W_BYTES);
                 }
-            }
+                if (seg_p3)
+                    for (int q = 0; q < 6; ++q) FF_EMIT(reinterpret_cast<const uint8_t*>(p.w_qkv) + (size_t)q * FF_W_BYTES);
+                ++seg_it;
+            FF_SEG_END
+#undef FF_EMIT
         }
     } else if (warp <= 2) {
         // ===================== MMA issuers: warp 1 ↔ half 0, warp 2 ↔ half 1 =====================
         const int h = warp - 1;
-        if ((int)blockIdx.x >= n_tiles && h == 0)      // no tile: the prefetched weight stages must land before the CTA exits
-            for (int s0 = 0; s0 < FF_WSTAGES; ++s0) ptx::mbar_wait(&w_full[s0], 0);
+        if (w_hi <= w_lo && h == 0)      // no work: the prefetched weight stages must land before the CTA exits
+            for (int s0 = 0; s0 < n_pre; ++s0) ptx::mbar_wait(&w_full[s0], 0);
         if (h < halves) {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 128);
             const uint32_t aX = ptx::smem_u32(sX) + FF_OUT * h * 16, aHs = ptx::smem_u32(sHs) + h * 2 * FF_HS_BYTES, aW = ptx::smem_u32(sW);
@@ -265,7 +357,8 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             uint64_t* d2_full = &hb[9 * h + 6];
             uint64_t* d2_empty = &hb[9 * h + 7];
             uint64_t* y_full = &hb[9 * h + 8];
-            uint32_t tile_it = 0, w_phase = 0;
+            uint32_t seg_it = 0, w_phase = 0;
+            uint32_t u1 = 0, u2 = 0, n_hs = 0, n_y = 0;  // running use counts: D1, D2, Hs buffers, P3 A tiles
             int s = 0;                                   // ring slot and phase of the next weight stage
             // one weight stage = 4 MMAs of this half: A at a_base + kk * a_step (K-major, LBO a_lbo), B = the stage
 #define FF_STAGE(a_base, a_step, a_lbo, d_tmem, acc_first, ...)                                                         \
@@ -284,10 +377,9 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 __syncwarp();                                                                                           \
                 if (++s == FF_WSTAGES) { s = 0; w_phase ^= 1; }                                                         \
             } while (0)
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
-                uint32_t u1 = tile_it * d1_uses, u2 = tile_it * d2_uses;       // accumulator use counters
-                ptx::mbar_wait(x_full, tile_it & 1);
-                if (tile_it == 0 && has_p0) FF_TRACE(5);
+            FF_SEG_BEGIN
+                ptx::mbar_wait(x_full, seg_it & 1);
+                if (seg_it == 0 && has_p0) FF_TRACE(5);
                 if (has_p0) {
                     // ---- P0: D2[h] = attn[128 h .. +127] · W_out   (stage = K half)
                     ptx::mbar_wait(d2_empty, (u2 & 1) ^ 1);
@@ -295,51 +387,53 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                     for (int ks = 0; ks < 2; ++ks)
                         FF_STAGE(aP0 + ks * 8 * p0_lbo, 2 * p0_lbo, p0_lbo, td2, ks != 0, if (ks == 1) ptx::mma_commit(d2_full));
                     ++u2;
-                    ptx::mbar_wait(x_ready, tile_it & 1);      // X tile written by the epilogue warps of both halves
+                    ptx::mbar_wait(x_ready, seg_it & 1);       // X tile written by the epilogue warps of both halves
                     ptx::tc_fence_after();
                 }
-                if (tile_it == 0) FF_TRACE(1);
+                if (seg_it == 0) FF_TRACE(1);
                 ptx::mbar_wait(d2_empty, (u2 & 1) ^ 1);
                 ptx::tc_fence_after();
-                for (int c = 0; c <= FF_NCH; ++c) {
-                    if (c < FF_NCH) {
+                for (int c = a; c <= b + 1; ++c) {
+                    if (c <= b) {
                         // ---- G1(c): D1[h] = X_h (*) W1[c]   (stage = (K half, tap): 64 input channels x 128 hidden)
                         ptx::mbar_wait(d1_empty, (u1 & 1) ^ 1);
                         ptx::tc_fence_after();
-                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 0);
+                        if (seg_it == 0) FF_TRACE(8 + 12 * c + 0);
 #pragma unroll
                         for (int st = 0; st < 6; ++st) {
                             const int kh = st / 3, tap = st % 3;
                             FF_STAGE(aX + kh * 8 * 4096 + tap * 16, 2 * 4096, 4096, td1, st != 0, if (st == 5) ptx::mma_commit(d1_full));
                         }
                         ++u1;
-                        if (tile_it == 0) FF_TRACE(8 + 12 * c + 1);
+                        if (seg_it == 0) FF_TRACE(8 + 12 * c + 1);
                     }
-                    if (c >= 1) {
+                    if (c > a) {
                         // ---- G2(c-1, sub): D2[h] += Hs[h][sub] (*) W2[c-1, sub]   (stage = (sub, tap): 64 hidden x 128 out)
                         const int cc = c - 1;
-                        const uint32_t k = tile_it * FF_NCH + cc;
+                        const bool first = cc == a, last = cc == b;
 #pragma unroll
                         for (int st = 0; st < 6; ++st) {
                             const int sub = st / 3, tap = st % 3;
                             if (tap == 0) {
-                                ptx::mbar_wait(&hs_full[sub], k & 1);
+                                ptx::mbar_wait(&hs_full[sub], n_hs & 1);
                                 ptx::tc_fence_after();
-                                if (tile_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
+                                if (seg_it == 0 && sub == 0) FF_TRACE(8 + 12 * cc + 2);
                             }
-                            FF_STAGE(aHs + sub * FF_HS_BYTES + tap * 16, 2 * FF_HS_ROWS * 16, FF_HS_ROWS * 16, td2, (cc | st) != 0,
+                            FF_STAGE(aHs + sub * FF_HS_BYTES + tap * 16, 2 * FF_HS_ROWS * 16, FF_HS_ROWS * 16, td2, !first || st != 0,
                                      if (tap == 2) {
                                          ptx::mma_commit(&hs_empty[sub]);
-                                         if (cc == FF_NCH - 1 && sub == 1) ptx::mma_commit(d2_full);
+                                         if (last && sub == 1) ptx::mma_commit(d2_full);
                                      });
                         }
-                        if (tile_it == 0) FF_TRACE(8 + 12 * cc + 3);
+                        ++n_hs;
+                        if (seg_it == 0) FF_TRACE(8 + 12 * cc + 3);
                     }
                 }
                 ++u2;
-                if (has_p3) {
+                if (seg_p3) {
                     // ---- P3: next block's QKV projection of this half's outputs: tiles 0, 2 → D1[h], tile 1 → D2[h]
-                    ptx::mbar_wait(y_full, tile_it & 1);
+                    ptx::mbar_wait(y_full, n_y & 1);
+                    ++n_y;
                     ptx::tc_fence_after();
                     for (int nt = 0; nt < 3; ++nt) {
                         const bool on_d1 = nt != 1;
@@ -351,10 +445,13 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                         if (on_d1) ++u1; else ++u2;
                     }
                 }
-            }
+                ++seg_it;
+            FF_SEG_END
 #undef FF_STAGE
         }
-    } else if (warp >= FF_EPI_WARP0 && ((warp - FF_EPI_WARP0) >> 3) < halves) {
+    }
+    } else {
+    if (((warp - FF_EPI_WARP0) >> 3) < halves) {
         // ===================== epilogue: 16 warps; (half, channel part, lane quadrant); thread ↔ (row, 64 channels) ==========
         const int e = warp - FF_EPI_WARP0;
         const int h = e >> 3;
@@ -375,8 +472,9 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
         float* my_red = s_red + (h * 2 + part) * 128 + j;
         const float* peer_red = s_red + (h * 2 + (part ^ 1)) * 128 + j;
         const int pair_bar = 1 + h * 4 + lane_grp;                   // named barrier of the two warps that share these 32 rows
+        const int64_t part_off = (int64_t)((h * 2 + part) * 64) * 128 + j;     // this thread's column 0 inside a partial slot
         if (h != 0 || part != 0) tr = nullptr;
-        uint32_t tile_it = 0;
+        uint32_t seg_it = 0, u1 = 0, u2 = 0, n_hs = 0;
         // this part's 64 accumulator columns → registers, then hand the accumulator back to the issuer
 #define FF_LOAD64(v, taddr, full_bar, empty_bar, use)                                                       \
         do {                                                                                                \
@@ -389,26 +487,12 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
             __syncwarp();                                                                                   \
             if (lane == 0) ptx::mbar_arrive(empty_bar);                                                     \
         } while (0)
-        // mean and 1/std of the row from the two parts' partial sums (combined as part 0 + part 1 by both threads)
-#define FF_ROW_STATS(v, part_sum, mean, rstd)                                                               \
-        do {                                                                                                \
-            my_red[0] = (part_sum);                                                                         \
-            ptx::named_bar_sync(pair_bar, 64);                                                              \
-            const float o_ = peer_red[0];                                                                   \
-            mean = (part == 0 ? (part_sum) + o_ : o_ + (part_sum)) * (1.f / 128.f);                         \
-            const float sq_ = ffn_row_sq((v), mean);                                                        \
-            my_red[512] = sq_;                                                                              \
-            ptx::named_bar_sync(pair_bar, 64);                                                              \
-            const float p_ = peer_red[512];                                                                 \
-            rstd = rsqrtf((part == 0 ? sq_ + p_ : p_ + sq_) * (1.f / 128.f) + 1e-5f);                       \
-        } while (0)
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tile_it) {
-            uint32_t u1 = tile_it * d1_uses, u2 = tile_it * d2_uses;
+        FF_SEG_BEGIN
             const int64_t R0 = (int64_t)tile * tile_rows;
             const int64_t sh = R0 + FF_OUT * h - 1 + j;             // stream row of hidden row j
             const bool hid_live = sh >= 0 && sh < total && row_live(p.R, sh, 1);
             const int64_t so = R0 + FF_OUT * h + j;                 // stream row of output row j
-            const bool out_write = j < out_rows && so < total;
+            const bool out_write = owner && j < out_rows && so < total;
             const bool out_live = out_write && row_live(p.R, so, 0);
             const int row_b = out_write ? p.R.row_b[so] : -1;
             const int b_idx = max(row_b, 0);
@@ -419,70 +503,120 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
                 float v[64];
                 FF_LOAD64(v, td2, d2_full, d2_empty, u2);
                 ++u2;
-                if (tile_it == 0) FF_TRACE(6);
-                float psum = 0.f, mean, rstd;
-                if (x_live)
+                if (seg_it == 0) FF_TRACE(6);
+                float psum = 0.f;
+                if (x_live && !(p.exp & 4))
                     psum = ffn_row_add(v, s_bo + 64 * part, reinterpret_cast<const uint8_t*>(p.x_in + ((int64_t)8 * part * p.rows_phys + DX_HALO + sx) * 8),
                                        p.rows_phys * 16);
-                FF_ROW_STATS(v, psum, mean, rstd);
+                my_red[0] = psum;
+                ptx::named_bar_sync(pair_bar, 64);
+                const float o_ = peer_red[0];
+                const float mean = (part == 0 ? psum + o_ : o_ + psum) * (1.f / 128.f);
+                const float sq_ = ffn_row_sq(v, mean);
+                my_red[512] = sq_;
+                ptx::named_bar_sync(pair_bar, 64);
+                const float p_ = peer_red[512];
+                const float rstd = rsqrtf((part == 0 ? sq_ + p_ : p_ + sq_) * (1.f / 128.f) + 1e-5f);
                 ffn_row_store(v, mean, rstd, s_g1 + 64 * part, s_be1 + 64 * part, nullptr, x_live, nullptr, 0,
                               sX + 8 * part * 4096 + (128 * h + j) * 16, 4096);
                 ptx::fence_proxy_async();        // X writes → visible to the tensor core's async proxy
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(x_ready);
             } else {
-                ptx::mbar_wait(x_full, tile_it & 1);                 // residual rows are read from sX in E2
+                ptx::mbar_wait(x_full, seg_it & 1);                  // residual rows are read from sX in E2
             }
-            for (int c = 0; c < FF_NCH; ++c, ++u1) {
+            if (owner && p.film != nullptr && !(p.exp & 16)) {
+                // E2 reads this row's FiLM gamma / beta (2 x 256 B) in pass C, group by group: bring the lines into L1 now
+                const float* fp = p.film + (int64_t)b_idx * p.film_stride + 64 * part;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(fp));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(fp + 32));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(fp + 128));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(fp + 160));
+            }
+            for (int c = a; c <= b; ++c, ++u1, ++n_hs) {
                 // ---- E1(c): this part's 64 hidden channels (= G2's K sub-block `part`)
-                const uint32_t n = tile_it * FF_NCH + c;
                 float v[64];
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 6);
+                if (seg_it == 0) FF_TRACE(8 + 12 * c + 6);
                 FF_LOAD64(v, td1, d1_full, d1_empty, u1);            // D1 is in registers: G1(c+1) may overwrite it
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 7);
-                ptx::mbar_wait(&hs_empty[part], (n & 1) ^ 1);        // G2(c-1, part) has finished reading this buffer
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 8);
+                if (seg_it == 0) FF_TRACE(8 + 12 * c + 7);
+                ptx::mbar_wait(&hs_empty[part], (n_hs & 1) ^ 1);     // G2 of the previous chunk has finished reading this buffer
+                if (seg_it == 0) FF_TRACE(8 + 12 * c + 8);
                 if (!(FF_EXPERIMENT & 4))
                     ffn_e1_store(v, s_b1 + c * 128 + part * 64, hid_live, sHs + (h * 2 + part) * FF_HS_BYTES + j * 16, FF_HS_ROWS * 16);
                 ptx::fence_proxy_async();        // Hs writes → visible to the tensor core's async proxy
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&hs_full[part]);
-                if (tile_it == 0) FF_TRACE(8 + 12 * c + 9);
+                if (seg_it == 0) FF_TRACE(8 + 12 * c + 9);
             }
-            {   // ---- E2: LN epilogue of this half (all G2 MMAs of the half have completed: its Hs buffers are free)
-                float v[64];
-                FF_LOAD64(v, td2, d2_full, d2_empty, u2);
+            {   // ---- E2: the segment's D2 (all its G2 MMAs of the half have completed: the Hs buffers are free)
+                ptx::mbar_wait(d2_full, u2 & 1);
                 ++u2;
-                if (tile_it == 0) FF_TRACE(2);
-                float mean, rstd;
-                const float psum = ffn_row_add(v, s_b2 + 64 * part, sX + 8 * part * 4096 + (FF_OUT * h + j + 2) * 16, 4096);
-                FF_ROW_STATS(v, psum, mean, rstd);
-                ffn_row_store(v, mean, rstd, s_g + 64 * part, s_be + 64 * part,
-                              p.film ? p.film + (int64_t)b_idx * p.film_stride + 64 * part : nullptr, out_live,
-                              out_write ? p.out + ((int64_t)8 * part * p.rows_phys + DX_HALO + so) * 8 : nullptr, p.rows_phys * 8,
-                              has_p3 ? sY + 8 * part * 2048 + j * 16 : nullptr, 2048);
-                if (tile_it == 0) FF_TRACE(3);
+                ptx::tc_fence_after();
+                if (seg_it == 0) FF_TRACE(2);
+                if (!owner) {
+                    // partial sum of chunks a..b → this CTA's slot; published once every epilogue thread has stored
+                    ffn_dump_rolled(td2, p.partial + (int64_t)blockIdx.x * FF_PARTIAL_FLOATS + part_off);
+                    __threadfence();
+                    ptx::named_bar_sync(9, 256 * halves);
+                    if (e == 0 && lane == 0) {
+                        __threadfence();
+                        ff_st_release(p.flags + blockIdx.x, p.epoch);
+                    }
+                } else {
+                    // y = mask(FiLM(LN2(D2 (+ the tile's other segments) + b2 + x1))): the row stays in TMEM (rolled, see
+                    // dx_ffn_epilogue.cuh: the unrolled form took 11-18 k cycles here, mostly instruction fetch)
+                    FfnRowEpi E;
+                    E.taddr = td2;
+                    E.part_base = p.partial + part_off; E.part_slot = FF_PARTIAL_FLOATS; E.k_hi = (int)blockIdx.x - 1; E.n_contrib = 0;
+                    if (a > 0) {
+                        // CTAs i-1, i-2, .. down to the one that holds chunk 0 (fixed order)
+                        int n = 0;
+                        for (int64_t k = (int64_t)blockIdx.x - 1; k >= 0 && (k + 1) * n_groups / ctas > t0; --k, ++n)
+                            if (lane == 0) ff_wait_flag(p.flags + k, p.epoch);
+                        __syncwarp();
+                        E.n_contrib = n;
+                    }
+                    E.bias = s_b2 + 64 * part;
+                    E.res = sX + 8 * part * 4096 + (FF_OUT * h + j + 2) * 16;
+                    E.res_stride = 4096;
+                    E.g = s_g + 64 * part; E.be = s_be + 64 * part;
+                    E.film = (p.film && !(p.exp & 8)) ? p.film + (int64_t)b_idx * p.film_stride + 64 * part : nullptr;
+                    E.live = out_live;
+                    E.out_g = (out_write && !(p.exp & 1)) ? p.out + ((int64_t)8 * part * p.rows_phys + DX_HALO + so) * 8 : nullptr;
+                    E.out_chunk = p.rows_phys * 8;
+                    E.out_s = seg_p3 ? sY + 8 * part * 2048 + j * 16 : nullptr; E.smem_chunk = 2048;
+                    ffn_ln_rolled(E, my_red, peer_red, pair_bar, part);
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(d2_empty);           // the accumulator goes back to the issuer
+                if (seg_it == 0) FF_TRACE(3);
             }
-            if (has_p3) {
+            if (seg_p3) {
                 ptx::fence_proxy_async();            // Y writes → async proxy
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(y_full);
                 const bool in_utt = row_b >= 0;
                 for (int nt = 0; nt < 3; ++nt) {
-                    float v[64];
-                    if (nt != 1) { FF_LOAD64(v, td1, d1_full, d1_empty, u1); ++u1; }
-                    else { FF_LOAD64(v, td2, d2_full, d2_empty, u2); ++u2; }
-                    if (out_write)
-                        ffn_qkv_store(v, s_bq + nt * 128 + 64 * part, in_utt,
-                                      p.qkv_out + ((int64_t)(nt * 16 + 8 * part) * p.rows_phys + DX_HALO + so) * 8, p.rows_phys * 8);
+                    const bool on_d1 = nt != 1;
+                    ptx::mbar_wait(on_d1 ? d1_full : d2_full, (on_d1 ? u1 : u2) & 1);
+                    if (on_d1) ++u1; else ++u2;
+                    ptx::tc_fence_after();
+                    ffn_qkv_rolled(on_d1 ? td1 : td2, s_bq + nt * 128 + 64 * part, in_utt,
+                                   p.qkv_out + ((int64_t)(nt * 16 + 8 * part) * p.rows_phys + DX_HALO + so) * 8, p.rows_phys * 8,
+                                   out_write && !(p.exp & 2));
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(on_d1 ? d1_empty : d2_empty);
                 }
-                if (tile_it == 0) FF_TRACE(7);
+                if (seg_it == 0) FF_TRACE(7);
             }
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(x_empty);
-        }
+            ++seg_it;
+        FF_SEG_END
 #undef FF_LOAD64
-#undef FF_ROW_STATS
+    }
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -494,7 +628,7 @@ __global__ void __launch_bounds__(FF_THREADS, 1) ffn_tc_kernel(const FfnParams p
 }
 
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
-             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse) {
+             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse, const FfnSplit* split) {
     DX_REQUIRE(bw.w_ffn1_bf && bw.w_ffn2_bf, "ffn_bf16: fused-FFN packed weights missing");
     int num_sms = 0;
     DX_TRY(device_sm_count(&num_sms));
@@ -523,16 +657,32 @@ int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, cons
         p.qkv_out = fuse->qkv_out;
     }
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
-    if (p.trace != nullptr && debug_knob(10) > 0) {       // knob 10 = n: trace only every n-th .. launch (n = 1..12 of a step)
+    if (p.trace != nullptr && debug_knob(10) % 100 > 0) {       // knob 10 = n (+ 100: trace the last working CTA): trace only the n-th launch of a step (1..12)
         static int n_traced = 0;
-        if ((n_traced++ % 12) + 1 != debug_knob(10)) p.trace = nullptr;
+        if ((n_traced++ % 12) + 1 != debug_knob(10) % 100) p.trace = nullptr;
     }
+    p.trace_last = debug_knob(10) >= 100;
+    p.exp = debug_knob(15);
     int64_t tiles = (R.cap + FF_OUT1 - 1) / FF_OUT1;     // enough CTAs for the one-half-per-CTA mode of short streams
+    if (split != nullptr && split->partial != nullptr && split->flags != nullptr && !debug_knob(6)) {
+        // split over the hidden dimension: every launch gets its own epoch (flags never have to be cleared between
+        // launches; the caller zeroes them once per pass against stale memory)
+        static std::atomic<uint32_t> g_epoch{0};
+        uint32_t ep = g_epoch.fetch_add(1, std::memory_order_relaxed) + 1;
+        if (ep == 0) ep = g_epoch.fetch_add(1, std::memory_order_relaxed) + 1;
+        p.partial = split->partial; p.flags = split->flags; p.epoch = ep;
+        p.min_units = debug_knob(7) > 0 ? debug_knob(7) : 0;
+        p.split_pct = debug_knob(8) > 0 ? debug_knob(8) : 35;
+        tiles *= FF_NCH;
+    }
     int grid = (int)(tiles < num_sms ? tiles : num_sms);
+    if (grid > FF_MAX_CTAS) grid = FF_MAX_CTAS;
     ProfScope prof(fuse != nullptr && fuse->tag != nullptr ? fuse->tag : "tc_ffn_fused", s);
     DX_LAUNCH_PDL((ffn_tc_kernel), grid, FF_THREADS, FF_SMEM, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }
+
+int64_t ffn_partial_floats() { return (int64_t)FF_MAX_CTAS * FF_PARTIAL_FLOATS; }
 
 }  // namespace dx

@@ -41,8 +41,16 @@ struct FfnFuse {
     __nv_bfloat16* qkv_out;
     const char* tag;            // profiler tag (null: "tc_ffn_fused")
 };
+// split of a tile's hidden dimension across CTAs (stream-K, see dx_ffn_tc.cu): scratch for the partial sums
+// (ffn_partial_floats() floats) and FF_MAX_CTAS flags the caller zeroes once per pass; null = whole tiles per CTA
+constexpr int FF_MAX_CTAS = 160;
+struct FfnSplit {
+    float* partial;
+    uint32_t* flags;
+};
+int64_t ffn_partial_floats();
 int ffn_bf16(const __nv_bfloat16* x, __nv_bfloat16* out, int64_t rows_phys, const DxBlockWeights& bw, const float* film,
-             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse = nullptr);
+             int film_stride, const Rows& R, cudaStream_t s, const FfnFuse* fuse = nullptr, const FfnSplit* split = nullptr);
 
 // dx_style.cu
 int style(const DxModelWeights* w, int B, const float* spk_embs, const float* spk_emb_in, const float* accent,

@@ -62,6 +62,8 @@ int plan_layout(Plan* p, int B, int L_max, int T_max, int mode, void* workspace,
         p->h1b = c.take<__nv_bfloat16>(rp * DX_C);
         p->h2b = c.take<__nv_bfloat16>(rp * DX_C);
         p->melb = c.take<__nv_bfloat16>(rp * DX_MEL_PAD);
+        p->ffn_partial = c.take<float>(ffn_partial_floats());
+        p->ffn_flags = c.take<uint32_t>(FF_MAX_CTAS);
     }
     p->bytes = round_up(c.off, 256);
     if (workspace != nullptr) {
@@ -123,7 +125,8 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
     }
     if (!debug_knob(3)) {
         const float* fp = film ? film + film_block * 256 : nullptr;
-        return ffn_bf16(p.yb, p.xb, rp, bw, fp, 8 * 256, R, s);
+        const FfnSplit sp = p.ffn_split();
+        return ffn_bf16(p.yb, p.xb, rp, bw, fp, 8 * 256, R, s, nullptr, &sp);
     }
     {   // conv1 + ReLU (hidden live one row past the utterance: H1)
         TcGemmArgs g = tc_args(p.yb, rp, DX_D, DX_C, DX_TAPS, bw.w_c1_bf, 256, 32, bw.b_c1, 1, TC_EPI_BF16, 1);
@@ -167,13 +170,17 @@ static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Row
         f.qkv_out = i < 3 ? p.qkvb : nullptr;
         f.tag = tag;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
-        DX_TRY(ffn_bf16(nullptr, nxt, rp, bw, fp, 8 * 256, R, s, &f));
+        const FfnSplit sp = p.ffn_split();
+        DX_TRY(ffn_bf16(nullptr, nxt, rp, bw, fp, 8 * 256, R, s, &f, &sp));
         __nv_bfloat16* t = cur; cur = nxt; nxt = t;
     }
     return 0;
 }
 
-static int zero_plan_halos(const Plan& p, cudaStream_t s) {
+int zero_plan_halos(const Plan& p, cudaStream_t s) {
+    // flags of the fused FFN kernel's hidden-dimension split: every launch publishes under its own epoch, this only guards
+    // against stale memory that happens to hold a future epoch
+    DX_CHECK_CUDA(cudaMemsetAsync(p.ffn_flags, 0, FF_MAX_CTAS * sizeof(uint32_t), s));
     HaloList hl;
     memset(&hl, 0, sizeof(hl));
     __nv_bfloat16* bufs[7] = {p.xb, p.yb, p.ob, p.qkvb, p.h1b, p.h2b, p.melb};

@@ -26,6 +26,10 @@ struct Plan {
     // bf16 mode activations (channel-interleaved [C/8][rows_phys][8])
     __nv_bfloat16 *xb, *yb, *ob, *qkvb, *h1b, *h2b, *melb;
     float* melo;                        // [cap_t][80] fp32 mel projection rows (both modes)
+    // fused FFN kernel, bf16 mode: partial sums + flags of the hidden-dimension split (dx_ffn_tc.cu)
+    float* ffn_partial;
+    uint32_t* ffn_flags;
+    FfnSplit ffn_split() const { return FfnSplit{ffn_partial, ffn_flags}; }
 
     Rows rows_t(const int64_t* lengths) const {
         return Rows{t_row_start, t_row_b, t_row_p, lengths, B, T_max, cap_t};
@@ -38,6 +42,9 @@ struct Plan {
 // workspace == nullptr: only compute sizes.
 int plan_layout(Plan* p, int B, int L_max, int T_max, int mode, void* workspace, int64_t workspace_bytes);
 
+// bf16 mode, once per pass before the first kernel: zero rows around the row range of every channel-interleaved buffer,
+// cleared split flags of the fused FFN kernel
+int zero_plan_halos(const Plan& p, cudaStream_t s);
 int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, const float* frames_energy,
                        const float* frames_pitch, const float* mel_specs, float* accent_emb, cudaStream_t s,
                        bool packed_frames = false);

@@ -19,6 +19,10 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---- register reallocation between warpgroups (4 aligned warps; every warp of the group must execute it) -----------
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---- programmatic dependent launch (PDL) -------------------------------------------------------------------
 // griddep_launch: this CTA allows the next kernel in the stream to start launching (it fires once every CTA of
 // this grid has called it or exited, i.e. when no CTA of this grid is still waiting for an SM).
@@ -53,13 +57,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 // Bounded spin: a protocol bug must not hang the GPU box (a hang is a strike).  ~2^28 polls ≈ seconds.
+// The report-and-trap path is ONE out-of-line function: inlined, its printf argument set-up (~35 instructions and a
+// local-memory buffer) was repeated at each of the hundreds of unrolled wait sites of the tensor-core kernels - 40 KB
+// of the fused FFN kernel's 130 KB of code, enough to push its once-per-tile epilogues out of the instruction cache
+// (ncu: stall_no_inst was the top stall reason of the LayerNorm epilogues).
+static __device__ __noinline__ void mbar_timeout(uint32_t parity) {
+    printf("dx: mbarrier wait timeout (block %d thread %d parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, parity);
+    __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 28)) {
-            printf("dx: mbarrier wait timeout (block %d thread %d parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, parity);
-            __trap();
-        }
+        if (++spins > (1u << 28)) mbar_timeout(parity);
     }
 }
 
@@ -72,10 +81,7 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, 
     uint32_t spins = 0;
     do {
         __nanosleep(ns);
-        if (++spins > (1u << 26)) {
-            printf("dx: mbarrier wait timeout (block %d thread %d parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, parity);
-            __trap();
-        }
+        if (++spins > (1u << 26)) mbar_timeout(parity);
     } while (!mbar_try_wait(bar, parity));
 }
 
@@ -208,6 +214,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
           "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr)
+        : "memory");
+}
+// 16-column variants (rolled epilogues that keep the row in TMEM and visit it group by group)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }

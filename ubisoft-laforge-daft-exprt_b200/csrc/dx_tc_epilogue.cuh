@@ -59,9 +59,9 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
             float sq_lo = 0.f, sq_hi = 0.f;
 #pragma unroll
             for (int i = 0; i < 64; ++i) {
-                const float d0 = v[i] - mean, d1 = v[64 + i] - mean;
-                sq_lo = fmaf(d0, d0, sq_lo);
-                sq_hi = fmaf(d1, d1, sq_hi);
+                const float d0 = __fsub_rn(v[i], mean), d1 = __fsub_rn(v[64 + i], mean);
+                sq_lo = __fmaf_rn(d0, d0, sq_lo);
+                sq_hi = __fmaf_rn(d1, d1, sq_hi);
             }
             const float rstd = rsqrtf((sq_lo + sq_hi) * (1.f / 128.f) + 1e-5f);
             const float* fp = g.film ? g.film + (int64_t)b_idx * g.film_stride : nullptr;
@@ -82,10 +82,8 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
 #pragma unroll
                 for (int e = 0; e < 8; e += 2) {
                     const int i = c * 8 + e;
-                    float y0 = (v[i] - mean) * rstd * gg[e] + ee[e];
-                    float y1 = (v[i + 1] - mean) * rstd * gg[e + 1] + ee[e + 1];
-                    y0 = fg[e] * y0 + fb[e];
-                    y1 = fg[e + 1] * y1 + fb[e + 1];
+                    float y0 = ln_film(v[i], mean, rstd, gg[e], ee[e], fg[e], fb[e]);
+                    float y1 = ln_film(v[i + 1], mean, rstd, gg[e + 1], ee[e + 1], fg[e + 1], fb[e + 1]);
                     if (!live) { y0 = 0.f; y1 = 0.f; }
                     o2[e / 2] = __floats2bfloat162_rn(y0, y1);
                 }
