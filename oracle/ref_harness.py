@@ -131,3 +131,56 @@ def run_reference_generate(model, hp, output_dir, batch=None, **kw):
             return G.generate_mel_specs(model=model, output_dir=output_dir, hparams=hp, vocoder=_ZeroVocoder(), **kw)
     finally:
         torch.Tensor.cuda, G.plot_2d_data = saved_cuda, saved_plot
+
+
+def run_reference_fine_tuning(hp, batches, predictions):
+    """Run the reference's ``fine_tuning`` main loop (``fine_tune.py:22-129``) on the CPU with a stand-in model.
+
+    ``batches``: what its data loader would yield (tuples whose items 11 / 12 are feature_dirs / feature_files);
+    ``predictions[k] = (mel_spec_preds (B, n_mels, T_max) tensor, output_lengths (B,) tensor)`` for batch k.  Only the writer
+    half is under test, so the model, the checkpoint and the loader are replaced; ``librosa.load`` (absent) is replaced by
+    the product's scipy reader for files already at the target rate and ``librosa_mel_fn`` by a constant filter bank (the
+    loop only uses the target mel's shape).  Files land in ``dirname(hp.training_files)/fine_tuning_dataset``."""
+    import numpy as np
+    import torch
+    import_reference_model()
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        import daft_exprt.fine_tune as FT
+        import daft_exprt.extract_features as EF
+    from daft_exprt_b200.fine_tune import default_wav_loader
+
+    class _Model:
+        def __init__(self, *_a, **_k):
+            self.k = -1
+
+        def cuda(self, *_a, **_k):
+            return self
+
+        def load_state_dict(self, *_a, **_k):
+            return None
+
+        def eval(self):
+            return self
+
+        def parse_batch(self, _gpu, batch):
+            self.k += 1
+            return batch, None
+
+        def __call__(self, _inputs):
+            return None, None, None, predictions[self.k], None
+
+    saved = (FT.DaftExprt, FT.prepare_data_loaders, FT.librosa, torch.cuda.set_device, torch.load, EF.librosa_mel_fn)
+    fake_librosa = types.SimpleNamespace(load=lambda path, sr=None: default_wav_loader(path, sr))
+    FT.DaftExprt = _Model
+    FT.prepare_data_loaders = lambda *_a, **_k: (list(batches), None, None, None)
+    FT.librosa = fake_librosa
+    torch.cuda.set_device = lambda *_a, **_k: None
+    torch.load = lambda *_a, **_k: {"state_dict": {}}
+    EF.librosa_mel_fn = lambda sr, n_fft, n_mels, fmin, fmax: np.ones((n_mels, 1 + n_fft // 2), dtype=np.float32)
+    try:
+        FT.fine_tuning(hp)
+    finally:
+        FT.DaftExprt, FT.prepare_data_loaders, FT.librosa, torch.cuda.set_device, torch.load, EF.librosa_mel_fn = saved
+    return os.path.join(os.path.dirname(hp.training_files), "fine_tuning_dataset")
