@@ -524,7 +524,7 @@ def main():
     ap.add_argument("--mode", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the cfg1 / cfg3 / cfg4 blocks")
-    ap.add_argument("--cfg3-utterances", type=int, default=16384)
+    ap.add_argument("--cfg3-utterances", type=int, default=32768)
     ap.add_argument("--no-bind", action="store_true", help="leave the rank on the default CPU affinity")
     args = ap.parse_args()
     if args.impl == "reference":
