@@ -403,26 +403,15 @@ def run_configs(args, model, hp, sd, dev, rank, world, timed, profile_step, sync
 def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
     """BASELINE config 5: the training step (forward + loss + backward, gradient all-reduce over NCCL, Adam) at B = 32
     utterances per GPU drawn as cfg2; weak scaling (each rank its own batch), K steps timed as one region with CUDA
-    events on the launching stream, max over ranks.  fp32 arithmetic (train.TrainEngine)."""
+    events on the launching stream, max over ranks.  Headline: the tensor-core GEMM mode; the all-fp32 parity mode beside it."""
     import torch
     from daft_exprt_b200 import synthetic
     from daft_exprt_b200.train import TrainEngine, flops_per_step, loss_dict
     batch = synthetic.forward_batch(hp, batch=32, lmin=20, lmax=150, seed=42 + 1000 * rank)
     d = tuple(t.to(dev) for t in batch)
     frames = int(batch[9].sum())
-    eng = TrainEngine(hp, sd, device=dev)
     steps, warm = max(5, min(args.steps, 10)), 3
-    for it in range(1, warm + 1):
-        eng.step(d, iteration=it)
-    sync_all()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for it in range(warm + 1, warm + 1 + steps):
-        eng.step(d, iteration=it)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    # the pieces, on rank 0's clock: forward + backward, all-reduce, Adam
+
     def span(fn, n=3):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
@@ -432,27 +421,54 @@ def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
         b.record()
         torch.cuda.synchronize()
         return a.elapsed_time(b) / n
-    ms_fb = span(lambda: eng.forward_backward(d, iteration=100))
-    ms_ar = span(eng.all_reduce_grads) if world > 1 else 0.0
-    ms_fwd = span(lambda: eng.forward_backward(d, iteration=100, forward_only=True))
-    losses = loss_dict(eng.losses)
-    tt = torch.tensor([ms, float(frames)], dtype=torch.float64, device=dev)
-    if world > 1:
-        mx, sm = tt.clone(), tt.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms, tot = float(mx[0]), float(sm[1])
-    else:
-        tot = float(frames)
+
+    def measure(gemm):
+        eng = TrainEngine(hp, sd, device=dev, gemm=gemm)
+        for it in range(1, warm + 1):
+            eng.step(d, iteration=it)
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for it in range(warm + 1, warm + 1 + steps):
+            eng.step(d, iteration=it)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        # the pieces, on this rank's clock: forward + backward, all-reduce, forward + loss alone
+        ms_fb = span(lambda: eng.forward_backward(d, iteration=100))
+        ms_ar = span(eng.all_reduce_grads) if world > 1 else 0.0
+        ms_fwd = span(lambda: eng.forward_backward(d, iteration=100, forward_only=True))
+        losses = loss_dict(eng.losses)
+        tt = torch.tensor([ms, float(frames)], dtype=torch.float64, device=dev)
+        if world > 1:
+            mx, sm = tt.clone(), tt.clone()
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+            ms, tot = float(mx[0]), float(sm[1])
+        else:
+            tot = float(frames)
+        numel = eng.numel
+        del eng
+        torch.cuda.empty_cache()
+        return {"step_ms": ms, "frames_s": tot / (ms * 1e-3), "forward_backward_ms": ms_fb, "forward_loss_ms": ms_fwd,
+                "all_reduce_ms": ms_ar, "all_reduce_bytes": int(numel * 4),
+                "tflops_algorithmic": flops_per_step(batch[5].tolist(), batch[9].tolist()) * world / (ms * 1e-3) / 1e12,
+                "loss_after": losses["loss"]}
+
+    tc = measure("bf16")
+    f32 = measure("fp32")
     if rank != 0:
         return None
+    ms = tc["step_ms"]
     out = {"workload": "cfg5: training step, B=32 per GPU drawn as cfg2 (20-150 symbols), DaftExprt.forward + DaftExprtLoss (energy "
                        "consistency 0.05, pitch consistency off) + backward, dropout = identity, one SUM all-reduce of the flat fp32 "
                        "gradient buffer over NCCL, Adam(0.9, 0.98, eps 1e-9, wd 1e-6)",
-           "scaling": "weak", "dtype": "f32", "step_ms": ms, "frames_s": tot / (ms * 1e-3), "steps": steps, "warmup": warm,
-           "forward_backward_ms": ms_fb, "forward_loss_ms": ms_fwd, "all_reduce_ms": ms_ar, "all_reduce_bytes": int(eng.numel * 4),
-           "tflops_algorithmic": flops_per_step(batch[5].tolist(), batch[9].tolist()) * world / (ms * 1e-3) / 1e12,
-           "loss_after": losses["loss"], "timing": "CUDA events around the timed steps on the launching stream, max over ranks"}
+           "scaling": "weak",
+           "dtype": "bf16 operands on tcgen05 for the conv / linear forward, dgrad and wgrad contractions (fp32 accumulation); fp32 "
+                    "activations, LayerNorm, attention, length regulator, loss, reductions, Adam (TrainEngine(gemm='bf16'))",
+           "steps": steps, "warmup": warm, **tc,
+           "fp32_mode": dict(f32, what="every contraction in fp32 SIMT (TrainEngine(gemm='fp32')): the 1e-3 gradient-parity mode"),
+           "timing": "CUDA events around the timed steps on the launching stream, max over ranks"}
     if world == 1 and not args.no_cpu_baseline:
         # the unmodified reference on this GPU (eager fp32, TF32 off) and on the host cores: forward + loss + backward + Adam
         try:

@@ -179,6 +179,9 @@ int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream);
  * accumulation); the kernels are deterministic.  The data-parallel exchange (DDP's gradient averaging, train.py:269-272) is
  * one all-reduce of the caller's flat gradient buffer between dx_train_step and dx_adam_step.  fp32 arithmetic. */
 #define DX_TRAIN_FORWARD_ONLY 1    /* flags: stop after the loss (validation: train.py:155-209) */
+#define DX_TRAIN_TC_GEMM 2         /* flags: run the large dense contractions (forward convs / linears, their dgrad and wgrad)
+                                      on tcgen05 with bf16 copies of the fp32 operands and fp32 accumulation; everything else
+                                      (LayerNorm, attention, length regulator, loss, reductions, Adam) stays fp32 */
 typedef struct {
     int32_t B, L_max, T_max, flags;
     /* DaftExprt.forward inputs (model.py:893-896), reference layouts */

@@ -139,3 +139,64 @@ def test_step_does_not_depend_on_what_the_workspace_held():
         got.append((losses, eng.grads.clone()))
     assert torch.isfinite(got[1][1]).all()
     assert torch.equal(got[0][0], got[1][0]) and torch.equal(got[0][1], got[1][1])
+
+
+# ---- tensor-core GEMM mode (TrainEngine(gemm="bf16"), DX_TRAIN_TC_GEMM) --------------------------------------------------
+# bf16 operands with fp32 accumulation for the conv / linear forward, dgrad and wgrad contractions; everything else fp32.
+# Gates set from the measured errors (profiles/r02_parity_measured.json: train_tc_*): the loss within 5e-3 relative of
+# the reference's; every one of the 184 gradients within 1.5e-1 relative L1 of the reference's autograd and their median
+# within 3e-2 (bf16 rounding of activations and gradients accumulates through the ~30 contractions of the backward chain:
+# the deepest tensors, the accent pre-net's, carry the largest error).
+TC_LOSS_REL = 5e-3
+TC_GRAD_REL_L1_MAX = 1.5e-1
+TC_GRAD_REL_L1_MEDIAN = 3e-2
+
+
+@pytest.mark.parametrize("kw,iteration,tag", [
+    (dict(batch=4, lmin=5, lmax=30, seed=17), 1234, "B4"),
+    (dict(batch=32, lmin=20, lmax=150, seed=42), 5000, "B32"),
+])
+def test_tensor_core_mode_gradients_against_reference_autograd(kw, iteration, tag):
+    hp = C.hparams()
+    sd = C.state_dict()
+    batch = C.synthetic.forward_batch(hp, **kw)
+    ref_loss, _, ref_grads = TO.reference_step(hp, sd, batch, iteration)
+    eng = TrainEngine(hp, sd, gemm="bf16")
+    losses = loss_dict(eng.forward_backward(tuple(t.cuda() for t in batch), iteration=iteration))
+    assert abs(losses["loss"] - ref_loss) <= TC_LOSS_REL * abs(ref_loss), (losses["loss"], ref_loss)
+    grads = eng.grads_state_dict()
+    rels = []
+    for name, r in ref_grads.items():
+        o = grads[name].cpu()
+        assert torch.isfinite(o).all(), name
+        if r.abs().sum().item() < 1e-6:
+            continue
+        rel = (o - r).abs().sum().item() / r.abs().sum().item()
+        rels.append(rel)
+        assert rel <= TC_GRAD_REL_L1_MAX, f"{name}: rel-L1 {rel:.3e}"
+    rels.sort()
+    C.record(f"train_tc_grad_rel_l1_max_{tag}", rels[-1])
+    C.record(f"train_tc_grad_rel_l1_median_{tag}", rels[len(rels) // 2])
+    C.record(f"train_tc_loss_rel_{tag}", abs(losses["loss"] - ref_loss) / abs(ref_loss))
+    assert rels[len(rels) // 2] <= TC_GRAD_REL_L1_MEDIAN, rels[len(rels) // 2]
+
+
+def test_tensor_core_mode_is_deterministic_workspace_independent_and_learns():
+    hp = C.hparams()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=8, lmin=10, lmax=40, seed=29))
+    got = []
+    for fill in (0x00, 0xFF, 0xFF):
+        eng = TrainEngine(hp, C.state_dict(), gemm="bf16")
+        eng._workspace(batch[0].shape[0], batch[0].shape[1], batch[8].shape[2]).fill_(fill)
+        losses = eng.forward_backward(batch, iteration=1).clone()
+        torch.cuda.synchronize()
+        got.append((losses, eng.grads.clone()))
+    assert torch.isfinite(got[1][1]).all()
+    for other in got[1:]:
+        assert torch.equal(got[0][0], other[0]) and torch.equal(got[0][1], other[1])
+    eng = TrainEngine(hp, C.state_dict(), gemm="bf16")
+    first = None
+    for it in range(1, 11):
+        v = float(eng.step(batch, iteration=it, lr=2e-4)[0])
+        first = v if first is None else first
+    assert v < 0.97 * first, (first, v)

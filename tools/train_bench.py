@@ -21,7 +21,9 @@ def main():
     batch = synthetic.forward_batch(hp, batch=B, lmin=20, lmax=150, seed=42)
     dev = tuple(t.cuda() for t in batch)
     frames = int(batch[9].sum())
-    eng = TrainEngine(hp, sd)
+    mode = sys.argv[2] if len(sys.argv) > 2 else "fp32"
+    eng = TrainEngine(hp, sd, gemm=mode)
+    print("GEMM mode:", mode)
     for it in range(1, 4):
         eng.step(dev, iteration=it)
     torch.cuda.synchronize()

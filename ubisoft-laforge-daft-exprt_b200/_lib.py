@@ -56,6 +56,7 @@ class DxForwardArgs(C.Structure):
 
 
 TRAIN_FORWARD_ONLY = 1
+TRAIN_TC_GEMM = 2
 
 
 class DxTrainArgs(C.Structure):

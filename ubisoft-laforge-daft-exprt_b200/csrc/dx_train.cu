@@ -50,7 +50,36 @@ struct TrainPlan {
     float *dA, *dB, *dC, *dQKV, *dH1, *dH2, *dmel, *Dr, *wt, *scratch;
     float *dfilm, *dlogits, *sv, *gat1, *gat2, *lpart, *dpost_reg, *ct, *gd, *gr, *dpre;
     int64_t scratch_floats;
+    // DX_TRAIN_TC_GEMM: bf16 channel-interleaved copies of a GEMM's operands, packed bf16 weight, row stride of the copies
+    bool tc;
+    __nv_bfloat16 *il_a, *il_g, *w_bf;
+    int64_t rows_phys;
 };
+
+// out = conv(A, W) (+ bias, ReLU, liveness mask): gemm_f32, or - tensor-core mode, K a multiple of 128 - tcgen05 on bf16 copies
+int gemm(const TrainPlan& p, const float* A, int K, const float* W, const float* bias, int N, int taps, bool relu, const Rows& R,
+         int live_ext, float* out, cudaStream_t s) {
+    if (!(p.tc && K % 128 == 0 && N <= 1024 && (taps == 1 || taps == 3)))
+        return gemm_f32(A, K, W, bias, N, taps, relu, R, live_ext, out, s);
+    const int nt = (N % 256 == 0) ? 256 : 128, ks = nt == 256 ? 32 : 64;
+    DX_TRY(rows_to_il(A, K, R, p.il_a, p.rows_phys, s));
+    DX_TRY(pack_weight_bf16(W, taps, K, N, nt, ks, p.w_bf, s));
+    TcGemmArgs g;
+    memset(&g, 0, sizeof(g));
+    g.a = p.il_a; g.a_rows_phys = p.rows_phys; g.K = K; g.N = N; g.taps = taps;
+    g.w = p.w_bf; g.nt = nt; g.ks = ks;
+    g.bias = bias; g.relu = relu ? 1 : 0; g.epilogue = TC_EPI_F32; g.live_ext = live_ext;
+    g.out_f32 = out; g.tag = "tc_gemm_train";
+    return tc_gemm(g, R, s);
+}
+
+// dW[tap][k][n] = sum_r A[r + tap - half][k] G[r][n]: wgrad_f32, or - tensor-core mode, K and N multiples of 128 - wgrad_tc
+int wgrad(const TrainPlan& p, const float* A, int K, const float* G, int N, int taps, const Rows& R, float* dW, cudaStream_t s) {
+    if (!(p.tc && K % 128 == 0 && N % 128 == 0)) return wgrad_f32(A, K, G, N, taps, R, dW, p.scratch, s);
+    DX_TRY(rows_to_il(A, K, R, p.il_a, p.rows_phys, s));
+    DX_TRY(rows_to_il(G, N, R, p.il_g, p.rows_phys, s));
+    return wgrad_tc(p.il_a, K, p.il_g, N, taps, R, p.rows_phys, dW, p.scratch, s);
+}
 
 void carve_stack(Carver& c, StackSave& st, int64_t cap) {
     st.cap = cap;
@@ -117,6 +146,7 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
     sf = max64(sf, ln_bwd_scratch_floats(p->cap, DX_C));
     sf = max64(sf, colsum_scratch_floats(p->cap, DX_C));
     sf = max64(sf, scalar_conv_scratch_floats(p->cap));
+    sf = max64(sf, wgrad_tc_scratch_floats());
     p->scratch_floats = sf;
     p->scratch = c.take<float>(sf);
     p->dfilm = c.take<float>((int64_t)B * 8 * 256);
@@ -130,6 +160,10 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
     p->gd = c.take<float>(p->cap_l * DX_D);
     p->gr = c.take<float>(p->cap_l * DX_D);
     p->dpre = c.take<float>(p->cap_l);
+    p->rows_phys = p->cap + DX_HALO + DX_TAIL;
+    p->il_a = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
+    p->il_g = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
+    p->w_bf = c.take<__nv_bfloat16>((int64_t)DX_TAPS * DX_C * DX_C);
     p->bytes = round_up(c.off, 256);
     if (ws != nullptr) {
         DX_REQUIRE(ws_bytes >= p->bytes, "train plan: workspace of %lld bytes < required %lld", (long long)ws_bytes, (long long)p->bytes);
@@ -141,18 +175,19 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
 inline float* G(const float* p) { return const_cast<float*>(p); }
 
 // ---- forward of one stack with saved activations (FFTBlock.forward x 4, model.py:249-259) -----------------------------
-int stack_forward(const DxBlockWeights* blocks, StackSave& st, const Rows& R, const float* film, int film_block0, cudaStream_t s) {
+int stack_forward(const TrainPlan& p, const DxBlockWeights* blocks, StackSave& st, const Rows& R, const float* film, int film_block0,
+                  cudaStream_t s) {
     for (int i = 0; i < 4; ++i) {
         const DxBlockWeights& bw = blocks[i];
         BlockSave& b = st.blk[i];
         float* y = i < 3 ? st.blk[i + 1].xin : st.out;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
-        DX_TRY(gemm_f32(b.xin, DX_D, bw.w_qkv, bw.b_qkv, 3 * DX_D, 1, false, R, -1, b.qkv, s));
+        DX_TRY(gemm(p, b.xin, DX_D, bw.w_qkv, bw.b_qkv, 3 * DX_D, 1, false, R, -1, b.qkv, s));
         DX_TRY(attention_f32(b.qkv, R, b.o, s, b.lse));
-        DX_TRY(gemm_f32(b.o, DX_D, bw.w_out, bw.b_out, DX_D, 1, false, R, -1, b.t1, s));
+        DX_TRY(gemm(p, b.o, DX_D, bw.w_out, bw.b_out, DX_D, 1, false, R, -1, b.t1, s));
         DX_TRY(ln_rows_f32(b.t1, b.xin, bw.ln1_g, bw.ln1_b, DX_D, nullptr, 0, R, 0, b.x1, s));
-        DX_TRY(gemm_f32(b.x1, DX_D, bw.w_c1, bw.b_c1, DX_C, DX_TAPS, true, R, 1, b.h, s));
-        DX_TRY(gemm_f32(b.h, DX_C, bw.w_c2, bw.b_c2, DX_D, DX_TAPS, false, R, -1, b.t2, s));
+        DX_TRY(gemm(p, b.x1, DX_D, bw.w_c1, bw.b_c1, DX_C, DX_TAPS, true, R, 1, b.h, s));
+        DX_TRY(gemm(p, b.h, DX_C, bw.w_c2, bw.b_c2, DX_D, DX_TAPS, false, R, -1, b.t2, s));
         DX_TRY(ln_rows_f32(b.t2, b.x1, bw.ln2_g, bw.ln2_b, DX_D, fp, 8 * 256, R, 0, y, s));
     }
     return 0;
@@ -162,6 +197,7 @@ int stack_forward(const DxBlockWeights* blocks, StackSave& st, const Rows& R, co
 int dgrad(const TrainPlan& p, const float* dY, int N_out, const float* W, int K_in, int taps, const Rows& R, float* dX,
           const float* addend, cudaStream_t s) {
     DX_TRY(transpose_weight(W, taps, K_in, N_out, p.wt, s));
+    if (addend == nullptr) return gemm(p, dY, N_out, p.wt, nullptr, K_in, taps, false, R, -1, dX, s);
     return gemm_f32(dY, N_out, p.wt, nullptr, K_in, taps, false, R, -1, dX, s, addend);
 }
 
@@ -191,22 +227,22 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
         if (film) DX_TRY(film_bwd(b.t2, b.x1, bw.ln2_g, bw.ln2_b, dy1, dy2, R, dfilm + (film_block0 + i) * 256, 8 * 256, s));
         // conv2 (A = dT2)
         DX_TRY(colsum_rows(A, DX_D, R, G(g.b_c2), p.scratch, s));
-        DX_TRY(wgrad_f32(b.h, DX_C, A, DX_D, DX_TAPS, R, G(g.w_c2), p.scratch, s));
+        DX_TRY(wgrad(p, b.h, DX_C, A, DX_D, DX_TAPS, R, G(g.w_c2), s));
         DX_TRY(dgrad(p, A, DX_D, bw.w_c2, DX_C, DX_TAPS, R, p.dH1, nullptr, s));
         DX_TRY(relu_bwd(p.dH1, b.h, R.cap * DX_C, s));
         // conv1
         DX_TRY(colsum_rows(p.dH1, DX_C, R, G(g.b_c1), p.scratch, s));
-        DX_TRY(wgrad_f32(b.x1, DX_D, p.dH1, DX_C, DX_TAPS, R, G(g.w_c1), p.scratch, s));
+        DX_TRY(wgrad(p, b.x1, DX_D, p.dH1, DX_C, DX_TAPS, R, G(g.w_c1), s));
         DX_TRY(dgrad(p, p.dH1, DX_C, bw.w_c1, DX_D, DX_TAPS, R, Bf, nullptr, s));          // Bf = d x1 through the FFN
         // LN1 + mask: d x1 = Bf + A (residual of the FFN)
         DX_TRY(ln_bwd_rows(b.t1, b.xin, bw.ln1_g, DX_D, nullptr, 0, Bf, A, R, 0, C, G(g.ln1_g), G(g.ln1_b), p.scratch, s));
         // out-proj (C = dT1)
         DX_TRY(colsum_rows(C, DX_D, R, G(g.b_out), p.scratch, s));
-        DX_TRY(wgrad_f32(b.o, DX_D, C, DX_D, 1, R, G(g.w_out), p.scratch, s));
+        DX_TRY(wgrad(p, b.o, DX_D, C, DX_D, 1, R, G(g.w_out), s));
         DX_TRY(dgrad(p, C, DX_D, bw.w_out, DX_D, 1, R, A, nullptr, s));                     // A = dO
         DX_TRY(attention_bwd_f32(b.qkv, b.o, b.lse, A, R, p.Dr, p.dQKV, s));
         DX_TRY(colsum_rows(p.dQKV, 3 * DX_D, R, G(g.b_qkv), p.scratch, s));
-        DX_TRY(wgrad_f32(b.xin, DX_D, p.dQKV, 3 * DX_D, 1, R, G(g.w_qkv), p.scratch, s));
+        DX_TRY(wgrad(p, b.xin, DX_D, p.dQKV, 3 * DX_D, 1, R, G(g.w_qkv), s));
         DX_TRY(dgrad(p, p.dQKV, 3 * DX_D, bw.w_qkv, DX_D, 1, R, Bf, nullptr, s));           // Bf = d x through QKV
         // gradient of the block input = Bf + C (residual of the attention); becomes (dy1, dy2) of block i - 1
         dy1 = Bf; dy2 = C;          // the next block's first LayerNorm backward writes into A, which holds neither
@@ -228,6 +264,8 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_REQUIRE(w.n_speakers >= 1 && w.n_speakers <= 64, "train: n_speakers=%d out of range (1..64)", w.n_speakers);
     DX_TRY(train_layout(&p, a.B, a.L_max, a.T_max, w.n_speakers, a.workspace, a.workspace_bytes));
     DX_REQUIRE(a.workspace != nullptr, "dx_train_step: workspace required");
+    DX_REQUIRE((a.flags & ~(DX_TRAIN_FORWARD_ONLY | DX_TRAIN_TC_GEMM)) == 0, "dx_train_step: unknown flags 0x%x", a.flags);
+    p.tc = (a.flags & DX_TRAIN_TC_GEMM) != 0;
     DX_REQUIRE(a.symbols && a.durations_float && a.durations_int && a.symbols_energy && a.symbols_pitch && a.input_lengths &&
                    a.frames_energy && a.frames_pitch && a.mel_specs && a.output_lengths && a.speaker_ids && a.spk_embs && a.losses,
                "dx_train_step: every input of DaftExprt.forward, speaker_ids and the losses buffer are required");
@@ -243,25 +281,25 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(pack_mel(a.mel_specs, RT, p.melp, nullptr, 0, s));
     DX_TRY(gemm_f32(p.melp, DX_MEL, w.ae_c0_w, w.ae_c0_b, DX_C, DX_TAPS, true, RT, -1, p.a0, s));
     DX_TRY(ln_rows_f32(p.a0, nullptr, w.ae_ln0_g, w.ae_ln0_b, DX_C, nullptr, 0, RT, 2, p.z0, s));
-    DX_TRY(gemm_f32(p.z0, DX_C, w.ae_c1_w, w.ae_c1_b, DX_C, DX_TAPS, true, RT, -1, p.a1, s));
+    DX_TRY(gemm(p, p.z0, DX_C, w.ae_c1_w, w.ae_c1_b, DX_C, DX_TAPS, true, RT, -1, p.a1, s));
     DX_TRY(ln_rows_f32(p.a1, nullptr, w.ae_ln1_g, w.ae_ln1_b, DX_C, nullptr, 0, RT, 1, p.z1, s));
-    DX_TRY(gemm_f32(p.z1, DX_C, w.ae_c2_w, w.ae_c2_b, DX_D, DX_TAPS, true, RT, -1, p.a2, s));
+    DX_TRY(gemm(p, p.z1, DX_C, w.ae_c2_w, w.ae_c2_b, DX_D, DX_TAPS, true, RT, -1, p.a2, s));
     DX_TRY(ln_rows_f32(p.a2, nullptr, w.ae_ln2_g, w.ae_ln2_b, DX_D, nullptr, 0, RT, 0, p.z2, s));
     DX_TRY(accent_input(p.z2, nullptr, a.frames_energy, a.frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w, w.ae_pitch_b,
                         w.pos_table, RT, p.acc.blk[0].xin, nullptr, 0, s));
-    DX_TRY(stack_forward(w.ae_blocks, p.acc, RT, nullptr, 0, s));
+    DX_TRY(stack_forward(p, w.ae_blocks, p.acc, RT, nullptr, 0, s));
     DX_TRY(masked_mean(p.acc.out, nullptr, 0, RT, p.accent, s));
     // conditioning (model.py:904-920)
     DX_TRY(style(&w, B, a.spk_embs, nullptr, p.accent, p.film, p.logits, s));
     // phoneme encoder (model.py:590-610)
     DX_TRY(embed_symbols(a.symbols, w.symbols_embedding, w.n_symbols, w.pos_table, RL, p.enc.blk[0].xin, nullptr, 0, s));
-    DX_TRY(stack_forward(w.pe_blocks, p.enc, RL, p.film, 0, s));
+    DX_TRY(stack_forward(p, w.pe_blocks, p.enc, RL, p.film, 0, s));
     // length regulator (model.py:417-510)
     DX_TRY(lenreg_symbols(p.enc.out, nullptr, 0, RL, a.durations_float, a.symbols_energy, a.symbols_pitch, &w, p.xs, p.sigma, s));
     DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, p.weights, p.dec.blk[0].xin, nullptr, 0, s));
     // frame decoder (model.py:548-564)
-    DX_TRY(stack_forward(w.fd_blocks, p.dec, RT, p.film, 4, s));
-    DX_TRY(gemm_f32(p.dec.out, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
+    DX_TRY(stack_forward(p, w.fd_blocks, p.dec, RT, p.film, 4, s));
+    DX_TRY(gemm(p, p.dec.out, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
     if (a.mel_out) DX_TRY(unpack_mel(p.melo, RT, a.mel_out, s));
 
     // ======================================= loss (loss.py:57-159) ============================================
@@ -274,7 +312,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     const float *g1 = nullptr, *g2 = nullptr;
     // mel projection (model.py:561)
     DX_TRY(colsum_rows(p.dmel, DX_MEL, RT, G(g.mel_b), p.scratch, s));
-    DX_TRY(wgrad_f32(p.dec.out, DX_D, p.dmel, DX_MEL, 1, RT, G(g.mel_w), p.scratch, s));
+    DX_TRY(wgrad(p, p.dec.out, DX_D, p.dmel, DX_MEL, 1, RT, G(g.mel_w), s));
     DX_TRY(dgrad(p, p.dmel, DX_MEL, w.mel_w, DX_D, 1, RT, p.dB, nullptr, s));
     DX_CHECK_CUDA(cudaMemsetAsync(p.dfilm, 0, (size_t)B * 8 * 256 * sizeof(float), s));
     // frame decoder
@@ -325,17 +363,17 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(ln_bwd_rows(p.a2, nullptr, w.ae_ln2_g, DX_D, nullptr, 0, gacc, nullptr, RT, 0, d2, G(g.ae_ln2_g), G(g.ae_ln2_b), p.scratch, s));
     DX_TRY(relu_bwd(d2, p.a2, p.cap_t * DX_D, s));
     DX_TRY(colsum_rows(d2, DX_D, RT, G(g.ae_c2_b), p.scratch, s));
-    DX_TRY(wgrad_f32(p.z1, DX_C, d2, DX_D, DX_TAPS, RT, G(g.ae_c2_w), p.scratch, s));
+    DX_TRY(wgrad(p, p.z1, DX_C, d2, DX_D, DX_TAPS, RT, G(g.ae_c2_w), s));
     DX_TRY(dgrad(p, d2, DX_D, w.ae_c2_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
     DX_TRY(ln_bwd_rows(p.a1, nullptr, w.ae_ln1_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 1, p.dH2, G(g.ae_ln1_g), G(g.ae_ln1_b), p.scratch, s));
     DX_TRY(relu_bwd(p.dH2, p.a1, p.cap_t * DX_C, s));
     DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c1_b), p.scratch, s));
-    DX_TRY(wgrad_f32(p.z0, DX_C, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c1_w), p.scratch, s));
+    DX_TRY(wgrad(p, p.z0, DX_C, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c1_w), s));
     DX_TRY(dgrad(p, p.dH2, DX_C, w.ae_c1_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
     DX_TRY(ln_bwd_rows(p.a0, nullptr, w.ae_ln0_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 2, p.dH2, G(g.ae_ln0_g), G(g.ae_ln0_b), p.scratch, s));
     DX_TRY(relu_bwd(p.dH2, p.a0, p.cap_t * DX_C, s));
     DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c0_b), p.scratch, s));
-    DX_TRY(wgrad_f32(p.melp, DX_MEL, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c0_w), p.scratch, s));
+    DX_TRY(wgrad(p, p.melp, DX_MEL, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c0_w), s));
     return 0;
 }
 

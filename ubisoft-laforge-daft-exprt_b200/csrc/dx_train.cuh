@@ -49,6 +49,12 @@ int post_mult_grad(const float* v, int B, const float* dreg, float* out, cudaStr
 int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps, float wd, int step,
               float gscale, cudaStream_t s);
 
+// dx_train_tc.cu: tensor-core GEMMs of the training step (DX_TRAIN_TC_GEMM)
+int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64_t rows_phys, cudaStream_t s);
+int wgrad_tc(const __nv_bfloat16* a_il, int K, const __nv_bfloat16* g_il, int N, int taps, const Rows& R, int64_t rows_phys, float* dW,
+             float* part, cudaStream_t s);
+int64_t wgrad_tc_scratch_floats();
+
 int64_t train_workspace_bytes(int B, int L_max, int T_max);
 int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTrainArgs& a, cudaStream_t s);
 

@@ -112,9 +112,16 @@ def adversarial_weight(hparams, iteration):
 
 
 class TrainEngine:
-    def __init__(self, hparams, state_dict, device="cuda"):
+    def __init__(self, hparams, state_dict, device="cuda", gemm="fp32"):
+        """``gemm``: "fp32" - every contraction in fp32 SIMT (the 1e-3 gradient-parity mode); "bf16" - the large dense
+        contractions (forward convs / linears, their dgrad and wgrad) on tcgen05 with bf16 copies of the fp32 operands
+        and fp32 accumulation (``DX_TRAIN_TC_GEMM``); LayerNorm, attention, length regulator, loss, reductions and Adam
+        stay fp32 either way."""
         from .model import DaftExprt
         DaftExprt._check_hparams(hparams)
+        if gemm not in ("fp32", "bf16"):
+            raise ValueError("gemm must be 'fp32' or 'bf16'")
+        self.gemm = gemm
         self.hp = hparams
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -210,7 +217,8 @@ class TrainEngine:
                 raise ValueError(f"{n}: expected shape {s}, got {tuple(x.shape)}")
         ws = self._workspace(B, L, T)
         a = _lib.DxTrainArgs()
-        a.B, a.L_max, a.T_max, a.flags = B, L, T, (_lib.TRAIN_FORWARD_ONLY if forward_only else 0)
+        a.B, a.L_max, a.T_max, a.flags = B, L, T, ((_lib.TRAIN_FORWARD_ONLY if forward_only else 0) |
+                                                (_lib.TRAIN_TC_GEMM if self.gemm == "bf16" else 0))
         for name, x in zip(("symbols", "durations_float", "durations_int", "symbols_energy", "symbols_pitch", "input_lengths",
                             "frames_energy", "frames_pitch", "mel_specs", "output_lengths", "speaker_ids", "spk_embs"), t):
             setattr(a, name, x.data_ptr())
