@@ -3,6 +3,7 @@
     python tools/ncu_summary.py launches gpurun_out/launches.csv  > profiles/rNN_launches.txt
     python tools/ncu_summary.py full gpurun_out/prof.ncu-rep      > profiles/rNN_<kernel>_full.txt
     python tools/ncu_summary.py traffic gpurun_out/prof.ncu-rep profiles/rNN_<kernel>_full.txt   # updates profiles/ncu_traffic.json
+    (full / traffic take an optional last argument: keep only launches whose kernel name contains it)
 """
 import csv
 import subprocess
@@ -45,10 +46,19 @@ def launches(path):
         print(f"{k:48s} {v[0]:4d} {v[1]:10.1f} {100 * v[1] / tot:6.1f}%")
 
 
-def full(path):
+def _rows(path, only=None):
+    """Rows of the raw page; `only`: keep launches whose kernel name contains it (a report may hold several kernels);
+    launches without a duration (a capture that was cut short) are dropped."""
     txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(txt.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
+    ik, it = hdr.index("Kernel Name"), hdr.index("gpu__time_duration.sum")
+    data = [r for r in data if (only is None or only in r[ik]) and r[it] not in ("", "nan", "-nan")]
+    return hdr, units, data
+
+
+def full(path, only=None):
+    hdr, units, data = _rows(path, only)
     ik = hdr.index("Kernel Name")
     print(f"# ncu --set full --clock-control none: {len(data)} captured launches of {data[0][ik]}")
     for i, h in enumerate(hdr):
@@ -56,14 +66,12 @@ def full(path):
             print(f"{h:75s} {units[i]:14s} " + "  ".join(r[i] for r in data))
 
 
-def traffic(path, source):
+def traffic(path, source, only=None):
     """DRAM bytes per launch (read + write, averaged over the captured launches) → profiles/ncu_traffic.json,
     which bench.py reports as roofline.traffic."""
     import json
     import os
-    txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-    rows = list(csv.reader(txt.splitlines()))
-    hdr, units, data = rows[0], rows[1], rows[2:]
+    hdr, units, data = _rows(path, only)
     ik, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
     scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     tot = sum(float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]] for r in data)
