@@ -100,7 +100,7 @@ def test_step_is_deterministic_and_adam_equals_torch():
         p_ref.grad = eng.grads.clone()
         opt.step()
         eng.adam(lr)
-        assert (eng.params - p_ref.detach()).abs().max().item() <= 1e-7
+        assert (eng.params - p_ref.detach()).abs().max().item() <= 2.5e-7      # 1-2 ulp at |w| ~ 1
     # the updated weights still export in checkpoint layout and load into the inference mirror
     from daft_exprt_b200.model import DaftExprt
     m = DaftExprt(hp, mode="fp32").cuda()

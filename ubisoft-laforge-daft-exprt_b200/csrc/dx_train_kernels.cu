@@ -224,26 +224,43 @@ int film_bwd(const float* in, const float* res, const float* g, const float* bta
 // =========================================================================================================
 // colsum_rows: part[chunk][n] = sum over the chunk's rows (< total) of in[r][n]; then reduce_partials.
 // =========================================================================================================
-constexpr int CS_ROWS = 256;
+constexpr int CS_ROWS = 128;
 
+// 256 threads = 32 column quads (float4, 128 columns) x 8 row lanes; a row lane adds rows r0 + lane, r0 + lane + 8, ...
+// (16 independent 16-byte loads in flight per thread), the 8 lanes are combined in lane order: a fixed summation order.
 __global__ void __launch_bounds__(256)
 colsum_rows_kernel(const float* __restrict__ in, int N, Rows R, float* __restrict__ part) {
-    __shared__ float s_half[128];
+    __shared__ float4 s_acc[8][32];
     const int64_t total = R.row_start[R.B];
-    const int c = blockIdx.y * 128 + (threadIdx.x & 127), hf = threadIdx.x >> 7;
+    const int q = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = blockIdx.y * 128 + q * 4;
     const int64_t r0 = (int64_t)blockIdx.x * CS_ROWS;
-    float acc = 0.f;
-    if (c < N)
-        for (int k = hf; k < CS_ROWS; k += 2) {
-            const int64_t r = r0 + k;
-            if (r < total) acc += in[r * N + c];
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < N) {
+#pragma unroll
+        for (int k = 0; k < CS_ROWS / 8; ++k) {
+            const int64_t r = r0 + rl + 8 * k;
+            if (r < total) {
+                const float4 v = *reinterpret_cast<const float4*>(in + r * N + c);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
         }
-    if (hf == 1) s_half[threadIdx.x & 127] = acc;
+    }
+    s_acc[rl][q] = acc;
     __syncthreads();
-    if (hf == 0 && c < N) part[(int64_t)blockIdx.x * N + c] = acc + s_half[threadIdx.x];
+    if (rl == 0 && c < N) {
+        float4 t = s_acc[0][q];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) {
+            const float4 v = s_acc[k][q];
+            t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+        }
+        *reinterpret_cast<float4*>(part + (int64_t)blockIdx.x * N + c) = t;
+    }
 }
 
 int colsum_rows(const float* in, int N, const Rows& R, float* out, float* scratch, cudaStream_t s) {
+    DX_REQUIRE(N % 4 == 0, "colsum_rows: N=%d must be a multiple of 4", N);
     const int S = (int)((R.cap + CS_ROWS - 1) / CS_ROWS);
     dim3 grid(S, (N + 127) / 128);
     colsum_rows_kernel<<<grid, 256, 0, s>>>(in, N, R, scratch);
@@ -673,7 +690,7 @@ int add_mask_rows(const float* a, const float* b, const Rows& R, float* out, cud
 
 // Scalar-input conv k=3 (ConvNorm1D(1 -> 128), model.py:402-410,640-646): y[r][c] = b[c] + sum_j w[c][j] x[b, p + j - 1].
 // dW[c][j] = sum_{valid rows} g[r][c] x[b, p + j - 1];  db[c] = sum g[r][c].  part[chunk][128][4] (3 taps + bias).
-constexpr int SC_ROWS = 256;
+constexpr int SC_ROWS = 32;
 __global__ void __launch_bounds__(128)
 scalar_conv_wgrad_kernel(const float* __restrict__ g, const float* __restrict__ x, Rows R, float* __restrict__ part) {
     const int c = threadIdx.x;
@@ -717,16 +734,30 @@ int64_t scalar_conv_scratch_floats(int64_t cap) { return ((cap + SC_ROWS - 1) / 
 // per symbol scans the row stream in order (deterministic); symbols are clamped like embed_symbols clamps them.
 __global__ void __launch_bounds__(128)
 embed_bwd_kernel(const float* __restrict__ g, const int64_t* __restrict__ symbols, int n_symbols, Rows R, float* __restrict__ demb) {
+    __shared__ int s_match[128];
     const int sym = blockIdx.x, c = threadIdx.x;
     const int64_t total = R.row_start[R.B];
     float acc = 0.f;
-    for (int64_t r = 0; r < total; ++r) {
-        const int b = R.row_b[r];
-        const int p = R.row_p[r];
-        if (p >= R.len[b]) continue;
-        long long sv = symbols[(int64_t)b * R.n_max + p];
-        sv = sv < 0 ? 0 : (sv >= n_symbols ? n_symbols - 1 : sv);
-        if ((int)sv == sym) acc += g[r * DX_D + c];
+    // chunks of 128 rows: every thread classifies one row (parallel loads), then all threads add the matching rows of
+    // the chunk in row order (the summation order of the serial scan)
+    for (int64_t r0 = 0; r0 < total; r0 += 128) {
+        const int64_t r = r0 + c;
+        int m = 0;
+        if (r < total) {
+            const int b = R.row_b[r];
+            const int p = R.row_p[r];
+            if (b >= 0 && p < R.len[b] && p < R.n_max) {
+                long long sv = symbols[(int64_t)b * R.n_max + p];
+                sv = sv < 0 ? 0 : (sv >= n_symbols ? n_symbols - 1 : sv);
+                m = (int)sv == sym;
+            }
+        }
+        s_match[c] = m;
+        __syncthreads();
+        const int lim = (int)min((int64_t)128, total - r0);
+        for (int k = 0; k < lim; ++k)
+            if (s_match[k]) acc += g[(r0 + k) * DX_D + c];
+        __syncthreads();
     }
     demb[(int64_t)sym * DX_D + c] = acc;
 }
