@@ -24,8 +24,8 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
-static int g_knobs[16] = {0};
-int debug_knob(int key) { return (key >= 0 && key < 16) ? g_knobs[key] : 0; }
+static int g_knobs[32] = {0};
+int debug_knob(int key) { return (key >= 0 && key < 32) ? g_knobs[key] : 0; }
 static void* g_trace = nullptr;
 static size_t g_trace_bytes = 0;
 void* trace_buffer(size_t min_bytes) { return (g_trace != nullptr && g_trace_bytes >= min_bytes) ? g_trace : nullptr; }
@@ -77,7 +77,7 @@ int dx_version(void) { return 100; }
 const char* dx_last_error_string(void) { return g_error; }
 int64_t dx_launch_count(void) { return g_launches.load(); }
 int dx_set_debug(int key, int value) {
-    if (key < 0 || key >= 16) return 2;
+    if (key < 0 || key >= 32) return 2;
     g_knobs[key] = value;
     return 0;
 }

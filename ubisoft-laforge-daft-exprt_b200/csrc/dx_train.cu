@@ -240,7 +240,15 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
         DX_TRY(colsum_rows(C, DX_D, R, G(g.b_out), p.scratch, s));
         DX_TRY(wgrad(p, b.o, DX_D, C, DX_D, 1, R, G(g.w_out), s));
         DX_TRY(dgrad(p, C, DX_D, bw.w_out, DX_D, 1, R, A, nullptr, s));                     // A = dO
-        DX_TRY(attention_bwd_f32(b.qkv, b.o, b.lse, A, R, p.Dr, p.dQKV, s));
+        if (p.tc && !debug_knob(16)) {
+            // attention backward on tcgen05 (dx_attn_bwd_tc.cu) from bf16 copies of the saved QKV rows and of dO
+            DX_TRY(attn_rowdot(A, b.o, R, p.Dr, s));
+            DX_TRY(rows_to_il(b.qkv, 3 * DX_D, R, p.il_a, p.rows_phys, s));
+            DX_TRY(rows_to_il(A, DX_D, R, p.il_g, p.rows_phys, s));
+            DX_TRY(attention_bwd_tc(p.il_a, p.il_g, p.rows_phys, b.lse, p.Dr, R, p.dQKV, s));
+        } else {
+            DX_TRY(attention_bwd_f32(b.qkv, b.o, b.lse, A, R, p.Dr, p.dQKV, s));
+        }
         DX_TRY(colsum_rows(p.dQKV, 3 * DX_D, R, G(g.b_qkv), p.scratch, s));
         DX_TRY(wgrad(p, b.xin, DX_D, p.dQKV, 3 * DX_D, 1, R, G(g.w_qkv), s));
         DX_TRY(dgrad(p, p.dQKV, 3 * DX_D, bw.w_qkv, DX_D, 1, R, Bf, nullptr, s));           // Bf = d x through QKV

@@ -54,6 +54,10 @@ int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64
 int wgrad_tc(const __nv_bfloat16* a_il, int K, const __nv_bfloat16* g_il, int N, int taps, const Rows& R, int64_t rows_phys, float* dW,
              float* part, cudaStream_t s);
 int64_t wgrad_tc_scratch_floats();
+// dx_attn_bwd_tc.cu: attention backward on tcgen05 from bf16 interleaved copies of QKV and dO
+int attention_bwd_tc(const __nv_bfloat16* qkv_il, const __nv_bfloat16* dO_il, int64_t rows_phys, const float* lse, const float* Dr,
+                     const Rows& R, float* dqkv, cudaStream_t s);
+int attn_rowdot(const float* dO, const float* O, const Rows& R, float* Dr, cudaStream_t s);      // Dr[r][h] = dO[r] . O[r] per head
 
 int64_t train_workspace_bytes(int B, int L_max, int T_max);
 int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTrainArgs& a, cudaStream_t s);

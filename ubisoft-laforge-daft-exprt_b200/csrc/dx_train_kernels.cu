@@ -625,6 +625,12 @@ attn_bwd_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ dO,
     }
 }
 
+int attn_rowdot(const float* dO, const float* O, const Rows& R, float* Dr, cudaStream_t s) {
+    attn_rowdot_kernel<<<(unsigned)((R.cap + 7) / 8), 256, 0, s>>>(dO, O, R, Dr);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
 // dqkv must be zero at rows that are not valid positions (gap rows); the caller memsets it once per call.
 int attention_bwd_f32(const float* qkv, const float* O, const float* lse, const float* dO, const Rows& R, float* Dr, float* dqkv,
                       cudaStream_t s) {
