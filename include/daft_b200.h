@@ -56,7 +56,7 @@ int64_t     dx_launch_count(void);
  * key 7: its fewest hidden chunks per CTA when it splits (default 0 = 2 or 4 by the stream's size);
  * key 8: it splits when whole tiles would occupy at most this percentage of the grid (default 0 = 35; 1000 = always);
  * key 15: its timing experiments (wrong results; bit 0 no E2 stores, 1 no P3 stores, 2 no P0 residual, 3 no FiLM);
- * key 16: training step in tensor-core mode: keep the fp32 attention backward (A/B);
+ * key 16 / 17: training step in tensor-core mode: keep the fp32 attention backward / forward (A/B);
  * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two;
  * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch);
  *         + 100: trace the last working CTA (always a tile owner) instead of CTA 0. */

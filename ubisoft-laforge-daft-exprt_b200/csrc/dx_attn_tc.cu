@@ -44,6 +44,7 @@ struct AtcParams {
     __nv_bfloat16* out;         // attention output [16][rows_phys][8]
     int64_t rows_phys;
     Rows R;
+    float* lse;                 // training: natural-log log-sum-exp of the scaled scores per (row, head), [rows][2], or null
     uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
     long long* trace;           // bring-up: clock64 timeline of CTA (0,0,0) (dx_set_trace_buffer) or null
     int trace_ctas;             // > 0: the buffer also holds [256 + 4 i ..] = (start ns, end ns, SM id, K/V tiles) of CTA i
@@ -332,11 +333,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         const float2 mlA = s_ml[row], mlB = s_ml[128 + row];
         const float m = fmaxf(mlA.x, mlB.x);
         const float wa = ptx::ex2_approx(mlA.x - m), wb = n_kv > 1 ? ptx::ex2_approx(mlB.x - m) : 0.f;
-        const float inv = 1.f / (mlA.y * wa + mlB.y * wb);
+        const float l_tot = mlA.y * wa + mlB.y * wb;
+        const float inv = 1.f / l_tot;
         ptx::mbar_wait(o_done, 0);
         ptx::tc_fence_after();
         const int64_t r = rs + q0 + row;
         const bool row_ok = q0 + row < len;
+        // P = 2^(s sl2 - m) whatever reference m the lazy update kept, so ln sum_k exp(s_k / 8) = m ln 2 + ln l exactly
+        if (p.lse != nullptr && grp == 0 && row_ok) p.lse[r * DX_HEADS + h] = m * 0.6931471805599453f + __logf(l_tot);
         {
             float oa[32], ob[32];
             ptx::tmem_ld32(tm_o + lane_off + 32 * grp, oa);
@@ -397,16 +401,16 @@ int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Row
 }
 
 // out [16][rows_phys][8] = concat_h softmax(Q_h K_h^T / 8) V_h
-int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s) {
+int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s, float* lse) {
     static SmemConfigured configured;
     DX_TRY(ensure_dyn_smem(attention_tc_kernel, ATC_SMEM, configured));
     AtcParams p;
     memset(&p, 0, sizeof(p));
-    p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R;
+    p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R; p.lse = lse;
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
-    if (p.trace != nullptr && debug_knob(10) > 0) {       // knob 10 = n: trace only the n-th attention launch of a step (1..12)
+    if (p.trace != nullptr && debug_knob(10) % 100 > 0) {       // knob 10 = n: trace only the n-th attention launch of a step (1..12)
         static int n_traced = 0;
-        if ((n_traced++ % 12) + 1 != debug_knob(10)) p.trace = nullptr;
+        if ((n_traced++ % 12) + 1 != debug_knob(10) % 100) p.trace = nullptr;
     }
     dim3 grid((unsigned)((R.n_max + ATC_BQ - 1) / ATC_BQ), DX_HEADS, (unsigned)R.B);
     const size_t n_cta = (size_t)grid.x * grid.y * grid.z;

@@ -53,32 +53,43 @@ struct TrainPlan {
     // DX_TRAIN_TC_GEMM: bf16 channel-interleaved copies of a GEMM's operands, packed bf16 weight, row stride of the copies
     bool tc;
     __nv_bfloat16 *il_a, *il_g, *w_bf;
+    float* wpad;                // zero-padded weight / padded weight gradient (widths that are not multiples of 128)
     int64_t rows_phys;
 };
 
-// out = conv(A, W) (+ bias, ReLU, liveness mask): gemm_f32, or - tensor-core mode, K a multiple of 128 - tcgen05 on bf16 copies
+// out = conv(A, W) (+ bias, ReLU, liveness mask): gemm_f32, or - tensor-core mode - tcgen05 on bf16 copies (dx_train_tc.cu).  An input
+// width that is not a multiple of 128 (the 80 mel channels) is zero-padded in the copies.
 int gemm(const TrainPlan& p, const float* A, int K, const float* W, const float* bias, int N, int taps, bool relu, const Rows& R,
          int live_ext, float* out, cudaStream_t s) {
-    if (!(p.tc && K % 128 == 0 && N <= 1024 && (taps == 1 || taps == 3)))
+    if (!(p.tc && K % 4 == 0 && K <= 1024 && N <= 1024 && (taps == 1 || taps == 3)))
         return gemm_f32(A, K, W, bias, N, taps, relu, R, live_ext, out, s);
+    const int Kp = (K + 127) / 128 * 128;
     const int nt = (N % 256 == 0) ? 256 : 128, ks = nt == 256 ? 32 : 64;
-    DX_TRY(rows_to_il(A, K, R, p.il_a, p.rows_phys, s));
-    DX_TRY(pack_weight_bf16(W, taps, K, N, nt, ks, p.w_bf, s));
+    DX_TRY(rows_to_il(A, Kp, R, p.il_a, p.rows_phys, s, K));
+    if (Kp != K) {
+        DX_TRY(copy_pad3(W, taps, K, N, p.wpad, Kp, N, s));
+        W = p.wpad;
+    }
+    DX_TRY(pack_weight_bf16(W, taps, Kp, N, nt, ks, p.w_bf, s));
     TcGemmArgs g;
     memset(&g, 0, sizeof(g));
-    g.a = p.il_a; g.a_rows_phys = p.rows_phys; g.K = K; g.N = N; g.taps = taps;
+    g.a = p.il_a; g.a_rows_phys = p.rows_phys; g.K = Kp; g.N = N; g.taps = taps;
     g.w = p.w_bf; g.nt = nt; g.ks = ks;
     g.bias = bias; g.relu = relu ? 1 : 0; g.epilogue = TC_EPI_F32; g.live_ext = live_ext;
     g.out_f32 = out; g.tag = "tc_gemm_train";
     return tc_gemm(g, R, s);
 }
 
-// dW[tap][k][n] = sum_r A[r + tap - half][k] G[r][n]: wgrad_f32, or - tensor-core mode, K and N multiples of 128 - wgrad_tc
+// dW[tap][k][n] = sum_r A[r + tap - half][k] G[r][n]: wgrad_f32, or - tensor-core mode - wgrad_tc on bf16 copies (widths padded to
+// multiples of 128, the padded gradient cropped afterwards)
 int wgrad(const TrainPlan& p, const float* A, int K, const float* G, int N, int taps, const Rows& R, float* dW, cudaStream_t s) {
-    if (!(p.tc && K % 128 == 0 && N % 128 == 0)) return wgrad_f32(A, K, G, N, taps, R, dW, p.scratch, s);
-    DX_TRY(rows_to_il(A, K, R, p.il_a, p.rows_phys, s));
-    DX_TRY(rows_to_il(G, N, R, p.il_g, p.rows_phys, s));
-    return wgrad_tc(p.il_a, K, p.il_g, N, taps, R, p.rows_phys, dW, p.scratch, s);
+    if (!(p.tc && K % 4 == 0 && N % 4 == 0 && K <= 1024 && N <= 1024)) return wgrad_f32(A, K, G, N, taps, R, dW, p.scratch, s);
+    const int Kp = (K + 127) / 128 * 128, Np = (N + 127) / 128 * 128;
+    DX_TRY(rows_to_il(A, Kp, R, p.il_a, p.rows_phys, s, K));
+    DX_TRY(rows_to_il(G, Np, R, p.il_g, p.rows_phys, s, N));
+    if (Kp == K && Np == N) return wgrad_tc(p.il_a, K, p.il_g, N, taps, R, p.rows_phys, dW, p.scratch, s);
+    DX_TRY(wgrad_tc(p.il_a, Kp, p.il_g, Np, taps, R, p.rows_phys, p.wpad, p.scratch, s));
+    return copy_pad3(p.wpad, taps, Kp, Np, dW, K, N, s);
 }
 
 void carve_stack(Carver& c, StackSave& st, int64_t cap) {
@@ -164,6 +175,7 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
     p->il_a = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
     p->il_g = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
     p->w_bf = c.take<__nv_bfloat16>((int64_t)DX_TAPS * DX_C * DX_C);
+    p->wpad = c.take<float>((int64_t)DX_TAPS * DX_C * DX_C);
     p->bytes = round_up(c.off, 256);
     if (ws != nullptr) {
         DX_REQUIRE(ws_bytes >= p->bytes, "train plan: workspace of %lld bytes < required %lld", (long long)ws_bytes, (long long)p->bytes);
@@ -183,7 +195,14 @@ int stack_forward(const TrainPlan& p, const DxBlockWeights* blocks, StackSave& s
         float* y = i < 3 ? st.blk[i + 1].xin : st.out;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
         DX_TRY(gemm(p, b.xin, DX_D, bw.w_qkv, bw.b_qkv, 3 * DX_D, 1, false, R, -1, b.qkv, s));
-        DX_TRY(attention_f32(b.qkv, R, b.o, s, b.lse));
+        if (p.tc && !debug_knob(17)) {
+            // the inference path's tcgen05 attention on a bf16 copy of the QKV rows; it also writes the log-sum-exp
+            DX_TRY(rows_to_il(b.qkv, 3 * DX_D, R, p.il_a, p.rows_phys, s));
+            DX_TRY(attention_bf16(p.il_a, p.il_g, p.rows_phys, R, s, b.lse));
+            DX_TRY(il_to_rows(p.il_g, DX_D, R, p.rows_phys, b.o, s));
+        } else {
+            DX_TRY(attention_f32(b.qkv, R, b.o, s, b.lse));
+        }
         DX_TRY(gemm(p, b.o, DX_D, bw.w_out, bw.b_out, DX_D, 1, false, R, -1, b.t1, s));
         DX_TRY(ln_rows_f32(b.t1, b.xin, bw.ln1_g, bw.ln1_b, DX_D, nullptr, 0, R, 0, b.x1, s));
         DX_TRY(gemm(p, b.x1, DX_D, bw.w_c1, bw.b_c1, DX_C, DX_TAPS, true, R, 1, b.h, s));
@@ -287,7 +306,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(lenreg_scan(a.durations_int, B, a.L_max, false, nullptr, p.mu, p.out_len, nullptr, s));
     // accent encoder (model.py:679-716)
     DX_TRY(pack_mel(a.mel_specs, RT, p.melp, nullptr, 0, s));
-    DX_TRY(gemm_f32(p.melp, DX_MEL, w.ae_c0_w, w.ae_c0_b, DX_C, DX_TAPS, true, RT, -1, p.a0, s));
+    DX_TRY(gemm(p, p.melp, DX_MEL, w.ae_c0_w, w.ae_c0_b, DX_C, DX_TAPS, true, RT, -1, p.a0, s));
     DX_TRY(ln_rows_f32(p.a0, nullptr, w.ae_ln0_g, w.ae_ln0_b, DX_C, nullptr, 0, RT, 2, p.z0, s));
     DX_TRY(gemm(p, p.z0, DX_C, w.ae_c1_w, w.ae_c1_b, DX_C, DX_TAPS, true, RT, -1, p.a1, s));
     DX_TRY(ln_rows_f32(p.a1, nullptr, w.ae_ln1_g, w.ae_ln1_b, DX_C, nullptr, 0, RT, 1, p.z1, s));

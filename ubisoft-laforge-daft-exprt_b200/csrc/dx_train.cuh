@@ -50,7 +50,9 @@ int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr,
               float gscale, cudaStream_t s);
 
 // dx_train_tc.cu: tensor-core GEMMs of the training step (DX_TRAIN_TC_GEMM)
-int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64_t rows_phys, cudaStream_t s);
+int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64_t rows_phys, cudaStream_t s, int C_src = 0);
+int copy_pad3(const float* src, int T, int Ks, int Ns, float* dst, int Kd, int Nd, cudaStream_t s);
+int il_to_rows(const __nv_bfloat16* src, int C, const Rows& R, int64_t rows_phys, float* dst, cudaStream_t s);
 int wgrad_tc(const __nv_bfloat16* a_il, int K, const __nv_bfloat16* g_il, int N, int taps, const Rows& R, int64_t rows_phys, float* dW,
              float* part, cudaStream_t s);
 int64_t wgrad_tc_scratch_floats();

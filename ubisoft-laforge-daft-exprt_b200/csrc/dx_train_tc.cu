@@ -24,8 +24,8 @@ namespace dx {
 
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-rows_to_il_kernel(const float* __restrict__ src, int C, const int32_t* __restrict__ total_ptr, __nv_bfloat16* __restrict__ dst,
-                  int64_t rows_phys) {
+rows_to_il_kernel(const float* __restrict__ src, int C, int C_src, const int32_t* __restrict__ total_ptr,
+                  __nv_bfloat16* __restrict__ dst, int64_t rows_phys) {
     __shared__ __align__(16) __nv_bfloat16 tile[32][128 + 8];
     const int64_t total = *total_ptr;
     const int64_t pr0 = (int64_t)blockIdx.x * 32;        // physical row of the tile: stream row = physical - DX_HALO
@@ -36,7 +36,7 @@ rows_to_il_kernel(const float* __restrict__ src, int C, const int32_t* __restric
         const int idx = t + i * 256, row = idx >> 5, c4 = idx & 31;
         const int64_t r = pr0 + row - DX_HALO;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r >= 0 && r < total) v = *reinterpret_cast<const float4*>(src + r * C + c0 + c4 * 4);
+        if (r >= 0 && r < total && c0 + c4 * 4 < C_src) v = *reinterpret_cast<const float4*>(src + r * C_src + c0 + c4 * 4);
         __nv_bfloat162* d2 = reinterpret_cast<__nv_bfloat162*>(&tile[row][c4 * 4]);
         d2[0] = __floats2bfloat162_rn(v.x, v.y);
         d2[1] = __floats2bfloat162_rn(v.z, v.w);
@@ -51,12 +51,73 @@ rows_to_il_kernel(const float* __restrict__ src, int C, const int32_t* __restric
     }
 }
 
-int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64_t rows_phys, cudaStream_t s) {
-    DX_REQUIRE(C % 128 == 0, "rows_to_il: C=%d must be a multiple of 128", C);
+// C_src < C: the source rows have C_src channels (a multiple of 4); channels C_src .. C - 1 of the copy are zero
+int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64_t rows_phys, cudaStream_t s, int C_src) {
+    if (C_src <= 0) C_src = C;
+    DX_REQUIRE(C % 128 == 0 && C_src % 4 == 0 && C_src <= C, "rows_to_il: C=%d (multiple of 128), C_src=%d (multiple of 4, <= C)", C, C_src);
     DX_REQUIRE(rows_phys >= R.cap + DX_HALO + DX_TAIL, "rows_to_il: rows_phys too small");
     dim3 grid((unsigned)((rows_phys + 31) / 32), (unsigned)(C / 128));
     ProfScope prof("rows_to_il", s);
-    rows_to_il_kernel<<<grid, 256, 0, s>>>(src, C, R.row_start + R.B, dst, rows_phys);
+    rows_to_il_kernel<<<grid, 256, 0, s>>>(src, C, C_src, R.row_start + R.B, dst, rows_phys);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+// dst[t][k][n] = src[t][k][n] inside the source's extent, 0 outside: zero-pads (Kd >= Ks, Nd >= Ns) or crops a weight tensor
+__global__ void copy_pad3_kernel(const float* __restrict__ src, int Ks, int Ns, float* __restrict__ dst, int Kd, int Nd, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int nn = (int)(i % Nd);
+    const int k = (int)((i / Nd) % Kd);
+    const int t = (int)(i / ((int64_t)Nd * Kd));
+    dst[i] = (k < Ks && nn < Ns) ? src[((int64_t)t * Ks + k) * Ns + nn] : 0.f;
+}
+int copy_pad3(const float* src, int T, int Ks, int Ns, float* dst, int Kd, int Nd, cudaStream_t s) {
+    const int64_t n = (int64_t)T * Kd * Nd;
+    copy_pad3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(src, Ks, Ns, dst, Kd, Nd, n);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
+// il_to_rows: bf16 [C/8][rows_phys][8] -> fp32 [rows][C]; rows that are not valid positions (gap rows, rows beyond the
+// stream) get zeros: the producer (attention) only writes valid rows and the buffer may hold anything elsewhere
+__global__ void __launch_bounds__(256)
+il_to_rows_kernel(const __nv_bfloat16* __restrict__ src, int C, Rows R, int64_t rows_phys, float* __restrict__ dst) {
+    __shared__ __align__(16) __nv_bfloat16 tile[32][128 + 8];
+    const int64_t total = R.row_start[R.B];
+    const int64_t r0 = (int64_t)blockIdx.x * 32;
+    const int c0 = blockIdx.y * 128;
+    const int t = threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int idx = t + i * 256, chunk = idx >> 5, row = idx & 31;
+        *reinterpret_cast<uint4*>(&tile[row][chunk * 8]) =
+            *reinterpret_cast<const uint4*>(src + ((int64_t)(c0 / 8 + chunk) * rows_phys + DX_HALO + r0 + row) * 8);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int idx = t + i * 256, row = idx >> 5, c4 = idx & 31;
+        const int64_t r = r0 + row;
+        if (r >= R.cap) continue;
+        bool ok = r < total;
+        if (ok) {
+            const int b = R.row_b[r];
+            ok = b >= 0 && R.row_p[r] < R.len[b];
+        }
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) {
+            const __nv_bfloat162* s2 = reinterpret_cast<const __nv_bfloat162*>(&tile[row][c4 * 4]);
+            v = make_float4(__low2float(s2[0]), __high2float(s2[0]), __low2float(s2[1]), __high2float(s2[1]));
+        }
+        *reinterpret_cast<float4*>(dst + r * C + c0 + c4 * 4) = v;
+    }
+}
+
+int il_to_rows(const __nv_bfloat16* src, int C, const Rows& R, int64_t rows_phys, float* dst, cudaStream_t s) {
+    DX_REQUIRE(C % 128 == 0, "il_to_rows: C=%d must be a multiple of 128", C);
+    dim3 grid((unsigned)((R.cap + 31) / 32), (unsigned)(C / 128));
+    il_to_rows_kernel<<<grid, 256, 0, s>>>(src, C, R, rows_phys, dst);
     DX_CHECK_LAUNCH();
     return 0;
 }
