@@ -220,6 +220,29 @@ int dgrad(const TrainPlan& p, const float* dY, int N_out, const float* W, int K_
     return gemm_f32(dY, N_out, p.wt, nullptr, K_in, taps, false, R, -1, dX, s, addend);
 }
 
+// Backward of one conv / linear layer y = conv(act, W): dW = wgrad(act, G) and dX = dgrad(G).  In tensor-core mode the bf16 copy
+// of G serves both contractions (B operand of the weight gradient, A operand of the data gradient).
+int conv_bwd(const TrainPlan& p, const float* act, int K, const float* Gr, int N, const float* W, int taps, const Rows& R, float* dW,
+             float* dX, cudaStream_t s) {
+    if (!(p.tc && K % 128 == 0 && N % 128 == 0 && K <= 1024 && N <= 1024)) {
+        DX_TRY(wgrad(p, act, K, Gr, N, taps, R, dW, s));
+        return dgrad(p, Gr, N, W, K, taps, R, dX, nullptr, s);
+    }
+    DX_TRY(rows_to_il(act, K, R, p.il_a, p.rows_phys, s));
+    DX_TRY(rows_to_il(Gr, N, R, p.il_g, p.rows_phys, s));
+    DX_TRY(wgrad_tc(p.il_a, K, p.il_g, N, taps, R, p.rows_phys, dW, p.scratch, s));
+    DX_TRY(transpose_weight(W, taps, K, N, p.wt, s));
+    const int nt = (K % 256 == 0) ? 256 : 128, ks = nt == 256 ? 32 : 64;
+    DX_TRY(pack_weight_bf16(p.wt, taps, N, K, nt, ks, p.w_bf, s));
+    TcGemmArgs g;
+    memset(&g, 0, sizeof(g));
+    g.a = p.il_g; g.a_rows_phys = p.rows_phys; g.K = N; g.N = K; g.taps = taps;
+    g.w = p.w_bf; g.nt = nt; g.ks = ks;
+    g.epilogue = TC_EPI_F32; g.live_ext = -1;
+    g.out_f32 = dX; g.tag = "tc_gemm_train";
+    return tc_gemm(g, R, s);
+}
+
 // ---- backward of one stack.  In: gradient of the stack output = dy1 (+ dy2).  Out: gradient of the stack input = *g1 + *g2
 // (two buffers of the plan; the caller masks and adds them).  Parameter gradients go to gb[i].
 int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlockWeights* gb, const StackSave& st, const Rows& R,
@@ -246,19 +269,16 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
         if (film) DX_TRY(film_bwd(b.t2, b.x1, bw.ln2_g, bw.ln2_b, dy1, dy2, R, dfilm + (film_block0 + i) * 256, 8 * 256, s));
         // conv2 (A = dT2)
         DX_TRY(colsum_rows(A, DX_D, R, G(g.b_c2), p.scratch, s));
-        DX_TRY(wgrad(p, b.h, DX_C, A, DX_D, DX_TAPS, R, G(g.w_c2), s));
-        DX_TRY(dgrad(p, A, DX_D, bw.w_c2, DX_C, DX_TAPS, R, p.dH1, nullptr, s));
+        DX_TRY(conv_bwd(p, b.h, DX_C, A, DX_D, bw.w_c2, DX_TAPS, R, G(g.w_c2), p.dH1, s));
         DX_TRY(relu_bwd(p.dH1, b.h, R.cap * DX_C, s));
         // conv1
         DX_TRY(colsum_rows(p.dH1, DX_C, R, G(g.b_c1), p.scratch, s));
-        DX_TRY(wgrad(p, b.x1, DX_D, p.dH1, DX_C, DX_TAPS, R, G(g.w_c1), s));
-        DX_TRY(dgrad(p, p.dH1, DX_C, bw.w_c1, DX_D, DX_TAPS, R, Bf, nullptr, s));          // Bf = d x1 through the FFN
+        DX_TRY(conv_bwd(p, b.x1, DX_D, p.dH1, DX_C, bw.w_c1, DX_TAPS, R, G(g.w_c1), Bf, s));          // Bf = d x1 through the FFN
         // LN1 + mask: d x1 = Bf + A (residual of the FFN)
         DX_TRY(ln_bwd_rows(b.t1, b.xin, bw.ln1_g, DX_D, nullptr, 0, Bf, A, R, 0, C, G(g.ln1_g), G(g.ln1_b), p.scratch, s));
         // out-proj (C = dT1)
         DX_TRY(colsum_rows(C, DX_D, R, G(g.b_out), p.scratch, s));
-        DX_TRY(wgrad(p, b.o, DX_D, C, DX_D, 1, R, G(g.w_out), s));
-        DX_TRY(dgrad(p, C, DX_D, bw.w_out, DX_D, 1, R, A, nullptr, s));                     // A = dO
+        DX_TRY(conv_bwd(p, b.o, DX_D, C, DX_D, bw.w_out, 1, R, G(g.w_out), A, s));                     // A = dO
         if (p.tc && !debug_knob(16)) {
             // attention backward on tcgen05 (dx_attn_bwd_tc.cu) from bf16 copies of the saved QKV rows and of dO
             DX_TRY(attn_rowdot(A, b.o, R, p.Dr, s));
@@ -269,8 +289,7 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
             DX_TRY(attention_bwd_f32(b.qkv, b.o, b.lse, A, R, p.Dr, p.dQKV, s));
         }
         DX_TRY(colsum_rows(p.dQKV, 3 * DX_D, R, G(g.b_qkv), p.scratch, s));
-        DX_TRY(wgrad(p, b.xin, DX_D, p.dQKV, 3 * DX_D, 1, R, G(g.w_qkv), s));
-        DX_TRY(dgrad(p, p.dQKV, 3 * DX_D, bw.w_qkv, DX_D, 1, R, Bf, nullptr, s));           // Bf = d x through QKV
+        DX_TRY(conv_bwd(p, b.xin, DX_D, p.dQKV, 3 * DX_D, bw.w_qkv, 1, R, G(g.w_qkv), Bf, s));           // Bf = d x through QKV
         // gradient of the block input = Bf + C (residual of the attention); becomes (dy1, dy2) of block i - 1
         dy1 = Bf; dy2 = C;          // the next block's first LayerNorm backward writes into A, which holds neither
     }
@@ -339,8 +358,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     const float *g1 = nullptr, *g2 = nullptr;
     // mel projection (model.py:561)
     DX_TRY(colsum_rows(p.dmel, DX_MEL, RT, G(g.mel_b), p.scratch, s));
-    DX_TRY(wgrad(p, p.dec.out, DX_D, p.dmel, DX_MEL, 1, RT, G(g.mel_w), s));
-    DX_TRY(dgrad(p, p.dmel, DX_MEL, w.mel_w, DX_D, 1, RT, p.dB, nullptr, s));
+    DX_TRY(conv_bwd(p, p.dec.out, DX_D, p.dmel, DX_MEL, w.mel_w, 1, RT, G(g.mel_w), p.dB, s));
     DX_CHECK_CUDA(cudaMemsetAsync(p.dfilm, 0, (size_t)B * 8 * 256 * sizeof(float), s));
     // frame decoder
     DX_TRY(stack_backward(p, w.fd_blocks, g.fd_blocks, p.dec, RT, p.film, p.dfilm, 4, p.dB, nullptr, &g1, &g2, s));
@@ -390,13 +408,11 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(ln_bwd_rows(p.a2, nullptr, w.ae_ln2_g, DX_D, nullptr, 0, gacc, nullptr, RT, 0, d2, G(g.ae_ln2_g), G(g.ae_ln2_b), p.scratch, s));
     DX_TRY(relu_bwd(d2, p.a2, p.cap_t * DX_D, s));
     DX_TRY(colsum_rows(d2, DX_D, RT, G(g.ae_c2_b), p.scratch, s));
-    DX_TRY(wgrad(p, p.z1, DX_C, d2, DX_D, DX_TAPS, RT, G(g.ae_c2_w), s));
-    DX_TRY(dgrad(p, d2, DX_D, w.ae_c2_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
+    DX_TRY(conv_bwd(p, p.z1, DX_C, d2, DX_D, w.ae_c2_w, DX_TAPS, RT, G(g.ae_c2_w), p.dH1, s));
     DX_TRY(ln_bwd_rows(p.a1, nullptr, w.ae_ln1_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 1, p.dH2, G(g.ae_ln1_g), G(g.ae_ln1_b), p.scratch, s));
     DX_TRY(relu_bwd(p.dH2, p.a1, p.cap_t * DX_C, s));
     DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c1_b), p.scratch, s));
-    DX_TRY(wgrad(p, p.z0, DX_C, p.dH2, DX_C, DX_TAPS, RT, G(g.ae_c1_w), s));
-    DX_TRY(dgrad(p, p.dH2, DX_C, w.ae_c1_w, DX_C, DX_TAPS, RT, p.dH1, nullptr, s));
+    DX_TRY(conv_bwd(p, p.z0, DX_C, p.dH2, DX_C, w.ae_c1_w, DX_TAPS, RT, G(g.ae_c1_w), p.dH1, s));
     DX_TRY(ln_bwd_rows(p.a0, nullptr, w.ae_ln0_g, DX_C, nullptr, 0, p.dH1, nullptr, RT, 2, p.dH2, G(g.ae_ln0_g), G(g.ae_ln0_b), p.scratch, s));
     DX_TRY(relu_bwd(p.dH2, p.a0, p.cap_t * DX_C, s));
     DX_TRY(colsum_rows(p.dH2, DX_C, RT, G(g.ae_c0_b), p.scratch, s));
