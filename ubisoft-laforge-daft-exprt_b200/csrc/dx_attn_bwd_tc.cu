@@ -44,6 +44,8 @@ struct AbtParams {
 
 template <bool DQ>
 __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtParams p) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(1024) uint8_t ab_smem[];
     const int b = blockIdx.z, h = blockIdx.y;
     const int len = (int)min((long long)p.R.len[b], (long long)p.R.n_max);
@@ -259,9 +261,9 @@ int attention_bwd_tc(const __nv_bfloat16* qkv_il, const __nv_bfloat16* dO_il, in
     ProfScope prof("attn_bwd_tc", s);
     DX_CHECK_CUDA(cudaMemsetAsync(dqkv, 0, (size_t)R.cap * 384 * sizeof(float), s));
     dim3 grid((unsigned)((R.n_max + 127) / 128), DX_HEADS, (unsigned)R.B);
-    attn_bwd_tc_kernel<true><<<grid, ABT_THREADS, ABT_SMEM, s>>>(p);
+    DX_LAUNCH_PDL((attn_bwd_tc_kernel<true>), grid, ABT_THREADS, ABT_SMEM, s, p);
     DX_CHECK_LAUNCH();
-    attn_bwd_tc_kernel<false><<<grid, ABT_THREADS, ABT_SMEM, s>>>(p);
+    DX_LAUNCH_PDL((attn_bwd_tc_kernel<false>), grid, ABT_THREADS, ABT_SMEM, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -2,6 +2,7 @@
 // flash-style masked multi-head attention.  These back DX_MODE_F32, whose gate is mel max-abs <= 1e-3 against
 // the reference CPU forward (TF32 tensor-core inputs miss that gate: SURVEY.md §7.3 H2).
 #include "dx_common.cuh"
+#include "dx_ptx.cuh"
 #include "dx_kernels.cuh"
 
 namespace dx {
@@ -16,6 +17,8 @@ constexpr int GF_BM = 128, GF_BN = 64, GF_BK = 16;
 __global__ void __launch_bounds__(256)
 gemm_f32_kernel(const float* __restrict__ A, int K, const float* __restrict__ W, const float* __restrict__ bias,
                 int N, int taps, int relu, Rows R, int live_ext, float* __restrict__ out, const float* __restrict__ addend) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) float As[2][GF_BK][GF_BM + 4];
     __shared__ __align__(16) float Bs[2][GF_BK][GF_BN];
     const int64_t total = R.row_start[R.B];
@@ -123,7 +126,7 @@ int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, in
     DX_REQUIRE(K % GF_BK == 0 && N % 4 == 0, "gemm_f32: K=%d must be a multiple of 16 and N=%d of 4", K, N);
     dim3 grid((unsigned)(R.cap / GF_BM), (unsigned)((N + GF_BN - 1) / GF_BN));
     ProfScope prof("gemm_f32", s);
-    gemm_f32_kernel<<<grid, 256, 0, s>>>(A, K, W, bias, N, taps, relu ? 1 : 0, R, live_ext, out, addend);
+    DX_LAUNCH_PDL((gemm_f32_kernel), grid, 256, 0, s, A, K, W, bias, N, taps, relu ? 1 : 0, R, live_ext, out, addend);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -139,6 +142,8 @@ __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __
                                    const float* __restrict__ g, const float* __restrict__ bta,
                                    const float* __restrict__ film, int film_stride, Rows R, int live_ext,
                                    float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     constexpr int V = C / 128;  // float4 per lane
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -197,9 +202,9 @@ int ln_rows_f32(const float* in, const float* res, const float* g, const float* 
     int grid = (int)((R.cap + 7) / 8);
     ProfScope prof("ln_rows_f32", s);
     if (C == 128)
-        ln_rows_f32_kernel<128><<<grid, 256, 0, s>>>(in, res, g, b, film, film_stride, R, live_ext, out);
+        DX_LAUNCH_PDL((ln_rows_f32_kernel<128>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out);
     else if (C == 1024)
-        ln_rows_f32_kernel<1024><<<grid, 256, 0, s>>>(in, res, g, b, film, film_stride, R, live_ext, out);
+        DX_LAUNCH_PDL((ln_rows_f32_kernel<1024>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out);
     else
         DX_REQUIRE(false, "ln_rows_f32: unsupported width %d", C);
     DX_CHECK_LAUNCH();
@@ -217,6 +222,8 @@ constexpr int AT_Q = 64, AT_K = 64;
 
 __global__ void __launch_bounds__(256)
 attention_f32_kernel(const float* __restrict__ qkv, Rows R, float* __restrict__ out, float* __restrict__ lse) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(16) float smem[];
     float(*Qt)[AT_Q] = reinterpret_cast<float(*)[AT_Q]>(smem);                          // [64 d][64 q]
     float(*Kt)[AT_K + 1] = reinterpret_cast<float(*)[AT_K + 1]>(smem + 64 * AT_Q);      // [64 d][65]
@@ -346,7 +353,7 @@ int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s, f
     DX_TRY(ensure_dyn_smem(attention_f32_kernel, (size_t)AT_SMEM, configured));
     dim3 grid((unsigned)((R.n_max + AT_Q - 1) / AT_Q), DX_HEADS, (unsigned)R.B);
     ProfScope prof("attn_f32", s);
-    attention_f32_kernel<<<grid, 256, AT_SMEM, s>>>(qkv, R, out, lse);
+    DX_LAUNCH_PDL((attention_f32_kernel), grid, 256, AT_SMEM, s, qkv, R, out, lse);
     DX_CHECK_LAUNCH();
     return 0;
 }

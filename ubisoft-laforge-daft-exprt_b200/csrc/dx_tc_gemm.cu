@@ -264,6 +264,8 @@ int64_t packed_weight_elems(int taps, int K, int N, int nt, int ks) {
 
 __global__ void pack_weight_kernel(const float* __restrict__ w, int taps, int K, int N, int nt, int ks,
                                    __nv_bfloat16* __restrict__ out, int64_t n_elems) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_elems) return;
     const int kc = ks / 8, nks = K / ks;
@@ -283,7 +285,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int taps, int K,
 int pack_weight_bf16(const float* w, int taps, int K, int N, int nt, int ks, __nv_bfloat16* out, cudaStream_t s) {
     const int64_t n = packed_weight_elems(taps, K, N, nt, ks);
     DX_REQUIRE(n > 0, "pack_weight_bf16: bad shape taps=%d K=%d N=%d nt=%d ks=%d", taps, K, N, nt, ks);
-    pack_weight_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(w, taps, K, N, nt, ks, out, n);
+    DX_LAUNCH_PDL((pack_weight_kernel), (int)((n + 255) / 256), 256, 0, s, w, taps, K, N, nt, ks, out, n);
     DX_CHECK_LAUNCH();
     return 0;
 }

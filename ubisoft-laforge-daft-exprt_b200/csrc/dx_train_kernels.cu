@@ -17,6 +17,7 @@
 #include <math.h>
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
+#include "dx_ptx.cuh"
 #include "dx_train.cuh"
 
 namespace dx {
@@ -36,6 +37,8 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
                    const float* __restrict__ film, int film_stride, const float* __restrict__ dy1,
                    const float* __restrict__ dy2, Rows R, int live_ext, float* __restrict__ dv,
                    float* __restrict__ part) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     constexpr int V = C / 128;
     __shared__ __align__(16) float s_acc[2 * C];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -126,6 +129,8 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
 // part [S][n] -> out[n] = scale * sum_s part[s][n] (s ascending); S_valid chunks carry data when `total_rows` is given
 __global__ void reduce_partials_kernel(const float* __restrict__ part, int S, int64_t n, float* __restrict__ out,
                                        const int32_t* __restrict__ total_rows, int chunk_rows, float scale) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int s_lim = S;
@@ -140,7 +145,7 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int S, in
 
 int reduce_partials(const float* part, int S, int64_t n, float* out, const int32_t* total_rows, int chunk_rows, float scale,
                     cudaStream_t s) {
-    reduce_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(part, S, n, out, total_rows, chunk_rows, scale);
+    DX_LAUNCH_PDL((reduce_partials_kernel), (unsigned)((n + 255) / 256), 256, 0, s, part, S, n, out, total_rows, chunk_rows, scale);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -150,9 +155,9 @@ int ln_bwd_rows(const float* in, const float* res, const float* g, int C, const 
     const int S = (int)((R.cap + LNB_ROWS - 1) / LNB_ROWS);
     ProfScope prof("ln_bwd", s);
     if (C == 128)
-        ln_bwd_rows_kernel<128><<<S, 256, 0, s>>>(in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
+        DX_LAUNCH_PDL((ln_bwd_rows_kernel<128>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
     else if (C == 1024)
-        ln_bwd_rows_kernel<1024><<<S, 256, 0, s>>>(in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
+        DX_LAUNCH_PDL((ln_bwd_rows_kernel<1024>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
     else
         DX_REQUIRE(false, "ln_bwd_rows: unsupported width %d", C);
     DX_CHECK_LAUNCH();
@@ -172,6 +177,8 @@ __global__ void __launch_bounds__(256)
 film_bwd_kernel(const float* __restrict__ in, const float* __restrict__ res, const float* __restrict__ g,
                 const float* __restrict__ bta, const float* __restrict__ dy1, const float* __restrict__ dy2, Rows R,
                 float* __restrict__ dfilm, int film_stride) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) float s_acc[256];
     const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int len = (int)min((long long)R.len[b], (long long)R.n_max);
@@ -216,7 +223,7 @@ film_bwd_kernel(const float* __restrict__ in, const float* __restrict__ res, con
 
 int film_bwd(const float* in, const float* res, const float* g, const float* bta, const float* dy1, const float* dy2,
              const Rows& R, float* dfilm, int film_stride, cudaStream_t s) {
-    film_bwd_kernel<<<R.B, 256, 0, s>>>(in, res, g, bta, dy1, dy2, R, dfilm, film_stride);
+    DX_LAUNCH_PDL((film_bwd_kernel), R.B, 256, 0, s, in, res, g, bta, dy1, dy2, R, dfilm, film_stride);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -230,6 +237,8 @@ constexpr int CS_ROWS = 128;
 // (16 independent 16-byte loads in flight per thread), the 8 lanes are combined in lane order: a fixed summation order.
 __global__ void __launch_bounds__(256)
 colsum_rows_kernel(const float* __restrict__ in, int N, Rows R, float* __restrict__ part) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ float4 s_acc[8][32];
     const int64_t total = R.row_start[R.B];
     const int q = threadIdx.x & 31, rl = threadIdx.x >> 5;
@@ -263,7 +272,7 @@ int colsum_rows(const float* in, int N, const Rows& R, float* out, float* scratc
     DX_REQUIRE(N % 4 == 0, "colsum_rows: N=%d must be a multiple of 4", N);
     const int S = (int)((R.cap + CS_ROWS - 1) / CS_ROWS);
     dim3 grid(S, (N + 127) / 128);
-    colsum_rows_kernel<<<grid, 256, 0, s>>>(in, N, R, scratch);
+    DX_LAUNCH_PDL((colsum_rows_kernel), grid, 256, 0, s, in, N, R, scratch);
     DX_CHECK_LAUNCH();
     return reduce_partials(scratch, S, N, out, R.row_start + R.B, CS_ROWS, 1.f, s);
 }
@@ -279,6 +288,8 @@ constexpr int WG_ROWS = 1024, WG_BR = 16;
 __global__ void __launch_bounds__(256)
 wgrad_f32_kernel(const float* __restrict__ A, int K, const float* __restrict__ G, int N, int taps, Rows R,
                  float* __restrict__ part) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) float As[WG_BR][128];
     __shared__ __align__(16) float Gs[WG_BR][128];
     const int64_t total = R.row_start[R.B];
@@ -349,7 +360,7 @@ int wgrad_f32(const float* A, int K, const float* G, int N, int taps, const Rows
     const int S = (int)((R.cap + WG_ROWS - 1) / WG_ROWS);
     dim3 grid((N + 127) / 128, (K + 127) / 128, S * taps);
     ProfScope prof("wgrad_f32", s);
-    wgrad_f32_kernel<<<grid, 256, 0, s>>>(A, K, G, N, taps, R, scratch);
+    DX_LAUNCH_PDL((wgrad_f32_kernel), grid, 256, 0, s, A, K, G, N, taps, R, scratch);
     DX_CHECK_LAUNCH();
     return reduce_partials(scratch, S, (int64_t)taps * K * N, dW, R.row_start + R.B, WG_ROWS, 1.f, s);
 }
@@ -357,6 +368,8 @@ int64_t wgrad_scratch_floats(int64_t cap, int K, int N, int taps) { return ((cap
 
 // dgrad weight: Wt[taps - 1 - j][n][k] = W[j][k][n]
 __global__ void transpose_weight_kernel(const float* __restrict__ W, int taps, int K, int N, float* __restrict__ Wt) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ float tile[32][33];
     const int j = blockIdx.z;
     const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
@@ -374,12 +387,14 @@ __global__ void transpose_weight_kernel(const float* __restrict__ W, int taps, i
 
 int transpose_weight(const float* W, int taps, int K, int N, float* Wt, cudaStream_t s) {
     dim3 grid((N + 31) / 32, (K + 31) / 32, taps);
-    transpose_weight_kernel<<<grid, 256, 0, s>>>(W, taps, K, N, Wt);
+    DX_LAUNCH_PDL((transpose_weight_kernel), grid, 256, 0, s, W, taps, K, N, Wt);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 __global__ void relu_bwd_kernel(float* __restrict__ d, const float* __restrict__ act, int64_t n4) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n4) return;
     float4 g = reinterpret_cast<float4*>(d)[i];
@@ -389,7 +404,7 @@ __global__ void relu_bwd_kernel(float* __restrict__ d, const float* __restrict__
 }
 
 int relu_bwd(float* d, const float* act, int64_t n, cudaStream_t s) {
-    relu_bwd_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, s>>>(d, act, n / 4);
+    DX_LAUNCH_PDL((relu_bwd_kernel), (unsigned)((n / 4 + 255) / 256), 256, 0, s, d, act, n / 4);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -402,6 +417,8 @@ int relu_bwd(float* d, const float* act, int64_t n, cudaStream_t s) {
 // attn_bwd_dkv: one CTA per (utterance, head, 64-key tile), loops over query tiles.  Both recompute S and P.
 // =========================================================================================================
 __global__ void attn_rowdot_kernel(const float* __restrict__ dO, const float* __restrict__ O, Rows R, float* __restrict__ Dr) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -419,6 +436,8 @@ constexpr int AB_DQ_SMEM = (4 * 64 * 64 + 2 * 64 * 65 + 64 * 68) * (int)sizeof(f
 __global__ void __launch_bounds__(256)
 attn_bwd_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ dO, const float* __restrict__ lse,
                    const float* __restrict__ Dr, Rows R, float* __restrict__ dqkv) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(16) float ab_smem[];
     float(*Qt)[64] = reinterpret_cast<float(*)[64]>(ab_smem);                 // [d][q], pre-scaled
     float(*dOt)[64] = reinterpret_cast<float(*)[64]>(ab_smem + 64 * 64);      // [d][q]
@@ -520,6 +539,8 @@ constexpr int AB_DKV_SMEM = (2 * 64 * 64 + 2 * 64 * 65 + 2 * 64 * 64 + 2 * 64 * 
 __global__ void __launch_bounds__(256)
 attn_bwd_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ dO, const float* __restrict__ lse,
                     const float* __restrict__ Dr, Rows R, float* __restrict__ dqkv) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(16) float ab_smem[];
     float(*Qt)[64] = reinterpret_cast<float(*)[64]>(ab_smem);                       // [d][q], pre-scaled
     float(*dOt)[64] = reinterpret_cast<float(*)[64]>(ab_smem + 64 * 64);            // [d][q]
@@ -626,7 +647,7 @@ attn_bwd_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ dO,
 }
 
 int attn_rowdot(const float* dO, const float* O, const Rows& R, float* Dr, cudaStream_t s) {
-    attn_rowdot_kernel<<<(unsigned)((R.cap + 7) / 8), 256, 0, s>>>(dO, O, R, Dr);
+    DX_LAUNCH_PDL((attn_rowdot_kernel), (unsigned)((R.cap + 7) / 8), 256, 0, s, dO, O, R, Dr);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -639,12 +660,12 @@ int attention_bwd_f32(const float* qkv, const float* O, const float* lse, const 
     DX_TRY(ensure_dyn_smem(attn_bwd_dkv_kernel, (size_t)AB_DKV_SMEM, c2));
     ProfScope prof("attn_bwd", s);
     DX_CHECK_CUDA(cudaMemsetAsync(dqkv, 0, (size_t)R.cap * 384 * sizeof(float), s));
-    attn_rowdot_kernel<<<(unsigned)((R.cap + 7) / 8), 256, 0, s>>>(dO, O, R, Dr);
+    DX_LAUNCH_PDL((attn_rowdot_kernel), (unsigned)((R.cap + 7) / 8), 256, 0, s, dO, O, R, Dr);
     DX_CHECK_LAUNCH();
     dim3 grid((unsigned)((R.n_max + AB_T - 1) / AB_T), DX_HEADS, (unsigned)R.B);
-    attn_bwd_dq_kernel<<<grid, 256, AB_DQ_SMEM, s>>>(qkv, dO, lse, Dr, R, dqkv);
+    DX_LAUNCH_PDL((attn_bwd_dq_kernel), grid, 256, AB_DQ_SMEM, s, qkv, dO, lse, Dr, R, dqkv);
     DX_CHECK_LAUNCH();
-    attn_bwd_dkv_kernel<<<grid, 256, AB_DKV_SMEM, s>>>(qkv, dO, lse, Dr, R, dqkv);
+    DX_LAUNCH_PDL((attn_bwd_dkv_kernel), grid, 256, AB_DKV_SMEM, s, qkv, dO, lse, Dr, R, dqkv);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -654,6 +675,8 @@ int attention_bwd_f32(const float* qkv, const float* O, const float* lse, const 
 // =========================================================================================================
 // masked mean pool backward (model.py:714): dx[r] = daccent[b] / len[b] at valid rows, 0 elsewhere
 __global__ void masked_mean_bwd_kernel(const float* __restrict__ dacc, Rows R, float* __restrict__ dx) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -667,13 +690,15 @@ __global__ void masked_mean_bwd_kernel(const float* __restrict__ dacc, Rows R, f
     reinterpret_cast<float4*>(dx + r * DX_D)[lane] = v;
 }
 int masked_mean_bwd(const float* dacc, const Rows& R, float* dx, cudaStream_t s) {
-    masked_mean_bwd_kernel<<<(unsigned)((R.cap + 7) / 8), 256, 0, s>>>(dacc, R, dx);
+    DX_LAUNCH_PDL((masked_mean_bwd_kernel), (unsigned)((R.cap + 7) / 8), 256, 0, s, dacc, R, dx);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // out[r] = (a[r] + b[r]) at valid rows (p < len), 0 elsewhere: the pad mask of a stack input (model.py:604,706,557)
 __global__ void add_mask_rows_kernel(const float* __restrict__ a, const float* __restrict__ b2, Rows R, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= R.cap) return;
@@ -689,7 +714,7 @@ __global__ void add_mask_rows_kernel(const float* __restrict__ a, const float* _
     reinterpret_cast<float4*>(out + r * DX_D)[lane] = v;
 }
 int add_mask_rows(const float* a, const float* b, const Rows& R, float* out, cudaStream_t s) {
-    add_mask_rows_kernel<<<(unsigned)((R.cap + 7) / 8), 256, 0, s>>>(a, b, R, out);
+    DX_LAUNCH_PDL((add_mask_rows_kernel), (unsigned)((R.cap + 7) / 8), 256, 0, s, a, b, R, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -699,6 +724,8 @@ int add_mask_rows(const float* a, const float* b, const Rows& R, float* out, cud
 constexpr int SC_ROWS = 32;
 __global__ void __launch_bounds__(128)
 scalar_conv_wgrad_kernel(const float* __restrict__ g, const float* __restrict__ x, Rows R, float* __restrict__ part) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int c = threadIdx.x;
     const int64_t r0 = (int64_t)blockIdx.x * SC_ROWS;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, ab = 0.f;
@@ -720,17 +747,19 @@ scalar_conv_wgrad_kernel(const float* __restrict__ g, const float* __restrict__ 
     o[0] = a0; o[1] = a1; o[2] = a2; o[3] = ab;
 }
 __global__ void scalar_conv_split_kernel(const float* __restrict__ red, float* __restrict__ dw, float* __restrict__ db) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int c = threadIdx.x;
     dw[c * 3 + 0] = red[c * 4 + 0]; dw[c * 3 + 1] = red[c * 4 + 1]; dw[c * 3 + 2] = red[c * 4 + 2];
     db[c] = red[c * 4 + 3];
 }
 int scalar_conv_wgrad(const float* g, const float* x, const Rows& R, float* dw, float* db, float* scratch, cudaStream_t s) {
     const int S = (int)((R.cap + SC_ROWS - 1) / SC_ROWS);
-    scalar_conv_wgrad_kernel<<<S, 128, 0, s>>>(g, x, R, scratch);
+    DX_LAUNCH_PDL((scalar_conv_wgrad_kernel), S, 128, 0, s, g, x, R, scratch);
     DX_CHECK_LAUNCH();
     float* red = scratch + (int64_t)S * DX_D * 4;
     DX_TRY(reduce_partials(scratch, S, DX_D * 4, red, nullptr, 0, 1.f, s));
-    scalar_conv_split_kernel<<<1, 128, 0, s>>>(red, dw, db);
+    DX_LAUNCH_PDL((scalar_conv_split_kernel), 1, 128, 0, s, red, dw, db);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -740,6 +769,8 @@ int64_t scalar_conv_scratch_floats(int64_t cap) { return ((cap + SC_ROWS - 1) / 
 // per symbol scans the row stream in order (deterministic); symbols are clamped like embed_symbols clamps them.
 __global__ void __launch_bounds__(128)
 embed_bwd_kernel(const float* __restrict__ g, const int64_t* __restrict__ symbols, int n_symbols, Rows R, float* __restrict__ demb) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ int s_match[128];
     const int sym = blockIdx.x, c = threadIdx.x;
     const int64_t total = R.row_start[R.B];
@@ -768,7 +799,7 @@ embed_bwd_kernel(const float* __restrict__ g, const int64_t* __restrict__ symbol
     demb[(int64_t)sym * DX_D + c] = acc;
 }
 int embed_bwd(const float* g, const int64_t* symbols, int n_symbols, const Rows& R, float* demb, cudaStream_t s) {
-    embed_bwd_kernel<<<n_symbols, 128, 0, s>>>(g, symbols, n_symbols, R, demb);
+    DX_LAUNCH_PDL((embed_bwd_kernel), n_symbols, 128, 0, s, g, symbols, n_symbols, R, demb);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -776,6 +807,8 @@ int embed_bwd(const float* g, const int64_t* symbols, int n_symbols, const Rows&
 // dW[n][k] = sum_b dOut[b][n] In[b][k],  db[n] = sum_b dOut[b][n]   (nn.Linear in torch layout [out][in]; B utterances)
 __global__ void outer_wgrad_kernel(const float* __restrict__ dOut, int N, const float* __restrict__ In, int K, int B,
                                    float* __restrict__ dW, float* __restrict__ db) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < (int64_t)N * K) {
         const int n = (int)(i / K), k = (int)(i % K);
@@ -790,7 +823,7 @@ __global__ void outer_wgrad_kernel(const float* __restrict__ dOut, int N, const 
     }
 }
 int outer_wgrad(const float* dOut, int N, const float* In, int K, int B, float* dW, float* db, cudaStream_t s) {
-    outer_wgrad_kernel<<<(unsigned)(((int64_t)N * K + 255) / 256), 256, 0, s>>>(dOut, N, In, K, B, dW, db);
+    DX_LAUNCH_PDL((outer_wgrad_kernel), (unsigned)(((int64_t)N * K + 255) / 256), 256, 0, s, dOut, N, In, K, B, dW, db);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -805,6 +838,8 @@ int outer_wgrad(const float* dOut, int N, const float* In, int K, int B, float* 
 // =========================================================================================================
 __global__ void lenreg_bwd_ct_kernel(const float* __restrict__ g, const float* __restrict__ xdec, const float* __restrict__ pos,
                                      Rows RT, float* __restrict__ ct) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= RT.cap) return;
@@ -827,6 +862,8 @@ lenreg_bwd_sym_kernel(const float* __restrict__ g, const float* __restrict__ ct,
                       const float* __restrict__ xs, const float* __restrict__ mu, const float* __restrict__ sigma,
                       const float* __restrict__ dur, DxModelWeights w, Rows RL, Rows RT, float* __restrict__ gx,
                       float* __restrict__ gd, float* __restrict__ gr, float* __restrict__ dpre_out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= RL.cap) return;
@@ -890,15 +927,17 @@ int lenreg_bwd(const float* g, const float* xdec, const float* pos, const float*
                const float* sigma, const float* dur, const DxModelWeights* w, const Rows& RL, const Rows& RT, float* ct, float* gx,
                float* gd, float* gr, float* dpre, cudaStream_t s) {
     ProfScope prof("lenreg_bwd", s);
-    lenreg_bwd_ct_kernel<<<(unsigned)((RT.cap + 7) / 8), 256, 0, s>>>(g, xdec, pos, RT, ct);
+    DX_LAUNCH_PDL((lenreg_bwd_ct_kernel), (unsigned)((RT.cap + 7) / 8), 256, 0, s, g, xdec, pos, RT, ct);
     DX_CHECK_LAUNCH();
-    lenreg_bwd_sym_kernel<<<(unsigned)((RL.cap + 7) / 8), 256, 0, s>>>(g, ct, weights, xs, mu, sigma, dur, *w, RL, RT, gx, gd, gr, dpre);
+    DX_LAUNCH_PDL((lenreg_bwd_sym_kernel), (unsigned)((RL.cap + 7) / 8), 256, 0, s, g, ct, weights, xs, mu, sigma, dur, *w, RL, RT, gx, gd, gr, dpre);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // rows [cap] -> single sum (d b_r): part by chunks of 1024 rows, ordered
 __global__ void sum_rows_scalar_kernel(const float* __restrict__ v, Rows R, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ float s_w[32];
     const int64_t total = R.row_start[R.B];
     float acc = 0.f;
@@ -913,7 +952,7 @@ __global__ void sum_rows_scalar_kernel(const float* __restrict__ v, Rows R, floa
     }
 }
 int sum_rows_scalar(const float* v, const Rows& R, float* out, cudaStream_t s) {
-    sum_rows_scalar_kernel<<<1, 1024, 0, s>>>(v, R, out);
+    DX_LAUNCH_PDL((sum_rows_scalar_kernel), 1, 1024, 0, s, v, R, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -929,6 +968,8 @@ __global__ void __launch_bounds__(256)
 style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ accent, DxModelWeights w,
                  const float* __restrict__ dfilm, const float* __restrict__ dlogits, float lambda_rev,
                  float* __restrict__ v) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) float s_e[DX_SPK], s_c[DX_D], s_a[DX_D], s_h1[DX_D], s_h2[DX_D], s_t[DX_D], s_dh2[DX_D], s_dh1[DX_D];
     __shared__ float s_g[1024], s_q[1024], s_dg[1024], s_dq[1024];
     __shared__ float s_red[8];
@@ -1029,19 +1070,21 @@ style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ a
 }
 int style_bwd(const float* spk_embs, const float* accent, const DxModelWeights* w, const float* dfilm, const float* dlogits,
               float lambda_rev, int B, float* v, cudaStream_t s) {
-    style_bwd_kernel<<<B, 256, 0, s>>>(spk_embs, accent, *w, dfilm, dlogits, lambda_rev, v);
+    DX_LAUNCH_PDL((style_bwd_kernel), B, 256, 0, s, spk_embs, accent, *w, dfilm, dlogits, lambda_rev, v);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // gather a strided per-utterance vector into a dense [B][n] matrix
 __global__ void gather_strided_kernel(const float* __restrict__ v, int64_t stride, int off, int n, int B, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)B * n) return;
     out[i] = v[(i / n) * stride + off + (i % n)];
 }
 int gather_strided(const float* v, int64_t stride, int off, int n, int B, float* out, cudaStream_t s) {
-    gather_strided_kernel<<<(unsigned)(((int64_t)B * n + 255) / 256), 256, 0, s>>>(v, stride, off, n, B, out);
+    DX_LAUNCH_PDL((gather_strided_kernel), (unsigned)(((int64_t)B * n + 255) / 256), 256, 0, s, v, stride, off, n, B, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -1057,6 +1100,8 @@ __global__ void __launch_bounds__(256)
 loss_utt_kernel(const float* __restrict__ melo, const float* __restrict__ tgt, Rows RT, const float* __restrict__ logits,
                 const int64_t* __restrict__ speaker_ids, int n_spk, DxLossParams lp, float* __restrict__ part,
                 float* __restrict__ dmel, float* __restrict__ dlogits) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(16) float ls[];
     const int T = RT.n_max, B = RT.B;
     float* s_ep = ls;             // [T + 4] pooled-energy inputs of the prediction (2 zero frames each side)
@@ -1152,6 +1197,8 @@ loss_utt_kernel(const float* __restrict__ melo, const float* __restrict__ tgt, R
 // losses[8]: total, speaker_loss, speaker_ce_raw, post_mult_loss, mel_l1, mel_l2, energy_consistency, pitch_consistency (0)
 __global__ void loss_finish_kernel(const float* __restrict__ part, int B, Rows RT, const float* __restrict__ post_mult,
                                    DxLossParams lp, float* __restrict__ losses, float* __restrict__ dpost_reg) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     float l1 = 0.f, l2 = 0.f, e = 0.f, ce = 0.f, tl = 0.f;
     for (int b = 0; b < B; ++b) {
@@ -1188,15 +1235,17 @@ int loss_forward_backward(const float* melo, const float* tgt, const Rows& RT, c
     if (smem > 40 * 1024) DX_TRY(ensure_dyn_smem(loss_utt_kernel, smem, cfg));
     DX_CHECK_CUDA(cudaMemsetAsync(dmel, 0, (size_t)RT.cap * DX_MEL * sizeof(float), s));
     ProfScope prof("loss", s);
-    loss_utt_kernel<<<RT.B, 256, smem, s>>>(melo, tgt, RT, logits, speaker_ids, n_spk, lp, part, dmel, dlogits);
+    DX_LAUNCH_PDL((loss_utt_kernel), RT.B, 256, smem, s, melo, tgt, RT, logits, speaker_ids, n_spk, lp, part, dmel, dlogits);
     DX_CHECK_LAUNCH();
-    loss_finish_kernel<<<1, 32, 0, s>>>(part, RT.B, RT, post_mult, lp, losses, dpost_reg);
+    DX_LAUNCH_PDL((loss_finish_kernel), 1, 32, 0, s, part, RT.B, RT, post_mult, lp, losses, dpost_reg);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // d post_mult = sum_b dpost_b (FiLM path) + the regulariser's gradient
 __global__ void post_mult_grad_kernel(const float* __restrict__ v, int B, const float* __restrict__ dreg, float* __restrict__ out) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int i = threadIdx.x;
     if (i >= 16) return;
     float acc = 0.f;
@@ -1204,7 +1253,7 @@ __global__ void post_mult_grad_kernel(const float* __restrict__ v, int B, const 
     out[i] = acc + dreg[i];
 }
 int post_mult_grad(const float* v, int B, const float* dreg, float* out, cudaStream_t s) {
-    post_mult_grad_kernel<<<1, 32, 0, s>>>(v, B, dreg, out);
+    DX_LAUNCH_PDL((post_mult_grad_kernel), 1, 32, 0, s, v, B, dreg, out);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -1215,6 +1264,8 @@ int post_mult_grad(const float* v, int B, const float* dreg, float* out, cudaStr
 // =========================================================================================================
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                             int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt, float gscale) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float gi = g[i] * gscale;
@@ -1231,7 +1282,7 @@ int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr,
     DX_REQUIRE(step >= 1, "adam_step: step counts from 1");
     const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
     ProfScope prof("adam", s);
-    adam_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, g, m, v, n, lr, b1, b2, eps, wd, bc1, sqrtf(bc2), gscale);
+    DX_LAUNCH_PDL((adam_kernel), (unsigned)((n + 255) / 256), 256, 0, s, p, g, m, v, n, lr, b1, b2, eps, wd, bc1, sqrtf(bc2), gscale);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -26,6 +26,8 @@ namespace dx {
 __global__ void __launch_bounds__(256)
 rows_to_il_kernel(const float* __restrict__ src, int C, int C_src, const int32_t* __restrict__ total_ptr,
                   __nv_bfloat16* __restrict__ dst, int64_t rows_phys) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) __nv_bfloat16 tile[32][128 + 8];
     const int64_t total = *total_ptr;
     const int64_t pr0 = (int64_t)blockIdx.x * 32;        // physical row of the tile: stream row = physical - DX_HALO
@@ -58,13 +60,15 @@ int rows_to_il(const float* src, int C, const Rows& R, __nv_bfloat16* dst, int64
     DX_REQUIRE(rows_phys >= R.cap + DX_HALO + DX_TAIL, "rows_to_il: rows_phys too small");
     dim3 grid((unsigned)((rows_phys + 31) / 32), (unsigned)(C / 128));
     ProfScope prof("rows_to_il", s);
-    rows_to_il_kernel<<<grid, 256, 0, s>>>(src, C, C_src, R.row_start + R.B, dst, rows_phys);
+    DX_LAUNCH_PDL((rows_to_il_kernel), grid, 256, 0, s, src, C, C_src, R.row_start + R.B, dst, rows_phys);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // dst[t][k][n] = src[t][k][n] inside the source's extent, 0 outside: zero-pads (Kd >= Ks, Nd >= Ns) or crops a weight tensor
 __global__ void copy_pad3_kernel(const float* __restrict__ src, int Ks, int Ns, float* __restrict__ dst, int Kd, int Nd, int64_t n) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int nn = (int)(i % Nd);
@@ -74,7 +78,7 @@ __global__ void copy_pad3_kernel(const float* __restrict__ src, int Ks, int Ns, 
 }
 int copy_pad3(const float* src, int T, int Ks, int Ns, float* dst, int Kd, int Nd, cudaStream_t s) {
     const int64_t n = (int64_t)T * Kd * Nd;
-    copy_pad3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(src, Ks, Ns, dst, Kd, Nd, n);
+    DX_LAUNCH_PDL((copy_pad3_kernel), (unsigned)((n + 255) / 256), 256, 0, s, src, Ks, Ns, dst, Kd, Nd, n);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -83,6 +87,8 @@ int copy_pad3(const float* src, int T, int Ks, int Ns, float* dst, int Kd, int N
 // stream) get zeros: the producer (attention) only writes valid rows and the buffer may hold anything elsewhere
 __global__ void __launch_bounds__(256)
 il_to_rows_kernel(const __nv_bfloat16* __restrict__ src, int C, Rows R, int64_t rows_phys, float* __restrict__ dst) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) __nv_bfloat16 tile[32][128 + 8];
     const int64_t total = R.row_start[R.B];
     const int64_t r0 = (int64_t)blockIdx.x * 32;
@@ -117,7 +123,7 @@ il_to_rows_kernel(const __nv_bfloat16* __restrict__ src, int C, Rows R, int64_t 
 int il_to_rows(const __nv_bfloat16* src, int C, const Rows& R, int64_t rows_phys, float* dst, cudaStream_t s) {
     DX_REQUIRE(C % 128 == 0, "il_to_rows: C=%d must be a multiple of 128", C);
     dim3 grid((unsigned)((R.cap + 31) / 32), (unsigned)(C / 128));
-    il_to_rows_kernel<<<grid, 256, 0, s>>>(src, C, R, rows_phys, dst);
+    DX_LAUNCH_PDL((il_to_rows_kernel), grid, 256, 0, s, src, C, R, rows_phys, dst);
     DX_CHECK_LAUNCH();
     return 0;
 }
@@ -142,6 +148,8 @@ struct WgradTcParams {
 };
 
 __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WgradTcParams p) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
     extern __shared__ __align__(1024) uint8_t wt_smem[];
     uint8_t* stage_base = wt_smem;
     float* s_tr = reinterpret_cast<float*>(wt_smem + WT_STAGES * WT_STAGE_BYTES);
@@ -274,7 +282,7 @@ int wgrad_tc(const __nv_bfloat16* a_il, int K, const __nv_bfloat16* g_il, int N,
     const int grid = (K / 128) * (N / 128) * p.S;
     {
         ProfScope prof("wgrad_tc", s);
-        wgrad_tc_kernel<<<grid, WT_THREADS, WT_SMEM, s>>>(p);
+        DX_LAUNCH_PDL((wgrad_tc_kernel), grid, WT_THREADS, WT_SMEM, s, p);
         DX_CHECK_LAUNCH();
     }
     return reduce_partials(part, p.S, (int64_t)taps * K * N, dW, nullptr, 0, 1.f, s);
