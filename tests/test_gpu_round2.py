@@ -241,3 +241,46 @@ def test_forward_does_not_depend_on_what_the_workspace_held(mode):
     for a, b in zip(*outs):
         assert torch.isfinite(b).all()
         assert torch.equal(a, b)
+
+
+def test_nothing_is_written_outside_the_workspaces():
+    """compute-sanitizer is not available on the pool, so out-of-bounds WRITES are looked for with guard regions: the
+    forward (both modes) and the training step (both GEMM modes) get workspaces that are views into larger buffers filled
+    with a pattern; the bytes in front of and behind the view must be untouched afterwards."""
+    from daft_exprt_b200 import _lib
+    from daft_exprt_b200.train import TrainEngine
+    hp = C.hparams()
+    host = C.synthetic.forward_batch(hp, batch=5, lmin=2, lmax=50, seed=91)
+    batch = tuple(t.cuda() for t in host)
+    B, L, T = host[0].shape[0], host[0].shape[1], host[8].shape[2]
+    guard = 1 << 20
+    lib = _lib.load()
+
+    def guarded(n):
+        big = torch.full((n + 2 * guard,), 0xA5, dtype=torch.uint8, device="cuda")
+        return big, big[guard:guard + n]
+
+    def check(big, n, what):
+        torch.cuda.synchronize()
+        assert bool((big[:guard] == 0xA5).all()), f"{what}: bytes in front of the workspace were overwritten"
+        assert bool((big[guard + n:] == 0xA5).all()), f"{what}: bytes behind the workspace were overwritten"
+
+    for mode in ("fp32", "bf16"):
+        m = DaftExprt(hp, mode=mode).cuda()
+        m.load_state_dict(C.state_dict())
+        n = lib.dx_forward_workspace_bytes(B, L, T, _lib.MODE_BF16 if mode == "bf16" else _lib.MODE_F32)
+        big, view = guarded(n)
+        m._workspaces[0] = view
+        out = m(batch)
+        assert m._workspaces[0].data_ptr() == view.data_ptr()
+        assert torch.isfinite(out[3][0]).all()
+        check(big, n, f"forward {mode}")
+    for gemm in ("fp32", "bf16"):
+        eng = TrainEngine(hp, C.state_dict(), gemm=gemm)
+        n = lib.dx_train_workspace_bytes(B, L, T)
+        big, view = guarded(n)
+        eng._ws = view
+        eng.step(batch, iteration=3)
+        assert eng._ws.data_ptr() == view.data_ptr()
+        assert torch.isfinite(eng.grads).all()
+        check(big, n, f"train {gemm}")
