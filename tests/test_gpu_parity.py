@@ -331,3 +331,43 @@ def test_hidden_dimension_split_of_the_fused_block_kernel(models, cfg):
     if ref is not None:
         for got in (split, whole, forced, deep):
             _check_mel(got[0], ref[3][0], host[9], "bf16")
+
+
+def test_hidden_dimension_split_sweep_over_row_counts(models):
+    """The split of the fused block kernel is the default for short streams (the serving case), and its segment walk has
+    many boundary cases (a tile's chunks on 2..8 CTAs, segments that span two tiles, last tiles with a handful of rows,
+    1-row streams).  Sweep the row count of both streams through those cases and compare with whole tiles per CTA (debug
+    knob 6, itself checked against the oracle elsewhere): same outputs to bf16 rounding, nothing non-finite, exact zeros
+    in the padding."""
+    from daft_exprt_b200 import _lib
+    hp = C.hparams()
+    m = models["bf16"]
+    lib = _lib.load()
+    cases = [(1, 1, 1), (1, 2, 3), (1, 17, 7), (1, 60, 2), (1, 61, 2), (1, 62, 2), (1, 40, 3), (1, 41, 3), (1, 124, 1),
+             (1, 125, 1), (2, 121, 1), (2, 122, 2), (3, 83, 3), (1, 200, 5), (1, 249, 1), (4, 30, 9), (5, 150, 1), (7, 9, 1),
+             (2, 248, 2), (6, 100, 4)]
+    worst = 0.0
+    for knob7 in (0, 1):                   # default policy, then the deepest split
+        for i, (B, L, d) in enumerate(cases):
+            host = C.synthetic.forward_batch(hp, batch=B, lmin=max(1, L - 3 * (i % 3)), lmax=L, seed=300 + i, const_dur=d)
+            batch = tuple(t.cuda() for t in host)
+            lib.dx_set_debug(7, knob7)
+            try:
+                got = m(batch)
+                got = (got[3][0].clone(), got[4].clone(), got[0].clone())
+                lib.dx_set_debug(6, 1)
+                want = m(batch)
+                want = (want[3][0].clone(), want[4].clone(), want[0].clone())
+                torch.cuda.synchronize()
+            finally:
+                lib.dx_set_debug(6, 0)
+                lib.dx_set_debug(7, 0)
+            for a, b in zip(got, want):
+                assert torch.isfinite(a).all(), (B, L, d)
+            rel = ((got[0] - want[0]).abs().sum() / want[0].abs().sum().clamp_min(1e-9)).item()
+            worst = max(worst, rel)
+            assert rel <= 2e-2, (B, L, d, knob7, rel)
+            out_len = host[9]
+            for b in range(B):
+                assert float(got[0][b, :, int(out_len[b]):].abs().sum()) == 0.0, (B, L, d, "padding must be exactly zero")
+    C.record("ffn_split_sweep_rel_l1_vs_whole_tiles", worst)
