@@ -201,3 +201,30 @@ def test_tensor_core_mode_is_deterministic_workspace_independent_and_learns():
         v = float(eng.step(batch, iteration=it, lr=2e-4)[0])
         first = v if first is None else first
     assert v < 0.97 * first, (first, v)
+
+
+def test_accumulation_and_gradient_clipping_follow_the_reference_iteration():
+    """train.py:421-445: loss / accumulation_steps per micro-batch, summed gradients, clip_grad_norm_, Adam.  Checked
+    against torch's own clip_grad_norm_ + Adam applied to the engine's per-micro-batch gradients."""
+    hp = C.hparams()
+    hp.accumulation_steps = 2
+    hp.grad_clip_thresh = 0.05
+    sd = C.state_dict()
+    mbs = [tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=3, lmin=5, lmax=25, seed=s)) for s in (71, 72)]
+    eng = TrainEngine(hp, sd)
+    g = []
+    for mb in mbs:
+        eng.forward_backward(mb, iteration=7, loss_scale=0.5)
+        g.append(eng.grads.clone())
+    p_ref = eng.params.clone().requires_grad_(True)
+    p_ref.grad = g[0] + g[1]
+    ref_norm = torch.nn.utils.clip_grad_norm_([p_ref], hp.grad_clip_thresh)
+    assert float(ref_norm) > hp.grad_clip_thresh                  # the clip is active in this case
+    opt = torch.optim.Adam([p_ref], lr=1e-4, betas=tuple(hp.betas), eps=hp.epsilon, weight_decay=hp.weight_decay)
+    opt.step()
+    eng2 = TrainEngine(hp, sd)
+    total, norm = eng2.iterate(mbs, iteration=7, lr=1e-4)
+    assert abs(float(norm) - float(ref_norm)) <= 1e-5 * float(ref_norm)
+    assert (eng2.params - p_ref.detach()).abs().max().item() <= 2.5e-7
+    with pytest.raises(ValueError):
+        eng2.iterate(mbs[:1], iteration=8)

@@ -259,11 +259,47 @@ class TrainEngine:
                                              int(self.step_count), 1.0 / world, _lib.stream_ptr(self.device)), "dx_adam_step")
 
     def step(self, inputs, iteration=1, lr=None):
-        """One training iteration (accumulation_steps = 1).  Returns the loss terms (device tensor, no sync)."""
+        """One training iteration with ``accumulation_steps = 1`` and no gradient clipping (the defaults of the benchmark
+        configuration).  Returns the loss terms (device tensor, no sync).  ``iterate`` is the general form."""
         losses = self.forward_backward(inputs, iteration)
         world = self.all_reduce_grads()
         self.adam(update_learning_rate(self.hp, iteration) if lr is None else lr, world)
         return losses
+
+    def iterate(self, micro_batches, iteration=1, lr=None):
+        """The reference's full iteration (train.py:421-445) over ``hparams.accumulation_steps`` micro-batches:
+        ``loss / accumulation_steps`` per micro-batch (:423), gradients accumulated over them (:434-436), ONE all-reduce
+        of the flat buffer (DDP averages at the last backward, :269-272), ``clip_grad_norm_(parameters,
+        hparams.grad_clip_thresh)`` (:441), ``optimizer.step()`` (:445).  Returns (summed loss terms as a device tensor,
+        gradient norm before clipping as a device scalar).  A finite ``grad_clip_thresh`` costs one host
+        synchronisation per iteration (the reference has the same one: it logs the norm)."""
+        micro_batches = list(micro_batches)
+        n = len(micro_batches)
+        want = int(getattr(self.hp, "accumulation_steps", 1))
+        if n != want:
+            raise ValueError(f"expected hparams.accumulation_steps = {want} micro-batches, got {n}")
+        total = None
+        acc = None
+        for k, mb in enumerate(micro_batches):
+            losses = self.forward_backward(mb, iteration, loss_scale=1.0 / n)
+            total = losses.clone() if total is None else total + losses
+            if n > 1:
+                if acc is None:
+                    acc = self.grads.clone()
+                else:
+                    acc.add_(self.grads)
+        if acc is not None:
+            self.grads.copy_(acc)
+        world = self.all_reduce_grads()
+        norm = torch.linalg.vector_norm(self.grads) / world         # norm of the AVERAGED gradient, as DDP leaves it
+        scale = 1.0 / world
+        thresh = float(getattr(self.hp, "grad_clip_thresh", float("inf")))
+        if math.isfinite(thresh):
+            coef = thresh / (float(norm) + 1e-6)                        # torch.nn.utils.clip_grad_norm_
+            if coef < 1.0:
+                scale *= coef
+        self.adam(update_learning_rate(self.hp, iteration) if lr is None else lr, 1.0 / scale)
+        return total, norm
 
     def grad_norm(self):
         """What ``clip_grad_norm_(parameters, inf)`` reports (train.py:441); padding between slices is zero."""
