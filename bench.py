@@ -422,8 +422,8 @@ def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
         torch.cuda.synchronize()
         return a.elapsed_time(b) / n
 
-    def measure(gemm):
-        eng = TrainEngine(hp, sd, device=dev, gemm=gemm)
+    def measure(gemm, train_mode=False):
+        eng = TrainEngine(hp, sd, device=dev, gemm=gemm, train_mode=train_mode, seed=1234)
         for it in range(1, warm + 1):
             eng.step(d, iteration=it)
         sync_all()
@@ -455,18 +455,22 @@ def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
                 "tflops_algorithmic": flops_per_step(batch[5].tolist(), batch[9].tolist()) * world / (ms * 1e-3) / 1e12,
                 "loss_after": losses["loss"]}
 
-    tc = measure("bf16")
+    tc = measure("bf16", train_mode=True)
+    tc_eval = measure("bf16")
     f32 = measure("fp32")
     if rank != 0:
         return None
     ms = tc["step_ms"]
     out = {"workload": "cfg5: training step, B=32 per GPU drawn as cfg2 (20-150 symbols), DaftExprt.forward + DaftExprtLoss (energy "
-                       "consistency 0.05, pitch consistency off) + backward, dropout = identity, one SUM all-reduce of the flat fp32 "
-                       "gradient buffer over NCCL, Adam(0.9, 0.98, eps 1e-9, wd 1e-6)",
+                       "consistency 0.05, pitch consistency off) + backward, model.train(): dropout 0.1 at every site of "
+                       "model.py:165-168,189,216,656-670 (counter-based masks, regenerated in the backward), one SUM all-reduce of "
+                       "the flat fp32 gradient buffer over NCCL, Adam(0.9, 0.98, eps 1e-9, wd 1e-6)",
            "scaling": "weak",
            "dtype": "bf16 operands on tcgen05 for the conv / linear forward, dgrad and wgrad contractions (fp32 accumulation); fp32 "
-                    "activations, LayerNorm, attention, length regulator, loss, reductions, Adam (TrainEngine(gemm='bf16'))",
+                    "activations, LayerNorm, softmax, length regulator, loss, reductions, Adam (TrainEngine(gemm='bf16', train_mode=True))",
            "steps": steps, "warmup": warm, **tc,
+           "eval_mode": dict(tc_eval, what="same engine with dropout = identity (model.eval()): the configuration the gradient-parity "
+                                           "tests of the tensor-core mode run in"),
            "fp32_mode": dict(f32, what="every contraction in fp32 SIMT (TrainEngine(gemm='fp32')): the 1e-3 gradient-parity mode"),
            "timing": "CUDA events around the timed steps on the launching stream, max over ranks"}
     if world == 1 and not args.no_cpu_baseline:
@@ -477,6 +481,7 @@ def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
             from oracle import train_oracle as TO
             if R.reference_available():
                 ref = R.build_reference_model(hp, sd).to(dev)
+                ref.train()                      # train.py:411: dropout on, as in the headline above
                 import daft_exprt.loss as ref_loss
                 crit = ref_loss.DaftExprtLoss(str(dev), copy.deepcopy(hp))
                 opt = torch.optim.Adam(ref.parameters(), betas=tuple(hp.betas), eps=hp.epsilon, weight_decay=hp.weight_decay)
@@ -499,7 +504,7 @@ def run_cfg5(args, hp, sd, dev, rank, world, sync_all, dist):
                 g_ms = (time.perf_counter() - t0) / 3 * 1e3
                 torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
                 out["eager_gpu_reference"] = {"step_ms": g_ms, "frames_s": frames / (g_ms * 1e-3), "speedup": g_ms / ms,
-                                              "what": "unmodified reference classes (oracle/_ref) eager fp32 on this GPU, eval mode, TF32 off: "
+                                              "what": "unmodified reference classes (oracle/_ref) eager fp32 on this GPU, model.train() (torch's own dropout), TF32 off: "
                                                       "forward + DaftExprtLoss + backward + torch Adam, 3 steps after 2 warm-ups"}
                 del ref, opt
                 torch.set_num_threads(os.cpu_count() or 1)

@@ -173,8 +173,9 @@ int64_t dx_forward_workspace_bytes(int B, int L_max, int T_max, int mode);
 int dx_forward(const DxModelWeights* w, const DxForwardArgs* a, void* stream);
 
 /* ---- training step (BASELINE.json config 5) ------------------------------------------------------------------
- * One rank's share of the reference's training iteration (train.py:421-445): `outputs = model(inputs)` (model.py:889-948,
- * dropout = identity), `loss, individual = criterion(outputs, targets, iteration)` (loss.py:57-159, pitch-consistency term
+ * One rank's share of the reference's training iteration (train.py:421-445): `outputs = model(inputs)` (model.py:889-948;
+ * dropout = identity unless the attn_dropout / conv_dropout fields are set), `loss, individual = criterion(outputs, targets,
+ * iteration)` (loss.py:57-159, pitch-consistency term
  * off), `loss.backward()`.  `grads` is a DxModelWeights whose fp32 pointers say where the gradient of each weight is
  * written, in the same ENGINE layout as the weight (the *_bf fields are ignored).  Every gradient is overwritten (no
  * accumulation); the kernels are deterministic.  The data-parallel exchange (DDP's gradient averaging, train.py:269-272) is
@@ -199,9 +200,24 @@ typedef struct {
     float *mel_out;       /* (B, 80, T_max) mel prediction or NULL */
     void  *workspace;     /* dx_train_workspace_bytes(B, L_max, T_max) bytes, 256-byte aligned */
     int64_t workspace_bytes;
+    /* train-mode forward (model.train(), train.py:411): dropout probabilities per stack - [0] accent encoder (its pre-net
+     * uses conv_dropout[0], model.py:656-670), [1] phoneme encoder, [2] frame decoder (hparams.py:105-127; attn_dropout is
+     * both nn.MultiheadAttention's weight dropout, model.py:165-167, and the nn.Dropout behind it, :168,189; conv_dropout
+     * is the one that ends PositionWiseConvFF.convs, :216).  All zero = eval-mode forward (the parity configuration).  Any
+     * non-zero value needs DX_TRAIN_TC_GEMM.  Masks are a pure function of (dropout_seed, site, position): pass a fresh
+     * seed per step; dx_dropout_mask returns the mask of a site for checking against the reference. */
+    float attn_dropout[3], conv_dropout[3];
+    uint64_t dropout_seed;
 } DxTrainArgs;
 
 int64_t dx_train_workspace_bytes(int B, int L_max, int T_max);
+/* Keep-mask (uint8, 1 = kept) of one dropout site of dx_train_step, in the reference's padded coordinates.  kind 0: the
+ * nn.Dropout behind the attention (model.py:189), 1: the one ending the conv feed-forward (:216), 2: layer `block` (0..2)
+ * of the accent encoder's pre-net (:656,663,670; stack must be 0) - out is (B, n_max, C); kind 3: the attention-weight
+ * dropout inside nn.MultiheadAttention - out is (B, 2 heads, n_max, n_max), C ignored.  stack: 0 accent encoder,
+ * 1 phoneme encoder, 2 frame decoder; block 0..3; p: the site's probability; n_max: T_max (stacks 0, 2) or L_max (1). */
+int dx_dropout_mask(uint64_t seed, int kind, int stack, int block, float p, int B, int n_max, int C, uint8_t* out,
+                    void* stream);
 int dx_train_step(const DxModelWeights* w, const DxModelWeights* grads, const DxTrainArgs* a, void* stream);
 /* torch.optim.Adam(betas, eps, weight_decay, amsgrad=False) (train.py:278-280) on flat fp32 buffers of n elements:
  * g = grad * grad_scale + weight_decay * p; m, v moments; step counts from 1.  grad_scale = 1 / world_size after a SUM

@@ -228,3 +228,132 @@ def test_accumulation_and_gradient_clipping_follow_the_reference_iteration():
     assert (eng2.params - p_ref.detach()).abs().max().item() <= 2.5e-7
     with pytest.raises(ValueError):
         eng2.iterate(mbs[:1], iteration=8)
+
+
+# ---- train-mode forward: dropout (model.py:165-168,189,216,656-670) -----------------------------------------------------
+# The engine draws its masks from a counter-based generator; dx_dropout_mask exports them in the reference's padded
+# coordinates and the oracle injects them into the UNMODIFIED reference model in train() mode (oracle/train_oracle.py), so
+# both sides drop exactly the same elements.  Same gates as the eval-mode tensor-core step.
+
+def _dropout_case(hp, kw, iteration, seed, p=None):
+    if p is not None:
+        for name in ("phoneme_encoder", "frame_decoder", "accent_encoder"):
+            if hasattr(hp, name):
+                d = dict(getattr(hp, name))
+                d["attn_dropout"], d["conv_dropout"] = p
+                setattr(hp, name, d)
+    sd = C.state_dict()
+    batch = C.synthetic.forward_batch(hp, **kw)
+    eng = TrainEngine(hp, sd, gemm="bf16", train_mode=True, seed=seed)
+    B, L = batch[0].shape
+    T = batch[8].shape[2]
+    masks = [(m.cpu(), pm) for m, pm in eng.dropout_masks(B, L, T, iteration=iteration)]
+    losses = loss_dict(eng.forward_backward(tuple(t.cuda() for t in batch), iteration=iteration))
+    return eng, batch, sd, masks, losses
+
+
+def _rel_l1(grads, ref_grads):
+    rels = {}
+    for name, r in ref_grads.items():
+        o = grads[name].cpu()
+        assert torch.isfinite(o).all(), name
+        if r.abs().sum().item() < 1e-6:
+            continue
+        rels[name] = (o - r).abs().sum().item() / r.abs().sum().item()
+    return rels
+
+
+# worst-tensor gate 0.4 (eval mode: TC_GRAD_REL_L1_MAX = 0.25): the worst tensors are one- to 128-element biases whose
+# gradient is a sum with heavy cancellation (measured: the range predictor's scalar bias 0.26 at B = 8, a speaker-classifier
+# bias behind the gradient reversal 0.29 at B = 3 with p = 0.3); dropout's 1 / (1 - p) rescale widens the bf16 rounding of
+# every branch it touches.  The median gate is the eval-mode one, the loss gate too (profiles/r02_parity_measured.json).
+TC_DROPOUT_GRAD_REL_L1_MAX = 0.4
+
+
+@pytest.mark.parametrize("kw,iteration,p,tag", [
+    (dict(batch=4, lmin=5, lmax=30, seed=17), 1234, None, "B4"),              # hparams' own 0.1 / 0.1
+    (dict(batch=3, lmin=8, lmax=24, seed=31), 300, (0.3, 0.2), "B3_p03"),     # heavier dropout: a wrong mask cannot hide
+    (dict(batch=8, lmin=20, lmax=150, seed=43), 5000, None, "B8"),            # several attention tiles per utterance
+])
+def test_train_mode_dropout_against_reference_with_the_same_masks(kw, iteration, p, tag):
+    hp = C.hparams()
+    eng, batch, sd, masks, losses = _dropout_case(hp, kw, iteration, seed=2024, p=p)
+    assert len(masks) == 39
+    for m, pm in masks:                         # keep rate of every site is 1 - p within 5 sigma
+        n = m.numel()
+        assert abs(m.float().mean().item() - (1 - pm)) <= 5 * (pm * (1 - pm) / n) ** 0.5 + 1e-6
+    ref_loss, _, ref_grads = TO.reference_step(hp, sd, batch, iteration, dropout_masks=masks)
+    eval_loss, _, _ = TO.reference_step(hp, sd, batch, iteration)
+    assert abs(ref_loss - eval_loss) > 2 * TC_LOSS_REL * abs(ref_loss), "the case must tell train mode from eval mode"
+    assert abs(losses["loss"] - ref_loss) <= TC_LOSS_REL * abs(ref_loss), (losses["loss"], ref_loss, eval_loss)
+    rels = sorted(_rel_l1(eng.grads_state_dict(), ref_grads).items(), key=lambda kv: kv[1])
+    C.record(f"train_dropout_grad_rel_l1_max_{tag}", rels[-1][1])
+    C.record(f"train_dropout_grad_rel_l1_median_{tag}", rels[len(rels) // 2][1])
+    C.record(f"train_dropout_loss_rel_{tag}", abs(losses["loss"] - ref_loss) / abs(ref_loss))
+    assert rels[-1][1] <= TC_DROPOUT_GRAD_REL_L1_MAX, rels[-1]
+    assert rels[len(rels) // 2][1] <= TC_GRAD_REL_L1_MEDIAN, rels[len(rels) // 2]
+
+
+def test_train_mode_masks_of_another_seed_do_not_match():
+    """Control for the test above: against the reference run with the masks of a DIFFERENT seed the gradients are far
+    outside the gate, so the gate really checks that both sides dropped the same elements."""
+    hp = C.hparams()
+    kw, iteration = dict(batch=3, lmin=8, lmax=24, seed=31), 300
+    eng, batch, sd, masks, _ = _dropout_case(hp, kw, iteration, seed=1)
+    other = TrainEngine(hp, sd, gemm="bf16", train_mode=True, seed=2)
+    B, L = batch[0].shape
+    wrong = [(m.cpu(), pm) for m, pm in other.dropout_masks(B, L, batch[8].shape[2], iteration=iteration)]
+    assert any(not torch.equal(a[0], b[0]) for a, b in zip(masks, wrong))
+    _, _, g_right = TO.reference_step(hp, sd, batch, iteration, dropout_masks=masks)
+    _, _, g_wrong = TO.reference_step(hp, sd, batch, iteration, dropout_masks=wrong)
+    right = sorted(_rel_l1(eng.grads_state_dict(), g_right).values())
+    wrong_r = sorted(_rel_l1(eng.grads_state_dict(), g_wrong).values())
+    assert right[len(right) // 2] <= TC_GRAD_REL_L1_MEDIAN
+    assert wrong_r[len(wrong_r) // 2] > 5 * right[len(right) // 2], (right[len(right) // 2], wrong_r[len(wrong_r) // 2])
+
+
+def test_train_mode_seeding_determinism_and_zero_probability():
+    hp = C.hparams()
+    sd = C.state_dict()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=4, lmin=5, lmax=30, seed=17))
+    eng = TrainEngine(hp, sd, gemm="bf16", train_mode=True, seed=7)
+    eng.forward_backward(batch, iteration=3)
+    g3 = eng.grads.clone()
+    eng.forward_backward(batch, iteration=4)
+    g4 = eng.grads.clone()
+    eng.forward_backward(batch, iteration=3)
+    assert torch.equal(g3, eng.grads), "same (seed, iteration): same masks, bit-identical gradients"
+    assert not torch.equal(g3, g4), "another iteration draws other masks"
+    eng.forward_backward(batch, iteration=3, micro_batch=1)
+    assert not torch.equal(g3, eng.grads), "micro-batches of one iteration draw different masks"
+    # validation (forward_only) is eval mode whatever the engine's mode (train.py:155-209)
+    ev = TrainEngine(hp, sd, gemm="bf16")
+    a = eng.forward_backward(batch, iteration=3, forward_only=True).clone()
+    b = ev.forward_backward(batch, iteration=3, forward_only=True).clone()
+    assert torch.equal(a, b)
+    # p = 0 everywhere in train mode is the eval-mode step, bit for bit
+    hp0 = C.hparams()
+    for name in ("phoneme_encoder", "frame_decoder", "accent_encoder"):
+        if hasattr(hp0, name):
+            d = dict(getattr(hp0, name))
+            d["attn_dropout"] = d["conv_dropout"] = 0.0
+            setattr(hp0, name, d)
+    z = TrainEngine(hp0, sd, gemm="bf16", train_mode=True, seed=7)
+    z.forward_backward(batch, iteration=3)
+    ev.forward_backward(batch, iteration=3)
+    assert torch.equal(z.grads, ev.grads)
+    # dropout needs the tensor-core path; the fp32 path refuses instead of silently skipping it
+    with pytest.raises(ValueError):
+        TrainEngine(hp, sd, gemm="fp32", train_mode=True)
+
+
+def test_train_mode_learns():
+    hp = C.hparams()
+    batch = tuple(t.cuda() for t in C.synthetic.forward_batch(hp, batch=8, lmin=10, lmax=40, seed=29))
+    eng = TrainEngine(hp, C.state_dict(), gemm="bf16", train_mode=True, seed=11)
+    for it in range(1, 21):
+        eng.step(batch, iteration=it, lr=2e-4)
+    first = float(TrainEngine(hp, C.state_dict(), gemm="bf16").forward_backward(batch, iteration=1, forward_only=True)[0])
+    ev = TrainEngine(hp, eng.state_dict(), gemm="bf16")
+    last = float(ev.forward_backward(batch, iteration=1, forward_only=True)[0])
+    assert last < 0.97 * first, (first, last)

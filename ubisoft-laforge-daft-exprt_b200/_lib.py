@@ -67,6 +67,7 @@ class DxTrainArgs(C.Structure):
         + [(n, C.c_float) for n in ("mel_spec_weight", "post_mult_weight", "energy_consistency_weight", "speaker_weight",
                                     "lambda_reversal", "loss_scale")]
         + [("losses", _p), ("mel_out", _p), ("workspace", _p), ("workspace_bytes", C.c_int64)]
+        + [("attn_dropout", C.c_float * 3), ("conv_dropout", C.c_float * 3), ("dropout_seed", C.c_uint64)]
     )
 
 
@@ -106,6 +107,7 @@ SIGNATURES = {
     "dx_forward_workspace_bytes": (C.c_int64, [C.c_int] * 4),
     "dx_forward": (C.c_int, [C.POINTER(DxModelWeights), C.POINTER(DxForwardArgs), _p]),
     "dx_train_workspace_bytes": (C.c_int64, [C.c_int] * 3),
+    "dx_dropout_mask": (C.c_int, [C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, _p, _p]),
     "dx_train_step": (C.c_int, [C.POINTER(DxModelWeights), C.POINTER(DxModelWeights), C.POINTER(DxTrainArgs), _p]),
     "dx_adam_step": (C.c_int, [_p, _p, _p, _p, C.c_int64] + [C.c_float] * 5 + [C.c_int, C.c_float, _p]),
     "dx_accent_encoder": (C.c_int, [C.POINTER(DxModelWeights), C.c_int, C.c_int, C.c_int, _p, _p, _p, _p, _p, _p,

@@ -38,11 +38,13 @@ struct AbtParams {
     const __nv_bfloat16* dO;    // [16][rows_phys][8]
     int64_t rows_phys;
     const float *lse, *Dr;      // [rows][2]
+    DropSpec drop;              // DROP instantiations: the forward's attention-weight dropout, regenerated here
+    uint32_t drop_site;
     Rows R;
     float* dqkv;                // [rows][384] fp32
 };
 
-template <bool DQ>
+template <bool DQ, bool DROP>
 __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtParams p) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
@@ -175,6 +177,7 @@ __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtPa
             const int q = q0 + row;
             const bool q_ok = q < len;
             float lse = 0.f, dr = 0.f;
+            const uint64_t drop_row = DROP ? drop_pair_attn_row(b, h, q, p.R.n_max) + (uint64_t)(k0 >> 1) : 0;
             if (q_ok) {
                 lse = p.lse[(rs + q) * DX_HEADS + h];
                 dr = p.Dr[(rs + q) * DX_HEADS + h];
@@ -194,13 +197,24 @@ __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtPa
 #pragma unroll
                     for (int e = 0; e < 8; e += 2) {
                         float pv[2], dv[2];
+                        uint64_t z = 0;
+                        if constexpr (DROP) z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g4 * 32 + c * 8 + e) >> 1));
 #pragma unroll
                         for (int u = 0; u < 2; ++u) {
                             const int col = g4 * 32 + c * 8 + e + u;
                             const bool ok = q_ok && (k0 + col < len);
                             const float pe = ok ? __expf(fmaf(sv[c * 8 + e + u], 0.125f, -lse)) : 0.f;
-                            pv[u] = pe;
-                            dv[u] = pe * (dp[c * 8 + e + u] - dr) * 0.125f;
+                            if constexpr (DROP) {
+                                // O = (mask * scale * P) V: dV takes the dropped weights, dP = mask * scale * (dO Vᵀ); the row
+                                // term D = sum_k P dP = dO · O is unchanged
+                                const bool keep = drop_keep(z, u, p.drop.thr);
+                                pv[u] = keep ? pe * p.drop.scale : 0.f;
+                                const float dpm = keep ? dp[c * 8 + e + u] * p.drop.scale : 0.f;
+                                dv[u] = pe * (dpm - dr) * 0.125f;
+                            } else {
+                                pv[u] = pe;
+                                dv[u] = pe * (dp[c * 8 + e + u] - dr) * 0.125f;
+                            }
                         }
                         p2[e / 2] = __floats2bfloat162_rn(pv[0], pv[1]);
                         d2[e / 2] = __floats2bfloat162_rn(dv[0], dv[1]);
@@ -252,18 +266,31 @@ __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtPa
 // qkv_il / dO_il: bf16 channel-interleaved copies of the block's saved QKV rows and of dO (rows_to_il); lse, Dr fp32 [rows][2];
 // dqkv fp32 [rows][384] is fully overwritten at valid positions and zeroed elsewhere.
 int attention_bwd_tc(const __nv_bfloat16* qkv_il, const __nv_bfloat16* dO_il, int64_t rows_phys, const float* lse, const float* Dr,
-                     const Rows& R, float* dqkv, cudaStream_t s) {
-    static SmemConfigured c1, c2;
-    DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<true>, (size_t)ABT_SMEM, c1));
-    DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<false>, (size_t)ABT_SMEM, c2));
+                     const Rows& R, float* dqkv, cudaStream_t s, const DropSpec* drop, uint32_t drop_site_id) {
+    static SmemConfigured c1, c2, c3, c4;
+    const bool use_drop = drop != nullptr && drop->thr != 0;
+    if (use_drop) {
+        DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<true, true>, (size_t)ABT_SMEM, c3));
+        DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<false, true>, (size_t)ABT_SMEM, c4));
+    } else {
+        DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<true, false>, (size_t)ABT_SMEM, c1));
+        DX_TRY(ensure_dyn_smem(attn_bwd_tc_kernel<false, false>, (size_t)ABT_SMEM, c2));
+    }
     AbtParams p;
+    if (use_drop) { p.drop = *drop; p.drop_site = drop_site_id; }
     p.qkv = qkv_il; p.dO = dO_il; p.rows_phys = rows_phys; p.lse = lse; p.Dr = Dr; p.R = R; p.dqkv = dqkv;
     ProfScope prof("attn_bwd_tc", s);
     DX_CHECK_CUDA(cudaMemsetAsync(dqkv, 0, (size_t)R.cap * 384 * sizeof(float), s));
     dim3 grid((unsigned)((R.n_max + 127) / 128), DX_HEADS, (unsigned)R.B);
-    DX_LAUNCH_PDL((attn_bwd_tc_kernel<true>), grid, ABT_THREADS, ABT_SMEM, s, p);
-    DX_CHECK_LAUNCH();
-    DX_LAUNCH_PDL((attn_bwd_tc_kernel<false>), grid, ABT_THREADS, ABT_SMEM, s, p);
+    if (use_drop) {
+        DX_LAUNCH_PDL((attn_bwd_tc_kernel<true, true>), grid, ABT_THREADS, ABT_SMEM, s, p);
+        DX_CHECK_LAUNCH();
+        DX_LAUNCH_PDL((attn_bwd_tc_kernel<false, true>), grid, ABT_THREADS, ABT_SMEM, s, p);
+    } else {
+        DX_LAUNCH_PDL((attn_bwd_tc_kernel<true, false>), grid, ABT_THREADS, ABT_SMEM, s, p);
+        DX_CHECK_LAUNCH();
+        DX_LAUNCH_PDL((attn_bwd_tc_kernel<false, false>), grid, ABT_THREADS, ABT_SMEM, s, p);
+    }
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -22,6 +22,7 @@
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
 #include "dx_ptx.cuh"
+#include "dx_dropout.cuh"
 #include <string.h>
 
 namespace dx {
@@ -45,6 +46,8 @@ struct AtcParams {
     int64_t rows_phys;
     Rows R;
     float* lse;                 // training: natural-log log-sum-exp of the scaled scores per (row, head), [rows][2], or null
+    DropSpec drop;              // training (DROP instantiation): dropout of the attention weights inside nn.MultiheadAttention
+    uint32_t drop_site;
     uint32_t v_lbo, v_sbo;      // MN-major descriptor strides of the V operand (debug knob 1 swaps them)
     long long* trace;           // bring-up: clock64 timeline of CTA (0,0,0) (dx_set_trace_buffer) or null
     int trace_ctas;             // > 0: the buffer also holds [256 + 4 i ..] = (start ns, end ns, SM id, K/V tiles) of CTA i
@@ -53,6 +56,7 @@ struct AtcParams {
 // issuer +0 kv_full ok, +1 S issued, +2 p_full ok, +3 PV issued;  softmax +4 s_full ok, +5 max done, +6 P stored
 #define AT_TRACE(slot) do { if (tr) tr[(slot)] = clock64(); } while (0)
 
+template <bool DROP>
 __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcParams p) {
     extern __shared__ __align__(1024) uint8_t at_smem[];
     ptx::griddep_wait();      // PDL: the lengths and QKV come from earlier kernels
@@ -210,6 +214,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
         uint8_t* sPg = sP + grp * ATC_P_BYTES;
         const float sl2 = 0.125f * 1.4426950408889634f;   // d^-0.5 * log2(e)
         float m_ref = -INFINITY, l = 0.f;
+        const uint64_t drop_row = DROP ? drop_pair_attn_row(b, h, q0 + row, p.R.n_max) : 0;
         for (int g = grp; g < n_kv; g += 2) {
             const uint32_t par = (g >> 1) & 1;
             const int nvalid = len - g * ATC_BK;               // keys of this tile that exist (>= 1)
@@ -296,6 +301,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
 #pragma unroll
                             for (int e = 0; e < 8; ++e) pe[e] = ptx::ex2_approx(fmaf(v[c * 8 + e], sl2, -m_ref));
                             ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+                            if constexpr (DROP) {       // the row sum above is of the UNdropped weights (softmax, then dropout)
+#pragma unroll
+                                for (int e = 0; e < 8; e += 2) {
+                                    const uint64_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
+                                    pe[e] = drop_keep(z, 0, p.drop.thr) ? pe[e] * p.drop.scale : 0.f;
+                                    pe[e + 1] = drop_keep(z, 1, p.drop.thr) ? pe[e + 1] * p.drop.scale : 0.f;
+                                }
+                            }
 #pragma unroll
                             for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
                             *reinterpret_cast<uint4*>(sPg + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
@@ -311,6 +324,14 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                                 if (q * 32 + c * 8 + e >= nvalid) pe[e] = 0.f;
                             }
                             ps0 += pe[0] + pe[4]; ps1 += pe[1] + pe[5]; ps2 += pe[2] + pe[6]; ps3 += pe[3] + pe[7];
+                            if constexpr (DROP) {
+#pragma unroll
+                                for (int e = 0; e < 8; e += 2) {
+                                    const uint64_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
+                                    pe[e] = drop_keep(z, 0, p.drop.thr) ? pe[e] * p.drop.scale : 0.f;
+                                    pe[e + 1] = drop_keep(z, 1, p.drop.thr) ? pe[e + 1] * p.drop.scale : 0.f;
+                                }
+                            }
 #pragma unroll
                             for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(pe[2 * e], pe[2 * e + 1]);
                             *reinterpret_cast<uint4*>(sPg + (size_t)(q * 4 + c) * 2048 + row * 16) = *reinterpret_cast<const uint4*>(o2);
@@ -401,12 +422,16 @@ int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Row
 }
 
 // out [16][rows_phys][8] = concat_h softmax(Q_h K_h^T / 8) V_h
-int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s, float* lse) {
-    static SmemConfigured configured;
-    DX_TRY(ensure_dyn_smem(attention_tc_kernel, ATC_SMEM, configured));
+int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s, float* lse,
+                   const DropSpec* drop, uint32_t drop_site_id) {
+    static SmemConfigured configured, configured_drop;
+    const bool use_drop = drop != nullptr && drop->thr != 0;
+    if (use_drop) DX_TRY(ensure_dyn_smem(attention_tc_kernel<true>, ATC_SMEM, configured_drop));
+    else DX_TRY(ensure_dyn_smem(attention_tc_kernel<false>, ATC_SMEM, configured));
     AtcParams p;
     memset(&p, 0, sizeof(p));
     p.qkv = qkv; p.out = out; p.rows_phys = rows_phys; p.R = R; p.lse = lse;
+    if (use_drop) { p.drop = *drop; p.drop_site = drop_site_id; }
     p.trace = reinterpret_cast<long long*>(trace_buffer(256 * sizeof(long long)));
     if (p.trace != nullptr && debug_knob(10) % 100 > 0) {       // knob 10 = n: trace only the n-th attention launch of a step (1..12)
         static int n_traced = 0;
@@ -418,7 +443,8 @@ int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_ph
     p.v_lbo = 128; p.v_sbo = ATC_BK * 16;
     if (debug_knob(1)) { p.v_lbo = ATC_BK * 16; p.v_sbo = 128; }
     ProfScope prof("attn_tc", s);
-    DX_LAUNCH_PDL((attention_tc_kernel), grid, ATC_THREADS, ATC_SMEM, s, p);
+    if (use_drop) DX_LAUNCH_PDL((attention_tc_kernel<true>), grid, ATC_THREADS, ATC_SMEM, s, p);
+    else DX_LAUNCH_PDL((attention_tc_kernel<false>), grid, ATC_THREADS, ATC_SMEM, s, p);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -154,8 +154,9 @@ __device__ __forceinline__ float ln_film(float v, float mean, float rstd, float 
 int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, int taps, bool relu,
              const Rows& R, int live_ext, float* out, cudaStream_t s, const float* addend = nullptr);
 // out = live(ext) ? film(LN(in + res) * g + b) : 0   (one warp per row; C = 128 or 1024)
+struct LnDrop;      // dx_dropout.cuh (training step)
 int ln_rows_f32(const float* in, const float* res, const float* g, const float* b, int C, const float* film,
-                int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s);
+                int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s, const LnDrop* drop = nullptr);
 // masked multi-head self attention on packed rows; qkv [rows][384] → out [rows][128]
 int attention_f32(const float* qkv, const Rows& R, float* out, cudaStream_t s, float* lse = nullptr);
 

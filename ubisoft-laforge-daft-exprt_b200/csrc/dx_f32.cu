@@ -2,6 +2,7 @@
 // flash-style masked multi-head attention.  These back DX_MODE_F32, whose gate is mel max-abs <= 1e-3 against
 // the reference CPU forward (TF32 tensor-core inputs miss that gate: SURVEY.md §7.3 H2).
 #include "dx_common.cuh"
+#include "dx_dropout.cuh"
 #include "dx_ptx.cuh"
 #include "dx_kernels.cuh"
 
@@ -137,11 +138,11 @@ int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, in
 // Reference: MultiHeadAttention.forward model.py:191 + FFTBlock mask :256; PositionWiseConvFF.forward
 // model.py:226-233 + mask :258; accent pre-net LayerNorms model.py:655,662,669.
 // =========================================================================================================
-template <int C>
+template <int C, bool DROP>
 __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __restrict__ res,
                                    const float* __restrict__ g, const float* __restrict__ bta,
                                    const float* __restrict__ film, int film_stride, Rows R, int live_ext,
-                                   float* __restrict__ out) {
+                                   float* __restrict__ out, LnDrop drop) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
     constexpr int V = C / 128;  // float4 per lane
@@ -159,9 +160,17 @@ __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __
     float4 v[V];
     const float4* irow = reinterpret_cast<const float4*>(in + r * C);
     float sum = 0.f;
+    const int b_idx = R.row_b[r];
+    const int pos = DROP ? R.row_p[r] : 0;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         v[i] = irow[lane + 32 * i];
+        if constexpr (DROP) {
+            if (drop.where == LN_DROP_IN) {         // training: dropout of the branch before the residual add, kept for the backward
+                v[i] = drop_apply4(v[i], drop.d, drop.site, b_idx, pos, R.n_max, C, (lane + 32 * i) * 4);
+                reinterpret_cast<float4*>(const_cast<float*>(in) + r * C)[lane + 32 * i] = v[i];
+            }
+        }
         if (res != nullptr) {
             float4 q = reinterpret_cast<const float4*>(res + r * C)[lane + 32 * i];
             v[i].x += q.x; v[i].y += q.y; v[i].z += q.z; v[i].w += q.w;
@@ -176,7 +185,6 @@ __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __
         sq += (a * a + b * b) + (c * c + d * d);
     }
     const float rstd = rsqrtf(warp_sum(sq) * (1.f / C) + 1e-5f);
-    const int b_idx = R.row_b[r];
 #pragma unroll
     for (int i = 0; i < V; ++i) {
         const int c4 = lane + 32 * i;
@@ -193,18 +201,31 @@ __global__ void ln_rows_f32_kernel(const float* __restrict__ in, const float* __
             float4 be = reinterpret_cast<const float4*>(fp + C)[c4];
             y.x = ga.x * y.x + be.x; y.y = ga.y * y.y + be.y; y.z = ga.z * y.z + be.z; y.w = ga.w * y.w + be.w;
         }
+        if constexpr (DROP) {
+            if (drop.where == LN_DROP_OUT) y = drop_apply4(y, drop.d, drop.site, b_idx, pos, R.n_max, C, c4 * 4);
+        }
         orow[c4] = y;
     }
 }
 
 int ln_rows_f32(const float* in, const float* res, const float* g, const float* b, int C, const float* film,
-                int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s) {
+                int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s, const LnDrop* drop) {
     int grid = (int)((R.cap + 7) / 8);
     ProfScope prof("ln_rows_f32", s);
-    if (C == 128)
-        DX_LAUNCH_PDL((ln_rows_f32_kernel<128>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out);
+    LnDrop nd;
+    memset(&nd, 0, sizeof(nd));
+    if (drop != nullptr && drop->d.thr != 0) {
+        DX_REQUIRE(in != out && in != res, "ln_rows_f32: the dropped input is rewritten in place and cannot alias res / out");
+        if (C == 128)
+            DX_LAUNCH_PDL((ln_rows_f32_kernel<128, true>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out, *drop);
+        else if (C == 1024)
+            DX_LAUNCH_PDL((ln_rows_f32_kernel<1024, true>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out, *drop);
+        else
+            DX_REQUIRE(false, "ln_rows_f32: unsupported width %d", C);
+    } else if (C == 128)
+        DX_LAUNCH_PDL((ln_rows_f32_kernel<128, false>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out, nd);
     else if (C == 1024)
-        DX_LAUNCH_PDL((ln_rows_f32_kernel<1024>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out);
+        DX_LAUNCH_PDL((ln_rows_f32_kernel<1024, false>), grid, 256, 0, s, in, res, g, b, film, film_stride, R, live_ext, out, nd);
     else
         DX_REQUIRE(false, "ln_rows_f32: unsupported width %d", C);
     DX_CHECK_LAUNCH();

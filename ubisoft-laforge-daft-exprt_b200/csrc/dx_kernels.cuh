@@ -30,7 +30,10 @@ int ln_apply_bf16(__nv_bfloat16* x, int64_t rows_phys, int C, const float* stats
 // dx_attn_tc.cu: masked multi-head self-attention, bf16 operands on tcgen05, fp32 softmax
 int zero_tail_rows(__nv_bfloat16* buf, int nchunks, int64_t rows_phys, const Rows& R, int n_rows, cudaStream_t s);
 // lse (training): natural-log log-sum-exp of the scaled scores, fp32 [rows][2], written at valid rows
-int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s, float* lse = nullptr);
+// drop (training): dropout of the attention weights (after the softmax normalisation, as nn.MultiheadAttention applies it)
+struct DropSpec;
+int attention_bf16(const __nv_bfloat16* qkv, __nv_bfloat16* out, int64_t rows_phys, const Rows& R, cudaStream_t s, float* lse = nullptr,
+                   const DropSpec* drop = nullptr, uint32_t drop_site_id = 0);
 
 // dx_ffn_tc.cu: fused conv1 + ReLU + conv2 + residual + LN + FiLM + mask; optionally with the attention output
 // projection + residual + LN1 in front (attn != null: x is ignored, x_in is the block input) and the next block's QKV

@@ -3,6 +3,7 @@
 #pragma once
 #include "dx_common.cuh"
 #include "dx_kernels.cuh"
+#include "dx_dropout.cuh"
 
 namespace dx {
 
@@ -15,9 +16,10 @@ constexpr int SB_E = 0, SB_C = 192, SB_DG = 320, SB_DQ = 1344, SB_DC = 2368, SB_
               SB_DH2 = 2880, SB_DPOST = 3008, SB_DACC = 3024, SB_STRIDE = 3152;
 
 int reduce_partials(const float* part, int S, int64_t n, float* out, const int32_t* total_rows, int chunk_rows, float scale,
-                    cudaStream_t s);
+                    cudaStream_t s, float* out2 = nullptr, int64_t split = 0);
 int ln_bwd_rows(const float* in, const float* res, const float* g, int C, const float* film, int film_stride, const float* dy1,
-                const float* dy2, const Rows& R, int live_ext, float* dv, float* dg, float* db, float* scratch, cudaStream_t s);
+                const float* dy2, const Rows& R, int live_ext, float* dv, float* dg, float* db, float* scratch, cudaStream_t s,
+                const LnDrop* drop = nullptr);
 int64_t ln_bwd_scratch_floats(int64_t cap, int C);
 int film_bwd(const float* in, const float* res, const float* g, const float* bta, const float* dy1, const float* dy2,
              const Rows& R, float* dfilm, int film_stride, cudaStream_t s);
@@ -58,7 +60,7 @@ int wgrad_tc(const __nv_bfloat16* a_il, int K, const __nv_bfloat16* g_il, int N,
 int64_t wgrad_tc_scratch_floats();
 // dx_attn_bwd_tc.cu: attention backward on tcgen05 from bf16 interleaved copies of QKV and dO
 int attention_bwd_tc(const __nv_bfloat16* qkv_il, const __nv_bfloat16* dO_il, int64_t rows_phys, const float* lse, const float* Dr,
-                     const Rows& R, float* dqkv, cudaStream_t s);
+                     const Rows& R, float* dqkv, cudaStream_t s, const DropSpec* drop = nullptr, uint32_t drop_site_id = 0);
 int attn_rowdot(const float* dO, const float* O, const Rows& R, float* Dr, cudaStream_t s);      // Dr[r][h] = dO[r] . O[r] per head
 
 int64_t train_workspace_bytes(int B, int L_max, int T_max);

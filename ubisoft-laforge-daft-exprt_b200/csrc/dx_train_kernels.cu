@@ -31,12 +31,12 @@ namespace dx {
 // =========================================================================================================
 constexpr int LNB_ROWS = 64;
 
-template <int C>
+template <int C, bool DROP>
 __global__ void __launch_bounds__(256)
 ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, const float* __restrict__ g,
                    const float* __restrict__ film, int film_stride, const float* __restrict__ dy1,
                    const float* __restrict__ dy2, Rows R, int live_ext, float* __restrict__ dv,
-                   float* __restrict__ part) {
+                   float* __restrict__ part, LnDrop drop) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
     constexpr int V = C / 128;
@@ -54,8 +54,16 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
         if (!live) {
 #pragma unroll
             for (int i = 0; i < V; ++i) orow[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (DROP) {
+                if (drop.where == LN_DROP_IN) {
+#pragma unroll
+                    for (int i = 0; i < V; ++i) reinterpret_cast<float4*>(drop.dvm + r * C)[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
             continue;
         }
+        const int b_idx = R.row_b[r];
+        const int pos = DROP ? R.row_p[r] : 0;
         float4 v[V];
         float sum = 0.f;
 #pragma unroll
@@ -75,7 +83,7 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
             sq += (a * a + b * b) + (c * c + d * d);
         }
         const float rstd = rsqrtf(warp_sum(sq) * (1.f / C) + 1e-5f);
-        const float* fp = film ? film + (int64_t)R.row_b[r] * film_stride : nullptr;
+        const float* fp = film ? film + (int64_t)b_idx * film_stride : nullptr;
         float4 dxh[V];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
@@ -85,6 +93,9 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
             if (dy2 != nullptr) {
                 const float4 e = reinterpret_cast<const float4*>(dy2 + r * C)[c4];
                 d.x += e.x; d.y += e.y; d.z += e.z; d.w += e.w;
+            }
+            if constexpr (DROP) {           // the forward dropped this LayerNorm's OUTPUT: mask the incoming gradient
+                if (drop.where == LN_DROP_OUT) d = drop_apply4(d, drop.d, drop.site, b_idx, pos, R.n_max, C, c4 * 4);
             }
             if (fp != nullptr) {
                 const float4 fg = reinterpret_cast<const float4*>(fp)[c4];
@@ -101,9 +112,16 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
         }
         const float m1 = warp_sum(s1) * (1.f / C), m2 = warp_sum(s2) * (1.f / C);
 #pragma unroll
-        for (int i = 0; i < V; ++i)
-            orow[lane + 32 * i] = make_float4(rstd * (dxh[i].x - m1 - v[i].x * m2), rstd * (dxh[i].y - m1 - v[i].y * m2),
-                                              rstd * (dxh[i].z - m1 - v[i].z * m2), rstd * (dxh[i].w - m1 - v[i].w * m2));
+        for (int i = 0; i < V; ++i) {
+            const float4 o = make_float4(rstd * (dxh[i].x - m1 - v[i].x * m2), rstd * (dxh[i].y - m1 - v[i].y * m2),
+                                         rstd * (dxh[i].z - m1 - v[i].z * m2), rstd * (dxh[i].w - m1 - v[i].w * m2));
+            orow[lane + 32 * i] = o;
+            if constexpr (DROP) {           // the forward dropped the branch `in`: its gradient is the masked copy
+                if (drop.where == LN_DROP_IN)
+                    reinterpret_cast<float4*>(drop.dvm + r * C)[lane + 32 * i] =
+                        drop_apply4(o, drop.d, drop.site, b_idx, pos, R.n_max, C, (lane + 32 * i) * 4);
+            }
+        }
     }
     // ordered combination of the 8 warps' partial sums
     for (int w = 0; w < 8; ++w) {
@@ -126,9 +144,11 @@ ln_bwd_rows_kernel(const float* __restrict__ in, const float* __restrict__ res, 
     for (int i = threadIdx.x; i < 2 * C; i += 256) part[(int64_t)blockIdx.x * 2 * C + i] = s_acc[i];
 }
 
-// part [S][n] -> out[n] = scale * sum_s part[s][n] (s ascending); S_valid chunks carry data when `total_rows` is given
+// part [S][n] -> out[n] = scale * sum_s part[s][n] (s ascending); S_valid chunks carry data when `total_rows` is given.
+// With out2: columns >= split go to out2[i - split] (two gradients reduced by one launch).
 __global__ void reduce_partials_kernel(const float* __restrict__ part, int S, int64_t n, float* __restrict__ out,
-                                       const int32_t* __restrict__ total_rows, int chunk_rows, float scale) {
+                                       const int32_t* __restrict__ total_rows, int chunk_rows, float scale,
+                                       float* __restrict__ out2, int64_t split) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -140,32 +160,43 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int S, in
     }
     float acc = 0.f;
     for (int s = 0; s < s_lim; ++s) acc += part[(int64_t)s * n + i];
-    out[i] = acc * scale;
+    if (out2 != nullptr && i >= split) out2[i - split] = acc * scale;
+    else out[i] = acc * scale;
 }
 
 int reduce_partials(const float* part, int S, int64_t n, float* out, const int32_t* total_rows, int chunk_rows, float scale,
-                    cudaStream_t s) {
-    DX_LAUNCH_PDL((reduce_partials_kernel), (unsigned)((n + 255) / 256), 256, 0, s, part, S, n, out, total_rows, chunk_rows, scale);
+                    cudaStream_t s, float* out2, int64_t split) {
+    DX_LAUNCH_PDL((reduce_partials_kernel), (unsigned)((n + 255) / 256), 256, 0, s, part, S, n, out, total_rows, chunk_rows, scale,
+                  out2, split);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 int ln_bwd_rows(const float* in, const float* res, const float* g, int C, const float* film, int film_stride, const float* dy1,
-                const float* dy2, const Rows& R, int live_ext, float* dv, float* dg, float* db, float* scratch, cudaStream_t s) {
+                const float* dy2, const Rows& R, int live_ext, float* dv, float* dg, float* db, float* scratch, cudaStream_t s,
+                const LnDrop* drop) {
     const int S = (int)((R.cap + LNB_ROWS - 1) / LNB_ROWS);
     ProfScope prof("ln_bwd", s);
-    if (C == 128)
-        DX_LAUNCH_PDL((ln_bwd_rows_kernel<128>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
+    LnDrop nd;
+    memset(&nd, 0, sizeof(nd));
+    if (drop != nullptr && drop->d.thr != 0) {
+        DX_REQUIRE(drop->where == LN_DROP_OUT || (drop->dvm != nullptr && drop->dvm != dv && drop->dvm != dy1 && drop->dvm != dy2),
+                   "ln_bwd_rows: the masked gradient needs its own buffer");
+        if (C == 128)
+            DX_LAUNCH_PDL((ln_bwd_rows_kernel<128, true>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch, *drop);
+        else if (C == 1024)
+            DX_LAUNCH_PDL((ln_bwd_rows_kernel<1024, true>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch, *drop);
+        else
+            DX_REQUIRE(false, "ln_bwd_rows: unsupported width %d", C);
+    } else if (C == 128)
+        DX_LAUNCH_PDL((ln_bwd_rows_kernel<128, false>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch, nd);
     else if (C == 1024)
-        DX_LAUNCH_PDL((ln_bwd_rows_kernel<1024>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch);
+        DX_LAUNCH_PDL((ln_bwd_rows_kernel<1024, false>), S, 256, 0, s, in, res, g, film, film_stride, dy1, dy2, R, live_ext, dv, scratch, nd);
     else
         DX_REQUIRE(false, "ln_bwd_rows: unsupported width %d", C);
     DX_CHECK_LAUNCH();
-    // part[s] = [dg(C) | db(C)]: one reduction over 2C columns, then split
-    DX_TRY(reduce_partials(scratch, S, 2 * C, scratch + (int64_t)S * 2 * C, R.row_start + R.B, LNB_ROWS, 1.f, s));
-    DX_CHECK_CUDA(cudaMemcpyAsync(dg, scratch + (int64_t)S * 2 * C, C * sizeof(float), cudaMemcpyDeviceToDevice, s));
-    DX_CHECK_CUDA(cudaMemcpyAsync(db, scratch + (int64_t)S * 2 * C + C, C * sizeof(float), cudaMemcpyDeviceToDevice, s));
-    return 0;
+    // part[s] = [dg(C) | db(C)]: one reduction over 2C columns, split between the two gradients
+    return reduce_partials(scratch, S, 2 * C, dg, R.row_start + R.B, LNB_ROWS, 1.f, s, db, C);
 }
 int64_t ln_bwd_scratch_floats(int64_t cap, int C) { return ((cap + LNB_ROWS - 1) / LNB_ROWS + 1) * 2 * C; }
 

@@ -23,6 +23,7 @@ import math
 import torch
 
 from . import _lib
+from .hparams import accent_encoder_params
 from .model import _pos_table
 from .weights import state_dict_spec, strip_module_prefix
 
@@ -112,8 +113,13 @@ def adversarial_weight(hparams, iteration):
 
 
 class TrainEngine:
-    def __init__(self, hparams, state_dict, device="cuda", gemm="fp32"):
-        """``gemm``: "fp32" - every contraction in fp32 SIMT (the 1e-3 gradient-parity mode); "bf16" - the large dense
+    def __init__(self, hparams, state_dict, device="cuda", gemm="fp32", train_mode=False, seed=0):
+        """``train_mode``: ``model.train()`` (train.py:411) - the dropout layers of the three stacks and of the accent
+        encoder's pre-net are active, with the probabilities of ``hparams.{accent_encoder, phoneme_encoder,
+        frame_decoder}``; needs ``gemm="bf16"``.  False = ``model.eval()``: dropout is the identity (the gradient-parity
+        configuration).  ``seed``: the masks of an iteration are a pure function of (seed, iteration, micro-batch index).
+
+        ``gemm``: "fp32" - every contraction in fp32 SIMT (the 1e-3 gradient-parity mode); "bf16" - the large dense
         contractions (forward convs / linears, their dgrad and wgrad) on tcgen05 with bf16 copies of the fp32 operands
         and fp32 accumulation (``DX_TRAIN_TC_GEMM``); LayerNorm, attention, length regulator, loss, reductions and Adam
         stay fp32 either way."""
@@ -123,6 +129,10 @@ class TrainEngine:
             raise ValueError("gemm must be 'fp32' or 'bf16'")
         self.gemm = gemm
         self.hp = hparams
+        self.train_mode = bool(train_mode)
+        self.seed = int(seed)
+        if self.train_mode and gemm != "bf16":
+            raise ValueError("train_mode=True (dropout) is implemented on the gemm='bf16' path only")
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _lib.DxError("TrainEngine needs a CUDA device; there is no CPU fallback")
@@ -198,9 +208,58 @@ class TrainEngine:
             self._ws = torch.empty(n, dtype=torch.uint8, device=self.device)
         return self._ws
 
-    def forward_backward(self, inputs, iteration=1, loss_scale=1.0, forward_only=False, want_mel=False):
+    def dropout_probabilities(self):
+        """(attn_dropout[3], conv_dropout[3]) by stack: accent encoder, phoneme encoder, frame decoder."""
+        stacks = (accent_encoder_params(self.hp), self.hp.phoneme_encoder, self.hp.frame_decoder)
+        return ([float(s.get("attn_dropout", 0.0)) for s in stacks], [float(s.get("conv_dropout", 0.0)) for s in stacks])
+
+    def dropout_seed(self, iteration, micro_batch=0):
+        """64-bit seed of one forward pass: splitmix64 of (seed, iteration, micro-batch, rank), so that consecutive
+        iterations and the ranks of a data-parallel job draw unrelated masks."""
+        rank = 0
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                rank = dist.get_rank()
+        except Exception:        # noqa: BLE001
+            rank = 0
+        m = (1 << 64) - 1
+        z = (self.seed * 0x9E3779B97F4A7C15 + int(iteration) * 0xD1B54A32D192ED03 + int(micro_batch) * 0x8CB92BA72F3D8DD7
+             + rank * 0xABC98388FB8FAC03 + 0x2545F4914F6CDD1D) & m
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & m
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & m
+        return z ^ (z >> 31)
+
+    def dropout_masks(self, B, L_max, T_max, iteration=1, micro_batch=0):
+        """The keep-masks the next ``forward_backward(..., iteration, micro_batch=...)`` applies, in the ORDER the reference's
+        forward reaches its dropout calls (model.py:889-948): accent encoder pre-net x 3, then per stack (accent encoder,
+        phoneme encoder, frame decoder) and block: attention weights (B * 2, n, n), attention output (B, n, 128),
+        feed-forward output (B, n, 128).  Returns a list of (bool tensor on the device, p).  Test / debugging surface."""
+        pa, pc = self.dropout_probabilities()
+        seed = self.dropout_seed(iteration, micro_batch)
+        out = []
+
+        def site(kind, stack, block, p, n, Cdim):
+            shape = (B * 2, n, n) if kind == 3 else (B, n, Cdim)
+            m = torch.empty(shape, dtype=torch.uint8, device=self.device)
+            with torch.cuda.device(self.device):
+                _lib.check(self.lib.dx_dropout_mask(seed, kind, stack, block, float(p), B, n, Cdim, _lib.ptr(m),
+                                                    _lib.stream_ptr(self.device)), "dx_dropout_mask")
+            out.append((m.bool(), float(p)))
+
+        for k, Cdim in enumerate((_lib.CCH, _lib.CCH, _lib.D)):
+            site(2, 0, k, pc[0], T_max, Cdim)
+        for stack, n in ((0, T_max), (1, L_max), (2, T_max)):
+            for blk in range(4):
+                site(3, stack, blk, pa[stack], n, _lib.D)
+                site(0, stack, blk, pa[stack], n, _lib.D)
+                site(1, stack, blk, pc[stack], n, _lib.D)
+        return out
+
+    def forward_backward(self, inputs, iteration=1, loss_scale=1.0, forward_only=False, want_mel=False, micro_batch=0):
         """``inputs``: the 12-tuple of ``DaftExprt.forward`` (targets are a subset of it, model.py:884-885) on the device.
-        Fills ``self.grads`` (this rank's gradients) and returns the 8 loss terms as a device tensor (no sync)."""
+        Fills ``self.grads`` (this rank's gradients) and returns the 8 loss terms as a device tensor (no sync).
+        ``forward_only`` is the validation pass (train.py:155-209, ``model.eval()``): dropout is off there."""
         (symbols, dfl, dint, sen, spi, in_len, fen, fpi, mel, out_len, spk_ids, spk_embs) = inputs
         B, L = symbols.shape
         T = mel.shape[2]
@@ -233,6 +292,11 @@ class TrainEngine:
         mel_out = torch.empty(B, _lib.MEL, T, device=self.device) if want_mel else None
         a.mel_out = None if mel_out is None else mel_out.data_ptr()
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        if self.train_mode and not forward_only:
+            pa, pc = self.dropout_probabilities()
+            for k in range(3):
+                a.attn_dropout[k], a.conv_dropout[k] = pa[k], pc[k]
+            a.dropout_seed = self.dropout_seed(iteration, micro_batch)
         with torch.cuda.device(self.device):
             _lib.check(self.lib.dx_train_step(C.byref(self.W), C.byref(self.G), C.byref(a), _lib.stream_ptr(self.device)),
                        "dx_train_step")
@@ -281,7 +345,7 @@ class TrainEngine:
         total = None
         acc = None
         for k, mb in enumerate(micro_batches):
-            losses = self.forward_backward(mb, iteration, loss_scale=1.0 / n)
+            losses = self.forward_backward(mb, iteration, loss_scale=1.0 / n, micro_batch=k)
             total = losses.clone() if total is None else total + losses
             if n > 1:
                 if acc is None:
