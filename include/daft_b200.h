@@ -57,6 +57,8 @@ int64_t     dx_launch_count(void);
  * key 8: it splits when whole tiles would occupy at most this percentage of the grid (default 0 = 35; 1000 = always);
  * key 15: its timing experiments (wrong results; bit 0 no E2 stores, 1 no P3 stores, 2 no P0 residual, 3 no FiLM);
  * key 16 / 17: training step in tensor-core mode: keep the fp32 attention backward / forward (A/B);
+ * key 18: its weight-gradient kernel's CTA budget per launch (default 0 = 148); key 19: pack each weight where it is used
+ *         instead of all of them in one launch at the start of the step (A/B);
  * key 9: run every FFT block as four launches (QKV, attention, out-proj + LN, FFN) instead of two;
  * key 10: with a trace buffer set, trace only the n-th block-tail launch of a step (1..12; 0 = every launch);
  *         + 100: trace the last working CTA (always a tile owner) instead of CTA 0. */

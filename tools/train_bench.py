@@ -24,6 +24,11 @@ def main():
     mode = sys.argv[2] if len(sys.argv) > 2 else "fp32"
     eng = TrainEngine(hp, sd, gemm=mode)
     print("GEMM mode:", mode)
+    for kv in os.environ.get("DX_KNOBS", "").split(","):        # e.g. DX_KNOBS=18=148
+        if kv:
+            k, v = kv.split("=")
+            _lib.load().dx_set_debug(int(k), int(v))
+            print("knob", k, "=", v)
     for it in range(1, 4):
         eng.step(dev, iteration=it)
     torch.cuda.synchronize()
@@ -46,6 +51,8 @@ def main():
     lib.dx_profile_enable(0)
     print(buf.value.decode())
     print("workspace MB", eng._ws.numel() / 1e6)
+    if os.environ.get("DX_NO_REF"):
+        return
     # the reference, eager, on this GPU
     try:
         from oracle import ref_harness as R

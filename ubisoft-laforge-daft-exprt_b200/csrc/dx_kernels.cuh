@@ -96,6 +96,7 @@ struct TcGemmArgs {
     int live_ext;               // -1: no liveness masking
     // TC_EPI_F32
     float* out_f32;             // [rows][N]
+    const float* relu_mask;     // [rows][N] or null: out = relu_mask > 0 ? out : 0 (training: ReLU backward fused into the dgrad)
     // TC_EPI_BF16 / TC_EPI_LN
     __nv_bfloat16* out_bf;      // [N/8][out_rows_phys][8]
     int64_t out_rows_phys;
@@ -114,6 +115,13 @@ int tc_gemm(const TcGemmArgs& g, const Rows& R, cudaStream_t s);
 int tc_linear(const TcGemmArgs& g, const Rows& R, cudaStream_t s);
 int tc_gemm_plain(const TcGemmArgs& g, int64_t M, cudaStream_t s);   // no row map: rows [0, M) all live
 int pack_weight_bf16(const float* w, int taps, int K, int N, int nt, int ks, __nv_bfloat16* out, cudaStream_t s);
+struct PackEntry {              // one weight of pack_weight_batch; (taps, K, N) are the GEMM's
+    const float* src;
+    __nv_bfloat16* dst;
+    int64_t n_elems;
+    int taps, K, N, nt, ks, transposed;
+};
+int pack_weight_batch(const PackEntry* tab_dev, int n_entries, cudaStream_t s);
 int64_t packed_weight_elems(int taps, int K, int N, int nt, int ks);
 
 }  // namespace dx

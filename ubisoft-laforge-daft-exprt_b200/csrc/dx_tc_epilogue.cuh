@@ -111,6 +111,15 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcGemmArgs& g, const Rows
                 }
                 if constexpr (EPI == TC_EPI_F32) {
                     float* orow = g.out_f32 + r * g.N + nb;
+                    if (g.relu_mask != nullptr && nb + 32 <= g.N) {
+                        const float4* m4 = reinterpret_cast<const float4*>(g.relu_mask + r * g.N + nb);
+#pragma unroll
+                        for (int e = 0; e < 32; e += 4) {
+                            const float4 m = m4[e / 4];
+                            v[e] = m.x > 0.f ? v[e] : 0.f; v[e + 1] = m.y > 0.f ? v[e + 1] : 0.f;
+                            v[e + 2] = m.z > 0.f ? v[e + 2] : 0.f; v[e + 3] = m.w > 0.f ? v[e + 3] : 0.f;
+                        }
+                    }
                     if (nb + 32 <= g.N) {
 #pragma unroll
                         for (int e = 0; e < 32; e += 4)

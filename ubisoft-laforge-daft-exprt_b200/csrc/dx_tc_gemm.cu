@@ -282,6 +282,39 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int taps, int K,
     out[i] = __float2bfloat16(v);
 }
 
+// Many weights in one launch (training step: every dense layer's weight, and its tap-flipped transpose for the data gradient,
+// is packed once per step).  blockIdx.y = entry; an entry with `transposed` packs Wt[tap][n][k] = W[taps - 1 - tap][k][n],
+// i.e. the GEMM's (K, N) are the weight's (N, K).
+__global__ void __launch_bounds__(256) pack_weight_batch_kernel(const PackEntry* __restrict__ tab) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
+    const PackEntry en = tab[blockIdx.y];
+    const int kc = en.ks / 8, nks = en.K / en.ks;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < en.n_elems; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t t = i;
+        const int e = (int)(t % 8); t /= 8;
+        const int n_in = (int)(t % en.nt); t /= en.nt;
+        const int c = (int)(t % kc); t /= kc;
+        const int tap = (int)(t % en.taps); t /= en.taps;
+        const int ksg = (int)(t % nks); t /= nks;
+        const int n_tile = (int)t;
+        const int k = ksg * en.ks + c * 8 + e;
+        const int n = n_tile * en.nt + n_in;
+        float v = 0.f;
+        if (n < en.N)
+            v = en.transposed ? en.src[((int64_t)(en.taps - 1 - tap) * en.N + n) * en.K + k]     // W is [taps][N][K] in GEMM terms
+                              : en.src[((int64_t)tap * en.K + k) * en.N + n];
+        en.dst[i] = __float2bfloat16(v);
+    }
+}
+
+int pack_weight_batch(const PackEntry* tab_dev, int n_entries, cudaStream_t s) {
+    if (n_entries <= 0) return 0;
+    DX_LAUNCH_PDL((pack_weight_batch_kernel), dim3(192, (unsigned)n_entries), 256, 0, s, tab_dev);
+    DX_CHECK_LAUNCH();
+    return 0;
+}
+
 int pack_weight_bf16(const float* w, int taps, int K, int N, int nt, int ks, __nv_bfloat16* out, cudaStream_t s) {
     const int64_t n = packed_weight_elems(taps, K, N, nt, ks);
     DX_REQUIRE(n > 0, "pack_weight_bf16: bad shape taps=%d K=%d N=%d nt=%d ks=%d", taps, K, N, nt, ks);

@@ -29,6 +29,13 @@ struct Carver {
     }
 };
 
+constexpr int TRAIN_MAX_PACKED = 128;
+// bf16 elements of the packed forms of the step's dense weights: per block QKV, out-proj, conv1, conv2; the pre-net's second and
+// third convs; each in forward and transposed form (both have taps * K * N elements: every width is a multiple of 128)
+constexpr int64_t TRAIN_PACKED_ELEMS =
+    2 * (12 * ((int64_t)DX_D * 3 * DX_D + DX_D * DX_D + 2 * (int64_t)DX_TAPS * DX_D * DX_C) + (int64_t)DX_TAPS * DX_C * DX_C +
+         (int64_t)DX_TAPS * DX_C * DX_D);
+
 struct BlockSave {
     float *xin, *qkv, *lse, *o, *t1, *x1, *h, *t2;
     // tensor-core mode: the bf16 channel-interleaved copies the forward's contractions made of their inputs, kept for the
@@ -52,15 +59,29 @@ struct TrainPlan {
     int64_t* out_len;
     // backward
     float *dA, *dB, *dC, *dQKV, *dH1, *dH2, *dmel, *Dr, *wt, *scratch;
+    float *fb_part;
     float *dfilm, *dlogits, *sv, *gat1, *gat2, *lpart, *dpost_reg, *ct, *gd, *gr, *dpre;
     int64_t scratch_floats;
     DropSpec drop_attn[3], drop_conv[3];       // per stack (accent encoder, phoneme encoder, frame decoder); thr = 0: off
+    // DX_TRAIN_TC_GEMM: every dense weight packed to bf16 once per step, forward form and transposed (data gradient) form
+    PackEntry pk[TRAIN_MAX_PACKED];
+    int n_pk;
+    PackEntry* pk_dev;
+    __nv_bfloat16* pk_store;
+    int64_t pk_store_elems;
     // DX_TRAIN_TC_GEMM: bf16 channel-interleaved copies of a GEMM's operands, packed bf16 weight, row stride of the copies
     bool tc;
     __nv_bfloat16 *il_a, *il_g, *w_bf;
     float* wpad;                // zero-padded weight / padded weight gradient (widths that are not multiples of 128)
     int64_t rows_phys;
 };
+
+// the step's pre-packed bf16 form of weight W (forward, or transposed for the data gradient), or null
+const __nv_bfloat16* find_packed(const TrainPlan& p, const float* W, bool transposed) {
+    for (int i = 0; i < p.n_pk; ++i)
+        if (p.pk[i].src == W && (p.pk[i].transposed != 0) == transposed) return p.pk[i].dst;
+    return nullptr;
+}
 
 // out = conv(A, W) (+ bias, ReLU, liveness mask): gemm_f32, or - tensor-core mode - tcgen05 on bf16 copies (dx_train_tc.cu).  An input
 // width that is not a multiple of 128 (the 80 mel channels) is zero-padded in the copies.
@@ -73,15 +94,19 @@ int gemm(const TrainPlan& p, const float* A, int K, const float* W, const float*
     const int nt = (N % 256 == 0) ? 256 : 128, ks = nt == 256 ? 32 : 64;
     __nv_bfloat16* a_il = il_keep ? il_keep : p.il_a;
     DX_TRY(rows_to_il(A, Kp, R, a_il, p.rows_phys, s, K));
-    if (Kp != K) {
-        DX_TRY(copy_pad3(W, taps, K, N, p.wpad, Kp, N, s));
-        W = p.wpad;
+    const __nv_bfloat16* w_bf = find_packed(p, W, false);
+    if (w_bf == nullptr) {
+        if (Kp != K) {
+            DX_TRY(copy_pad3(W, taps, K, N, p.wpad, Kp, N, s));
+            W = p.wpad;
+        }
+        DX_TRY(pack_weight_bf16(W, taps, Kp, N, nt, ks, p.w_bf, s));
+        w_bf = p.w_bf;
     }
-    DX_TRY(pack_weight_bf16(W, taps, Kp, N, nt, ks, p.w_bf, s));
     TcGemmArgs g;
     memset(&g, 0, sizeof(g));
     g.a = a_il; g.a_rows_phys = p.rows_phys; g.K = Kp; g.N = N; g.taps = taps;
-    g.w = p.w_bf; g.nt = nt; g.ks = ks;
+    g.w = w_bf; g.nt = nt; g.ks = ks;
     g.bias = bias; g.relu = relu ? 1 : 0; g.epilogue = TC_EPI_F32; g.live_ext = live_ext;
     g.out_f32 = out; g.tag = "tc_gemm_train";
     return tc_gemm(g, R, s);
@@ -176,6 +201,7 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
     p->scratch_floats = sf;
     p->scratch = c.take<float>(sf);
     p->dfilm = c.take<float>((int64_t)B * 8 * 256);
+    p->fb_part = c.take<float>(film_bwd_scratch_floats(B));
     p->dlogits = c.take<float>((int64_t)B * (n_speakers > 0 ? n_speakers : 1));
     p->sv = c.take<float>((int64_t)B * SB_STRIDE);
     p->gat1 = c.take<float>((int64_t)B * 1024);
@@ -189,6 +215,8 @@ int train_layout(TrainPlan* p, int B, int L_max, int T_max, int n_speakers, void
     p->il_a = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
     p->il_g = c.take<__nv_bfloat16>(p->rows_phys * DX_C);
     p->w_bf = c.take<__nv_bfloat16>((int64_t)DX_TAPS * DX_C * DX_C);
+    p->pk_dev = c.take<PackEntry>(TRAIN_MAX_PACKED);
+    p->pk_store = c.take<__nv_bfloat16>(TRAIN_PACKED_ELEMS);
     p->wpad = c.take<float>((int64_t)DX_TAPS * DX_C * DX_C);
     p->bytes = round_up(c.off, 256);
     if (ws != nullptr) {
@@ -243,11 +271,13 @@ int dgrad(const TrainPlan& p, const float* dY, int N_out, const float* W, int K_
 // Backward of one conv / linear layer y = conv(act, W): dW = wgrad(act, G) and dX = dgrad(G).  In tensor-core mode the bf16 copy
 // of G serves both contractions (B operand of the weight gradient, A operand of the data gradient).
 // act_il: the forward's bf16 copy of `act` when it was kept (gemm's il_keep)
+// relu_src: `act` is the output of a ReLU whose input gradient is wanted: dX = (act > 0) * dgrad (fused into the dgrad's epilogue)
 int conv_bwd(const TrainPlan& p, const float* act, int K, const float* Gr, int N, const float* W, int taps, const Rows& R, float* dW,
-             float* dX, cudaStream_t s, const __nv_bfloat16* act_il = nullptr) {
+             float* dX, cudaStream_t s, const __nv_bfloat16* act_il = nullptr, bool relu_src = false) {
     if (!(p.tc && K % 128 == 0 && N % 128 == 0 && K <= 1024 && N <= 1024)) {
         DX_TRY(wgrad(p, act, K, Gr, N, taps, R, dW, s));
-        return dgrad(p, Gr, N, W, K, taps, R, dX, nullptr, s);
+        DX_TRY(dgrad(p, Gr, N, W, K, taps, R, dX, nullptr, s));
+        return relu_src ? relu_bwd(dX, act, R.cap * K, s) : 0;
     }
     if (act_il == nullptr) {
         DX_TRY(rows_to_il(act, K, R, p.il_a, p.rows_phys, s));
@@ -255,15 +285,20 @@ int conv_bwd(const TrainPlan& p, const float* act, int K, const float* Gr, int N
     }
     DX_TRY(rows_to_il(Gr, N, R, p.il_g, p.rows_phys, s));
     DX_TRY(wgrad_tc(act_il, K, p.il_g, N, taps, R, p.rows_phys, dW, p.scratch, s));
-    DX_TRY(transpose_weight(W, taps, K, N, p.wt, s));
     const int nt = (K % 256 == 0) ? 256 : 128, ks = nt == 256 ? 32 : 64;
-    DX_TRY(pack_weight_bf16(p.wt, taps, N, K, nt, ks, p.w_bf, s));
+    const __nv_bfloat16* w_bf = find_packed(p, W, true);
+    if (w_bf == nullptr) {
+        DX_TRY(transpose_weight(W, taps, K, N, p.wt, s));
+        DX_TRY(pack_weight_bf16(p.wt, taps, N, K, nt, ks, p.w_bf, s));
+        w_bf = p.w_bf;
+    }
     TcGemmArgs g;
     memset(&g, 0, sizeof(g));
     g.a = p.il_g; g.a_rows_phys = p.rows_phys; g.K = N; g.N = K; g.taps = taps;
-    g.w = p.w_bf; g.nt = nt; g.ks = ks;
+    g.w = w_bf; g.nt = nt; g.ks = ks;
     g.epilogue = TC_EPI_F32; g.live_ext = -1;
     g.out_f32 = dX; g.tag = "tc_gemm_train";
+    g.relu_mask = relu_src ? act : nullptr;
     return tc_gemm(g, R, s);
 }
 
@@ -295,11 +330,10 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
         const LnDrop d2{dc, drop_site(DROP_FFN_OUT, stack, i), LN_DROP_IN, p.dH2};
         const LnDrop d1{da, drop_site(DROP_ATTN_OUT, stack, i), LN_DROP_IN, p.dH2};
         DX_TRY(ln_bwd_rows(b.t2, b.x1, bw.ln2_g, DX_D, fp, 8 * 256, dy1, dy2, R, 0, A, G(g.ln2_g), G(g.ln2_b), p.scratch, s, &d2));
-        if (film) DX_TRY(film_bwd(b.t2, b.x1, bw.ln2_g, bw.ln2_b, dy1, dy2, R, dfilm + (film_block0 + i) * 256, 8 * 256, s));
+        if (film) DX_TRY(film_bwd(b.t2, b.x1, bw.ln2_g, bw.ln2_b, dy1, dy2, R, dfilm + (film_block0 + i) * 256, 8 * 256, p.fb_part, s));
         const float* dT2 = dc.thr ? p.dH2 : A;
         DX_TRY(colsum_rows(dT2, DX_D, R, G(g.b_c2), p.scratch, s));
-        DX_TRY(conv_bwd(p, b.h, DX_C, dT2, DX_D, bw.w_c2, DX_TAPS, R, G(g.w_c2), p.dH1, s, tcs ? b.h_il : nullptr));
-        DX_TRY(relu_bwd(p.dH1, b.h, R.cap * DX_C, s));
+        DX_TRY(conv_bwd(p, b.h, DX_C, dT2, DX_D, bw.w_c2, DX_TAPS, R, G(g.w_c2), p.dH1, s, tcs ? b.h_il : nullptr, true));
         // conv1
         DX_TRY(colsum_rows(p.dH1, DX_C, R, G(g.b_c1), p.scratch, s));
         DX_TRY(conv_bwd(p, b.x1, DX_D, p.dH1, DX_C, bw.w_c1, DX_TAPS, R, G(g.w_c1), Bf, s, tcs ? b.x1_il : nullptr));   // Bf = d x1 through the FFN
@@ -364,6 +398,35 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     Rows RL{p.l_row_start, p.l_row_b, p.l_row_p, a.input_lengths, B, a.L_max, p.cap_l};
     DX_TRY(build_rows(a.output_lengths, B, a.T_max, p.t_row_start, p.t_row_b, p.t_row_p, p.cap_t, s));
     DX_TRY(build_rows(a.input_lengths, B, a.L_max, p.l_row_start, p.l_row_b, p.l_row_p, p.cap_l, s));
+
+    if (p.tc && !debug_knob(19)) {
+        // pack every dense weight (forward form, and transposed for the data gradient) in ONE launch; knob 19: per use, as before
+        auto add = [&](const float* W, int taps, int K, int N) {
+            for (int tr = 0; tr < 2; ++tr) {
+                PackEntry& e = p.pk[p.n_pk++];
+                e.src = W; e.transposed = tr; e.taps = taps;
+                e.K = tr ? N : K; e.N = tr ? K : N;
+                e.nt = (e.N % 256 == 0) ? 256 : 128; e.ks = e.nt == 256 ? 32 : 64;
+                e.n_elems = packed_weight_elems(taps, e.K, e.N, e.nt, e.ks);
+                e.dst = p.pk_store + p.pk_store_elems;
+                p.pk_store_elems += e.n_elems;
+            }
+        };
+        const DxBlockWeights* stacks[3] = {w.ae_blocks, w.pe_blocks, w.fd_blocks};
+        for (int k = 0; k < 3; ++k)
+            for (int i = 0; i < 4; ++i) {
+                const DxBlockWeights& bw = stacks[k][i];
+                add(bw.w_qkv, 1, DX_D, 3 * DX_D);
+                add(bw.w_out, 1, DX_D, DX_D);
+                add(bw.w_c1, DX_TAPS, DX_D, DX_C);
+                add(bw.w_c2, DX_TAPS, DX_C, DX_D);
+            }
+        add(w.ae_c1_w, DX_TAPS, DX_C, DX_C);
+        add(w.ae_c2_w, DX_TAPS, DX_C, DX_D);
+        DX_REQUIRE(p.n_pk <= TRAIN_MAX_PACKED && p.pk_store_elems <= TRAIN_PACKED_ELEMS, "train: packed-weight table overflow");
+        DX_CHECK_CUDA(cudaMemcpyAsync(p.pk_dev, p.pk, sizeof(PackEntry) * p.n_pk, cudaMemcpyHostToDevice, s));
+        DX_TRY(pack_weight_batch(p.pk_dev, p.n_pk, s));
+    }
 
     // ======================================= forward (model.py:889-948) =======================================
     DX_TRY(lenreg_scan(a.durations_int, B, a.L_max, false, nullptr, p.mu, p.out_len, nullptr, s));

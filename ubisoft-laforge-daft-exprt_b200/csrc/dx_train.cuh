@@ -22,7 +22,8 @@ int ln_bwd_rows(const float* in, const float* res, const float* g, int C, const 
                 const LnDrop* drop = nullptr);
 int64_t ln_bwd_scratch_floats(int64_t cap, int C);
 int film_bwd(const float* in, const float* res, const float* g, const float* bta, const float* dy1, const float* dy2,
-             const Rows& R, float* dfilm, int film_stride, cudaStream_t s);
+             const Rows& R, float* dfilm, int film_stride, float* scratch, cudaStream_t s);
+int64_t film_bwd_scratch_floats(int B);
 int colsum_rows(const float* in, int N, const Rows& R, float* out, float* scratch, cudaStream_t s);
 int64_t colsum_scratch_floats(int64_t cap, int N);
 int wgrad_f32(const float* A, int K, const float* G, int N, int taps, const Rows& R, float* dW, float* scratch, cudaStream_t s);

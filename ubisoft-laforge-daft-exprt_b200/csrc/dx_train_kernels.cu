@@ -164,8 +164,49 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int S, in
     else out[i] = acc * scale;
 }
 
+// Same result layout, for FEW columns and MANY partials (bias sums, LayerNorm gains: n <= a few thousand, S in the hundreds): a
+// thread per column would walk all S partials alone (one CTA busy, S dependent steps).  Here 16 lanes share a column (lane l adds
+// partials l, l + 16, ... in ascending order) and lane 0 adds the 16 lane sums in lane order: a different, still fixed, summation
+// order.
+constexpr int RP_LANES = 16;
+__global__ void __launch_bounds__(32 * RP_LANES)
+reduce_partials_lanes_kernel(const float* __restrict__ part, int S, int64_t n, float* __restrict__ out,
+                             const int32_t* __restrict__ total_rows, int chunk_rows, float scale, float* __restrict__ out2,
+                             int64_t split) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
+    __shared__ float s_acc[RP_LANES][33];
+    const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * 32 + c;
+    int s_lim = S;
+    if (total_rows != nullptr) {
+        const int v = (int)((*total_rows + chunk_rows - 1) / chunk_rows);
+        s_lim = v < S ? v : S;
+    }
+    float acc = 0.f;
+    if (i < n) {
+#pragma unroll 4
+        for (int s = l; s < s_lim; s += RP_LANES) acc += part[(int64_t)s * n + i];
+    }
+    s_acc[l][c] = acc;
+    __syncthreads();
+    if (l == 0 && i < n) {
+        float t = s_acc[0][c];
+#pragma unroll
+        for (int k = 1; k < RP_LANES; ++k) t += s_acc[k][c];
+        if (out2 != nullptr && i >= split) out2[i - split] = t * scale;
+        else out[i] = t * scale;
+    }
+}
+
 int reduce_partials(const float* part, int S, int64_t n, float* out, const int32_t* total_rows, int chunk_rows, float scale,
                     cudaStream_t s, float* out2, int64_t split) {
+    if (n <= 8192 && S >= 2 * RP_LANES) {
+        DX_LAUNCH_PDL((reduce_partials_lanes_kernel), (unsigned)((n + 31) / 32), 32 * RP_LANES, 0, s, part, S, n, out, total_rows,
+                      chunk_rows, scale, out2, split);
+        DX_CHECK_LAUNCH();
+        return 0;
+    }
     DX_LAUNCH_PDL((reduce_partials_kernel), (unsigned)((n + 255) / 256), 256, 0, s, part, S, n, out, total_rows, chunk_rows, scale,
                   out2, split);
     DX_CHECK_LAUNCH();
@@ -202,12 +243,16 @@ int64_t ln_bwd_scratch_floats(int64_t cap, int C) { return ((cap + LNB_ROWS - 1)
 
 // =========================================================================================================
 // film_bwd (C = 128): dfilm[b] = [ sum_rows dy * z | sum_rows dy ],  z = g * xh + b (the LayerNorm output FiLM scales).
-// One CTA per utterance; warp w takes the utterance's rows w, w + 8, ...; ordered combination of the warps.
+// CTA (b, y) takes the utterance's rows y * 8 + w, + 8 FB_SLICES, ... (w = warp) and writes one partial [256]; the warps are
+// combined in warp order and the FB_SLICES partials in slice order (film_bwd_finish): a fixed summation order.  (One CTA per
+// utterance - 32 CTAs on 148 SMs, each walking up to 750 rows - took 67 us per launch.)
 // =========================================================================================================
+constexpr int FB_SLICES = 8;
+
 __global__ void __launch_bounds__(256)
 film_bwd_kernel(const float* __restrict__ in, const float* __restrict__ res, const float* __restrict__ g,
                 const float* __restrict__ bta, const float* __restrict__ dy1, const float* __restrict__ dy2, Rows R,
-                float* __restrict__ dfilm, int film_stride) {
+                float* __restrict__ part) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
     __shared__ __align__(16) float s_acc[256];
@@ -216,7 +261,7 @@ film_bwd_kernel(const float* __restrict__ in, const float* __restrict__ res, con
     const int64_t rs = R.row_start[b];
     const float4 gg = reinterpret_cast<const float4*>(g)[lane], bb = reinterpret_cast<const float4*>(bta)[lane];
     float4 ag = make_float4(0.f, 0.f, 0.f, 0.f), ab = ag;
-    for (int p = warp; p < len; p += 8) {
+    for (int p = blockIdx.y * 8 + warp; p < len; p += 8 * FB_SLICES) {
         const int64_t r = rs + p;
         float4 v = reinterpret_cast<const float4*>(in + r * DX_D)[lane];
         if (res != nullptr) {
@@ -249,12 +294,27 @@ film_bwd_kernel(const float* __restrict__ in, const float* __restrict__ res, con
         }
         __syncthreads();
     }
-    dfilm[(int64_t)b * film_stride + threadIdx.x] = s_acc[threadIdx.x];
+    part[((int64_t)blockIdx.y * gridDim.x + b) * 256 + threadIdx.x] = s_acc[threadIdx.x];
 }
 
+__global__ void __launch_bounds__(256)
+film_bwd_finish_kernel(const float* __restrict__ part, int B, float* __restrict__ dfilm, int film_stride) {
+    ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
+    ptx::griddep_launch();    // let the next kernel start launching
+    const int b = blockIdx.x;
+    float acc = 0.f;
+#pragma unroll
+    for (int y = 0; y < FB_SLICES; ++y) acc += part[((int64_t)y * B + b) * 256 + threadIdx.x];
+    dfilm[(int64_t)b * film_stride + threadIdx.x] = acc;
+}
+
+int64_t film_bwd_scratch_floats(int B) { return (int64_t)FB_SLICES * B * 256; }
+
 int film_bwd(const float* in, const float* res, const float* g, const float* bta, const float* dy1, const float* dy2,
-             const Rows& R, float* dfilm, int film_stride, cudaStream_t s) {
-    DX_LAUNCH_PDL((film_bwd_kernel), R.B, 256, 0, s, in, res, g, bta, dy1, dy2, R, dfilm, film_stride);
+             const Rows& R, float* dfilm, int film_stride, float* scratch, cudaStream_t s) {
+    DX_LAUNCH_PDL((film_bwd_kernel), dim3((unsigned)R.B, FB_SLICES), 256, 0, s, in, res, g, bta, dy1, dy2, R, scratch);
+    DX_CHECK_LAUNCH();
+    DX_LAUNCH_PDL((film_bwd_finish_kernel), R.B, 256, 0, s, scratch, R.B, dfilm, film_stride);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -259,7 +259,11 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WgradTcPa
 
 static int wgrad_tc_splits(int K, int N) {
     const int tiles = (K / 128) * (N / 128);
-    int S = 296 / tiles;
+    // CTAs per launch.  One per SM: with two (296) every CTA's share of the rows halves while its fixed cost - TMEM allocation, the
+    // transposed fp32 dump of its 3 x 128 x 128 partial tile and the partial's trip through reduce_partials - does not (measured,
+    // B = 32 step: 296 -> 8.14 ms, 222 -> 8.15, 148 -> 7.77).  Debug knob 18 overrides.
+    const int budget = debug_knob(18) > 0 ? debug_knob(18) : 148;
+    int S = budget / tiles;
     if (S < 1) S = 1;
     if (S > 64) S = 64;
     return S;
