@@ -7,7 +7,8 @@
 // in model.py:165,187,206-217,546,649-671 under train.py:434.
 //
 // rows_to_il: fp32 [rows][C] -> the bf16 channel-interleaved layout [C/8][rows_phys][8] of the inference kernels (DESIGN.md
-// section 3), zero halo in front, zeros from the stream's total row count to the end: the buffer may hold anything before.
+// section 3), zero halo in front, zeros for DX_TAIL rows behind the stream's total row count (no reader goes further): the buffer
+// may hold anything before.
 //
 // wgrad_tc_kernel: the reduction runs over ROWS, so both operands are "MN-major" for the tensor core, and the interleaved
 // layout is exactly the no-swizzle MN-major canonical layout with rows as K (the way attention feeds V): for one 8-channel
@@ -31,6 +32,9 @@ rows_to_il_kernel(const float* __restrict__ src, int C, int C_src, const int32_t
     __shared__ __align__(16) __nv_bfloat16 tile[32][128 + 8];
     const int64_t total = *total_ptr;
     const int64_t pr0 = (int64_t)blockIdx.x * 32;        // physical row of the tile: stream row = physical - DX_HALO
+    // readers (GEMM row tiles of 128 + taps, 64-row weight-gradient stages, attention key tiles) stop within DX_TAIL rows of the
+    // stream's end; the buffer is sized for the worst case (every utterance at full length), typically 1.5-8x the stream
+    if (pr0 >= DX_HALO + total + DX_TAIL) return;
     const int c0 = blockIdx.y * 128;
     const int t = threadIdx.x;
 #pragma unroll
