@@ -108,8 +108,8 @@ typedef struct {
     /* speaker projection + classifier + style adapter (model.py:719-830, 855-856) */
     const float *spk_w, *spk_b;                                           /* [128][192] (torch layout) */
     const float *cls_w1, *cls_b1, *cls_w2, *cls_b2, *cls_w3, *cls_b3;     /* torch layouts */
-    const float *film_g_w, *film_g_b, *film_b_w, *film_b_b;               /* [1024][128], [1024] */
-    const float *post_mult;                                               /* [2][8] or NULL (== 1.0) */
+    const float *film_g_w, *film_g_b, *film_b_w, *film_b_b;               /* [1024][128], [1024] (default block counts) */
+    const float *post_mult;                                               /* [2][8] (default) or NULL (== 1.0) */
     /* phoneme encoder (model.py:567-610) */
     const float *symbols_embedding;                                       /* [n_symbols][128] */
     DxBlockWeights pe_blocks[4];
@@ -123,6 +123,11 @@ typedef struct {
     /* shared */
     const float *pos_table;                                               /* [5000][128], model.py:126-130 */
     int32_t n_symbols, n_speakers, pos_rows, pad_;
+    /* FFT blocks per stack, 1..4 each (hparams.{accent_encoder, phoneme_encoder, frame_decoder}['nb_blocks']); 0 = 4, the
+     * reference's default.  With P = n_pe_blocks and F = n_fd_blocks the style adapter predicts (P + F) * 128 gammas and
+     * betas (film_g_w / film_b_w are [(P + F) * 128][128], model.py:731-747), post_mult is [2][P + F], and block i of the
+     * decoder uses FiLM row P + i of the (B, 8, 256) film output.  The training step supports 4 / 4 / 4 only. */
+    int32_t n_ae_blocks, n_pe_blocks, n_fd_blocks, pad2_;
 } DxModelWeights;
 
 /* Pack an fp32 GEMM-layout weight [taps][K][N] into the bf16 tile layout the tensor-core kernels stream with
@@ -148,7 +153,7 @@ typedef struct {
     /* outputs */
     float   *accent_emb;               /* (B, 128)      */
     float   *speaker_preds;            /* (B, n_speakers) or NULL */
-    float   *film;                     /* (B, 8, 256): blocks 0-3 phoneme encoder, 4-7 frame decoder */
+    float   *film;                     /* (B, 8, 256): rows 0..P-1 phoneme encoder, P..P+F-1 frame decoder (P = F = 4 by default) */
     float   *enc_out;                  /* (B, L_max, 128) phoneme-encoder output or NULL (debug/tests) */
     float   *mel_out;                  /* (B, 80, T_max) */
     float   *weights_out;              /* (B, L_max, T_max) alignments */

@@ -76,3 +76,29 @@ def record(key, value):
         json.dump(old, open(path, "w"), indent=1, sort_keys=True)
     except (OSError, ValueError):
         pass
+
+
+# ---- architectures with other block counts / an accent_encoder sub-dict of its own (tests/golden/make_arch_golden.py) ----
+import make_arch_golden as MA                             # noqa: E402
+
+
+def arch_case(name):
+    """-> (hparams, state dict, forward batch, inference tuple or None, golden dict)"""
+    hp = MA.arch_hparams(name)
+    key = ("arch", name)
+    if key not in _SD:
+        _SD[key] = make_state_dict(hp, MG.WEIGHT_SEED)
+    sd = _SD[key]
+    fkw, ikw = MA.ARCH_CASES[name][3:5]
+    batch = synthetic.forward_batch(hp, **fkw)
+    g = load_golden(name)
+    assert str(g["inputs_digest"]) == MG.inputs_digest(batch), "synthetic generator drifted"
+    assert str(g["weights_digest"]) == MG.weights_digest(sd), "weight generator drifted"
+    inf = None
+    if ikw is not None:
+        kw = dict(ikw)
+        inputs, prosody, ext_emb, acc_emb = synthetic.inference_batch(hp, **kw)
+        dig = MG.inputs_digest(list(inputs) + [prosody[k] for k in sorted(prosody)] + [ext_emb, acc_emb])
+        assert str(g["inf_inputs_digest"]) == dig, "synthetic generator drifted"
+        inf = (kw["pitch_transform"], inputs, prosody, ext_emb, acc_emb)
+    return hp, sd, batch, inf, g

@@ -12,6 +12,7 @@ MODE_F32, MODE_BF16 = 0, 1
 IO_PACKED_FRAMES, IO_PACKED_MEL_OUT = 1, 2
 GAP, HALO, TAIL = 3, 8, 264
 D, HEADS, DH, CCH, TAPS, MEL, MEL_PAD, SPK = 128, 2, 64, 1024, 3, 80, 96, 192
+MAX_BLOCKS = 4          # FFT blocks per stack: DxModelWeights holds 4 slots (1..4 used)
 
 _p = C.c_void_p
 
@@ -40,6 +41,7 @@ class DxModelWeights(C.Structure):
         + [("fd_blocks", DxBlockWeights * 4)]
         + [(n, _p) for n in ("mel_w", "mel_b", "mel_w_bf", "pos_table")]
         + [("n_symbols", C.c_int32), ("n_speakers", C.c_int32), ("pos_rows", C.c_int32), ("pad_", C.c_int32)]
+        + [("n_ae_blocks", C.c_int32), ("n_pe_blocks", C.c_int32), ("n_fd_blocks", C.c_int32), ("pad2_", C.c_int32)]
     )
 
 

@@ -147,15 +147,15 @@ static int fft_block_bf16(const DxBlockWeights& bw, const Plan& p, const Rows& R
 // row stream in p.xb, result back in p.xb.  Two launches per block: attention, then ONE kernel for out-proj + LN1 +
 // FFN + LN2/FiLM + the next block's QKV projection; the stack's first QKV projection is its own launch.  The block
 // input and output alternate between p.xb and p.yb (neighbouring tiles read the input rows as residual halos).
-static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Rows& R, const float* film, int film_block0,
-                          const char* tag, cudaStream_t s) {
+static int fft_stack_bf16(const DxBlockWeights* blocks, int n_blocks, const Plan& p, const Rows& R, const float* film,
+                          int film_block0, const char* tag, cudaStream_t s) {
     if (debug_knob(9) || debug_knob(3)) {
-        for (int i = 0; i < 4; ++i) DX_TRY(fft_block_bf16(blocks[i], p, R, film, film_block0 + i, s));
+        for (int i = 0; i < n_blocks; ++i) DX_TRY(fft_block_bf16(blocks[i], p, R, film, film_block0 + i, s));
         return 0;
     }
     const int64_t rp = p.rows_phys;
     __nv_bfloat16 *cur = p.xb, *nxt = p.yb;
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < n_blocks; ++i) {
         const DxBlockWeights& bw = blocks[i];
         DX_REQUIRE(bw.w_qkv_bf && bw.w_out_bf && bw.w_ffn1_bf && bw.w_ffn2_bf, "bf16 mode: packed weights missing (model not prepared for DX_MODE_BF16)");
         if (i == 0) {
@@ -166,14 +166,16 @@ static int fft_stack_bf16(const DxBlockWeights* blocks, const Plan& p, const Row
         DX_TRY(attention_bf16(p.qkvb, p.ob, rp, R, s));
         FfnFuse f;
         f.attn = p.ob; f.x_in = cur;
-        f.next = i < 3 ? &blocks[i + 1] : nullptr;
-        f.qkv_out = i < 3 ? p.qkvb : nullptr;
+        f.next = i < n_blocks - 1 ? &blocks[i + 1] : nullptr;
+        f.qkv_out = i < n_blocks - 1 ? p.qkvb : nullptr;
         f.tag = tag;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
         const FfnSplit sp = p.ffn_split();
         DX_TRY(ffn_bf16(nullptr, nxt, rp, bw, fp, 8 * 256, R, s, &f, &sp));
         __nv_bfloat16* t = cur; cur = nxt; nxt = t;
     }
+    // an odd number of blocks leaves the result in p.yb: the consumers read p.xb
+    if (cur != p.xb) DX_CHECK_CUDA(cudaMemcpyAsync(p.xb, cur, (size_t)rp * DX_D * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, s));
     return 0;
 }
 
@@ -208,7 +210,7 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         DX_TRY(ln_rows_f32(p.tmp, nullptr, w.ae_ln2_g, w.ae_ln2_b, DX_D, nullptr, 0, RT, 0, p.o, s));
         DX_TRY(accent_input(p.o, nullptr, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
                             w.ae_pitch_b, w.pos_table, RT, p.x, nullptr, 0, s, packed_frames));
-        for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.ae_blocks[i], p, RT, nullptr, 0, s));
+        for (int i = 0; i < n_blocks_of(w.n_ae_blocks); ++i) DX_TRY(fft_block_f32(w.ae_blocks[i], p, RT, nullptr, 0, s));
         DX_TRY(masked_mean(p.x, nullptr, 0, RT, accent_emb, s));
     } else {
         const int64_t rp = p.rows_phys;
@@ -233,7 +235,7 @@ int run_accent_encoder(const DxModelWeights& w, const Plan& p, const Rows& RT, c
         }
         DX_TRY(accent_input(nullptr, p.ob, frames_energy, frames_pitch, w.ae_energy_w, w.ae_energy_b, w.ae_pitch_w,
                             w.ae_pitch_b, w.pos_table, RT, nullptr, p.xb, rp, s, packed_frames));
-        DX_TRY(fft_stack_bf16(w.ae_blocks, p, RT, nullptr, 0, "tc_block_tail_frames", s));
+        DX_TRY(fft_stack_bf16(w.ae_blocks, n_blocks_of(w.n_ae_blocks), p, RT, nullptr, 0, "tc_block_tail_frames", s));
         DX_TRY(masked_mean(nullptr, p.xb, rp, RT, accent_emb, s));
     }
     return 0;
@@ -250,6 +252,9 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
                "dx_forward: symbol-side inputs required");
     DX_REQUIRE(a.film && a.mel_out && a.weights_out && a.output_lengths_out, "dx_forward: film / mel_out / weights_out / output_lengths_out required");
     DX_REQUIRE((a.io_flags & ~(DX_IO_PACKED_FRAMES | DX_IO_PACKED_MEL_OUT)) == 0, "dx_forward: unknown io_flags 0x%x", a.io_flags);
+    DX_REQUIRE(w.n_ae_blocks >= 0 && w.n_ae_blocks <= 4 && w.n_pe_blocks >= 0 && w.n_pe_blocks <= 4 && w.n_fd_blocks >= 0 &&
+                   w.n_fd_blocks <= 4, "dx_forward: block counts %d / %d / %d out of range (1..4, 0 = 4)", w.n_ae_blocks,
+               w.n_pe_blocks, w.n_fd_blocks);
     const bool bf = a.mode == DX_MODE_BF16;
     const int64_t rp = p.rows_phys;
     if (bf) DX_TRY(zero_plan_halos(p, s));
@@ -280,8 +285,9 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     // 5. phoneme encoder
     DX_TRY(embed_symbols(a.symbols, w.symbols_embedding, w.n_symbols, w.pos_table, RL, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
-    if (bf) DX_TRY(fft_stack_bf16(w.pe_blocks, p, RL, a.film, 0, "tc_block_tail_symbols", s));
-    else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.pe_blocks[i], p, RL, a.film, i, s));
+    const int n_pe = n_blocks_of(w.n_pe_blocks), n_fd = n_blocks_of(w.n_fd_blocks);
+    if (bf) DX_TRY(fft_stack_bf16(w.pe_blocks, n_pe, p, RL, a.film, 0, "tc_block_tail_symbols", s));
+    else for (int i = 0; i < n_pe; ++i) DX_TRY(fft_block_f32(w.pe_blocks[i], p, RL, a.film, i, s));
     if (a.enc_out) DX_TRY(unpack_rows(bf ? nullptr : p.x, bf ? p.xb : nullptr, rp, RL, a.enc_out, s));
     // 6. length regulator → decoder input rows (x + P, masked)
     DX_TRY(lenreg_symbols(bf ? nullptr : p.x, bf ? p.xb : nullptr, rp, RL, a.durations_float, a.symbols_energy,
@@ -289,8 +295,8 @@ int run_forward(const DxModelWeights& w, const DxForwardArgs& a, cudaStream_t s)
     DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, a.weights_out, bf ? nullptr : p.x,
                          bf ? p.xb : nullptr, rp, s));
     // 7. frame decoder
-    if (bf) DX_TRY(fft_stack_bf16(w.fd_blocks, p, RT, a.film, 4, "tc_block_tail_frames", s));
-    else for (int i = 0; i < 4; ++i) DX_TRY(fft_block_f32(w.fd_blocks[i], p, RT, a.film, 4 + i, s));
+    if (bf) DX_TRY(fft_stack_bf16(w.fd_blocks, n_fd, p, RT, a.film, n_pe, "tc_block_tail_frames", s));
+    else for (int i = 0; i < n_fd; ++i) DX_TRY(fft_block_f32(w.fd_blocks[i], p, RT, a.film, n_pe + i, s));
     if (bf) {
         DX_REQUIRE(w.mel_w_bf, "bf16 mode: packed mel projection missing");
         TcGemmArgs g = tc_args(p.xb, rp, DX_D, DX_MEL, 1, w.mel_w_bf, 128, 64, w.mel_b, 0, TC_EPI_F32, -1);

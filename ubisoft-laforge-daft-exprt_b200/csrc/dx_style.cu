@@ -16,7 +16,8 @@ __device__ __forceinline__ float dot_row_128(const float* __restrict__ wrow, con
 
 // Reference: model.py:904-905 (F.normalize p=2 eps 1e-12 + spk_projection), :919 (accent + spk),
 // StyleAdapter.forward :764-806, SpeakerClassifier.forward :829-830 (GRL is the identity in forward).
-// Grid (B, 9): blockIdx.y = 0..7 → FiLM block (128 gammas + 128 betas), 8 → speaker classifier.  Every CTA
+// Grid (B, n_film + 1): blockIdx.y = 0..n_film-1 → FiLM block (128 gammas + 128 betas; n_film = phoneme-encoder + decoder
+// blocks, 8 by default), n_film → speaker classifier.  Every CTA
 // recomputes the 128-wide conditioning vector (24 K MACs) rather than synchronising across CTAs.
 __global__ void __launch_bounds__(256)
 style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_emb_in,
@@ -31,9 +32,10 @@ style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_e
     __shared__ __align__(16) float s_h2[DX_D];
     __shared__ float s_red[8];
     const int b = blockIdx.x, job = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_film = (int)gridDim.y - 1;
 
     if (tid < DX_D) s_a[tid] = accent[b * DX_D + tid];
-    if (job == 8) {
+    if (job == n_film) {
         if (speaker_preds == nullptr) return;
         __syncthreads();
         for (int n = warp; n < DX_D; n += 8) {
@@ -81,7 +83,7 @@ style_kernel(const float* __restrict__ spk_embs, const float* __restrict__ spk_e
     __syncthreads();
     // FiLM block `job`: outputs n = 128*job + i.  Each warp owns 16 outputs, 4 at a time for load-level parallelism.
     const float pg = w.post_mult ? w.post_mult[job] : 1.f;
-    const float pb = w.post_mult ? w.post_mult[8 + job] : 1.f;
+    const float pb = w.post_mult ? w.post_mult[n_film + job] : 1.f;
     const float4 x = reinterpret_cast<const float4*>(s_c)[lane];
     for (int i0 = warp * 16; i0 < warp * 16 + 16; i0 += 4) {
         float g[4], q[4];
@@ -112,7 +114,8 @@ int style(const DxModelWeights* w, int B, const float* spk_embs, const float* sp
           float* film, float* speaker_preds, cudaStream_t s) {
     DX_REQUIRE(spk_embs != nullptr || spk_emb_in != nullptr, "style: speaker embeddings required");
     ProfScope prof("style", s);
-    DX_LAUNCH_PDL((style_kernel), dim3(B, 9), 256, 0, s, spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
+    const int n_film = n_blocks_of(w->n_pe_blocks) + n_blocks_of(w->n_fd_blocks);
+    DX_LAUNCH_PDL((style_kernel), dim3(B, n_film + 1), 256, 0, s, spk_embs, spk_emb_in, accent, *w, film, speaker_preds);
     DX_CHECK_LAUNCH();
     return 0;
 }

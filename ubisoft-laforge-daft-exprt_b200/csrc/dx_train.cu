@@ -376,6 +376,8 @@ int64_t train_workspace_bytes(int B, int L_max, int T_max) {
 int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTrainArgs& a, cudaStream_t s) {
     TrainPlan p;
     DX_REQUIRE(w.n_speakers >= 1 && w.n_speakers <= 64, "train: n_speakers=%d out of range (1..64)", w.n_speakers);
+    DX_REQUIRE(n_blocks_of(w.n_ae_blocks) == 4 && n_blocks_of(w.n_pe_blocks) == 4 && n_blocks_of(w.n_fd_blocks) == 4,
+               "dx_train_step: the training step is built for 4 FFT blocks per stack (the reference's default)");
     DX_TRY(train_layout(&p, a.B, a.L_max, a.T_max, w.n_speakers, a.workspace, a.workspace_bytes));
     DX_REQUIRE(a.workspace != nullptr, "dx_train_step: workspace required");
     DX_REQUIRE((a.flags & ~(DX_TRAIN_FORWARD_ONLY | DX_TRAIN_TC_GEMM)) == 0, "dx_train_step: unknown flags 0x%x", a.flags);

@@ -90,15 +90,16 @@ class DaftExprt(nn.Module):
               and pe["attn_nb_heads"] == _lib.HEADS and fd["attn_nb_heads"] == _lib.HEADS and ae["attn_nb_heads"] == _lib.HEADS
               and pe["conv_channels"] == _lib.CCH and fd["conv_channels"] == _lib.CCH and ae["conv_channels"] == _lib.CCH
               and pe["conv_kernel"] == 3 and fd["conv_kernel"] == 3 and ae["conv_kernel"] == 3
-              and pe["nb_blocks"] == 4 and fd["nb_blocks"] == 4 and ae["nb_blocks"] == 4
+              and all(1 <= x["nb_blocks"] <= _lib.MAX_BLOCKS for x in (pe, fd, ae))
               and hp.gaussian_upsampling_module["conv_kernel"] == 3
               and hp.n_mel_channels == _lib.MEL and getattr(hp, "external_emb_dim", 192) == _lib.SPK
               and not hp.gaussian_upsampling_module.get("use_concatenation", False)
               and not hasattr(hp, "frame_decoder_input_dim"))
         if not ok:
             raise NotImplementedError(
-                "the B200 kernels are specialised for the reference's default architecture "
-                "(hparams.py:106-127: D=128, 2 heads, 1024 conv channels, k=3, 4 blocks, 80 mels, 192-d ECAPA)")
+                "the B200 kernels are specialised for the reference's default layer shapes "
+                "(hparams.py:106-127: D=128, 2 heads, 1024 conv channels, k=3, 80 mels, 192-d ECAPA) with 1 to 4 FFT blocks per "
+                "stack (phoneme_encoder / frame_decoder / accent_encoder 'nb_blocks' may differ from each other)")
 
     # invalidate packed weights whenever parameters may have changed / moved
     def _apply(self, fn, *a, **k):
@@ -197,9 +198,15 @@ class DaftExprt(nn.Module):
             setp(W, f"ae_ln{i}_g", f32(sd[p + f"convs.{4 * i + 2}.weight"]))
             setp(W, f"ae_ln{i}_b", f32(sd[p + f"convs.{4 * i + 2}.bias"]))
             setp(W, f"ae_c{i}_w_bf", packed(w, nt, ks, kpad))
-        for b in range(4):
+        hp = self._hp
+        W.n_ae_blocks = int(accent_encoder_params(hp)["nb_blocks"])
+        W.n_pe_blocks = int(hp.phoneme_encoder["nb_blocks"])
+        W.n_fd_blocks = int(hp.frame_decoder["nb_blocks"])
+        for b in range(W.n_ae_blocks):
             fill_block(W.ae_blocks[b], f"accent_encoder.blocks.{b}")
+        for b in range(W.n_pe_blocks):
             fill_block(W.pe_blocks[b], f"phoneme_encoder.blocks.{b}")
+        for b in range(W.n_fd_blocks):
             fill_block(W.fd_blocks[b], f"frame_decoder.blocks.{b}")
         setp(W, "spk_w", f32(sd["spk_projection.linear_layer.weight"]))
         setp(W, "spk_b", f32(sd["spk_projection.linear_layer.bias"]))
@@ -415,7 +422,8 @@ class DaftExprt(nn.Module):
             spk_embs=None if external_spk_emb is not None else self._dev(spk_embs, fl),
             accent_emb_in=self._dev(external_accent_emb, fl), spk_emb_in=self._dev(external_spk_emb, fl),
             want_enc_out=_want_enc_out, packed_frames=total_frames)
-        film_dec = out["film"][:, 4:8, :]
+        n_pe, n_fd = int(self._hp.phoneme_encoder["nb_blocks"]), int(self._hp.frame_decoder["nb_blocks"])
+        film_dec = out["film"][:, n_pe:n_pe + n_fd, :]
         film_params = [self.style_adapter.post_multipliers, None, None, film_dec]
         encoder_preds = [durations_float, symbols_energy, symbols_pitch, input_lengths]
         decoder_preds = [out["mel"], output_lengths]

@@ -125,6 +125,8 @@ class TrainEngine:
         stay fp32 either way."""
         from .model import DaftExprt
         DaftExprt._check_hparams(hparams)
+        if any(x["nb_blocks"] != 4 for x in (hparams.phoneme_encoder, hparams.frame_decoder, accent_encoder_params(hparams))):
+            raise NotImplementedError("the training step is built for 4 FFT blocks per stack (the reference's default)")
         if gemm not in ("fp32", "bf16"):
             raise ValueError("gemm must be 'fp32' or 'bf16'")
         self.gemm = gemm
