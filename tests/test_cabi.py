@@ -40,11 +40,11 @@ def test_host_only_queries():
 
 
 def test_struct_sizes_match_header():
-    # 18 pointers per block; the model struct is pointers + 3 block arrays + 4 int32
+    # 18 pointers per block; the model struct is pointers + 3 block arrays + 8 int32 (sizes, block counts)
     import ctypes
     assert ctypes.sizeof(_lib.DxBlockWeights) == 18 * 8
     n_ptr = 19 + 14 + 8 + 4
-    assert ctypes.sizeof(_lib.DxModelWeights) == n_ptr * 8 + 3 * 4 * 18 * 8 + 16
+    assert ctypes.sizeof(_lib.DxModelWeights) == n_ptr * 8 + 3 * 4 * 18 * 8 + 32
     assert ctypes.sizeof(_lib.DxForwardArgs) == 16 + 21 * 8 + 8 + 8
 
 
