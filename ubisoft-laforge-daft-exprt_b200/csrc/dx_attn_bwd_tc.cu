@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(ABT_THREADS, 1) attn_bwd_tc_kernel(const AbtPa
 #pragma unroll
                     for (int e = 0; e < 8; e += 2) {
                         float pv[2], dv[2];
-                        uint64_t z = 0;
+                        uint32_t z = 0;
                         if constexpr (DROP) z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g4 * 32 + c * 8 + e) >> 1));
 #pragma unroll
                         for (int u = 0; u < 2; ++u) {

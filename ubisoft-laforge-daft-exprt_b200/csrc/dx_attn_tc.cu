@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                             if constexpr (DROP) {       // the row sum above is of the UNdropped weights (softmax, then dropout)
 #pragma unroll
                                 for (int e = 0; e < 8; e += 2) {
-                                    const uint64_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
+                                    const uint32_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
                                     pe[e] = drop_keep(z, 0, p.drop.thr) ? pe[e] * p.drop.scale : 0.f;
                                     pe[e + 1] = drop_keep(z, 1, p.drop.thr) ? pe[e + 1] * p.drop.scale : 0.f;
                                 }
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(ATC_THREADS, 2) attention_tc_kernel(const AtcP
                             if constexpr (DROP) {
 #pragma unroll
                                 for (int e = 0; e < 8; e += 2) {
-                                    const uint64_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
+                                    const uint32_t z = drop_hash(p.drop.seed, p.drop_site, drop_row + ((g * ATC_BK + q * 32 + c * 8 + e) >> 1));
                                     pe[e] = drop_keep(z, 0, p.drop.thr) ? pe[e] * p.drop.scale : 0.f;
                                     pe[e + 1] = drop_keep(z, 1, p.drop.thr) ? pe[e + 1] * p.drop.scale : 0.f;
                                 }

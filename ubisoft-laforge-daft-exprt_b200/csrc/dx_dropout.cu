@@ -9,7 +9,7 @@ namespace dx {
 __global__ void dropout_mask_kernel(uint8_t* __restrict__ out, int attention, int B, int n_max, int C, DropSpec d, uint32_t site, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint64_t z;
+    uint32_t z;
     int e;
     if (!attention) {
         const int c = (int)(i % C);
