@@ -69,6 +69,46 @@ def test_what_is_still_refused():
     hp.frame_decoder = dict(hp.frame_decoder, conv_channels=512)
     with pytest.raises(NotImplementedError):
         DaftExprt(hp)
-    hp, sd, _, _, _ = C.arch_case("arch_143")
+    hp = C.hparams()
+    hp.accent_encoder = dict(hp.phoneme_encoder, attn_nb_heads=4)
     with pytest.raises(NotImplementedError):
-        TrainEngine(hp, sd)
+        TrainEngine(hp, C.state_dict())
+
+
+@pytest.mark.parametrize("name", ["arch_232", "arch_143"])
+def test_training_step_on_other_block_counts(name):
+    """Gradients of every parameter against the reference's autograd (fp32 mode: the 1e-3 gates of test_gpu_train.py;
+    tensor-core mode: its gates), and the train-mode step with the engine's dropout masks injected into the reference - the
+    accent encoder of these cases has its own dropout rates (0.2 / 0.05)."""
+    import test_gpu_train as T
+    from daft_exprt_b200.train import TrainEngine, loss_dict
+    from oracle import ref_harness as R
+    from oracle import train_oracle as TO
+    if not R.reference_available():
+        pytest.skip("reference (oracle/_ref) not present")
+    hp, sd, batch, _, _ = C.arch_case(name)
+    dev = tuple(t.cuda() for t in batch)
+    ref_loss, ref_ind, ref_grads = TO.reference_step(hp, sd, batch, 3000)
+    eng = TrainEngine(hp, sd)
+    losses = loss_dict(eng.forward_backward(dev, iteration=3000))
+    assert abs(losses["loss"] - ref_loss) <= T.LOSS_REL * abs(ref_loss)
+    for k, v in ref_ind.items():
+        assert abs(losses[k] - v) <= T.LOSS_REL * max(abs(v), 1e-3), (k, losses[k], v)
+    grads = eng.grads_state_dict()
+    assert sorted(grads) == sorted(ref_grads)
+    for n, r in ref_grads.items():
+        d = (grads[n].cpu() - r).abs()
+        assert d.max().item() <= T.GRAD_MAX_ABS, f"{n}: max-abs {d.max().item():.3e}"
+        assert d.sum().item() / max(r.abs().sum().item(), 1e-12) <= T.GRAD_REL_L1 or r.abs().sum().item() < 1e-6, n
+    # tensor-core mode, train mode: same masks on both sides
+    eng = TrainEngine(hp, sd, gemm="bf16", train_mode=True, seed=5)
+    B, L = batch[0].shape
+    masks = [(m.cpu(), pm) for m, pm in eng.dropout_masks(B, L, batch[8].shape[2], iteration=3000)]
+    n_ae, n_pe, n_fd = C.MA.ARCH_CASES[name][:3]
+    assert len(masks) == 3 + 3 * (n_ae + n_pe + n_fd)
+    assert masks[3][1] == pytest.approx(0.2) and masks[5][1] == pytest.approx(0.05)      # the accent encoder's own rates
+    losses = loss_dict(eng.forward_backward(dev, iteration=3000))
+    ref_loss, _, ref_grads = TO.reference_step(hp, sd, batch, 3000, dropout_masks=masks)
+    assert abs(losses["loss"] - ref_loss) <= T.TC_LOSS_REL * abs(ref_loss), (losses["loss"], ref_loss)
+    rels = sorted(T._rel_l1(eng.grads_state_dict(), ref_grads).values())
+    assert rels[-1] <= T.TC_DROPOUT_GRAD_REL_L1_MAX and rels[len(rels) // 2] <= T.TC_GRAD_REL_L1_MEDIAN, (rels[-1], rels[len(rels) // 2])

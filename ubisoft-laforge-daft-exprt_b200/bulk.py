@@ -284,6 +284,7 @@ class BulkRunner:
         h2d_done = [None] * S                 # the block may be refilled once its last H2D has completed
         fwd_done = [None] * S                 # the mirror may be overwritten once the forward reading it has completed
         copy_stream = torch.cuda.Stream(dev)
+        d2h_stream = torch.cuda.Stream(dev)
         q = queue.Queue(maxsize=4)
         writer = threading.Thread(target=self._writer, args=(q,), daemon=True)
         writer.start()
@@ -329,9 +330,14 @@ class BulkRunner:
                     fwd_done[s].record()
                     mel = out[3][0]
                     hmel = torch.empty(mel.shape, dtype=mel.dtype, pin_memory=True)
-                    hmel.copy_(mel, non_blocking=True)
-                    done = torch.cuda.Event()
-                    done.record()
+                    # the result leaves on its own stream: on the compute stream the next batch's forward would queue behind
+                    # this copy (8.7 MB per cfg2 batch: 0.2-0.35 ms of a 1.25 ms step)
+                    with torch.cuda.stream(d2h_stream):
+                        d2h_stream.wait_event(fwd_done[s])
+                        hmel.copy_(mel, non_blocking=True)
+                        done = torch.cuda.Event()
+                        done.record(d2h_stream)
+                    mel.record_stream(d2h_stream)       # the allocator must not hand the block out again before the copy ran
                     self.frames += int(out_len.sum())
                     if packed:               # per-utterance (80, T_b) numpy views of the pinned buffer: the crop is free
                         from .layouts import mel_views

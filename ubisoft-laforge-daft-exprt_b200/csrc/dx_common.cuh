@@ -156,7 +156,7 @@ int gemm_f32(const float* A, int K, const float* W, const float* bias, int N, in
 // out = live(ext) ? film(LN(in + res) * g + b) : 0   (one warp per row; C = 128 or 1024)
 struct LnDrop;      // dx_dropout.cuh (training step)
 // block counts of the three stacks (DxModelWeights.n_*_blocks: 0 = the reference's default of 4)
-static inline int n_blocks_of(int32_t n) { return n == 0 ? 4 : (int)n; }
+__host__ __device__ static inline int n_blocks_of(int32_t n) { return n == 0 ? 4 : (int)n; }
 int ln_rows_f32(const float* in, const float* res, const float* g, const float* b, int C, const float* film,
                 int film_stride, const Rows& R, int live_ext, float* out, cudaStream_t s, const LnDrop* drop = nullptr);
 // masked multi-head self attention on packed rows; qkv [rows][384] → out [rows][128]

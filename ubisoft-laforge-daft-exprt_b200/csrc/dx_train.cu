@@ -62,6 +62,7 @@ struct TrainPlan {
     float *fb_part;
     float *dfilm, *dlogits, *sv, *gat1, *gat2, *lpart, *dpost_reg, *ct, *gd, *gr, *dpre;
     int64_t scratch_floats;
+    int n_blk[3];                               // FFT blocks of the accent encoder, phoneme encoder, frame decoder (1..4)
     DropSpec drop_attn[3], drop_conv[3];       // per stack (accent encoder, phoneme encoder, frame decoder); thr = 0: off
     // DX_TRAIN_TC_GEMM: every dense weight packed to bf16 once per step, forward form and transposed (data gradient) form
     PackEntry pk[TRAIN_MAX_PACKED];
@@ -233,10 +234,11 @@ inline float* G(const float* p) { return const_cast<float*>(p); }
 int stack_forward(const TrainPlan& p, const DxBlockWeights* blocks, StackSave& st, const Rows& R, const float* film, int film_block0,
                   int stack, cudaStream_t s) {
     const DropSpec &da = p.drop_attn[stack], &dc = p.drop_conv[stack];
-    for (int i = 0; i < 4; ++i) {
+    const int nb = p.n_blk[stack];
+    for (int i = 0; i < nb; ++i) {
         const DxBlockWeights& bw = blocks[i];
         BlockSave& b = st.blk[i];
-        float* y = i < 3 ? st.blk[i + 1].xin : st.out;
+        float* y = i < nb - 1 ? st.blk[i + 1].xin : st.out;
         const float* fp = film ? film + (film_block0 + i) * 256 : nullptr;
         DX_TRY(gemm(p, b.xin, DX_D, bw.w_qkv, bw.b_qkv, 3 * DX_D, 1, false, R, -1, b.qkv, s, b.xin_il));
         if (p.tc && !debug_knob(17)) {
@@ -320,7 +322,7 @@ int stack_backward(const TrainPlan& p, const DxBlockWeights* blocks, const DxBlo
     // the two other plan buffers, in an order that keeps dy1 / dy2 alive until the first two kernels have read them
     Bf = bufs[(freei + 1) % 3];
     C = bufs[(freei + 2) % 3];
-    for (int i = 3; i >= 0; --i) {
+    for (int i = p.n_blk[stack] - 1; i >= 0; --i) {
         const DxBlockWeights& bw = blocks[i];
         const DxBlockWeights& g = gb[i];
         const BlockSave& b = st.blk[i];
@@ -376,12 +378,15 @@ int64_t train_workspace_bytes(int B, int L_max, int T_max) {
 int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTrainArgs& a, cudaStream_t s) {
     TrainPlan p;
     DX_REQUIRE(w.n_speakers >= 1 && w.n_speakers <= 64, "train: n_speakers=%d out of range (1..64)", w.n_speakers);
-    DX_REQUIRE(n_blocks_of(w.n_ae_blocks) == 4 && n_blocks_of(w.n_pe_blocks) == 4 && n_blocks_of(w.n_fd_blocks) == 4,
-               "dx_train_step: the training step is built for 4 FFT blocks per stack (the reference's default)");
+    DX_REQUIRE(w.n_ae_blocks >= 0 && w.n_ae_blocks <= 4 && w.n_pe_blocks >= 0 && w.n_pe_blocks <= 4 && w.n_fd_blocks >= 0 &&
+                   w.n_fd_blocks <= 4, "dx_train_step: block counts %d / %d / %d out of range (1..4, 0 = 4)", w.n_ae_blocks,
+               w.n_pe_blocks, w.n_fd_blocks);
     DX_TRY(train_layout(&p, a.B, a.L_max, a.T_max, w.n_speakers, a.workspace, a.workspace_bytes));
     DX_REQUIRE(a.workspace != nullptr, "dx_train_step: workspace required");
     DX_REQUIRE((a.flags & ~(DX_TRAIN_FORWARD_ONLY | DX_TRAIN_TC_GEMM)) == 0, "dx_train_step: unknown flags 0x%x", a.flags);
     p.tc = (a.flags & DX_TRAIN_TC_GEMM) != 0;
+    p.n_blk[0] = n_blocks_of(w.n_ae_blocks); p.n_blk[1] = n_blocks_of(w.n_pe_blocks); p.n_blk[2] = n_blocks_of(w.n_fd_blocks);
+    const int n_pe = p.n_blk[1], n_film = p.n_blk[1] + p.n_blk[2];       // FiLM rows: phoneme encoder first, then the decoder
     bool any_drop = false;
     for (int k = 0; k < 3; ++k) {
         DX_REQUIRE(a.attn_dropout[k] >= 0.f && a.attn_dropout[k] < 1.f && a.conv_dropout[k] >= 0.f && a.conv_dropout[k] < 1.f,
@@ -416,7 +421,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
         };
         const DxBlockWeights* stacks[3] = {w.ae_blocks, w.pe_blocks, w.fd_blocks};
         for (int k = 0; k < 3; ++k)
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < p.n_blk[k]; ++i) {
                 const DxBlockWeights& bw = stacks[k][i];
                 add(bw.w_qkv, 1, DX_D, 3 * DX_D);
                 add(bw.w_out, 1, DX_D, DX_D);
@@ -456,13 +461,13 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(lenreg_symbols(p.enc.out, nullptr, 0, RL, a.durations_float, a.symbols_energy, a.symbols_pitch, &w, p.xs, p.sigma, s));
     DX_TRY(lenreg_frames(p.xs, RL, RT, p.mu, p.sigma, w.pos_table, p.weights, p.dec.blk[0].xin, nullptr, 0, s));
     // frame decoder (model.py:548-564)
-    DX_TRY(stack_forward(p, w.fd_blocks, p.dec, RT, p.film, 4, 2, s));
+    DX_TRY(stack_forward(p, w.fd_blocks, p.dec, RT, p.film, n_pe, 2, s));
     DX_TRY(gemm(p, p.dec.out, DX_D, w.mel_w, w.mel_b, DX_MEL, 1, false, RT, -1, p.melo, s));
     if (a.mel_out) DX_TRY(unpack_mel(p.melo, RT, a.mel_out, s));
 
     // ======================================= loss (loss.py:57-159) ============================================
     DxLossParams lp{a.mel_spec_weight, a.post_mult_weight, a.energy_consistency_weight, a.speaker_weight, a.loss_scale};
-    DX_TRY(loss_forward_backward(p.melo, a.mel_specs, RT, p.logits, a.speaker_ids, w.n_speakers, w.post_mult, lp, p.lpart, p.dmel,
+    DX_TRY(loss_forward_backward(p.melo, a.mel_specs, RT, p.logits, a.speaker_ids, w.n_speakers, w.post_mult, 2 * n_film, lp, p.lpart, p.dmel,
                                  p.dlogits, a.losses, p.dpost_reg, s));
     if (a.flags & DX_TRAIN_FORWARD_ONLY) return 0;
 
@@ -473,7 +478,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(conv_bwd(p, p.dec.out, DX_D, p.dmel, DX_MEL, w.mel_w, 1, RT, G(g.mel_w), p.dB, s));
     DX_CHECK_CUDA(cudaMemsetAsync(p.dfilm, 0, (size_t)B * 8 * 256 * sizeof(float), s));
     // frame decoder
-    DX_TRY(stack_backward(p, w.fd_blocks, g.fd_blocks, p.dec, RT, p.film, p.dfilm, 4, 2, p.dB, nullptr, &g1, &g2, s));
+    DX_TRY(stack_backward(p, w.fd_blocks, g.fd_blocks, p.dec, RT, p.film, p.dfilm, n_pe, 2, p.dB, nullptr, &g1, &g2, s));
     // decoder input = (x_up + P) * valid: mask, then the length regulator
     float* gdec = (g1 != p.dA && g2 != p.dA) ? p.dA : ((g1 != p.dB && g2 != p.dB) ? p.dB : p.dC);
     DX_TRY(add_mask_rows(g1, g2, RT, gdec, s));
@@ -492,11 +497,11 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(embed_bwd(genc, a.symbols, w.n_symbols, RL, G(g.symbols_embedding), s));
     // conditioning heads (model.py:904-920, 764-806, 829-830)
     DX_TRY(style_bwd(a.spk_embs, p.accent, &w, p.dfilm, p.dlogits, a.lambda_reversal, B, p.sv, s));
-    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DG, 1024, B, p.gat1, s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DG, n_film * DX_D, B, p.gat1, s));
     DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_C, DX_D, B, p.gat2, s));
-    DX_TRY(outer_wgrad(p.gat1, 1024, p.gat2, DX_D, B, G(g.film_g_w), G(g.film_g_b), s));
-    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DQ, 1024, B, p.gat1, s));
-    DX_TRY(outer_wgrad(p.gat1, 1024, p.gat2, DX_D, B, G(g.film_b_w), G(g.film_b_b), s));
+    DX_TRY(outer_wgrad(p.gat1, n_film * DX_D, p.gat2, DX_D, B, G(g.film_g_w), G(g.film_g_b), s));
+    DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DQ, n_film * DX_D, B, p.gat1, s));
+    DX_TRY(outer_wgrad(p.gat1, n_film * DX_D, p.gat2, DX_D, B, G(g.film_b_w), G(g.film_b_b), s));
     DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DC, DX_D, B, p.gat1, s));
     DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_E, DX_SPK, B, p.gat2, s));
     DX_TRY(outer_wgrad(p.gat1, DX_D, p.gat2, DX_SPK, B, G(g.spk_w), G(g.spk_b), s));
@@ -507,7 +512,7 @@ int run_train_step(const DxModelWeights& w, const DxModelWeights& g, const DxTra
     DX_TRY(outer_wgrad(p.gat1, DX_D, p.gat2, DX_D, B, G(g.cls_w2), G(g.cls_b2), s));
     DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_H2, DX_D, B, p.gat2, s));
     DX_TRY(outer_wgrad(p.dlogits, w.n_speakers, p.gat2, DX_D, B, G(g.cls_w3), G(g.cls_b3), s));
-    if (g.post_mult) DX_TRY(post_mult_grad(p.sv, B, p.dpost_reg, G(g.post_mult), s));
+    if (g.post_mult) DX_TRY(post_mult_grad(p.sv, B, p.dpost_reg, 2 * n_film, G(g.post_mult), s));
     // accent encoder: mean pool, stack, pre-net
     DX_TRY(gather_strided(p.sv, SB_STRIDE, SB_DACC, DX_D, B, p.gat1, s));
     DX_TRY(masked_mean_bwd(p.gat1, RT, p.dB, s));

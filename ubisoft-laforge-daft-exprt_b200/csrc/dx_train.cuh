@@ -46,9 +46,9 @@ int style_bwd(const float* spk_embs, const float* accent, const DxModelWeights* 
               float lambda_rev, int B, float* v, cudaStream_t s);
 int gather_strided(const float* v, int64_t stride, int off, int n, int B, float* out, cudaStream_t s);
 int loss_forward_backward(const float* melo, const float* tgt, const Rows& RT, const float* logits, const int64_t* speaker_ids,
-                          int n_spk, const float* post_mult, const DxLossParams& lp, float* part, float* dmel, float* dlogits,
-                          float* losses, float* dpost_reg, cudaStream_t s);
-int post_mult_grad(const float* v, int B, const float* dreg, float* out, cudaStream_t s);
+                          int n_spk, const float* post_mult, int n_post, const DxLossParams& lp, float* part, float* dmel,
+                          float* dlogits, float* losses, float* dpost_reg, cudaStream_t s);
+int post_mult_grad(const float* v, int B, const float* dreg, int n_post, float* out, cudaStream_t s);
 int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps, float wd, int step,
               float gscale, cudaStream_t s);
 

@@ -1065,6 +1065,7 @@ style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ a
     __shared__ float s_g[1024], s_q[1024], s_dg[1024], s_dq[1024];
     __shared__ float s_red[8];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_film = n_blocks_of(w.n_pe_blocks) + n_blocks_of(w.n_fd_blocks), nf = n_film * DX_D;     // FiLM rows (8 by default)
     float* o = v + (int64_t)b * SB_STRIDE;
     if (tid < DX_D) s_a[tid] = accent[b * DX_D + tid];
     {
@@ -1092,7 +1093,7 @@ style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ a
     // raw FiLM predictor outputs and their gradients
     {
         const float4 x = reinterpret_cast<const float4*>(s_c)[lane];
-        for (int n = warp; n < 1024; n += 8) {
+        for (int n = warp; n < nf; n += 8) {
             const float4 wg = reinterpret_cast<const float4*>(w.film_g_w + (int64_t)n * DX_D)[lane];
             const float4 wb = reinterpret_cast<const float4*>(w.film_b_w + (int64_t)n * DX_D)[lane];
             const float gq = warp_sum((wg.x * x.x + wg.y * x.y) + (wg.z * x.z + wg.w * x.w));
@@ -1102,8 +1103,12 @@ style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ a
     }
     __syncthreads();
     for (int n = tid; n < 1024; n += 256) {
+        if (n >= nf) {           // unused rows of the record: the weight-gradient gathers stop at nf, keep them defined anyway
+            o[SB_DG + n] = 0.f; o[SB_DQ + n] = 0.f;
+            continue;
+        }
         const int k = n >> 7, i = n & 127;
-        const float pg = w.post_mult ? w.post_mult[k] : 1.f, pb = w.post_mult ? w.post_mult[8 + k] : 1.f;
+        const float pg = w.post_mult ? w.post_mult[k] : 1.f, pb = w.post_mult ? w.post_mult[n_film + k] : 1.f;
         const float df_g = dfilm[((int64_t)b * 8 + k) * 256 + i], df_b = dfilm[((int64_t)b * 8 + k) * 256 + 128 + i];
         s_dg[n] = df_g * pg; s_dq[n] = df_b * pb;
         o[SB_DG + n] = s_dg[n]; o[SB_DQ + n] = s_dq[n];
@@ -1111,17 +1116,19 @@ style_bwd_kernel(const float* __restrict__ spk_embs, const float* __restrict__ a
         s_q[n] = df_b * s_q[n];
     }
     __syncthreads();
-    if (tid < 16) {
-        const int k = tid & 7;
-        const float* src = (tid < 8 ? s_g : s_q) + k * 128;
+    if (tid < 16) {              // record slot tid = element tid of the flat (2, n_film) post-multiplier gradient
         float acc = 0.f;
-        for (int i = 0; i < 128; ++i) acc += src[i];
+        if (tid < 2 * n_film) {
+            const int k = tid % n_film;
+            const float* src = (tid < n_film ? s_g : s_q) + k * 128;
+            for (int i = 0; i < 128; ++i) acc += src[i];
+        }
         o[SB_DPOST + tid] = acc;
     }
     // dc[k] = sum_n Wg[n][k] dg[n] + Wb[n][k] dq[n]: thread k (< 128) walks the columns (coalesced over k)
     if (tid < DX_D) {
         float acc = 0.f;
-        for (int n = 0; n < 1024; ++n) acc += w.film_g_w[(int64_t)n * DX_D + tid] * s_dg[n] + w.film_b_w[(int64_t)n * DX_D + tid] * s_dq[n];
+        for (int n = 0; n < nf; ++n) acc += w.film_g_w[(int64_t)n * DX_D + tid] * s_dg[n] + w.film_b_w[(int64_t)n * DX_D + tid] * s_dq[n];
         s_t[tid] = acc;
         o[SB_DC + tid] = acc;
     }
@@ -1286,7 +1293,7 @@ loss_utt_kernel(const float* __restrict__ melo, const float* __restrict__ tgt, R
 }
 
 // losses[8]: total, speaker_loss, speaker_ce_raw, post_mult_loss, mel_l1, mel_l2, energy_consistency, pitch_consistency (0)
-__global__ void loss_finish_kernel(const float* __restrict__ part, int B, Rows RT, const float* __restrict__ post_mult,
+__global__ void loss_finish_kernel(const float* __restrict__ part, int B, Rows RT, const float* __restrict__ post_mult, int n_post,
                                    DxLossParams lp, float* __restrict__ losses, float* __restrict__ dpost_reg) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
@@ -1303,10 +1310,10 @@ __global__ void loss_finish_kernel(const float* __restrict__ part, int B, Rows R
     float pm = 0.f;
     if (post_mult != nullptr && lp.post_mult_weight != 0.f) {
         float ss = 0.f;
-        for (int i = 0; i < 16; ++i) ss += post_mult[i] * post_mult[i];
+        for (int i = 0; i < n_post; ++i) ss += post_mult[i] * post_mult[i];
         const float nrm = sqrtf(ss);
         pm = lp.post_mult_weight * nrm;
-        for (int i = 0; i < 16; ++i) dpost_reg[i] = nrm > 0.f ? lp.scale * lp.post_mult_weight * post_mult[i] / nrm : 0.f;
+        for (int i = 0; i < 16; ++i) dpost_reg[i] = (i < n_post && nrm > 0.f) ? lp.scale * lp.post_mult_weight * post_mult[i] / nrm : 0.f;
     } else if (dpost_reg != nullptr) {
         for (int i = 0; i < 16; ++i) dpost_reg[i] = 0.f;
     }
@@ -1318,8 +1325,8 @@ __global__ void loss_finish_kernel(const float* __restrict__ part, int B, Rows R
 }
 
 int loss_forward_backward(const float* melo, const float* tgt, const Rows& RT, const float* logits, const int64_t* speaker_ids,
-                          int n_spk, const float* post_mult, const DxLossParams& lp, float* part, float* dmel, float* dlogits,
-                          float* losses, float* dpost_reg, cudaStream_t s) {
+                          int n_spk, const float* post_mult, int n_post, const DxLossParams& lp, float* part, float* dmel,
+                          float* dlogits, float* losses, float* dpost_reg, cudaStream_t s) {
     const size_t smem = (size_t)3 * (RT.n_max + 4) * sizeof(float);
     DX_REQUIRE(smem <= 160 * 1024, "loss: T_max=%d too large", RT.n_max);
     static SmemConfigured cfg;
@@ -1328,23 +1335,24 @@ int loss_forward_backward(const float* melo, const float* tgt, const Rows& RT, c
     ProfScope prof("loss", s);
     DX_LAUNCH_PDL((loss_utt_kernel), RT.B, 256, smem, s, melo, tgt, RT, logits, speaker_ids, n_spk, lp, part, dmel, dlogits);
     DX_CHECK_LAUNCH();
-    DX_LAUNCH_PDL((loss_finish_kernel), 1, 32, 0, s, part, RT.B, RT, post_mult, lp, losses, dpost_reg);
+    DX_LAUNCH_PDL((loss_finish_kernel), 1, 32, 0, s, part, RT.B, RT, post_mult, n_post, lp, losses, dpost_reg);
     DX_CHECK_LAUNCH();
     return 0;
 }
 
 // d post_mult = sum_b dpost_b (FiLM path) + the regulariser's gradient
-__global__ void post_mult_grad_kernel(const float* __restrict__ v, int B, const float* __restrict__ dreg, float* __restrict__ out) {
+__global__ void post_mult_grad_kernel(const float* __restrict__ v, int B, const float* __restrict__ dreg, int n_post,
+                                      float* __restrict__ out) {
     ptx::griddep_wait();      // PDL: the previous kernel of the stream is complete and visible
     ptx::griddep_launch();    // let the next kernel start launching
     const int i = threadIdx.x;
-    if (i >= 16) return;
+    if (i >= n_post) return;
     float acc = 0.f;
     for (int b = 0; b < B; ++b) acc += v[(int64_t)b * SB_STRIDE + SB_DPOST + i];
     out[i] = acc + dreg[i];
 }
-int post_mult_grad(const float* v, int B, const float* dreg, float* out, cudaStream_t s) {
-    DX_LAUNCH_PDL((post_mult_grad_kernel), 1, 32, 0, s, v, B, dreg, out);
+int post_mult_grad(const float* v, int B, const float* dreg, int n_post, float* out, cudaStream_t s) {
+    DX_LAUNCH_PDL((post_mult_grad_kernel), 1, 32, 0, s, v, B, dreg, n_post, out);
     DX_CHECK_LAUNCH();
     return 0;
 }

@@ -125,12 +125,13 @@ class TrainEngine:
         stay fp32 either way."""
         from .model import DaftExprt
         DaftExprt._check_hparams(hparams)
-        if any(x["nb_blocks"] != 4 for x in (hparams.phoneme_encoder, hparams.frame_decoder, accent_encoder_params(hparams))):
-            raise NotImplementedError("the training step is built for 4 FFT blocks per stack (the reference's default)")
         if gemm not in ("fp32", "bf16"):
             raise ValueError("gemm must be 'fp32' or 'bf16'")
         self.gemm = gemm
         self.hp = hparams
+        # FFT blocks per stack: accent encoder, phoneme encoder, frame decoder (1..4 each, checked above)
+        self.n_blocks = tuple(int(x["nb_blocks"]) for x in (accent_encoder_params(hparams), hparams.phoneme_encoder,
+                                                              hparams.frame_decoder))
         self.train_mode = bool(train_mode)
         self.seed = int(seed)
         if self.train_mode and gemm != "bf16":
@@ -178,6 +179,7 @@ class TrainEngine:
         W.n_symbols = int(dict(self.spec)["phoneme_encoder.symbols_embedding.weight"][0])
         W.n_speakers = int(self.hp.n_speakers)
         W.pos_rows = int(self.pos.shape[0])
+        W.n_ae_blocks, W.n_pe_blocks, W.n_fd_blocks = self.n_blocks
         return W
 
     # ---- checkpoint layout in / out ---------------------------------------------------------------------------------
@@ -252,7 +254,7 @@ class TrainEngine:
         for k, Cdim in enumerate((_lib.CCH, _lib.CCH, _lib.D)):
             site(2, 0, k, pc[0], T_max, Cdim)
         for stack, n in ((0, T_max), (1, L_max), (2, T_max)):
-            for blk in range(4):
+            for blk in range(self.n_blocks[stack]):
                 site(3, stack, blk, pa[stack], n, _lib.D)
                 site(0, stack, blk, pa[stack], n, _lib.D)
                 site(1, stack, blk, pc[stack], n, _lib.D)
