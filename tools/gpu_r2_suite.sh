@@ -1,4 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q --durations=5 > gpurun_out/r2v_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/r2v_pytest.log
-tail -25 gpurun_out/r2v_pytest.log
+timeout 600 python tools/arch_grad_debug.py 2>&1 | grep -v "Warning\|re.findall" > gpurun_out/r2v_debug.txt; tail -5 gpurun_out/r2v_debug.txt
