@@ -126,7 +126,7 @@ typedef struct {
     /* FFT blocks per stack, 1..4 each (hparams.{accent_encoder, phoneme_encoder, frame_decoder}['nb_blocks']); 0 = 4, the
      * reference's default.  With P = n_pe_blocks and F = n_fd_blocks the style adapter predicts (P + F) * 128 gammas and
      * betas (film_g_w / film_b_w are [(P + F) * 128][128], model.py:731-747), post_mult is [2][P + F], and block i of the
-     * decoder uses FiLM row P + i of the (B, 8, 256) film output.  The training step supports 4 / 4 / 4 only. */
+     * decoder uses FiLM row P + i of the (B, 8, 256) film output.  dx_forward and dx_train_step both follow the counts. */
     int32_t n_ae_blocks, n_pe_blocks, n_fd_blocks, pad2_;
 } DxModelWeights;
 

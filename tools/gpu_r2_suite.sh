@@ -1,3 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python tools/arch_grad_debug.py 2>&1 | grep -v "Warning\|re.findall" > gpurun_out/r2v_debug.txt; tail -5 gpurun_out/r2v_debug.txt
+timeout 900 python -m pytest tests/test_gpu_arch.py -q > gpurun_out/r2v_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/r2v_pytest.log
+tail -4 gpurun_out/r2v_pytest.log
