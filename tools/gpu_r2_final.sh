@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-2 evidence run: full GPU suite, default bench, reference arm (short), ncu launch list and full captures of the two top kernels
+# round-2 evidence run: full GPU suite, default bench, reference arm (short), ncu launch list of one cfg2 step
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -q --durations=8 > gpurun_out/r2z_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/r2z_pytest.log
 tail -14 gpurun_out/r2z_pytest.log
@@ -8,15 +8,10 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r
 timeout 200 python tools/one_step.py > gpurun_out/r2z_one_step.log 2>&1 && \
 timeout 400 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r2z_launches.csv python tools/one_step.py > gpurun_out/r2z_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
-# the two top kernels in SEPARATE sessions (one session over both tripped a bounded mbarrier wait under replay)
-timeout 500 ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:ffn_tc_kernel" -c 12 -f -o gpurun_out/r2z_prof_ffn python tools/one_step.py > gpurun_out/r2z_ncu_full_ffn.log 2>&1
-echo "ncu full ffn rc=$?"; tail -2 gpurun_out/r2z_ncu_full_ffn.log
-timeout 500 ncu --profile-from-start off --set full --clock-control none --import-source on -k "regex:attention_tc_kernel" -c 12 -f -o gpurun_out/r2z_prof_attn python tools/one_step.py > gpurun_out/r2z_ncu_full_attn.log 2>&1
-echo "ncu full attn rc=$?"; tail -2 gpurun_out/r2z_ncu_full_attn.log
 python - <<'PY'
 import json
 d=json.loads(open('gpurun_out/r2z_bench.json').read().strip().splitlines()[-1])
 print({k:d[k] for k in ('value','ms_per_step','gpu_launches')}, 'e2e', d['e2e']['value'], 'frac', d['roofline']['frac'])
 c=d['configs']; print('cfg1', c['cfg1']['forward_ms'], c['cfg1']['p50_ms'], 'cfg4', c['cfg4']['b1_ms'], c['cfg4']['b8_ms'], 'cfg3', c['cfg3']['frames_s'], 'cfg5', c['cfg5']['step_ms'], c['cfg5']['eval_mode']['step_ms'], c['cfg5']['fp32_mode']['step_ms'], c['cfg5'].get('eager_gpu_reference',{}).get('step_ms'))
-print('vocoder', d['vocoder']['ms_per_batch'])
+print('vocoder', d['vocoder']['ms_per_batch'], 'cpu_baseline', d['cpu_baseline'])
 PY

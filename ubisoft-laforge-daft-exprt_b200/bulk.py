@@ -339,10 +339,8 @@ class BulkRunner:
                         done.record(d2h_stream)
                     mel.record_stream(d2h_stream)       # the allocator must not hand the block out again before the copy ran
                     self.frames += int(out_len.sum())
-                    if packed:               # per-utterance (80, T_b) numpy views of the pinned buffer: the crop is free
-                        from .layouts import mel_views
-                        hmel = [v.numpy() for v in mel_views(hmel, out_len, mel_channels)]
-                    q.put((batches[my_batch_ids[pos]], out_len, hmel, done))
+                    # packed output: the writer thread cuts the per-utterance (80, T_b) views out of the pinned buffer
+                    q.put((batches[my_batch_ids[pos]], out_len, hmel, done, mel_channels if packed else 0))
                 for f in futs.values():       # a failed run must not leave collate jobs writing into freed blocks
                     f.cancel()
         finally:
@@ -360,7 +358,7 @@ class BulkRunner:
                 host = collate(utterances, batches[k])
                 out = self.model(host)
                 self.frames += int(host[9].sum())
-                q.put((batches[k], host[9], out[3][0], None))
+                q.put((batches[k], host[9], out[3][0], None, 0))
         finally:
             self._finish_writer(q, writer)
         return self.frames
@@ -376,13 +374,15 @@ class BulkRunner:
             if self._writer_error is not None:
                 continue
             try:
-                ids, out_len, hmel, done = item
+                ids, out_len, hmel, done, packed_channels = item
                 if done is not None:
                     done.synchronize()
                 if self.sink is not None:
-                    if isinstance(hmel, (list, tuple)):          # packed output: per-utterance (80, T_b) views
-                        for i, v in zip(ids, hmel):
-                            self.sink(i, v)
+                    if packed_channels:          # packed output: per-utterance (80, T_b) numpy views, the crop is free
+                        arr, o = hmel.numpy(), 0
+                        for i, n in zip(ids, out_len.tolist()):
+                            self.sink(i, arr[o:o + packed_channels * n].reshape(packed_channels, n))
+                            o += packed_channels * n
                     else:
                         arr = hmel.numpy()
                         for b, i in enumerate(ids):
