@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_arch.py -q > gpurun_out/r2v_pytest.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/r2v_pytest.log
-tail -4 gpurun_out/r2v_pytest.log
+timeout 300 python tools/generate_profile.py > gpurun_out/r2v_generate_profile.txt 2>&1; head -40 gpurun_out/r2v_generate_profile.txt
+timeout 200 python -m pytest tests -m gpu -q -k "bulk or fine_tune or packed or generate" 2>&1 | tail -2
