@@ -65,3 +65,74 @@ def test_model_mirror_has_reference_layout_and_fails_loudly_on_cpu():
     if not torch.cuda.is_available():
         with pytest.raises(_lib.DxError):
             m(batch)           # no CPU fallback
+
+
+def test_ctypes_structs_match_the_header_compiled_as_c(tmp_path):
+    """The header is plain C: compile it with gcc, print sizeof / offsetof of every struct field the bindings declare, and
+    compare with the ctypes structures field by field (a mismatch would make every pointer after it garbage on the device)."""
+    import ctypes
+    import shutil
+    import subprocess
+    import pytest
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not available")
+    structs = {"DxBlockWeights": _lib.DxBlockWeights, "DxModelWeights": _lib.DxModelWeights, "DxForwardArgs": _lib.DxForwardArgs,
+               "DxTrainArgs": _lib.DxTrainArgs, "DxVcConv": _lib.DxVcConv, "DxVocoderWeights": _lib.DxVocoderWeights,
+               "DxVocoderArgs": _lib.DxVocoderArgs}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "daft_b200.h"', 'int main(void) {']
+    for name, cls in structs.items():
+        lines.append(f'  printf("{name} %zu\\n", sizeof({name}));')
+        for field, _t in cls._fields_:
+            lines.append(f'  printf("{name}.{field} %zu\\n", offsetof({name}, {field}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-I", os.path.dirname(HEADER), str(src), "-o", str(exe)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr       # also proves every ctypes field name exists in the header
+    got = dict(line.split() for line in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for name, cls in structs.items():
+        assert int(got[name]) == ctypes.sizeof(cls), (name, got[name], ctypes.sizeof(cls))
+        for field, _t in cls._fields_:
+            assert int(got[f"{name}.{field}"]) == getattr(cls, field).offset, (name, field)
+    # and no field of the header is missing from the bindings: struct sizes equal, fields contiguous up to padding
+
+
+def test_ctypes_signatures_have_the_headers_argument_counts_and_kinds():
+    """Every prototype of the header against its ctypes signature: same number of arguments, pointers bound as pointers,
+    64-bit integers as 64-bit, floats as floats (a wrong width silently shifts every later register / stack slot)."""
+    import ctypes
+    src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    protos = re.findall(r"\b([A-Za-z_][A-Za-z0-9_ \*]*?)\b(dx_[a-z0-9_]+)\s*\(([^()]*)\)\s*;", src)
+    assert len(protos) == len(_lib.SIGNATURES)
+
+    def kind(decl):
+        decl = decl.strip()
+        if decl in ("void", ""):
+            return None
+        if "*" in decl:
+            return "ptr"
+        base = decl.rsplit(None, 1)[0] if " " in decl else decl
+        if "int64_t" in base or "uint64_t" in base:
+            return "i64"
+        if "float" in base:
+            return "f32"
+        return "i32"
+
+    def ckind(t):
+        if t in (ctypes.c_void_p, ctypes.c_char_p) or isinstance(t, type(ctypes.POINTER(ctypes.c_int))) and issubclass(t, ctypes._Pointer):
+            return "ptr"
+        if t in (ctypes.c_int64, ctypes.c_uint64):
+            return "i64"
+        if t is ctypes.c_float:
+            return "f32"
+        return "i32"
+
+    for ret, name, args in protos:
+        want = [k for k in (kind(a) for a in args.split(",")) if k is not None]
+        restype, argtypes = _lib.SIGNATURES[name]
+        assert [ckind(t) for t in argtypes] == want, (name, want, [ckind(t) for t in argtypes])
+        rk = "ptr" if "*" in ret else ("i64" if "int64_t" in ret else "i32")
+        assert ckind(restype) == rk, (name, ret, restype)
