@@ -136,3 +136,25 @@ def test_ctypes_signatures_have_the_headers_argument_counts_and_kinds():
         assert [ckind(t) for t in argtypes] == want, (name, want, [ckind(t) for t in argtypes])
         rk = "ptr" if "*" in ret else ("i64" if "int64_t" in ret else "i32")
         assert ckind(restype) == rk, (name, ret, restype)
+
+
+def test_weight_cache_key_sees_updates_and_replaced_parameters():
+    """model._param_versions() (the key of the packed-weight cache, read on every call) without walking the module tree:
+    it must change on in-place updates, on load_state_dict and when a Parameter OBJECT is replaced."""
+    import torch
+    from daft_exprt_b200.model import DaftExprt
+    m = DaftExprt(C.hparams())
+    k0 = m._param_versions()
+    assert len(k0) == len(list(m.parameters())) == 184 and m._param_versions() == k0
+    with torch.no_grad():
+        m.frame_decoder.projection.linear_layer.bias.add_(1.0)                       # what an optimizer step does
+    k1 = m._param_versions()
+    assert k1 != k0
+    m.load_state_dict(C.state_dict())
+    k2 = m._param_versions()
+    assert k2 != k1
+    holder = m.frame_decoder.projection.linear_layer
+    holder.bias = torch.nn.Parameter(holder.bias.detach().clone())                   # a new object with a fresh version counter
+    k3 = m._param_versions()
+    assert k3 != k2 and len(k3) == 184
+    assert [id(p) for p in m.parameters()] == [i for i, _ in k3]                      # same order and objects as parameters()

@@ -128,18 +128,23 @@ class DaftExprt(nn.Module):
     # ------------------------------------------------------------------------------------------
     # weight preparation: GEMM layouts (fp32) and tile-packed bf16 for the tensor-core kernels
     # ------------------------------------------------------------------------------------------
+    def _param_versions(self):
+        """Identity and version counter of every parameter, the key of the packed-weight cache.  The MODULE tree is fixed
+        after construction, so the (module's parameter dict, name) slots are collected once: walking the tree with
+        ``self.parameters()`` on every call cost a third of the host time of a forward (``named_modules`` recursion over 184
+        parameters).  Reading through the dicts still sees a parameter OBJECT that was replaced (``m.x.weight =
+        nn.Parameter(...)``) as well as in-place updates (optimizer steps, ``load_state_dict``: version bumps)."""
+        slots = self._param_list
+        if slots is None:
+            slots = self._param_list = [(m._parameters, n) for m in self.modules() for n in m._parameters]
+        return tuple((id(d[n]), d[n]._version) for d, n in slots)
+
     def _prepare(self):
         dev = self.device
         if dev.type != "cuda":
             raise _lib.DxError("DaftExprt (B200) needs its parameters on a CUDA device; there is no CPU fallback")
         mode = _MODES[self.compute_mode]
-        # the parameter tree is fixed after construction: walking it with self.parameters() on every call cost a third of the
-        # host time of a forward (named_modules recursion over 184 parameters); the list is rebuilt after _apply / load
-        plist = self._param_list
-        if plist is None:
-            plist = self._param_list = list(self.parameters())
-        versions = tuple(p._version for p in plist)
-        key = (mode, str(dev), versions)
+        key = (mode, str(dev), self._param_versions())
         if self._prepared is not None and self._prepared[0] == key:
             return self._prepared[1]
         lib = _lib.load()
